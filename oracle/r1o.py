@@ -1,0 +1,159 @@
+"""ctypes binding of the CPU ORACLE (oracle/libr1o.so).  TEST INFRASTRUCTURE.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+``--impl reference`` legs may import this module.  The product package
+(rav1e_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libr1o.so")
+
+
+def build(force=False):
+    srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".c", ".h"))]
+    if force or not os.path.exists(_SO) or any(
+            os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "libr1o.so"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+class PlaneCfg(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in (
+        "stride", "alloc_height", "width", "height", "xdec", "ydec", "xpad", "ypad",
+        "xorigin", "yorigin")]
+
+
+class Mv(C.Structure):
+    _fields_ = [("row", C.c_int16), ("col", C.c_int16)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        vp, i, i64, u32, u64, pd = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_uint64, C.c_ssize_t
+        P = C.POINTER
+        L.r1o_block_width.restype = i
+        L.r1o_block_height.restype = i
+        L.r1o_tx_width.restype = i
+        L.r1o_tx_height.restype = i
+        L.r1o_plane_cfg_new.argtypes = [P(PlaneCfg), i64, i64, i64, i64, i64, i64, i]
+        L.r1o_plane_pad.argtypes = [vp, P(PlaneCfg), i64, i64, i]
+        L.r1o_plane_downsample.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i]
+        L.r1o_plane_downsample.restype = i
+        for f in (L.r1o_sad, L.r1o_satd):
+            f.argtypes = [vp, pd, vp, pd, i, i, i]
+            f.restype = u32
+        L.r1o_put_8tap.argtypes = [vp, pd, vp, pd, i, i, i, i, i, i, i, i]
+        L.r1o_prep_8tap.argtypes = [vp, vp, pd, i, i, i, i, i, i, i, i]
+        L.r1o_mc_avg.argtypes = [vp, pd, vp, vp, i, i, i, i]
+        L.r1o_mv_params.argtypes = [P(PlaneCfg), i64, i64, i, i, P(i), P(i), P(i64), P(i64)]
+        L.r1o_fwd_txfm1d.argtypes = [i, i, vp, vp]
+        L.r1o_fwd_txfm1d.restype = i
+        L.r1o_fht.argtypes = [vp, vp, i, i, i]
+        L.r1o_fht.restype = i
+        L.r1o_fht_valid.argtypes = [i, i]
+        L.r1o_fht_valid.restype = i
+        L.r1o_diff.argtypes = [vp, vp, pd, vp, pd, i, i, i]
+        L.r1o_mv_rate.argtypes = [Mv, Mv, i]
+        L.r1o_mv_rate.restype = u32
+        L.r1o_mv_range.argtypes = [i64, i64, i64, i64, i, i, P(i64 * 4)]
+        L.r1o_full_search.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i64, i64, i, i,
+                                      i64, i64, i, u32, P(Mv * 2), i, i, P(Mv), P(u64)]
+        L.r1o_full_search.restype = i
+        L.r1o_subpel_cost.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i, i, Mv,
+                                      P(Mv * 2), u32, i, i, P(i64 * 4), i, i]
+        L.r1o_subpel_cost.restype = u64
+        L.r1o_num_threads.restype = i
+        L.r1o_dist_batch.argtypes = [i, vp, P(PlaneCfg), vp, P(PlaneCfg), vp, i64, i, vp]
+        L.r1o_full_search_batch.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), vp, i64, i, vp, vp]
+        L.r1o_full_search_batch.restype = i
+        L.r1o_mc_batch.argtypes = [i, vp, P(PlaneCfg), vp, vp, vp, P(PlaneCfg), vp, i64, i, i]
+        L.r1o_avg_batch.argtypes = [vp, P(PlaneCfg), vp, vp, vp, vp, i64, i, i]
+        L.r1o_fht_batch.argtypes = [vp, vp, i, i, i, i64]
+        L.r1o_fht_batch.restype = i
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class OPlane:
+    """Host plane with the reference's geometry (src/frame/plane.rs:215-244)."""
+
+    def __init__(self, width, height, xdec=0, ydec=0, xpad=0, ypad=0, px_bytes=1, fill=128):
+        self.cfg = PlaneCfg()
+        lib().r1o_plane_cfg_new(C.byref(self.cfg), width, height, xdec, ydec, xpad, ypad, px_bytes)
+        self.px_bytes = px_bytes
+        self.dtype = np.uint8 if px_bytes == 1 else np.uint16
+        self.data = np.full((self.cfg.alloc_height, self.cfg.stride), fill, dtype=self.dtype)
+
+    @property
+    def visible(self):
+        c = self.cfg
+        return self.data[c.yorigin:c.yorigin + c.height, c.xorigin:c.xorigin + c.width]
+
+    def pad(self, w=None, h=None):
+        c = self.cfg
+        lib().r1o_plane_pad(_p(self.data), C.byref(self.cfg),
+                            (c.width << c.xdec) if w is None else w,
+                            (c.height << c.ydec) if h is None else h, self.px_bytes)
+
+    def origin_ptr(self):
+        """address of plane coordinate (0,0)"""
+        c = self.cfg
+        return self.data.ctypes.data + (c.yorigin * c.stride + c.xorigin) * self.px_bytes
+
+    def ptr(self, x, y):
+        return self.origin_ptr() + (y * self.cfg.stride + x) * self.px_bytes
+
+
+def sad(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
+    return lib().r1o_sad(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
+                         org.px_bytes)
+
+
+def satd(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
+    return lib().r1o_satd(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
+                          org.px_bytes)
+
+
+def fht(residual, tx_size, tx_type, bit_depth):
+    residual = np.ascontiguousarray(residual, dtype=np.int16)
+    out = np.empty(residual.size, dtype=np.int32)
+    rc = lib().r1o_fht(_p(residual), _p(out), tx_size, tx_type, bit_depth)
+    if rc != 0:
+        raise ValueError("invalid (tx_size, tx_type, bit_depth)")
+    return out.reshape(residual.shape)
+
+
+def fht_batch(residual, tx_size, tx_type, bit_depth):
+    residual = np.ascontiguousarray(residual, dtype=np.int16)
+    area = lib().r1o_tx_width(tx_size) * lib().r1o_tx_height(tx_size)
+    n = residual.size // area
+    out = np.empty(residual.size, dtype=np.int32)
+    rc = lib().r1o_fht_batch(_p(residual), _p(out), tx_size, tx_type, bit_depth, n)
+    if rc != 0:
+        raise ValueError("invalid (tx_size, tx_type)")
+    return out
+
+
+def txfm1d(type1d, vec):
+    vec = np.ascontiguousarray(vec, dtype=np.int32)
+    out = np.empty_like(vec)
+    rc = lib().r1o_fwd_txfm1d(type1d, vec.size, _p(vec), _p(out))
+    if rc != 0:
+        raise ValueError("unimplemented (type, n)")
+    return out

@@ -1,0 +1,225 @@
+"""Independent cross-checks of the UNPINNED parts of the oracle (MC, forward
+TX, ME): properties that must hold for any correct restatement, because the
+reference has no golden vectors for them."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+
+def _dct2(n):
+    k = np.arange(n)[:, None]
+    i = np.arange(n)[None, :]
+    m = np.cos(np.pi * (2 * i + 1) * k / (2 * n)) * np.sqrt(2 / n)
+    m[0] /= np.sqrt(2)
+    return m
+
+
+def _dst4(n):
+    k = np.arange(n)[:, None]
+    i = np.arange(n)[None, :]
+    return np.sin(np.pi * (2 * i + 1) * (2 * k + 1) / (4 * n)) * np.sqrt(2 / n)
+
+
+def _dst7(n):
+    k = np.arange(n)[:, None]
+    i = np.arange(n)[None, :]
+    return np.sin(np.pi * (2 * k + 1) * (i + 1) / (2 * n + 1)) * 2 / np.sqrt(2 * n + 1)
+
+
+def _mat(t1d, n):
+    if t1d == 0:
+        return _dct2(n)
+    if t1d == 1:
+        return _dst7(4) if n == 4 else _dst4(n)
+    return np.eye(n)
+
+
+@pytest.mark.parametrize("t1d,n", [(0, 4), (0, 8), (0, 16), (0, 32), (0, 64), (1, 4), (1, 8), (1, 16)])
+def test_txfm1d_is_orthonormal_transform(oracle, t1d, n):
+    """The Daala kernels of forward.rs approximate the ORTHONORMAL DCT-II /
+    DST-IV (DST-VII for n=4) to within integer rounding."""
+    rng = np.random.default_rng(n * 7 + t1d)
+    M = _mat(t1d, n)
+    X = rng.integers(-30000, 30000, size=(300, n)).astype(np.int32)
+    Y = np.stack([oracle.txfm1d(t1d, x) for x in X]).astype(np.float64)
+    assert np.abs(Y - X @ M.T).max() < 12.0
+    # linearity at small amplitude: T(0) == 0
+    assert not oracle.txfm1d(t1d, np.zeros(n, np.int32)).any()
+
+
+def test_txfm1d_unimplemented(oracle):
+    for t1d, n in [(1, 32), (1, 64), (2, 64)]:
+        with pytest.raises(ValueError):
+            oracle.txfm1d(t1d, np.zeros(n, np.int32))
+    x = np.arange(32, dtype=np.int32)
+    assert np.array_equal(oracle.txfm1d(2, x), x)  # identity == copy, forward.rs:1686-1700
+
+
+def test_fht_valid_pair_count(oracle):
+    L = oracle.lib()
+    n = sum(L.r1o_fht_valid(s, t) for s in range(19) for t in range(16))
+    assert n == 193
+
+
+# (col1d, colflip, row1d, rowflip) per TxType, src/transform/mod.rs:196-213
+TYPES = [(0, 0, 0, 0), (1, 0, 0, 0), (0, 0, 1, 0), (1, 0, 1, 0), (1, 1, 0, 0), (0, 0, 1, 1),
+         (1, 1, 1, 1), (1, 0, 1, 1), (1, 1, 1, 0), (2, 0, 2, 0), (0, 0, 2, 0), (2, 0, 0, 0),
+         (1, 0, 2, 0), (2, 0, 1, 0), (1, 1, 2, 0), (2, 0, 1, 1)]
+SHIFT_SUM = {  # total left-shift of the three stages per shift table row (forward.rs:22-40)
+}
+
+
+@pytest.mark.parametrize("bd", [8, 10, 12])
+def test_fht_matches_float_separable(oracle, bd):
+    """2-D fht == row_tx( col_tx(x << s0) >> s1 ) << / >> s2 up to rounding, for
+    every valid (size, type)."""
+    L = oracle.lib()
+    rng = np.random.default_rng(bd)
+    A = [[3, 0, 0], [2, 0, 1], [0, 0, 3]]
+    B = [[4, -1, 0], [2, 0, 1], [0, 0, 3]]
+    Cc = [[4, -2, 0], [2, 0, 0], [0, 0, 2]]
+    D = [[4, -1, -2], [2, 0, -1], [0, 0, 1]]
+    table = {0: A, 3: Cc, 9: Cc, 10: Cc, 17: Cc, 18: Cc, 4: D, 11: D, 12: D}
+    amp = (1 << bd) - 1
+    for s in range(19):
+        W, H = L.r1o_tx_width(s), L.r1o_tx_height(s)
+        sh = table.get(s, B)[(bd - 8) // 2]
+        for t in range(16):
+            if not L.r1o_fht_valid(s, t):
+                continue
+            ct, cf, rt, rf = TYPES[t]
+            x = rng.integers(-amp, amp + 1, size=(H, W)).astype(np.int16)
+            y = oracle.fht(x, s, t, bd).astype(np.float64)
+            f = x.astype(np.float64) * 2.0 ** sh[0]
+            if cf:
+                f = f[::-1, :]
+            f = _mat(ct, H) @ f
+            f = f * 2.0 ** sh[1]
+            if rf:
+                f = f[:, ::-1]
+            f = f @ _mat(rt, W).T
+            f = f * 2.0 ** sh[2]
+            tol = 8.0 * max(1.0, 2.0 ** sh[2]) + 4
+            assert np.abs(y - f).max() < tol, (s, t, bd, np.abs(y - f).max())
+
+
+# ---------------------------------------------------------------- MC ---------
+def _rand_plane(oracle, rng, w, h, pb, bd):
+    p = oracle.OPlane(w, h, 0, 0, 16, 16, pb)
+    p.data[...] = rng.integers(0, 1 << bd, size=p.data.shape).astype(p.dtype)
+    return p
+
+
+def _put(oracle, src, x, y, w, h, cf, rf, mx, my, bd):
+    dst = np.zeros((h, w), dtype=src.dtype)
+    oracle.lib().r1o_put_8tap(dst.ctypes.data, w, src.ptr(x, y), src.cfg.stride, w, h, cf, rf, mx,
+                              my, bd, src.px_bytes)
+    return dst
+
+
+def _prep(oracle, src, x, y, w, h, cf, rf, mx, my, bd):
+    tmp = np.zeros((h, w), dtype=np.int16)
+    oracle.lib().r1o_prep_8tap(tmp.ctypes.data, src.ptr(x, y), src.cfg.stride, w, h, cf, rf, mx, my,
+                               bd, src.px_bytes)
+    return tmp
+
+
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10), (2, 12)])
+def test_mc_identities(oracle, pb, bd):
+    rng = np.random.default_rng(bd)
+    src = _rand_plane(oracle, rng, 96, 80, pb, bd)
+    ib = 2 if bd == 12 else 4
+    for (w, h) in [(4, 4), (8, 16), (32, 8), (64, 64)]:
+        blk = src.visible[10:10 + h, 20:20 + w]
+        # frac (0,0): put == copy, prep == px << ib   (mc.rs:224-229, 320-327)
+        assert np.array_equal(_put(oracle, src, 20, 10, w, h, 0, 0, 0, 0, bd), blk)
+        assert np.array_equal(_prep(oracle, src, 20, 10, w, h, 0, 0, 2, 1, bd),
+                              (blk.astype(np.int32) << ib).astype(np.int16))
+        # mc_avg(prep, prep) at frac 0 reproduces the block
+        t = _prep(oracle, src, 20, 10, w, h, 0, 0, 0, 0, bd)
+        d = np.zeros((h, w), dtype=src.dtype)
+        oracle.lib().r1o_mc_avg(d.ctypes.data, w, t.ctypes.data, t.ctypes.data, w, h, bd, pb)
+        assert np.array_equal(d, blk)
+        # bilinear half-pel horizontal == rounded mean of neighbours
+        a = src.visible[10:10 + h, 20:20 + w].astype(np.int32)
+        b = src.visible[10:10 + h, 21:21 + w].astype(np.int32)
+        want = (a + b + 1) >> 1
+        got = _put(oracle, src, 20, 10, w, h, 8, 0, 3, 3, bd).astype(np.int32)
+        # two-stage rounding (7-ib then ib) of 64a+64b: may differ from the
+        # single-stage mean by at most the double-rounding LSB
+        assert np.abs(got - want).max() <= 1
+        # vertical bilinear half-pel: single rounding by 7 -> exact mean
+        b = src.visible[11:11 + h, 20:20 + w].astype(np.int32)
+        got = _put(oracle, src, 20, 10, w, h, 0, 8, 3, 3, bd).astype(np.int32)
+        assert np.array_equal(got, (a + b + 1) >> 1)
+
+
+def test_mc_spec_rounding_constant_plane(oracle):
+    """On a constant plane every filter (taps sum to 128) must return the
+    constant for put, and const << ib for prep, in all four frac cases."""
+    for pb, bd in [(1, 8), (2, 10), (2, 12)]:
+        src = oracle.OPlane(64, 64, 0, 0, 16, 16, pb, fill=(1 << bd) - 3)
+        ib = 2 if bd == 12 else 4
+        for cf, rf in [(0, 5), (7, 0), (3, 11), (15, 15)]:
+            for mx in range(4):
+                for w, h in [(4, 8), (16, 4), (16, 16)]:
+                    p = _put(oracle, src, 8, 8, w, h, cf, rf, mx, (mx + 1) % 4, bd)
+                    assert (p == (1 << bd) - 3).all()
+                    t = _prep(oracle, src, 8, 8, w, h, cf, rf, mx, (mx + 1) % 4, bd)
+                    assert (t == ((1 << bd) - 3) << ib).all()
+
+
+def test_mv_params(oracle):
+    """src/predict.rs:267-284: floor shift for the integer part, 1/16 fracs,
+    clamp applied to (origin - 3) then +3."""
+    cfg = oracle.OPlane(64, 48, 0, 0, 16, 16, 1).cfg
+    rf, cf, sx, sy = C.c_int(), C.c_int(), C.c_int64(), C.c_int64()
+    f = oracle.lib().r1o_mv_params
+    f(C.byref(cfg), 8, 8, -9, 13, C.byref(rf), C.byref(cf), C.byref(sx), C.byref(sy))
+    assert (rf.value, cf.value) == (((-9) - (-2 << 3)) << 1, (13 - 8) << 1)
+    assert (sx.value, sy.value) == (8 + 1, 8 - 2)
+    f(C.byref(cfg), 8, 8, -8000, 8000, C.byref(rf), C.byref(cf), C.byref(sx), C.byref(sy))
+    assert (sx.value, sy.value) == (cfg.width + 3, -cfg.yorigin + 3)
+    # chroma plane (xdec=ydec=1): shift 4, frac already in 1/16
+    ccfg = oracle.OPlane(32, 24, 1, 1, 8, 8, 1).cfg
+    f(C.byref(ccfg), 4, 4, 21, -5, C.byref(rf), C.byref(cf), C.byref(sx), C.byref(sy))
+    assert (rf.value, cf.value, sx.value, sy.value) == (5, 11, 4 - 1, 4 + 1)
+
+
+# ---------------------------------------------------------------- ME ---------
+def test_mv_rate(oracle):
+    Mv, f = oracle.Mv, oracle.lib().r1o_mv_rate
+    assert f(Mv(0, 0), Mv(0, 0), 0) == 0
+    assert f(Mv(1, 0), Mv(0, 0), 0) == 0          # 1 >> 1 == 0
+    assert f(Mv(-1, 0), Mv(0, 0), 0) == 2         # -1 >> 1 == -1 -> 1 bit
+    assert f(Mv(8, -8), Mv(0, 0), 0) == 2 * 3 + 2 * 3
+    assert f(Mv(8, -8), Mv(0, 0), 1) == 2 * 4 + 2 * 4
+
+
+def test_full_search_finds_shift_and_first_min(oracle):
+    rng = np.random.default_rng(3)
+    ref = oracle.OPlane(128, 96, 0, 0, 88, 88, 1)
+    ref.visible[...] = rng.integers(0, 256, size=(96, 128))
+    ref.pad()
+    org = oracle.OPlane(128, 96, 0, 0, 88, 88, 1)
+    org.visible[...] = np.roll(ref.visible, (-3, 5), axis=(0, 1))  # org(y,x) = ref(y+3, x-5)
+    org.pad()
+    best, cost = oracle.Mv(0, 0), C.c_uint64(2 ** 64 - 1)
+    pmv = (oracle.Mv * 2)()
+    rc = oracle.lib().r1o_full_search(org.origin_ptr(), C.byref(org.cfg), ref.origin_ptr(),
+                                      C.byref(ref.cfg), 32 - 16, 32 + 16, 32 - 16, 32 + 16, 16, 16,
+                                      32, 32, 1, 0, C.byref(pmv), 0, 1, C.byref(best), C.byref(cost))
+    assert rc == 0 and (best.row, best.col, cost.value) == (3 * 8, -5 * 8, 0)
+    # flat planes: every candidate ties -> the first raster position wins
+    flat = oracle.OPlane(128, 96, 0, 0, 88, 88, 1)
+    best, cost = oracle.Mv(0, 0), C.c_uint64(2 ** 64 - 1)
+    oracle.lib().r1o_full_search(flat.origin_ptr(), C.byref(flat.cfg), flat.origin_ptr(),
+                                 C.byref(flat.cfg), 30, 40, 28, 36, 8, 8, 32, 32, 2, 0,
+                                 C.byref(pmv), 0, 1, C.byref(best), C.byref(cost))
+    assert (best.row, best.col, cost.value) == ((28 - 32) * 8, (30 - 32) * 8, 0)
+    # a window leaving the allocation is an error (PlaneRegion::new asserts)
+    rc = oracle.lib().r1o_full_search(flat.origin_ptr(), C.byref(flat.cfg), flat.origin_ptr(),
+                                      C.byref(flat.cfg), -200, 40, 28, 36, 8, 8, 32, 32, 1, 0,
+                                      C.byref(pmv), 0, 1, C.byref(best), C.byref(cost))
+    assert rc == -1
