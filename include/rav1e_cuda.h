@@ -1,0 +1,335 @@
+/*
+ * rav1e_cuda.h -- C ABI of librav1e_cuda.so: the B200 (sm_100a) implementation
+ * of rav1e's data-parallel inner loop (distortion, sub-pel motion
+ * compensation, forward transforms, motion search).
+ *
+ * Boundary it replaces.  The reference (geobacter-rs/rav1e) has no FFI for
+ * this path; its closest equivalent -- and the pattern followed here -- is
+ * the C-ABI function-pointer boundary of its asm back-ends:
+ *     SadFn / SatdFn      src/asm/x86/dist.rs:16-32
+ *     PutFn / PutHBDFn    src/asm/x86/mc.rs:17-38
+ *     PrepFn / PrepHBDFn  src/asm/x86/mc.rs:40-59
+ *     AvgFn / AvgHBDFn    src/asm/x86/mc.rs:61-78
+ * plus the pure-Rust entry points that have no asm today:
+ *     forward_transform   src/transform/mod.rs:556-566
+ *     full_search         src/me.rs:943-990
+ *     telescopic_subpel_search  src/me.rs:858-941
+ * Conventions kept from that boundary: the caller owns every buffer, the
+ * callee never allocates caller-visible memory, preconditions are checked
+ * (the Rust side `assert!`s them, here they return R1C_ERR_*), functions are
+ * re-entrant per context (one r1c_ctx per rayon worker / tile).
+ *
+ * Conventions of this header
+ *   - every entry point returns 0 (R1C_OK) or a negative R1C_ERR_* code and
+ *     never aborts; r1c_last_error() gives the text for the last failure.
+ *   - enum values equal the Rust declaration order (BlockSize
+ *     src/partition.rs:116-140, TxSize / TxType src/transform/mod.rs:225-247,
+ *     123-140, FilterMode src/mc.rs:61-66).
+ *   - coordinates are plane coordinates (0,0 = first visible pixel; negative
+ *     values address the padding), strides are in PIXELS as in PlaneConfig.
+ *   - `*_batch` entry points take HOST job / result arrays and do the
+ *     host<->device copies themselves (the end-to-end path);
+ *     `*_batch_dev` take DEVICE job / result arrays, only enqueue work on the
+ *     context's stream and return (r1c_sync() to wait).
+ *   - there is no CPU fallback: without a CUDA device r1c_create() fails.
+ */
+#ifndef RAV1E_CUDA_H
+#define RAV1E_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define R1C_OK 0
+#define R1C_ERR_ARG (-1)         /* bad argument / unsupported combination   */
+#define R1C_ERR_CUDA (-2)        /* CUDA runtime error                       */
+#define R1C_ERR_BOUNDS (-3)      /* region leaves the allocated plane        */
+#define R1C_ERR_UNIMPLEMENTED (-4) /* `unimplemented!` in the reference too  */
+#define R1C_ERR_NOMEM (-5)
+
+/* BlockSize, src/partition.rs:116-140 */
+typedef enum {
+  R1C_BLOCK_4X4, R1C_BLOCK_4X8, R1C_BLOCK_8X4, R1C_BLOCK_8X8, R1C_BLOCK_8X16,
+  R1C_BLOCK_16X8, R1C_BLOCK_16X16, R1C_BLOCK_16X32, R1C_BLOCK_32X16,
+  R1C_BLOCK_32X32, R1C_BLOCK_32X64, R1C_BLOCK_64X32, R1C_BLOCK_64X64,
+  R1C_BLOCK_64X128, R1C_BLOCK_128X64, R1C_BLOCK_128X128, R1C_BLOCK_4X16,
+  R1C_BLOCK_16X4, R1C_BLOCK_8X32, R1C_BLOCK_32X8, R1C_BLOCK_16X64,
+  R1C_BLOCK_64X16, R1C_BLOCK_SIZES_ALL
+} r1c_block_size;
+
+/* FilterMode, src/mc.rs:61-66 */
+typedef enum { R1C_REGULAR = 0, R1C_SMOOTH = 1, R1C_SHARP = 2, R1C_BILINEAR = 3 } r1c_filter_mode;
+
+/* TxSize, src/transform/mod.rs:225-247 */
+typedef enum {
+  R1C_TX_4X4, R1C_TX_8X8, R1C_TX_16X16, R1C_TX_32X32, R1C_TX_64X64,
+  R1C_TX_4X8, R1C_TX_8X4, R1C_TX_8X16, R1C_TX_16X8, R1C_TX_16X32,
+  R1C_TX_32X16, R1C_TX_32X64, R1C_TX_64X32, R1C_TX_4X16, R1C_TX_16X4,
+  R1C_TX_8X32, R1C_TX_32X8, R1C_TX_16X64, R1C_TX_64X16, R1C_TX_SIZES_ALL
+} r1c_tx_size;
+
+/* TxType, src/transform/mod.rs:123-140 */
+typedef enum {
+  R1C_DCT_DCT, R1C_ADST_DCT, R1C_DCT_ADST, R1C_ADST_ADST, R1C_FLIPADST_DCT,
+  R1C_DCT_FLIPADST, R1C_FLIPADST_FLIPADST, R1C_ADST_FLIPADST,
+  R1C_FLIPADST_ADST, R1C_IDTX, R1C_V_DCT, R1C_H_DCT, R1C_V_ADST, R1C_H_ADST,
+  R1C_V_FLIPADST, R1C_H_FLIPADST, R1C_TX_TYPES
+} r1c_tx_type;
+
+int r1c_block_width(int bsize);   /* -1 if out of range */
+int r1c_block_height(int bsize);
+int r1c_tx_width(int tx_size);
+int r1c_tx_height(int tx_size);
+/* 1 if the reference can instantiate (tx_size, tx_type): DCT 4..64,
+ * ADST/FLIPADST 4..16, identity 4..32 (src/transform/forward.rs:1745-1768) */
+int r1c_fwd_txfm_valid(int tx_size, int tx_type);
+
+/* ------------------------------------------------------------------------
+ * Context: one device + one stream + scratch.  Not shared between threads.
+ * (replaces nothing in the reference: the asm boundary is stateless; state is
+ * needed here for the device, the stream and pinned staging buffers.)
+ * ---------------------------------------------------------------------- */
+typedef struct r1c_ctx r1c_ctx;
+r1c_ctx *r1c_create(int device);          /* NULL when there is no usable CUDA device */
+void r1c_destroy(r1c_ctx *ctx);
+int r1c_sync(r1c_ctx *ctx);               /* wait for everything enqueued on the ctx stream */
+const char *r1c_last_error(const r1c_ctx *ctx);
+void *r1c_stream(r1c_ctx *ctx);           /* the cudaStream_t, for event timing */
+int r1c_device(const r1c_ctx *ctx);
+/* number of kernels this context has launched so far (bench.py gpu_launches) */
+int64_t r1c_launch_count(const r1c_ctx *ctx);
+
+/* ------------------------------------------------------------------------
+ * Planes.  Mirrors Plane<T> / PlaneConfig (src/frame/plane.rs:22-47,154,
+ * 215-244): a padded allocation of stride*alloc_height pixels, visible area
+ * starting at (xorigin, yorigin).
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int64_t stride, alloc_height, width, height;
+  int64_t xdec, ydec, xpad, ypad, xorigin, yorigin;
+} r1c_plane_cfg;
+
+typedef struct r1c_plane r1c_plane;
+
+/* Plane::new geometry (src/frame/plane.rs:215-244); px_bytes 1 (u8) or 2 (u16) */
+int r1c_plane_cfg_new(r1c_plane_cfg *cfg, int64_t width, int64_t height, int64_t xdec,
+                      int64_t ydec, int64_t xpad, int64_t ypad, int px_bytes);
+/* device allocation, every pixel 128 like PlaneData::new (plane.rs:130-138) */
+int r1c_plane_create(r1c_ctx *ctx, const r1c_plane_cfg *cfg, int px_bytes, r1c_plane **out);
+/* adopt caller-owned DEVICE memory holding a whole allocation (not freed) */
+int r1c_plane_wrap(r1c_ctx *ctx, void *device_data, const r1c_plane_cfg *cfg, int px_bytes,
+                   r1c_plane **out);
+void r1c_plane_destroy(r1c_plane *plane);
+/* whole allocation (stride*alloc_height pixels) host -> device / device -> host */
+int r1c_plane_upload(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);
+int r1c_plane_download(r1c_ctx *ctx, const r1c_plane *plane, void *host_data);
+void *r1c_plane_device_ptr(const r1c_plane *plane);
+const r1c_plane_cfg *r1c_plane_config(const r1c_plane *plane);
+/* Plane::pad(w, h), src/frame/plane.rs:269-314, on the device */
+int r1c_plane_pad(r1c_ctx *ctx, r1c_plane *plane, int64_t w, int64_t h);
+/* Plane::downsample_from, src/frame/plane.rs:399-423, on the device */
+int r1c_plane_downsample(r1c_ctx *ctx, r1c_plane *dst, const r1c_plane *src);
+
+/* ------------------------------------------------------------------------
+ * Distortion: get_sad / get_satd, src/dist.rs:48-111,121-188 (semantics of
+ * get_sad_ref :25-46 and get_satd_ref :197-328).
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int32_t org_x, org_y; /* block origin in the `org` plane */
+  int32_t ref_x, ref_y; /* block origin in the `ref` plane */
+  int32_t bsize;        /* r1c_block_size */
+} r1c_dist_job;
+
+/* one block, blocking, result to host: signature-compatible with SadFn /
+ * SatdFn (region pointers become plane + offset). */
+int r1c_sad(r1c_ctx *ctx, const r1c_plane *org, int org_x, int org_y, const r1c_plane *ref,
+            int ref_x, int ref_y, int bsize, int bit_depth, uint32_t *out);
+int r1c_satd(r1c_ctx *ctx, const r1c_plane *org, int org_x, int org_y, const r1c_plane *ref,
+             int ref_x, int ref_y, int bsize, int bit_depth, uint32_t *out);
+/* n jobs -> n u32 */
+int r1c_sad_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                  const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out);
+int r1c_satd_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                   const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out);
+int r1c_dist_batch_dev(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
+                       const r1c_dist_job *d_jobs, int64_t n, int bit_depth, uint32_t *d_out);
+
+/* ------------------------------------------------------------------------
+ * Motion compensation: put_8tap / prep_8tap / mc_avg, src/mc.rs:410-706
+ * (semantics of the `_ref` functions :213-408).
+ * `src_x/src_y` is the block origin in the source plane AFTER the integer MV
+ * offset and the clamp of predict_inter (src/predict.rs:267-284; see
+ * r1c_mv_params); the filters read 3 px left/up and 4 px right/down of it.
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int32_t dst_x, dst_y;       /* put: block origin in the dst plane; prep: unused */
+  int32_t src_x, src_y;
+  int16_t w, h;               /* 2..128; any size, not only BlockSize shapes */
+  int8_t col_frac, row_frac;  /* 0..15, 1/16 px */
+  int8_t mode_x, mode_y;      /* r1c_filter_mode */
+  int32_t tmp_off;            /* prep: offset (in i16 elements) of the dense w*h output */
+} r1c_mc_job;
+
+typedef struct {
+  int32_t dst_x, dst_y;
+  int16_t w, h;
+  int32_t tmp_off; /* offset (i16 elements) of the dense w*h block inside tmp1 and tmp2 */
+} r1c_avg_job;
+
+/* predict_inter's get_params (src/predict.rs:267-284): MV in 1/8 luma px ->
+ * 1/16 fracs and the clamped source origin.  Pure host arithmetic. */
+void r1c_mv_params(const r1c_plane_cfg *rec_cfg, int64_t po_x, int64_t po_y, int mv_row,
+                   int mv_col, int *row_frac, int *col_frac, int64_t *src_x, int64_t *src_y);
+
+int r1c_put_8tap_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_plane *src, const r1c_mc_job *jobs,
+                       int64_t n, int bit_depth);
+/* tmp: HOST i16 array of tmp_len elements, written at jobs[i].tmp_off */
+int r1c_prep_8tap_batch(r1c_ctx *ctx, int16_t *tmp, int64_t tmp_len, const r1c_plane *src,
+                        const r1c_mc_job *jobs, int64_t n, int bit_depth);
+int r1c_mc_avg_batch(r1c_ctx *ctx, r1c_plane *dst, const int16_t *tmp1, const int16_t *tmp2,
+                     int64_t tmp_len, const r1c_avg_job *jobs, int64_t n, int bit_depth);
+/* device-resident variants (jobs, tmp on the device) */
+int r1c_put_8tap_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_plane *src,
+                           const r1c_mc_job *d_jobs, int64_t n, int bit_depth);
+int r1c_prep_8tap_batch_dev(r1c_ctx *ctx, int16_t *d_tmp, const r1c_plane *src,
+                            const r1c_mc_job *d_jobs, int64_t n, int bit_depth);
+int r1c_mc_avg_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_tmp1,
+                         const int16_t *d_tmp2, const r1c_avg_job *d_jobs, int64_t n,
+                         int bit_depth);
+
+/* ------------------------------------------------------------------------
+ * Forward transforms: forward_transform, src/transform/mod.rs:556-566 ->
+ * FwdTxfm2D::fht, src/transform/forward.rs:1804-1899.
+ * residual: dense W*H i16, row-major (stride W); coeffs: dense W*H i32,
+ * coeffs[r*W + c].  Blocks of one call are stored back to back.
+ * Row-FLIPPED types (DCT_FLIPADST, FLIPADST_FLIPADST, ADST_FLIPADST,
+ * H_FLIPADST) use the intended semantic "column c is written to W-1-c"
+ * (the fork's SIMD branch forward.rs:1858-1862 reads uninitialised memory
+ * and is unreachable from the encoder, which never selects FLIPADST).
+ * ---------------------------------------------------------------------- */
+int r1c_forward_transform(r1c_ctx *ctx, const int16_t *residual, int32_t *coeffs, int tx_size,
+                          int tx_type, int bit_depth); /* one block, host buffers */
+int r1c_fwd_txfm_batch(r1c_ctx *ctx, int tx_size, int tx_type, int bit_depth,
+                       const int16_t *residual, int32_t *coeffs, int64_t n);
+int r1c_fwd_txfm_batch_dev(r1c_ctx *ctx, int tx_size, int tx_type, int bit_depth,
+                           const int16_t *d_residual, int32_t *d_coeffs, int64_t n);
+/* fused diff (src/encoder.rs:1045-1059) + fht: residual = input - pred taken
+ * straight from two planes; block i -> coeffs + i*W*H */
+typedef struct {
+  int32_t in_x, in_y;     /* block origin in the input plane */
+  int32_t pred_x, pred_y; /* block origin in the prediction plane */
+} r1c_tx_job;
+int r1c_diff_fwd_txfm_batch(r1c_ctx *ctx, const r1c_plane *input, const r1c_plane *pred,
+                            const r1c_tx_job *jobs, int64_t n, int tx_size, int tx_type,
+                            int bit_depth, int32_t *coeffs);
+int r1c_diff_fwd_txfm_batch_dev(r1c_ctx *ctx, const r1c_plane *input, const r1c_plane *pred,
+                                const r1c_tx_job *d_jobs, int64_t n, int tx_size, int tx_type,
+                                int bit_depth, int32_t *d_coeffs);
+
+/* ------------------------------------------------------------------------
+ * Motion search, src/me.rs.
+ * ---------------------------------------------------------------------- */
+typedef struct { int16_t row, col; } r1c_mv; /* MotionVector, src/mc.rs:27-31; 1/8 px */
+
+typedef struct {
+  r1c_mv mv;
+  uint32_t reserved;
+  uint64_t cost; /* 256*dist + rate*lambda, src/me.rs:855,982; UINT64_MAX = none */
+} r1c_me_result;
+
+/* get_mv_range, src/me.rs:64-80: out = {mvx_min, mvx_max, mvy_min, mvy_max} */
+void r1c_mv_range(int64_t w_in_b, int64_t h_in_b, int64_t bo_x, int64_t bo_y, int blk_w,
+                  int blk_h, int64_t out[4]);
+/* get_mv_rate, src/me.rs:1005-1021 */
+uint32_t r1c_mv_rate(r1c_mv a, r1c_mv b, int allow_high_precision_mv);
+
+/* full_search, src/me.rs:943-990: every (y, x) of [y_lo..y_hi] x [x_lo..x_hi]
+ * with stride `step`, raster order, strict `<` (first minimum wins). */
+typedef struct {
+  int32_t po_x, po_y;              /* block origin (both planes) */
+  int32_t bsize;                   /* r1c_block_size */
+  int32_t x_lo, x_hi, y_lo, y_hi;  /* candidate positions in the ref plane */
+  int32_t step;
+  uint32_t lambda;
+  r1c_mv pmv[2];
+  int32_t allow_high_precision_mv;
+  int32_t has_init; /* != 0: results[i] holds best_mv / lowest_cost on entry */
+} r1c_fs_job;
+
+int r1c_full_search_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                          const r1c_fs_job *jobs, int64_t n, int bit_depth,
+                          r1c_me_result *results /* in/out */);
+int r1c_full_search_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                              const r1c_fs_job *d_jobs, int64_t n, int bit_depth,
+                              r1c_me_result *d_results);
+
+/* Whole-superblock full search: ONE pass over the reference window yields the
+ * result of full_search for EVERY block of every requested size inside a
+ * 64x64 region (4x4 SADs are computed once per candidate and summed up to
+ * the larger blocks).  Per block the window is the one
+ * FullSearch::full_pixel_me builds (src/me.rs:533-546) with `range` instead
+ * of 16 and `step` instead of 2:
+ *   x_lo = po.x + clamp(-range_x + cmv.col/8, mvx_min/8, mvx_max/8)   etc.
+ * with (mvx_min..mvy_max) = get_mv_range(w_in_b, h_in_b, po/4, blk_w, blk_h),
+ * starting from (best_mv = 0, lowest_cost = MAX).
+ * Results: out[job*R1C_SB_RESULTS + r1c_sb_result_offset(bsize) + k], k =
+ * raster index of the block inside the region; sizes not in bsize_mask are
+ * left untouched. */
+#define R1C_SB_RESULTS 849
+typedef struct {
+  int32_t po_x, po_y;   /* region origin, multiple of 4, region inside the frame */
+  uint32_t bsize_mask;  /* bit b = emit BlockSize b (sizes up to 64x64 only) */
+  r1c_mv cmv;           /* search centre */
+  r1c_mv pmv[2];
+} r1c_sb_job;
+typedef struct {
+  int32_t w_in_b, h_in_b; /* frame size in 4x4 units (fi.w_in_b / fi.h_in_b) */
+  int32_t range_x, range_y;
+  int32_t step;           /* 1 or 2 */
+  uint32_t lambda;
+  int32_t allow_high_precision_mv;
+} r1c_sb_params;
+int r1c_sb_result_offset(int bsize); /* -1 for sizes above 64x64 */
+int r1c_sb_result_count(int bsize);
+int r1c_me_sb_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                    const r1c_sb_params *params, const r1c_sb_job *jobs, int64_t n,
+                    int bit_depth, r1c_me_result *results);
+int r1c_me_sb_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                        const r1c_sb_params *params, const r1c_sb_job *d_jobs, int64_t n,
+                        int bit_depth, r1c_me_result *d_results);
+
+/* Sub-pel candidate costs (get_mv_rd_cost with a temp plane, src/me.rs:787-838):
+ * predict_inter (put_8tap, REGULAR/REGULAR = fi.default_filter) of the block at
+ * each candidate MV, then SAD|SATD + rate.  n_cand candidates per job, laid out
+ * cand[job*n_cand + k]; cost UINT64_MAX for MVs outside the job's range. */
+typedef struct {
+  int32_t po_x, po_y;
+  int32_t bsize;
+  uint32_t lambda;
+  r1c_mv pmv[2];
+  int32_t mvx_min, mvx_max, mvy_min, mvy_max;
+  int32_t use_satd;
+  int32_t allow_high_precision_mv;
+} r1c_subpel_job;
+int r1c_subpel_cost_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                          const r1c_subpel_job *jobs, int64_t n, const r1c_mv *cand, int n_cand,
+                          int bit_depth, uint64_t *costs);
+/* The sub-pel tail of MotionEstimation::motion_estimation for FullSearch
+ * (src/me.rs:232-271): when use_satd, lowest_cost is first re-evaluated with
+ * SATD at best_mv (full-pel path, :235-252); then telescopic_subpel_search
+ * (:858-941): steps 8, 4, 2 (and 1 with high-precision MVs), 8 neighbours per
+ * step in (i, j) raster order, strict `<`.  results[i] is in/out. */
+int r1c_subpel_refine_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                            const r1c_subpel_job *jobs, int64_t n, int bit_depth,
+                            r1c_me_result *results);
+int r1c_subpel_refine_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                const r1c_subpel_job *d_jobs, int64_t n, int bit_depth,
+                                r1c_me_result *d_results);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAV1E_CUDA_H */

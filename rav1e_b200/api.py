@@ -1,0 +1,352 @@
+"""Host-side mirror of the reference's interface for the hot path, on top of the
+C ABI (include/rav1e_cuda.h).  Names and argument meaning follow the reference:
+
+    Plane / PlaneConfig          src/frame/plane.rs:22-47, 154, 215-244
+    get_sad / get_satd           src/dist.rs:48, 121
+    put_8tap / prep_8tap / mc_avg  src/mc.rs:410, 520, 617
+    forward_transform            src/transform/mod.rs:556
+    full_search                  src/me.rs:943
+    get_mv_range / get_mv_rate   src/me.rs:64, 1005
+
+plus the batched entry points (job arrays are numpy structured arrays whose
+dtypes mirror the C structs).  Everything here runs on the GPU through
+librav1e_cuda.so; there is no CPU path.  Errors of the C ABI surface as
+Rav1eCudaError (the reference `assert!`s / panics in the same situations).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import Rav1eCudaError  # noqa: F401  (re-export)
+
+# numpy mirrors of the job / result structs of include/rav1e_cuda.h
+MV = np.dtype([("row", "<i2"), ("col", "<i2")])
+DIST_JOB = np.dtype([("org_x", "<i4"), ("org_y", "<i4"), ("ref_x", "<i4"), ("ref_y", "<i4"),
+                     ("bsize", "<i4")])
+MC_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("src_x", "<i4"), ("src_y", "<i4"),
+                   ("w", "<i2"), ("h", "<i2"), ("col_frac", "i1"), ("row_frac", "i1"),
+                   ("mode_x", "i1"), ("mode_y", "i1"), ("tmp_off", "<i4")])
+AVG_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
+                    ("tmp_off", "<i4")])
+TX_JOB = np.dtype([("in_x", "<i4"), ("in_y", "<i4"), ("pred_x", "<i4"), ("pred_y", "<i4")])
+ME_RESULT = np.dtype([("mv", MV), ("reserved", "<u4"), ("cost", "<u8")])
+FS_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("x_lo", "<i4"),
+                   ("x_hi", "<i4"), ("y_lo", "<i4"), ("y_hi", "<i4"), ("step", "<i4"),
+                   ("lambda_", "<u4"), ("pmv", MV, (2,)), ("allow_high_precision_mv", "<i4"),
+                   ("has_init", "<i4")])
+SB_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize_mask", "<u4"), ("cmv", MV),
+                   ("pmv", MV, (2,))])
+SUBPEL_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("lambda_", "<u4"),
+                       ("pmv", MV, (2,)), ("mvx_min", "<i4"), ("mvx_max", "<i4"),
+                       ("mvy_min", "<i4"), ("mvy_max", "<i4"), ("use_satd", "<i4"),
+                       ("allow_high_precision_mv", "<i4")])
+STRUCT_PAIRS = [(DIST_JOB, capi.DistJob), (MC_JOB, capi.McJob), (AVG_JOB, capi.AvgJob),
+                (TX_JOB, capi.TxJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
+                (SB_JOB, capi.SbJob), (SUBPEL_JOB, capi.SubpelJob), (MV, capi.Mv)]
+
+BLOCK = {n: i for i, n in enumerate(capi.BLOCK_SIZES)}
+TX_SIZE = {n: i for i, n in enumerate(capi.TX_SIZES)}
+TX_TYPE = {n: i for i, n in enumerate(capi.TX_TYPES)}
+FILTER = {n: i for i, n in enumerate(capi.FILTER_MODES)}
+SB_RESULTS = capi.R1C_SB_RESULTS
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _arr(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a
+
+
+class Context:
+    """One device + stream + scratch (r1c_ctx).  One per worker thread / rank."""
+
+    def __init__(self, device=0):
+        self.lib = capi.load()
+        self.h = self.lib.r1c_create(device)
+        if not self.h:
+            raise Rav1eCudaError(capi.R1C_ERR_CUDA, "no usable CUDA device %d (rav1e_b200 has no "
+                                 "CPU fallback)" % device)
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.r1c_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, rc):
+        if rc != 0:
+            raise Rav1eCudaError(rc, self.lib.r1c_last_error(self.h).decode())
+
+    def sync(self):
+        self.check(self.lib.r1c_sync(self.h))
+
+    @property
+    def stream(self):
+        return self.lib.r1c_stream(self.h)
+
+    @property
+    def launches(self):
+        return self.lib.r1c_launch_count(self.h)
+
+
+class Plane:
+    """Device-resident Plane<T> with the reference's geometry (Plane::new)."""
+
+    def __init__(self, ctx, width, height, xdec=0, ydec=0, xpad=0, ypad=0, px_bytes=1,
+                 cfg=None, device_ptr=None):
+        self.ctx = ctx
+        self.px_bytes = px_bytes
+        self.dtype = np.uint8 if px_bytes == 1 else np.uint16
+        self.cfg = capi.PlaneCfg()
+        if cfg is not None:
+            C.memmove(C.byref(self.cfg), C.byref(cfg), C.sizeof(capi.PlaneCfg))
+        else:
+            rc = ctx.lib.r1c_plane_cfg_new(C.byref(self.cfg), width, height, xdec, ydec, xpad,
+                                           ypad, px_bytes)
+            if rc:
+                raise Rav1eCudaError(rc, "bad plane geometry")
+        h = C.c_void_p()
+        if device_ptr is None:
+            ctx.check(ctx.lib.r1c_plane_create(ctx.h, C.byref(self.cfg), px_bytes, C.byref(h)))
+        else:
+            ctx.check(ctx.lib.r1c_plane_wrap(ctx.h, device_ptr, C.byref(self.cfg), px_bytes,
+                                             C.byref(h)))
+        self.h = h
+
+    @property
+    def shape(self):
+        return (self.cfg.alloc_height, self.cfg.stride)
+
+    def upload(self, host):
+        """host: the WHOLE allocation, shape (alloc_height, stride)."""
+        host = _arr(host, self.dtype)
+        assert host.shape == self.shape, (host.shape, self.shape)
+        self.ctx.check(self.ctx.lib.r1c_plane_upload(self.ctx.h, self.h, _p(host)))
+        return self
+
+    def download(self):
+        out = np.empty(self.shape, dtype=self.dtype)
+        self.ctx.check(self.ctx.lib.r1c_plane_download(self.ctx.h, self.h, _p(out)))
+        return out
+
+    def pad(self, w, h):
+        self.ctx.check(self.ctx.lib.r1c_plane_pad(self.ctx.h, self.h, w, h))
+
+    def downsample_from(self, src):
+        self.ctx.check(self.ctx.lib.r1c_plane_downsample(self.ctx.h, self.h, src.h))
+
+    @property
+    def device_ptr(self):
+        return self.ctx.lib.r1c_plane_device_ptr(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.ctx.lib.r1c_plane_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ------------------------------------------------------------------ distortion --
+def get_sad(ctx, plane_org, org_xy, plane_ref, ref_xy, bsize, bit_depth):
+    out = C.c_uint32()
+    ctx.check(ctx.lib.r1c_sad(ctx.h, plane_org.h, org_xy[0], org_xy[1], plane_ref.h, ref_xy[0],
+                              ref_xy[1], bsize, bit_depth, C.byref(out)))
+    return out.value
+
+
+def get_satd(ctx, plane_org, org_xy, plane_ref, ref_xy, bsize, bit_depth):
+    out = C.c_uint32()
+    ctx.check(ctx.lib.r1c_satd(ctx.h, plane_org.h, org_xy[0], org_xy[1], plane_ref.h, ref_xy[0],
+                               ref_xy[1], bsize, bit_depth, C.byref(out)))
+    return out.value
+
+
+def sad_batch(ctx, plane_org, plane_ref, jobs, bit_depth, satd=False):
+    jobs = _arr(jobs, DIST_JOB)
+    out = np.empty(jobs.size, dtype=np.uint32)
+    fn = ctx.lib.r1c_satd_batch if satd else ctx.lib.r1c_sad_batch
+    ctx.check(fn(ctx.h, plane_org.h, plane_ref.h, _p(jobs), jobs.size, bit_depth, _p(out)))
+    return out
+
+
+def satd_batch(ctx, plane_org, plane_ref, jobs, bit_depth):
+    return sad_batch(ctx, plane_org, plane_ref, jobs, bit_depth, satd=True)
+
+
+# ------------------------------------------------------- motion compensation --
+def mv_params(rec_cfg, po, mv):
+    """get_params of predict_inter: -> (row_frac, col_frac, src_x, src_y)"""
+    lib = capi.load()
+    rf, cf, sx, sy = C.c_int(), C.c_int(), C.c_int64(), C.c_int64()
+    lib.r1c_mv_params(C.byref(rec_cfg), po[0], po[1], mv[0], mv[1], C.byref(rf), C.byref(cf),
+                      C.byref(sx), C.byref(sy))
+    return rf.value, cf.value, sx.value, sy.value
+
+
+def put_8tap_batch(ctx, dst, src, jobs, bit_depth):
+    jobs = _arr(jobs, MC_JOB)
+    ctx.check(ctx.lib.r1c_put_8tap_batch(ctx.h, dst.h, src.h, _p(jobs), jobs.size, bit_depth))
+
+
+def prep_8tap_batch(ctx, tmp, src, jobs, bit_depth):
+    """tmp: int16 array written in place at jobs[i].tmp_off"""
+    jobs = _arr(jobs, MC_JOB)
+    assert tmp.dtype == np.int16 and tmp.flags.c_contiguous
+    ctx.check(ctx.lib.r1c_prep_8tap_batch(ctx.h, _p(tmp), tmp.size, src.h, _p(jobs), jobs.size,
+                                          bit_depth))
+
+
+def mc_avg_batch(ctx, dst, tmp1, tmp2, jobs, bit_depth):
+    jobs = _arr(jobs, AVG_JOB)
+    tmp1 = _arr(tmp1, np.int16)
+    tmp2 = _arr(tmp2, np.int16)
+    assert tmp1.size == tmp2.size
+    ctx.check(ctx.lib.r1c_mc_avg_batch(ctx.h, dst.h, _p(tmp1), _p(tmp2), tmp1.size, _p(jobs),
+                                       jobs.size, bit_depth))
+
+
+def put_8tap(ctx, dst, dst_xy, src, src_xy, width, height, col_frac, row_frac, mode_x, mode_y,
+             bit_depth):
+    j = np.zeros(1, dtype=MC_JOB)
+    j[0] = (dst_xy[0], dst_xy[1], src_xy[0], src_xy[1], width, height, col_frac, row_frac,
+            mode_x, mode_y, 0)
+    put_8tap_batch(ctx, dst, src, j, bit_depth)
+
+
+def prep_8tap(ctx, src, src_xy, width, height, col_frac, row_frac, mode_x, mode_y, bit_depth):
+    j = np.zeros(1, dtype=MC_JOB)
+    j[0] = (0, 0, src_xy[0], src_xy[1], width, height, col_frac, row_frac, mode_x, mode_y, 0)
+    tmp = np.zeros(width * height, dtype=np.int16)
+    prep_8tap_batch(ctx, tmp, src, j, bit_depth)
+    return tmp.reshape(height, width)
+
+
+def mc_avg(ctx, dst, dst_xy, tmp1, tmp2, width, height, bit_depth):
+    j = np.zeros(1, dtype=AVG_JOB)
+    j[0] = (dst_xy[0], dst_xy[1], width, height, 0)
+    mc_avg_batch(ctx, dst, tmp1.reshape(-1), tmp2.reshape(-1), j, bit_depth)
+
+
+# ------------------------------------------------------------ forward transform --
+def fwd_txfm_valid(tx_size, tx_type):
+    return bool(capi.load().r1c_fwd_txfm_valid(tx_size, tx_type))
+
+
+def forward_transform(ctx, residual, tx_size, tx_type, bit_depth):
+    """residual: int16 (H, W) or a batch (N, H, W) -> int32 coefficients, same shape."""
+    residual = _arr(residual, np.int16)
+    w = ctx.lib.r1c_tx_width(tx_size)
+    h = ctx.lib.r1c_tx_height(tx_size)
+    if w < 0:
+        raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad tx_size")
+    n = residual.size // (w * h)
+    assert n * w * h == residual.size
+    out = np.empty(residual.shape, dtype=np.int32)
+    ctx.check(ctx.lib.r1c_fwd_txfm_batch(ctx.h, tx_size, tx_type, bit_depth, _p(residual),
+                                         _p(out), n))
+    return out
+
+
+def diff_forward_transform(ctx, plane_in, plane_pred, jobs, tx_size, tx_type, bit_depth):
+    jobs = _arr(jobs, TX_JOB)
+    w = ctx.lib.r1c_tx_width(tx_size)
+    h = ctx.lib.r1c_tx_height(tx_size)
+    out = np.empty((jobs.size, h, w), dtype=np.int32)
+    ctx.check(ctx.lib.r1c_diff_fwd_txfm_batch(ctx.h, plane_in.h, plane_pred.h, _p(jobs),
+                                              jobs.size, tx_size, tx_type, bit_depth, _p(out)))
+    return out
+
+
+# ----------------------------------------------------------------- motion search --
+def get_mv_range(w_in_b, h_in_b, bo, blk_w, blk_h):
+    out = (C.c_int64 * 4)()
+    capi.load().r1c_mv_range(w_in_b, h_in_b, bo[0], bo[1], blk_w, blk_h, C.byref(out))
+    return tuple(out)
+
+
+def get_mv_rate(a, b, allow_high_precision_mv):
+    return capi.load().r1c_mv_rate(capi.Mv(*a), capi.Mv(*b), int(allow_high_precision_mv))
+
+
+def full_search_batch(ctx, plane_org, plane_ref, jobs, bit_depth, results=None):
+    jobs = _arr(jobs, FS_JOB)
+    if results is None:
+        results = np.zeros(jobs.size, dtype=ME_RESULT)
+        results["cost"] = np.iinfo(np.uint64).max
+    results = _arr(results, ME_RESULT)
+    ctx.check(ctx.lib.r1c_full_search_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs), jobs.size,
+                                            bit_depth, _p(results)))
+    return results
+
+
+def full_search(ctx, x_lo, x_hi, y_lo, y_hi, bsize, p_org, p_ref, best_mv, lowest_cost, po, step,
+                lambda_, pmv, allow_high_precision_mv, bit_depth):
+    """Argument order of the reference's full_search (src/me.rs:943-949);
+    returns the updated (best_mv, lowest_cost)."""
+    j = np.zeros(1, dtype=FS_JOB)
+    j["po_x"], j["po_y"], j["bsize"] = po[0], po[1], bsize
+    j["x_lo"], j["x_hi"], j["y_lo"], j["y_hi"], j["step"] = x_lo, x_hi, y_lo, y_hi, step
+    j["lambda_"] = lambda_
+    j["pmv"][0, 0] = tuple(pmv[0])
+    j["pmv"][0, 1] = tuple(pmv[1])
+    j["allow_high_precision_mv"] = int(allow_high_precision_mv)
+    j["has_init"] = 1
+    r = np.zeros(1, dtype=ME_RESULT)
+    r["mv"][0] = tuple(best_mv)
+    r["cost"] = lowest_cost
+    r = full_search_batch(ctx, p_org, p_ref, j, bit_depth, r)
+    return (int(r["mv"]["row"][0]), int(r["mv"]["col"][0])), int(r["cost"][0])
+
+
+def sb_result_offset(bsize):
+    return capi.load().r1c_sb_result_offset(bsize)
+
+
+def sb_result_count(bsize):
+    return capi.load().r1c_sb_result_count(bsize)
+
+
+def make_sb_params(w_in_b, h_in_b, range_x, range_y, step, lambda_, allow_hp=False):
+    return capi.SbParams(w_in_b, h_in_b, range_x, range_y, step, lambda_, int(allow_hp))
+
+
+def me_sb_batch(ctx, plane_org, plane_ref, params, jobs, bit_depth, results=None):
+    jobs = _arr(jobs, SB_JOB)
+    if results is None:
+        results = np.zeros(jobs.size * SB_RESULTS, dtype=ME_RESULT)
+        results["cost"] = np.iinfo(np.uint64).max
+    ctx.check(ctx.lib.r1c_me_sb_batch(ctx.h, plane_org.h, plane_ref.h, C.byref(params),
+                                      _p(jobs), jobs.size, bit_depth, _p(results)))
+    return results.reshape(jobs.size, SB_RESULTS)
+
+
+def subpel_cost_batch(ctx, plane_org, plane_ref, jobs, cand, bit_depth):
+    jobs = _arr(jobs, SUBPEL_JOB)
+    cand = _arr(cand, MV).reshape(jobs.size, -1)
+    out = np.empty(cand.shape, dtype=np.uint64)
+    ctx.check(ctx.lib.r1c_subpel_cost_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs), jobs.size,
+                                            _p(cand), cand.shape[1], bit_depth, _p(out)))
+    return out
+
+
+def subpel_refine_batch(ctx, plane_org, plane_ref, jobs, results, bit_depth):
+    jobs = _arr(jobs, SUBPEL_JOB)
+    results = _arr(results, ME_RESULT).copy()
+    ctx.check(ctx.lib.r1c_subpel_refine_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs),
+                                              jobs.size, bit_depth, _p(results)))
+    return results

@@ -1,0 +1,105 @@
+// common.cuh -- internals shared by the translation units of librav1e_cuda.so.
+// Product code: never includes anything from oracle/.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/rav1e_cuda.h"
+
+struct r1c_plane {
+  r1c_plane_cfg cfg;
+  int px_bytes;
+  void *d_data;   // whole allocation: stride * alloc_height pixels
+  bool owned;
+  int device;
+};
+
+struct r1c_ctx {
+  int device;
+  cudaStream_t stream;
+  char err[256];
+  int64_t launches;
+  int sm_count;
+  // pinned host staging + device scratch, grown on demand (never shrinks)
+  void *h_stage[4];
+  size_t h_stage_cap[4];
+  void *d_scratch[12];
+  size_t d_scratch_cap[12];
+};
+
+// Device-side view of a plane: pointer to plane coordinate (0,0) + geometry.
+struct PlaneView {
+  const void *p0;   // address of pixel (0,0)
+  int stride;       // pixels
+  int xorigin, yorigin;
+  int width, height;
+  int alloc_w;      // = stride
+  int alloc_h;
+};
+
+static inline PlaneView make_view(const r1c_plane *p) {
+  PlaneView v;
+  v.p0 = (const uint8_t *)p->d_data +
+         ((size_t)p->cfg.yorigin * p->cfg.stride + p->cfg.xorigin) * p->px_bytes;
+  v.stride = (int)p->cfg.stride;
+  v.xorigin = (int)p->cfg.xorigin;
+  v.yorigin = (int)p->cfg.yorigin;
+  v.width = (int)p->cfg.width;
+  v.height = (int)p->cfg.height;
+  v.alloc_w = (int)p->cfg.stride;
+  v.alloc_h = (int)p->cfg.alloc_height;
+  return v;
+}
+
+// PlaneRegion::new bounds (src/tiling/plane_region.rs:139-142)
+static inline bool region_in_plane(const r1c_plane_cfg &c, int64_t x, int64_t y, int64_t w,
+                                   int64_t h) {
+  return x >= -c.xorigin && y >= -c.yorigin && c.xorigin + x + w <= c.stride &&
+         c.yorigin + y + h <= c.alloc_height;
+}
+
+int r1c_set_err(r1c_ctx *ctx, int code, const char *fmt, ...);
+int r1c_stage_host(r1c_ctx *ctx, int slot, size_t bytes, void **out);
+int r1c_scratch_dev(r1c_ctx *ctx, int slot, size_t bytes, void **out);
+int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
+                         int64_t n, int bit_depth);
+
+#define R1C_CUDA(ctx, call)                                                              \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess)                                                               \
+      return r1c_set_err((ctx), R1C_ERR_CUDA, "%s: %s (%s:%d)", #call,                   \
+                         cudaGetErrorString(e_), __FILE__, __LINE__);                    \
+  } while (0)
+
+#define R1C_LAUNCH_CHECK(ctx)                                                            \
+  do {                                                                                   \
+    (ctx)->launches++;                                                                   \
+    cudaError_t e_ = cudaGetLastError();                                                 \
+    if (e_ != cudaSuccess)                                                               \
+      return r1c_set_err((ctx), R1C_ERR_CUDA, "kernel launch: %s (%s:%d)",               \
+                         cudaGetErrorString(e_), __FILE__, __LINE__);                    \
+  } while (0)
+
+#define R1C_REQUIRE(ctx, cond, code, ...)                                                \
+  do {                                                                                   \
+    if (!(cond)) return r1c_set_err((ctx), (code), __VA_ARGS__);                         \
+  } while (0)
+
+// BlockSize -> (w, h), order of src/partition.rs:116-140
+__host__ __device__ inline int blk_w_of(int b) {
+  const unsigned char t[22] = {4, 4, 8, 8, 8, 16, 16, 16, 32, 32, 32, 64, 64, 64, 128, 128, 4, 16, 8, 32, 16, 64};
+  return t[b];
+}
+__host__ __device__ inline int blk_h_of(int b) {
+  const unsigned char t[22] = {4, 8, 4, 8, 16, 8, 16, 32, 16, 32, 64, 32, 64, 128, 64, 128, 16, 4, 32, 8, 64, 16};
+  return t[b];
+}
+
+static inline bool bit_depth_ok(int bd, int px_bytes) {
+  return (bd == 8 && px_bytes == 1) || ((bd == 10 || bd == 12) && px_bytes == 2) ||
+         (bd == 8 && px_bytes == 2);  // the reference's tests also run 8-bit data in u16 planes
+}
