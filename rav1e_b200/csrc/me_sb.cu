@@ -480,7 +480,9 @@ extern "C" int r1c_me_sb_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_pla
     // the search centre must be a legal MV for every block of the region, so that each
     // block's window is a sub-window of the nominal one (cmv = 0 always qualifies)
     const int cx = j.cmv.col / 8, cy = j.cmv.row / 8;
-    R1C_REQUIRE(ctx, cx >= -(j.po_x + 16 + 4) && cx <= W4 - (j.po_x + 60) + 16 && cy >= -(j.po_y + 16 + 4) && cy <= H4 - (j.po_y + 60) + 16,
+    const int bx_max = j.po_x + 60 < W4 - 4 ? j.po_x + 60 : W4 - 4;  // last block origin that exists in the frame
+    const int by_max = j.po_y + 60 < H4 - 4 ? j.po_y + 60 : H4 - 4;
+    R1C_REQUIRE(ctx, cx >= -(j.po_x + 16 + 4) && cx <= W4 - bx_max + 16 && cy >= -(j.po_y + 16 + 4) && cy <= H4 - by_max + 16,
                 R1C_ERR_ARG, "sb job %lld: search centre outside the legal MV range of the region", (long long)i);
   }
   void *h_jobs, *h_res, *d_jobs, *d_res;

@@ -1,0 +1,492 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.  Bar: bit-exact (integer / byte / index work).
+Run on the B200 box: python -m pytest tests -m gpu"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from gpu_util import (U64_MAX, full_pixel_window, oracle_full_search, oracle_subpel_cost,
+                      oracle_telescopic, twin_plane)
+from test_oracle_golden import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def r():
+    import rav1e_b200 as mod
+    return mod
+
+
+@pytest.fixture(scope="module")
+def ctx(r):
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    c = r.Context(0)
+    yield c
+    c.close()
+
+
+BD = [(1, 8), (2, 10), (2, 12)]
+
+
+# ------------------------------------------------------------------ planes -----
+@pytest.mark.parametrize("pb,bd", BD)
+def test_plane_roundtrip_pad_downsample(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(bd)
+    o, d = twin_plane(r, oracle, ctx, 200, 120, pb, bd, rng, xpad=40, ypad=24, pad=False)
+    assert np.array_equal(d.download(), o.data)
+    o.pad()
+    d.pad(200, 120)
+    assert np.array_equal(d.download(), o.data)
+    # chroma-style plane: pad(w, h) takes luma dimensions
+    oc, dc = twin_plane(r, oracle, ctx, 100, 60, pb, bd, rng, xpad=20, ypad=12, xdec=1, ydec=1, pad=False)
+    oc.pad(200, 120)
+    dc.pad(200, 120)
+    assert np.array_equal(dc.download(), oc.data)
+    # downsample_from
+    oh = oracle.OPlane(100, 60, 1, 1, 20, 12, pb)
+    dh = r.Plane(ctx, 100, 60, 1, 1, 20, 12, pb)
+    assert oracle.lib().r1o_plane_downsample(oh.data.ctypes.data, C.byref(oh.cfg), o.data.ctypes.data,
+                                             C.byref(o.cfg), pb) == 0
+    dh.downsample_from(d)
+    assert np.array_equal(dh.download(), oh.data)
+    with pytest.raises(r.Rav1eCudaError):
+        dh.downsample_from(dc)  # not 2x
+
+
+# ------------------------------------------------------------ SAD / SATD -------
+@pytest.mark.parametrize("pb", [1, 2])
+def test_sad_satd_reference_goldens(r, ctx, oracle, pb):
+    """the 44 known answers of src/dist.rs:379-402,437-460 through the C ABI"""
+    from test_oracle_golden import setup_planes
+    inp, rec = setup_planes(oracle, pb)
+    d_in = r.Plane(ctx, 640, 480, 0, 0, 136, 136, pb).upload(inp.data)
+    d_rec = r.Plane(ctx, 640, 480, 0, 0, 264, 264, pb).upload(rec.data)
+    for b, (name, w, h, sad, satd) in enumerate(GOLDEN):
+        assert r.get_sad(ctx, d_in, (32, 40), d_rec, (32, 40), b, 8) == sad, name
+        assert r.get_satd(ctx, d_in, (32, 40), d_rec, (32, 40), b, 8) == satd, name
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_sad_satd_batch_random(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(100 + bd)
+    o_org, d_org = twin_plane(r, oracle, ctx, 320, 200, pb, bd, rng)
+    o_ref, d_ref = twin_plane(r, oracle, ctx, 320, 200, pb, bd, rng, xpad=136, ypad=100)
+    n = 3000
+    jobs = np.zeros(n, dtype=r.DIST_JOB)
+    L = oracle.lib()
+    for i in range(n):
+        b = int(rng.integers(0, 22))
+        w, h = L.r1o_block_width(b), L.r1o_block_height(b)
+        jobs[i] = (int(rng.integers(-88, 320 + 88 - w + 1)), int(rng.integers(-88, 200 + 88 - h + 1)),
+                   int(rng.integers(-136, 320 + 136 - w + 1)), int(rng.integers(-100, 200 + 100 - h + 1)), b)
+    jobs[0] = (-88, -88, -136, -100, 15)  # corner of the allocation, 128x128
+    want_sad = np.empty(n, np.uint32)
+    want_satd = np.empty(n, np.uint32)
+    flat = np.ascontiguousarray(jobs.view(np.int32).reshape(n, 5))
+    L.r1o_dist_batch(0, o_org.origin_ptr(), C.byref(o_org.cfg), o_ref.origin_ptr(), C.byref(o_ref.cfg),
+                     flat.ctypes.data, n, pb, want_sad.ctypes.data)
+    L.r1o_dist_batch(1, o_org.origin_ptr(), C.byref(o_org.cfg), o_ref.origin_ptr(), C.byref(o_ref.cfg),
+                     flat.ctypes.data, n, pb, want_satd.ctypes.data)
+    assert np.array_equal(r.sad_batch(ctx, d_org, d_ref, jobs, bd), want_sad)
+    assert np.array_equal(r.satd_batch(ctx, d_org, d_ref, jobs, bd), want_satd)
+
+
+def test_satd_extreme_amplitude(r, ctx, oracle):
+    """12-bit checkerboard vs inverse: the i32 / u64 path of get_satd_ref, which the
+    fork's generated i16 kernel would wrap"""
+    yy, xx = np.indices((128, 128))
+    a = (((xx + yy) & 1) * 4095).astype(np.uint16)
+    o_a, d_a = twin_plane(r, oracle, ctx, 128, 128, 2, 12, data=a)
+    o_b, d_b = twin_plane(r, oracle, ctx, 128, 128, 2, 12, data=4095 - a)
+    for b in range(22):
+        w, h = oracle.lib().r1o_block_width(b), oracle.lib().r1o_block_height(b)
+        assert r.get_satd(ctx, d_a, (0, 0), d_b, (0, 0), b, 12) == oracle.satd(o_a, 0, 0, o_b, 0, 0, w, h)
+        assert r.get_sad(ctx, d_a, (0, 0), d_b, (0, 0), b, 12) == w * h * 4095
+
+
+def test_dist_errors(r, ctx, oracle):
+    rng = np.random.default_rng(5)
+    _, d = twin_plane(r, oracle, ctx, 64, 64, 1, 8, rng, xpad=8, ypad=8)
+    _, d16 = twin_plane(r, oracle, ctx, 64, 64, 2, 10, rng, xpad=8, ypad=8)
+    with pytest.raises(r.Rav1eCudaError) as e:
+        r.get_sad(ctx, d, (60, 0), d, (0, 0), r.BLOCK["BLOCK_64X64"], 8)  # leaves the allocation
+    assert e.value.code == r.capi.R1C_ERR_BOUNDS
+    with pytest.raises(r.Rav1eCudaError) as e:
+        r.get_sad(ctx, d, (0, 0), d16, (0, 0), 0, 8)  # mixed pixel types
+    assert e.value.code == r.capi.R1C_ERR_ARG
+    with pytest.raises(r.Rav1eCudaError):
+        r.get_sad(ctx, d, (0, 0), d, (0, 0), 22, 8)  # BLOCK_INVALID
+    assert r.sad_batch(ctx, d, d, np.zeros(0, dtype=r.DIST_JOB), 8).size == 0  # empty batch
+
+
+# ----------------------------------------------------------- forward TX --------
+def _residual(rng, n, h, w, bd, kind):
+    amp = (1 << bd) - 1
+    if kind == "random":
+        return rng.integers(-amp, amp + 1, size=(n, h, w)).astype(np.int16)
+    if kind == "max":
+        return np.full((n, h, w), amp, np.int16)
+    if kind == "min":
+        return np.full((n, h, w), -amp, np.int16)
+    yy, xx = np.indices((h, w))
+    return np.broadcast_to((((xx + yy) & 1) * 2 - 1) * amp, (n, h, w)).astype(np.int16)
+
+
+@pytest.mark.parametrize("bd", [8, 10, 12])
+def test_fwd_txfm_all_pairs(r, ctx, oracle, bd):
+    """every (TxSize, TxType) the reference can instantiate (193 pairs), random +
+    saturating inputs, batch sizes that do not fill the last CTA"""
+    rng = np.random.default_rng(bd)
+    L = oracle.lib()
+    pairs = 0
+    for s in range(19):
+        w, h = L.r1o_tx_width(s), L.r1o_tx_height(s)
+        for t in range(16):
+            if not L.r1o_fht_valid(s, t):
+                with pytest.raises(r.Rav1eCudaError) as e:
+                    r.forward_transform(ctx, np.zeros((1, h, w), np.int16), s, t, bd)
+                assert e.value.code == r.capi.R1C_ERR_UNIMPLEMENTED
+                continue
+            pairs += 1
+            n = int(rng.integers(1, 70))
+            res = np.concatenate([_residual(rng, n, h, w, bd, "random"), _residual(rng, 1, h, w, bd, "max"),
+                                  _residual(rng, 1, h, w, bd, "min"), _residual(rng, 1, h, w, bd, "checker")])
+            got = r.forward_transform(ctx, res, s, t, bd)
+            want = oracle.fht_batch(res, s, t, bd).reshape(res.shape)
+            assert np.array_equal(got, want), (r.capi.TX_SIZES[s], r.capi.TX_TYPES[t], bd)
+    assert pairs == 193
+
+
+def test_fwd_txfm_single_and_empty(r, ctx, oracle):
+    rng = np.random.default_rng(3)
+    res = rng.integers(-255, 256, size=(16, 16)).astype(np.int16)
+    got = r.forward_transform(ctx, res, r.TX_SIZE["TX_16X16"], r.TX_TYPE["ADST_DCT"], 8)
+    assert np.array_equal(got, oracle.fht(res, 2, 1, 8))
+    assert r.forward_transform(ctx, np.zeros((0, 8, 8), np.int16), 1, 0, 8).size == 0
+    with pytest.raises(r.Rav1eCudaError):
+        r.forward_transform(ctx, res, r.TX_SIZE["TX_16X16"], 0, 9)  # bit depth
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_diff_fwd_txfm_fused(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(40 + bd)
+    o_in, d_in = twin_plane(r, oracle, ctx, 256, 128, pb, bd, rng)
+    o_pr, d_pr = twin_plane(r, oracle, ctx, 256, 128, pb, bd, rng, xpad=40, ypad=40)
+    L = oracle.lib()
+    for s, t in [(0, 0), (1, 3), (2, 0), (3, 0), (4, 0), (5, 1), (12, 0), (13, 9), (18, 0), (8, 11)]:
+        w, h = L.r1o_tx_width(s), L.r1o_tx_height(s)
+        n = 37
+        jobs = np.zeros(n, dtype=r.TX_JOB)
+        res = np.zeros((n, h, w), np.int16)
+        for i in range(n):
+            jobs[i] = (int(rng.integers(0, 256 - w + 1)), int(rng.integers(0, 128 - h + 1)),
+                       int(rng.integers(-40, 256 + 40 - w + 1)), int(rng.integers(-40, 128 + 40 - h + 1)))
+            L.r1o_diff(res[i].ctypes.data, o_in.ptr(int(jobs[i]["in_x"]), int(jobs[i]["in_y"])), o_in.cfg.stride,
+                       o_pr.ptr(int(jobs[i]["pred_x"]), int(jobs[i]["pred_y"])), o_pr.cfg.stride, w, h, pb)
+        got = r.diff_forward_transform(ctx, d_in, d_pr, jobs, s, t, bd)
+        assert np.array_equal(got, oracle.fht_batch(res, s, t, bd).reshape(n, h, w)), (s, t)
+
+
+# -------------------------------------------------------------------- MC -------
+SIZES_MC = [(4, 4), (4, 8), (8, 4), (8, 8), (8, 16), (16, 8), (16, 16), (16, 32), (32, 16), (32, 32),
+            (32, 64), (64, 32), (64, 64), (64, 128), (128, 64), (128, 128), (4, 16), (16, 4), (8, 32),
+            (32, 8), (16, 64), (64, 16), (2, 2), (4, 2), (2, 4), (2, 8), (6, 10)]
+
+
+def _mc_jobs(r, rng, n, W, H, pad, dst_wh=None):
+    jobs = np.zeros(n, dtype=r.MC_JOB)
+    off = 0
+    for i in range(n):
+        w, h = SIZES_MC[i % len(SIZES_MC)]
+        case = (i // len(SIZES_MC)) % 4
+        cf = 0 if case in (0, 1) else int(rng.integers(1, 16))
+        rf = 0 if case in (0, 2) else int(rng.integers(1, 16))
+        sx = int(rng.integers(-pad + 3, W + pad - w - 4))
+        sy = int(rng.integers(-pad + 3, H + pad - h - 4))
+        dx = int(rng.integers(0, (dst_wh or (W, H))[0] - w + 1))
+        dy = int(rng.integers(0, (dst_wh or (W, H))[1] - h + 1))
+        jobs[i] = (dx, dy, sx, sy, w, h, cf, rf, int(rng.integers(0, 4)), int(rng.integers(0, 4)), off)
+        off += w * h
+    return jobs, off
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_prep_8tap_batch(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(200 + bd)
+    o_src, d_src = twin_plane(r, oracle, ctx, 384, 256, pb, bd, rng, xpad=24, ypad=24)
+    jobs, total = _mc_jobs(r, rng, 4 * len(SIZES_MC) * 3, 384, 256, 24)
+    got = np.full(total + 5, -12345, np.int16)
+    r.prep_8tap_batch(ctx, got, d_src, jobs, bd)
+    want = np.full(total + 5, -12345, np.int16)
+    L = oracle.lib()
+    for j in jobs:
+        L.r1o_prep_8tap(want[int(j["tmp_off"]):].ctypes.data, o_src.ptr(int(j["src_x"]), int(j["src_y"])),
+                        o_src.cfg.stride, int(j["w"]), int(j["h"]), int(j["col_frac"]), int(j["row_frac"]),
+                        int(j["mode_x"]), int(j["mode_y"]), bd, pb)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_put_8tap_and_avg(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(300 + bd)
+    o_src, d_src = twin_plane(r, oracle, ctx, 384, 256, pb, bd, rng, xpad=24, ypad=24)
+    L = oracle.lib()
+    # put: jobs are applied one by one on a fresh dst each, so overlapping dst blocks of
+    # a batch cannot hide an error
+    jobs, _ = _mc_jobs(r, rng, 4 * len(SIZES_MC), 384, 256, 24)
+    for j in jobs:
+        o_dst, d_dst = twin_plane(r, oracle, ctx, 384, 256, pb, bd, pad=False, xpad=8, ypad=8)
+        r.put_8tap_batch(ctx, d_dst, d_src, j.reshape(1), bd)
+        L.r1o_put_8tap(o_dst.ptr(int(j["dst_x"]), int(j["dst_y"])), o_dst.cfg.stride,
+                       o_src.ptr(int(j["src_x"]), int(j["src_y"])), o_src.cfg.stride, int(j["w"]), int(j["h"]),
+                       int(j["col_frac"]), int(j["row_frac"]), int(j["mode_x"]), int(j["mode_y"]), bd, pb)
+        assert np.array_equal(d_dst.download(), o_dst.data), tuple(j)
+    # a non-overlapping tiling in ONE batch + compound average
+    o_dst, d_dst = twin_plane(r, oracle, ctx, 384, 256, pb, bd, pad=False, xpad=8, ypad=8)
+    tiles = [(x, y) for y in range(0, 256, 32) for x in range(0, 384, 32)]
+    jb = np.zeros(len(tiles), dtype=r.MC_JOB)
+    ab = np.zeros(len(tiles), dtype=r.AVG_JOB)
+    for i, (x, y) in enumerate(tiles):
+        jb[i] = (x, y, x + int(rng.integers(-8, 9)), y + int(rng.integers(-8, 9)), 32, 32,
+                 int(rng.integers(0, 16)), int(rng.integers(0, 16)), i % 4, (i // 4) % 4, i * 1024)
+        ab[i] = (x, y, 32, 32, i * 1024)
+    r.put_8tap_batch(ctx, d_dst, d_src, jb, bd)
+    for j in jb:
+        L.r1o_put_8tap(o_dst.ptr(int(j["dst_x"]), int(j["dst_y"])), o_dst.cfg.stride,
+                       o_src.ptr(int(j["src_x"]), int(j["src_y"])), o_src.cfg.stride, 32, 32,
+                       int(j["col_frac"]), int(j["row_frac"]), int(j["mode_x"]), int(j["mode_y"]), bd, pb)
+    assert np.array_equal(d_dst.download(), o_dst.data)
+    t1 = np.zeros(len(tiles) * 1024, np.int16)
+    t2 = np.zeros(len(tiles) * 1024, np.int16)
+    r.prep_8tap_batch(ctx, t1, d_src, jb, bd)
+    jb2 = jb.copy()
+    jb2["src_x"] += 5
+    jb2["row_frac"] = (jb2["row_frac"] + 7) % 16
+    r.prep_8tap_batch(ctx, t2, d_src, jb2, bd)
+    r.mc_avg_batch(ctx, d_dst, t1, t2, ab, bd)
+    for a in ab:
+        o = int(a["tmp_off"])
+        L.r1o_mc_avg(o_dst.ptr(int(a["dst_x"]), int(a["dst_y"])), o_dst.cfg.stride, t1[o:].ctypes.data,
+                     t2[o:].ctypes.data, 32, 32, bd, pb)
+    assert np.array_equal(d_dst.download(), o_dst.data)
+    # extreme intermediates: saturated tmp values must clamp, not wrap
+    t1[:] = 32767
+    t2[:] = 32767
+    r.mc_avg_batch(ctx, d_dst, t1, t2, ab, bd)
+    assert (d_dst.download()[8:8 + 256, o_dst.cfg.xorigin:o_dst.cfg.xorigin + 384] == (1 << bd) - 1).all()
+
+
+def test_mc_errors(r, ctx, oracle):
+    rng = np.random.default_rng(9)
+    _, d = twin_plane(r, oracle, ctx, 64, 64, 1, 8, rng, xpad=8, ypad=8)
+    j = np.zeros(1, dtype=r.MC_JOB)
+    xo = int(d.cfg.xorigin)  # Plane::new aligns the left padding up (8 -> 32 px)
+    j[0] = (0, 0, -xo, 0, 8, 8, 3, 0, 0, 0, 0)  # horizontal filter needs 3 px left of the allocation
+    with pytest.raises(r.Rav1eCudaError) as e:
+        r.put_8tap_batch(ctx, d, d, j, 8)
+    assert e.value.code == r.capi.R1C_ERR_BOUNDS
+    j[0] = (0, 0, -xo, 0, 8, 8, 0, 0, 0, 0, 0)  # the copy case at the same origin is legal
+    r.put_8tap_batch(ctx, d, d, j, 8)
+    j[0] = (0, 0, 0, 0, 8, 8, 16, 0, 0, 0, 0)
+    with pytest.raises(r.Rav1eCudaError):
+        r.put_8tap_batch(ctx, d, d, j, 8)
+    tmp = np.zeros(10, np.int16)
+    j[0] = (0, 0, 0, 0, 8, 8, 0, 0, 0, 0, 0)
+    with pytest.raises(r.Rav1eCudaError):  # tmp smaller than the compute block
+        r.prep_8tap_batch(ctx, tmp, d, j, 8)
+
+
+# ----------------------------------------------------------- full search -------
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+def test_full_search_batch(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(400 + bd)
+    o_ref, d_ref = twin_plane(r, oracle, ctx, 256, 160, pb, bd, rng, smooth=True)
+    shifted = np.roll(o_ref.visible, (3, -5), axis=(0, 1)).astype(np.int64) + rng.integers(-2, 3, size=(160, 256))
+    o_org, d_org = twin_plane(r, oracle, ctx, 256, 160, pb, bd,
+                              data=np.clip(shifted, 0, (1 << bd) - 1))
+    L = oracle.lib()
+    n = 120
+    jobs = np.zeros(n, dtype=r.FS_JOB)
+    init = np.zeros(n, dtype=r.ME_RESULT)
+    init["cost"] = U64_MAX
+    for i in range(n):
+        b = int(rng.integers(0, 22))
+        bw, bh = L.r1o_block_width(b), L.r1o_block_height(b)
+        po = (int(rng.integers(0, (256 - bw) // 4 + 1)) * 4, int(rng.integers(0, (160 - bh) // 4 + 1)) * 4)
+        rx, ry = int(rng.integers(0, 20)), int(rng.integers(0, 12))
+        x_lo, x_hi = max(po[0] - rx, -88), min(po[0] + rx, 256 + 88 - bw)
+        y_lo, y_hi = max(po[1] - ry, -88), min(po[1] + ry, 160 + 88 - bh)
+        jobs[i]["po_x"], jobs[i]["po_y"], jobs[i]["bsize"] = po[0], po[1], b
+        jobs[i]["x_lo"], jobs[i]["x_hi"], jobs[i]["y_lo"], jobs[i]["y_hi"] = x_lo, x_hi, y_lo, y_hi
+        jobs[i]["step"] = int(rng.integers(1, 4))
+        jobs[i]["lambda_"] = int(rng.choice([0, 1, 57, 4000, 1 << 20]))
+        jobs[i]["pmv"][0] = (int(rng.integers(-64, 64)), int(rng.integers(-64, 64)))
+        jobs[i]["pmv"][1] = (int(rng.integers(-64, 64)), int(rng.integers(-64, 64)))
+        jobs[i]["allow_high_precision_mv"] = i & 1
+        if i % 3 == 0:  # continue from an earlier result, like the loop over cmvs (src/me.rs:534-565)
+            jobs[i]["has_init"] = 1
+            init[i]["mv"] = (8, -8)
+            init[i]["cost"] = [0, 5000, 10 ** 7, U64_MAX][int(rng.integers(0, 4))]
+    got = r.full_search_batch(ctx, d_org, d_ref, jobs, bd, init.copy())
+    for i in range(n):
+        ini = ((int(init[i]["mv"]["row"]), int(init[i]["mv"]["col"])), int(init[i]["cost"])) if jobs[i]["has_init"] else None
+        want = oracle_full_search(oracle, o_org, o_ref, jobs[i], ini)
+        assert ((int(got[i]["mv"]["row"]), int(got[i]["mv"]["col"])), int(got[i]["cost"])) == want, i
+
+
+def test_full_search_ties_and_errors(r, ctx, oracle):
+    """flat planes: every candidate ties, the first raster position must win"""
+    o, d = twin_plane(r, oracle, ctx, 128, 96, 1, 8)
+    mv, cost = r.full_search(ctx, 30, 40, 28, 36, r.BLOCK["BLOCK_8X8"], d, d, (0, 0), U64_MAX, (32, 32), 2, 0,
+                             [(0, 0), (0, 0)], False, 8)
+    assert (mv, cost) == (((28 - 32) * 8, (30 - 32) * 8), 0)
+    # with a rate term the zero MV wins instead
+    mv, cost = r.full_search(ctx, 24, 40, 24, 40, r.BLOCK["BLOCK_8X8"], d, d, (0, 0), U64_MAX, (32, 32), 1, 10,
+                             [(0, 0), (0, 0)], False, 8)
+    assert (mv, cost) == ((0, 0), 0)
+    with pytest.raises(r.Rav1eCudaError) as e:
+        r.full_search(ctx, -200, 40, 28, 36, 3, d, d, (0, 0), U64_MAX, (32, 32), 1, 0, [(0, 0), (0, 0)], False, 8)
+    assert e.value.code == r.capi.R1C_ERR_BOUNDS
+    # quarter-resolution style job: 16x16 -> 4x4 blocks on a small plane (estimate_motion_ss4)
+    rng = np.random.default_rng(8)
+    o_q, d_q = twin_plane(r, oracle, ctx, 120, 68, 1, 8, rng, xpad=22, ypad=22, xdec=2, ydec=2)
+    o_p, d_p = twin_plane(r, oracle, ctx, 120, 68, 1, 8, rng, xpad=22, ypad=22, xdec=2, ydec=2)
+    j = np.zeros(1, dtype=r.FS_JOB)
+    j[0]["po_x"], j[0]["po_y"], j[0]["bsize"] = 16, 16, 0
+    j[0]["x_lo"], j[0]["x_hi"], j[0]["y_lo"], j[0]["y_hi"], j[0]["step"], j[0]["lambda_"] = -20, 64, 0, 32, 1, 3
+    got = r.full_search_batch(ctx, d_q, d_p, j, 8)
+    want = oracle_full_search(oracle, o_q, o_p, j[0])
+    assert ((int(got[0]["mv"]["row"]), int(got[0]["mv"]["col"])), int(got[0]["cost"])) == want
+
+
+# -------------------------------------------------- superblock full search -----
+def _check_sb(r, oracle, o_org, o_ref, params, jobs, out, W4, H4):
+    L = oracle.lib()
+    checked = 0
+    for ji, job in enumerate(jobs):
+        for b in range(22):
+            if r.sb_result_offset(b) < 0 or not (int(job["bsize_mask"]) >> b) & 1:
+                continue
+            bw, bh = L.r1o_block_width(b), L.r1o_block_height(b)
+            k = 0
+            for ry in range(0, 64, bh):
+                for rx in range(0, 64, bw):
+                    got = out[ji, r.sb_result_offset(b) + k]
+                    k += 1
+                    po = (int(job["po_x"]) + rx, int(job["po_y"]) + ry)
+                    if po[0] + bw > W4 or po[1] + bh > H4:
+                        assert int(got["cost"]) == 12345, "blocks outside the frame must stay untouched"
+                        continue
+                    cmv = (int(job["cmv"]["row"]), int(job["cmv"]["col"]))
+                    x_lo, x_hi, y_lo, y_hi, _ = full_pixel_window(oracle, params.w_in_b, params.h_in_b, po, bw, bh,
+                                                                  cmv, params.range_x, params.range_y)
+                    fj = np.zeros(1, dtype=r.FS_JOB)[0]
+                    fj["po_x"], fj["po_y"], fj["bsize"] = po[0], po[1], b
+                    fj["x_lo"], fj["x_hi"], fj["y_lo"], fj["y_hi"] = x_lo, x_hi, y_lo, y_hi
+                    fj["step"], fj["lambda_"] = params.step, params.lambda_
+                    fj["pmv"] = job["pmv"]
+                    fj["allow_high_precision_mv"] = params.allow_high_precision_mv
+                    want = oracle_full_search(oracle, o_org, o_ref, fj)
+                    assert want is not None
+                    assert ((int(got["mv"]["row"]), int(got["mv"]["col"])), int(got["cost"])) == want, \
+                        (ji, r.capi.BLOCK_SIZES[b], rx, ry)
+                    checked += 1
+    return checked
+
+
+@pytest.mark.parametrize("pb,bd,step,lam", [(1, 8, 1, 0), (1, 8, 1, 700), (1, 8, 2, 33), (2, 10, 1, 90)])
+def test_me_sb_matches_per_block_full_search(r, ctx, oracle, pb, bd, step, lam):
+    """every block of every size of every superblock (borders included) against the
+    oracle's full_search run block by block with the reference's window rule"""
+    rng = np.random.default_rng(500 + bd + step + lam)
+    W, H = 192, 136  # 136 = 2 full superblock rows + a partial one
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    noisy = np.roll(o_ref.visible, (-2, 6), axis=(0, 1)).astype(np.int64) + rng.integers(-3, 4, size=(H, W))
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.clip(noisy, 0, (1 << bd) - 1))
+    params = r.make_sb_params(W // 4, H // 4, 20, 12, step, lam)
+    pos = [(x, y) for y in range(0, H, 64) for x in range(0, W, 64)] + [(64, H - 64)]  # + an adjust_bo style row
+    jobs = np.zeros(len(pos), dtype=r.SB_JOB)
+    for i, (x, y) in enumerate(pos):
+        jobs[i]["po_x"], jobs[i]["po_y"], jobs[i]["bsize_mask"] = x, y, 0x3FFFFF
+        jobs[i]["pmv"][0] = (int(rng.integers(-40, 40)), int(rng.integers(-40, 40)))
+        jobs[i]["pmv"][1] = (int(rng.integers(-40, 40)), int(rng.integers(-40, 40)))
+    jobs[4]["cmv"] = (-16, 24)  # an off-centre search on an interior superblock
+    res = np.zeros(len(pos) * r.SB_RESULTS, dtype=r.ME_RESULT)
+    res["cost"] = 12345
+    out = r.me_sb_batch(ctx, d_org, d_ref, params, jobs, bd, res)
+    n = _check_sb(r, oracle, o_org, o_ref, params, jobs, out, W, H)
+    assert n > 849 * 6
+
+
+def test_me_sb_flat_ties_and_mask(r, ctx, oracle):
+    o, d = twin_plane(r, oracle, ctx, 128, 128, 1, 8)  # all 128: every candidate ties at SAD 0
+    params = r.make_sb_params(32, 32, 9, 7, 1, 0)
+    jobs = np.zeros(1, dtype=r.SB_JOB)
+    jobs[0]["po_x"], jobs[0]["po_y"] = 64, 64
+    jobs[0]["bsize_mask"] = (1 << r.BLOCK["BLOCK_8X8"]) | (1 << r.BLOCK["BLOCK_64X64"])
+    res = np.zeros(r.SB_RESULTS, dtype=r.ME_RESULT)
+    res["cost"] = 12345
+    out = r.me_sb_batch(ctx, d, d, params, jobs, 8, res)[0]
+    for b in range(22):
+        off, cnt = r.sb_result_offset(b), r.sb_result_count(b)
+        if off < 0:
+            continue
+        blk = out[off:off + cnt]
+        if (int(jobs[0]["bsize_mask"]) >> b) & 1:  # first raster candidate: (-7, -9) px
+            assert (blk["mv"]["row"] == -56).all() and (blk["mv"]["col"] == -72).all() and (blk["cost"] == 0).all()
+        else:
+            assert (blk["cost"] == 12345).all()
+    with pytest.raises(r.Rav1eCudaError):
+        jobs[0]["po_x"] = 62
+        r.me_sb_batch(ctx, d, d, params, jobs, 8)
+
+
+# ------------------------------------------------------------- sub-pel ---------
+@pytest.mark.parametrize("pb,bd,use_satd,hp", [(1, 8, 1, 0), (1, 8, 0, 1), (2, 10, 1, 0), (2, 12, 1, 1)])
+def test_subpel_cost_and_telescopic(r, ctx, oracle, pb, bd, use_satd, hp):
+    rng = np.random.default_rng(600 + bd + use_satd)
+    W, H = 192, 128
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    noisy = np.roll(o_ref.visible, (1, -2), axis=(0, 1)).astype(np.int64) + rng.integers(-2, 3, size=(H, W))
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.clip(noisy, 0, (1 << bd) - 1))
+    L = oracle.lib()
+    n = 60
+    jobs = np.zeros(n, dtype=r.SUBPEL_JOB)
+    start = np.zeros(n, dtype=r.ME_RESULT)
+    for i in range(n):
+        b = int(rng.choice([0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 16, 17, 18, 19, 20, 21]))
+        bw, bh = L.r1o_block_width(b), L.r1o_block_height(b)
+        po = (int(rng.integers(0, (W - bw) // 4 + 1)) * 4, int(rng.integers(0, (H - bh) // 4 + 1)) * 4)
+        rngv = (C.c_int64 * 4)()
+        L.r1o_mv_range(W // 4, H // 4, po[0] // 4, po[1] // 4, bw, bh, C.byref(rngv))
+        jobs[i]["po_x"], jobs[i]["po_y"], jobs[i]["bsize"] = po[0], po[1], b
+        jobs[i]["lambda_"] = int(rng.choice([0, 40, 900]))
+        jobs[i]["pmv"][0] = (int(rng.integers(-30, 30)), int(rng.integers(-30, 30)))
+        jobs[i]["mvx_min"], jobs[i]["mvx_max"], jobs[i]["mvy_min"], jobs[i]["mvy_max"] = tuple(rngv)
+        jobs[i]["use_satd"], jobs[i]["allow_high_precision_mv"] = use_satd, hp
+        start[i]["mv"] = (int(rng.integers(-3, 4)) * 8, int(rng.integers(-3, 4)) * 8)
+        start[i]["cost"] = [0, 30000, U64_MAX][int(rng.integers(0, 3))]
+    # a block in the corner whose candidates leave the legal MV range
+    jobs[0]["po_x"], jobs[0]["po_y"], jobs[0]["bsize"] = 0, 0, 3
+    rngv = (C.c_int64 * 4)()
+    L.r1o_mv_range(W // 4, H // 4, 0, 0, 8, 8, C.byref(rngv))
+    jobs[0]["mvx_min"], jobs[0]["mvx_max"], jobs[0]["mvy_min"], jobs[0]["mvy_max"] = tuple(rngv)
+    start[0]["mv"] = (rngv[2], rngv[0])
+    cand = np.zeros((n, 5), dtype=r.MV)
+    for i in range(n):
+        for k in range(5):
+            cand[i, k] = (int(start[i]["mv"]["row"]) + int(rng.integers(-9, 10)),
+                          int(start[i]["mv"]["col"]) + int(rng.integers(-9, 10)))
+    got = r.subpel_cost_batch(ctx, d_org, d_ref, jobs, cand, bd)
+    for i in range(n):
+        for k in range(5):
+            want = oracle_subpel_cost(oracle, o_org, o_ref, jobs[i], (int(cand[i, k]["row"]), int(cand[i, k]["col"])), bd)
+            assert int(got[i, k]) == want, (i, k)
+    ref = r.subpel_refine_batch(ctx, d_org, d_ref, jobs, start, bd)
+    for i in range(n):
+        want = oracle_telescopic(oracle, o_org, o_ref, jobs[i],
+                                 (int(start[i]["mv"]["row"]), int(start[i]["mv"]["col"])), int(start[i]["cost"]), bd)
+        assert ((int(ref[i]["mv"]["row"]), int(ref[i]["mv"]["col"])), int(ref[i]["cost"])) == want, i
