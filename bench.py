@@ -1,0 +1,378 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the rav1e hot path on B200 (one JSON line).
+
+Headline workload (BASELINE.json configs[1]): 1080p 8-bit full-search motion
+estimation, +-64 px, every block of all 19 sizes 4x4..64x64, SAD search then the
+SATD re-evaluation + telescopic sub-pel tail of MotionEstimation::motion_estimation
+(src/me.rs:193-271).  A "step" is one frame pair (cur, ref) -> every block's
+(best_mv, lowest_cost).  Metric: Mpix/s = frame pixels / time.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]      # the CUDA path
+    python bench.py --impl reference ...                     # CPU arm: the oracle
+        (C restatement of the reference's scalar functions; the reference itself
+        is Rust + NASM and cannot be built in this image) on all host threads.
+
+N > 1 (torchrun): frames are sharded over ranks (lookahead motion search is
+independent per frame) -- no collective on the data path; the time
+is the max over ranks, value = N frames' pixels / time ("weak").
+
+Only the `cpu_baseline` leg and `--impl reference` touch oracle/; the timed CUDA
+path is librav1e_cuda.so through its C ABI (rav1e_b200.capi).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+W, H, BD, PB = 1920, 1080, 8, 1
+RANGE = 64
+LAMBDA = 160  # (me_lambda * 256 * 0.5) as u32 at a mid-range quantizer
+LUMA_PAD = 88  # src/frame/mod.rs:23,60
+WORKLOAD = "me_1080p_8bit_fullsearch_pm64_19sizes_sad_then_satd_subpel"
+ALG_INT_OPS = 2.0 * W * H * (2 * RANGE + 1) ** 2  # SURVEY 8(d) cfg 1: abs-diff + add per (pixel, candidate)
+ALG_HBM_BYTES_SB = None  # filled once the plane geometry is known
+
+
+# ----------------------------------------------------------------- synthetic frames --
+def synth_frame_pair(seed):
+    """SURVEY 8(d) cfg 1: cur = smooth random field; ref = cur moved by a random integer MV
+    per 64x64 superblock (+-48 px) plus +-4 noise, so minima are unique and non-trivial."""
+    rng = np.random.default_rng(seed)
+    big = rng.integers(0, 256, size=(H + 256, W + 256)).astype(np.float32)
+    for _ in range(2):  # separable box blur, radius 2
+        big = (np.roll(big, 2, 0) + np.roll(big, 1, 0) + big + np.roll(big, -1, 0) + np.roll(big, -2, 0)) / 5
+        big = (np.roll(big, 2, 1) + np.roll(big, 1, 1) + big + np.roll(big, -1, 1) + np.roll(big, -2, 1)) / 5
+    big = (big - big.mean()) * 3.0 + 128.0
+    cur = np.clip(np.rint(big[128:128 + H, 128:128 + W]), 0, 255).astype(np.uint8)
+    ref = np.empty_like(cur)
+    for sy in range(0, H, 64):
+        for sx in range(0, W, 64):
+            dy, dx = (int(v) for v in rng.integers(-48, 49, size=2))
+            h, w = min(64, H - sy), min(64, W - sx)
+            ref[sy:sy + h, sx:sx + w] = np.clip(np.rint(big[128 + sy + dy:128 + sy + dy + h,
+                                                            128 + sx + dx:128 + sx + dx + w]), 0, 255)
+    noise = rng.integers(-4, 5, size=ref.shape)
+    ref = np.clip(ref.astype(np.int16) + noise, 0, 255).astype(np.uint8)
+    return cur, ref
+
+
+def padded(cfg, vis):
+    """whole allocation with Plane::pad semantics (edge replication) -- numpy, input prep only"""
+    a = np.empty((cfg.alloc_height, cfg.stride), dtype=vis.dtype)
+    yo, xo, h, w = cfg.yorigin, cfg.xorigin, cfg.height, cfg.width
+    a[yo:yo + h, xo:xo + w] = vis
+    a[yo:yo + h, :xo] = vis[:, :1]
+    a[yo:yo + h, xo + w:] = vis[:, -1:]
+    a[:yo, :] = a[yo:yo + 1, :]
+    a[yo + h:, :] = a[yo + h - 1:yo + h, :]
+    return a
+
+
+# ----------------------------------------------------------------------- clocks --
+class ClockSampler(threading.Thread):
+    """samples SM clock and throttle reasons of one GPU (NVML) while the timed region runs"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.max_mhz = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {getattr(nv, n): lab for n, lab in (
+            ("nvmlClocksThrottleReasonHwSlowdown", "hw_slowdown"),
+            ("nvmlClocksThrottleReasonHwThermalSlowdown", "hw_thermal_slowdown"),
+            ("nvmlClocksThrottleReasonSwThermalSlowdown", "sw_thermal_slowdown"),
+            ("nvmlClocksThrottleReasonSwPowerCap", "sw_power_cap"),
+            ("nvmlClocksThrottleReasonHwPowerBrakeSlowdown", "hw_power_brake"),
+            ("nvmlClocksThrottleReasonApplicationsClocksSetting", "app_clocks")) if hasattr(nv, n)}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, lab in names.items():
+                    if r & bit:
+                        self.reasons.add(lab)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def summary(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join()
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+# ------------------------------------------------------------------ CPU arm (oracle) --
+def cpu_sample_slots(rng, params_layout, frac):
+    """a stratified sample of frame-layout slots: `frac` of the blocks of every size"""
+    idx = []
+    for off, cols, rows in params_layout:
+        n = cols * rows
+        k = max(1, int(round(n * frac)))
+        idx.append(off + rng.choice(n, size=k, replace=False))
+    return np.sort(np.concatenate(idx)).astype(np.int64)
+
+
+def oracle_layout(r1o):
+    L = r1o.lib()
+    off, cols, rows = (C.c_int64 * 22)(), (C.c_int32 * 22)(), (C.c_int32 * 22)()
+    mask = sum(1 << b for b in range(22) if b not in (13, 14, 15))
+    L.r1o_frame_me_layout(W, H, mask, C.byref(off), C.byref(cols), C.byref(rows))
+    return mask, [(off[b], cols[b], rows[b]) for b in range(22) if off[b] >= 0]
+
+
+def run_cpu(seconds_target, steps=1, warmup=0):
+    """times the oracle (all host threads) on a bounded sample of the workload ->
+    (Mpix/s, cores, sample description, ms per step)"""
+    from oracle import r1o
+    r1o.build()
+    cur, ref = synth_frame_pair(1)
+    o_org = r1o.OPlane(W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
+    o_ref = r1o.OPlane(W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
+    o_org.visible[...] = cur
+    o_ref.visible[...] = ref
+    o_org.pad()
+    o_ref.pad()
+    mask, layout = oracle_layout(r1o)
+    rng = np.random.default_rng(7)
+    cores = r1o.lib().r1o_num_threads()
+    # calibrate on a tiny sample, then size the sample for the time target
+    frac = 1.0 / 4000
+    for _ in range(2):
+        idx = cpu_sample_slots(rng, layout, frac)
+        t0 = time.perf_counter()
+        r1o.frame_me(o_org, o_ref, RANGE, RANGE, LAMBDA, mask, 1, 1, 0, BD, idx)
+        dt = time.perf_counter() - t0
+        frac = min(1.0, frac * max(1.0, min(40.0, seconds_target / max(dt, 1e-3))))
+    idx = cpu_sample_slots(rng, layout, frac)
+    for _ in range(warmup):
+        r1o.frame_me(o_org, o_ref, RANGE, RANGE, LAMBDA, mask, 1, 1, 0, BD, idx[: max(19, idx.size // 8)])
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        r1o.frame_me(o_org, o_ref, RANGE, RANGE, LAMBDA, mask, 1, 1, 0, BD, idx)
+    dt = (time.perf_counter() - t0) / steps
+    # every size covers the frame once, so a fraction f of the blocks of every size is a
+    # fraction f of the frame's work
+    mpix = frac * W * H / 1e6
+    sample = ("%.4f of the blocks of each of the 19 sizes (%d blocks) of one 1080p frame pair, "
+              "full search +-64 + SATD/sub-pel tail, OpenMP over blocks" % (frac, idx.size))
+    return mpix / dt, cores, sample, dt * 1e3
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    v, cores, sample, ms = run_cpu(6.0, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": "Mpix/s", "value": v, "unit": "Mpix/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE,
+                   "lambda": LAMBDA},
+        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample,
+                         "note": "C restatement of the reference's scalar _ref functions; the reference's "
+                                 "own Rust/NASM build is unavailable on this box (no rustc/cargo/nasm)"},
+        "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+# -------------------------------------------------------------------- CUDA arm --
+def int_peak():
+    p = os.path.join(ROOT, "profiles", "int_peaks_r01.json")
+    try:
+        d = json.load(open(p))
+        return float(d["iadd"]), "measured (tools/int_peak.cu on B200: independent IADD3 stream, G lane-ops/s)", d
+    except Exception:
+        return 148 * 128 * 1.965, "fallback (148 SM x 128 lanes x 1.965 GHz)", {}
+
+
+def hbm_peak():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the MC / forward-TX kernel lines")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import rav1e_b200 as r
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (rav1e_b200 has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W_ = max(args.warmup, 3)
+    K = args.steps
+
+    ctx = r.Context(local)
+    lib = ctx.lib
+    ext = torch.cuda.ExternalStream(ctx.stream, device=local)
+
+    # this rank's frame pair (frame-sharded lookahead: rank i takes frame i)
+    cur, ref = synth_frame_pair(1 + 2 * rank)
+    p_org = r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
+    p_ref = r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
+    h_org = torch.from_numpy(padded(p_org.cfg, cur)).pin_memory()
+    h_ref = torch.from_numpy(padded(p_ref.cfg, ref)).pin_memory()
+    p_org.upload(h_org.numpy())
+    p_ref.upload(h_ref.numpy())
+    params = r.make_frame_me_params(W, H, RANGE, RANGE, LAMBDA, refine=1, use_satd=1)
+    n_res = r.frame_me_count(params)
+    d_res = torch.empty(n_res * 16, dtype=torch.uint8, device="cuda")
+    h_res = np.zeros(n_res, dtype=r.ME_RESULT)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step_dev():
+        ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, d_res.data_ptr()))
+
+    def step_e2e():
+        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org.h, h_org.data_ptr()))
+        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref.h, h_ref.data_ptr()))
+        ctx.check(lib.r1c_frame_me(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, h_res.ctypes.data))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        """K steps, each bracketed by events on the library's stream, L2 flushed (untimed)
+        between steps -> total ms (max over ranks)"""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+        barrier()
+        for a, b in evs:
+            with torch.cuda.stream(ext):
+                flush.zero_()
+                a.record(ext)
+            fn()
+            b.record(ext)
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(W_):
+        step_dev()
+    ctx.sync()
+    # ---- device-resident throughput + the dominant kernel's duration --------------
+    ctx.check(lib.r1c_profile(ctx.h, 1))
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launches
+    ms_total = timed(step_dev, K)
+    launches = ctx.launches - l0
+    prof = {}
+    for name, slot in (("me_sb_kernel", 0), ("subpel_mc", 1), ("subpel_cost", 2)):
+        ms, n = C.c_double(), C.c_int64()
+        ctx.check(lib.r1c_profile_read(ctx.h, slot, C.byref(ms), C.byref(n)))
+        prof[name] = (ms.value, n.value)
+    ctx.check(lib.r1c_profile(ctx.h, 0))
+    # ---- end to end: host planes in, host results out, every step ------------------
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, K)
+    clocks = sampler.summary()
+
+    mpix = W * H / 1e6
+    value = world * mpix / (ms_total / K / 1e3)
+    e2e = world * mpix / (ms_e2e / K / 1e3)
+    h2d = int(h_org.numel() + h_ref.numel())
+    d2h = int(n_res * 16)
+
+    if rank == 0:
+        ipeak, ipeak_how, ipk = int_peak()
+        hpeak, hpeak_how = hbm_peak()
+        sb_ms = prof["me_sb_kernel"][0] / max(1, prof["me_sb_kernel"][1])
+        n_sb = ((W + 63) // 64) * ((H + 63) // 64)
+        win = (64 + 2 * RANGE) ** 2 + 64 * 64
+        alg_bytes = n_sb * (win * PB + 849 * 16)  # window + org region per superblock, results out
+        achieved = ALG_INT_OPS / (sb_ms / 1e3) / 1e9  # G int-ops/s
+        roof = {"bound": "int32_alu", "kernel": "me_sb_kernel<1>", "achieved": achieved, "peak": ipeak,
+                "unit": "Gop/s", "frac": achieved / ipeak, "traffic": None,
+                "peak_source": ipeak_how,
+                "alg_ops_per_launch": ALG_INT_OPS, "ms_per_launch": sb_ms,
+                "share_of_step": prof["me_sb_kernel"][0] / ms_total,
+                "hbm": {"achieved": alg_bytes / (sb_ms / 1e3) / 1e9, "peak": hpeak, "unit": "GB/s",
+                        "frac": alg_bytes / (sb_ms / 1e3) / 1e9 / hpeak, "alg_bytes_per_launch": alg_bytes,
+                        "peak_source": hpeak_how},
+                "packed_simd": {"vabsdiff4_peak_Ginstr_s": ipk.get("vabsdiff4_acc"),
+                                "note": "1 VABSDIFF4.ACC = 8 byte-ops; packed peak = 8 x this"},
+                "other_kernels_ms_per_step": {k: v[0] / K for k, v in prof.items()}}
+        line = {
+            "metric": "Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K, "warmup": W_,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE,
+                       "lambda": LAMBDA, "blocks_per_frame": int(n_res),
+                       "l2": "flushed between steps (256 MiB memset, untimed)",
+                       "sharding": "one frame pair per GPU, no collective"},
+            "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / K,
+                    "path": "r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (host results)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roof,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            v, cores, sample, _ = run_cpu(12.0)
+            line["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample}
+        if world == 1 and not args.no_extras:
+            try:
+                import bench_kernels
+                line["kernels"] = bench_kernels.run(ctx, r, torch, ext, flush)
+            except Exception as e:  # the headline line must still print
+                line["kernels"] = {"error": repr(e)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -101,6 +101,19 @@ void *r1c_stream(r1c_ctx *ctx);           /* the cudaStream_t, for event timing 
 int r1c_device(const r1c_ctx *ctx);
 /* number of kernels this context has launched so far (bench.py gpu_launches) */
 int64_t r1c_launch_count(const r1c_ctx *ctx);
+/* Device-side timing of one kernel class, for the roofline report: while
+ * enabled, the launches of that class are bracketed by CUDA events on the
+ * context stream.  r1c_profile_read waits for the stream, returns the summed
+ * duration and the number of launches since the last read, and resets. */
+#define R1C_PROF_ME_SB 0      /* me_sb_kernel (superblock full search)        */
+#define R1C_PROF_SUBPEL_MC 1  /* put_8tap of the sub-pel candidates           */
+#define R1C_PROF_SUBPEL_COST 2 /* SAD / SATD of the predicted candidates      */
+#define R1C_PROF_MC 3         /* put / prep / avg batch kernels               */
+#define R1C_PROF_TX 4         /* forward transform kernels                    */
+#define R1C_PROF_DIST 5       /* SAD / SATD batch kernels                     */
+#define R1C_PROF_SLOTS 6
+int r1c_profile(r1c_ctx *ctx, int enable);
+int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches);
 
 /* ------------------------------------------------------------------------
  * Planes.  Mirrors Plane<T> / PlaneConfig (src/frame/plane.rs:22-47,154,
@@ -328,6 +341,48 @@ int r1c_subpel_refine_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane 
 int r1c_subpel_refine_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                                 const r1c_subpel_job *d_jobs, int64_t n, int bit_depth,
                                 r1c_me_result *d_results);
+
+/* ------------------------------------------------------------------------
+ * Whole-frame motion estimation: MotionEstimation::motion_estimation for
+ * FullSearch (src/me.rs:193-271) applied to EVERY block of every requested
+ * BlockSize on its natural grid, one call per (frame, reference) pair --
+ * the batched form of the loops in build_coarse_pmvs (src/encoder.rs:
+ * 2727-2742) and of the per-block calls of the RDO loop.  Per block:
+ *   full-pel : full_search over FullSearch::full_pixel_me's window
+ *              (src/me.rs:533-546, cmv = 0, `range` instead of 16, step 1),
+ *              SAD cost, from (best_mv = 0, lowest_cost = MAX);
+ *   refine 1 : + the tail of motion_estimation (src/me.rs:232-271): SATD
+ *              re-evaluation of the full-pel winner when use_satd, then
+ *              telescopic_subpel_search (steps 8, 4, 2 (,1)).
+ * pmv = {0, 0} for both predictors (what the lookahead passes).
+ * Result layout: for each BlockSize b of bsize_mask in enum order, the
+ * (width / bw) x (height / bh) whole blocks in raster order:
+ *   results[r1c_frame_me_offset(...b) + by * cols + bx].
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int32_t width, height;    /* frame size in pixels, multiples of 4 */
+  int32_t range_x, range_y; /* full-pel search range in pixels */
+  uint32_t lambda;
+  uint32_t bsize_mask;      /* sizes up to 64x64 only */
+  int32_t refine;           /* 0: full-pel only, 1: + SATD / sub-pel tail */
+  int32_t use_satd;         /* fi.config.speed_settings.use_satd_subpel */
+  int32_t allow_high_precision_mv;
+  /* multi-GPU sharding by superblock row: only blocks whose
+   * origin lies in superblock rows [sb_row_lo, sb_row_hi) are computed; the
+   * other entries of `results` are left untouched.  0, 0 = the whole frame. */
+  int32_t sb_row_lo, sb_row_hi;
+} r1c_frame_me_params;
+/* number of result entries of the whole frame; offset / grid of one size
+ * (returns -1 for sizes outside the mask) */
+int64_t r1c_frame_me_count(const r1c_frame_me_params *p);
+int64_t r1c_frame_me_offset(const r1c_frame_me_params *p, int bsize, int32_t *cols, int32_t *rows);
+int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                 const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results);
+int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                     const r1c_frame_me_params *p, int bit_depth, r1c_me_result *d_results);
+/* plane upload without the trailing synchronisation (pinned or pageable host
+ * memory; ordered on the context stream) */
+int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);
 
 #ifdef __cplusplus
 }

@@ -82,6 +82,11 @@ def lib():
         L.r1o_avg_batch.argtypes = [vp, P(PlaneCfg), vp, vp, vp, vp, i64, i, i]
         L.r1o_fht_batch.argtypes = [vp, vp, i, i, i, i64]
         L.r1o_fht_batch.restype = i
+        L.r1o_frame_me_layout.argtypes = [i, i, u32, P(i64 * 22), P(C.c_int32 * 22), P(C.c_int32 * 22)]
+        L.r1o_frame_me_layout.restype = i64
+        L.r1o_frame_me.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i, i, i, i, u32, u32, i, i, i, i, i,
+                                   vp, i64, vp, vp]
+        L.r1o_frame_me.restype = i64
         _lib = L
     return _lib
 
@@ -157,3 +162,23 @@ def txfm1d(type1d, vec):
     if rc != 0:
         raise ValueError("unimplemented (type, n)")
     return out
+
+
+def frame_me(org: OPlane, ref: OPlane, range_x, range_y, lambda_, bsize_mask, refine, use_satd,
+             allow_hp, bit_depth, idx=None):
+    """motion_estimation (src/me.rs:193-271) for every block of the frame (or the frame-layout
+    slots `idx`) -> (mv int16 (n, 2), cost uint64 (n,)); untouched slots hold cost 0 / mv 0"""
+    L = lib()
+    w, h = int(org.cfg.width), int(org.cfg.height)
+    off, cols, rows = (C.c_int64 * 22)(), (C.c_int32 * 22)(), (C.c_int32 * 22)()
+    total = L.r1o_frame_me_layout(w, h, bsize_mask, C.byref(off), C.byref(cols), C.byref(rows))
+    mv = np.zeros((total, 2), dtype=np.int16)
+    cost = np.zeros(total, dtype=np.uint64)
+    ip, n_idx = None, 0
+    if idx is not None:
+        idx = np.ascontiguousarray(idx, dtype=np.int64)
+        ip, n_idx = _p(idx), idx.size
+    L.r1o_frame_me(org.origin_ptr(), C.byref(org.cfg), ref.origin_ptr(), C.byref(ref.cfg), w, h,
+                   range_x, range_y, lambda_, bsize_mask, int(refine), int(use_satd), int(allow_hp),
+                   bit_depth, org.px_bytes, ip, n_idx, _p(mv), _p(cost))
+    return mv, cost

@@ -350,3 +350,39 @@ def subpel_refine_batch(ctx, plane_org, plane_ref, jobs, results, bit_depth):
     ctx.check(ctx.lib.r1c_subpel_refine_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs),
                                               jobs.size, bit_depth, _p(results)))
     return results
+
+
+# ----------------------------------------------------- whole-frame motion search --
+ALL_SIZES_TO_64 = sum(1 << b for b in range(22) if b not in (13, 14, 15))
+
+
+def make_frame_me_params(width, height, range_x, range_y, lambda_, bsize_mask=ALL_SIZES_TO_64,
+                         refine=1, use_satd=1, allow_hp=False, sb_rows=(0, 0)):
+    return capi.FrameMeParams(width, height, range_x, range_y, lambda_, bsize_mask, int(refine),
+                              int(use_satd), int(allow_hp), sb_rows[0], sb_rows[1])
+
+
+def frame_me_count(params):
+    return capi.load().r1c_frame_me_count(C.byref(params))
+
+
+def frame_me_layout(params, bsize):
+    """-> (offset, cols, rows) of one BlockSize inside the frame_me result array"""
+    cols, rows = C.c_int32(), C.c_int32()
+    off = capi.load().r1c_frame_me_offset(C.byref(params), bsize, C.byref(cols), C.byref(rows))
+    return off, cols.value, rows.value
+
+
+def frame_me(ctx, plane_org, plane_ref, params, bit_depth, results=None):
+    """MotionEstimation::motion_estimation (FullSearch, src/me.rs:193-271) for every block of
+    every size of the frame; `results` (ME_RESULT array, host) is in/out for sharded calls."""
+    n = frame_me_count(params)
+    if n < 0:
+        raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad frame_me parameters")
+    if results is None:
+        results = np.zeros(n, dtype=ME_RESULT)
+        results["cost"] = np.iinfo(np.uint64).max
+    assert results.dtype == ME_RESULT and results.size == n and results.flags.c_contiguous
+    ctx.check(ctx.lib.r1c_frame_me(ctx.h, plane_org.h, plane_ref.h, C.byref(params), bit_depth,
+                                   _p(results)))
+    return results

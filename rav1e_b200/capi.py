@@ -97,6 +97,14 @@ class SubpelJob(C.Structure):
                 ("use_satd", C.c_int32), ("allow_high_precision_mv", C.c_int32)]
 
 
+class FrameMeParams(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("range_x", C.c_int32),
+                ("range_y", C.c_int32), ("lambda_", C.c_uint32), ("bsize_mask", C.c_uint32),
+                ("refine", C.c_int32), ("use_satd", C.c_int32),
+                ("allow_high_precision_mv", C.c_int32), ("sb_row_lo", C.c_int32),
+                ("sb_row_hi", C.c_int32)]
+
+
 # every symbol include/rav1e_cuda.h declares: name -> (restype, argtypes)
 _vp, _i, _i64, _u32, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_uint64
 _P = C.POINTER
@@ -142,6 +150,13 @@ SIGNATURES = {
     "r1c_subpel_cost_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _vp]),
     "r1c_subpel_refine_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_subpel_refine_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
+    "r1c_frame_me_count": (_i64, [_P(FrameMeParams)]),
+    "r1c_frame_me_offset": (_i64, [_P(FrameMeParams), _i, _P(C.c_int32), _P(C.c_int32)]),
+    "r1c_frame_me": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
+    "r1c_frame_me_dev": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
+    "r1c_plane_upload_async": (_i, [_vp, _vp, _vp]),
+    "r1c_profile": (_i, [_vp, _i]),
+    "r1c_profile_read": (_i, [_vp, _i, _P(C.c_double), _P(_i64)]),
 }
 
 _lib = None

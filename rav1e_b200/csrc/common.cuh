@@ -17,6 +17,7 @@ struct r1c_plane {
   int device;
 };
 
+#define R1C_PROF_RING 512
 struct r1c_ctx {
   int device;
   cudaStream_t stream;
@@ -26,8 +27,26 @@ struct r1c_ctx {
   // pinned host staging + device scratch, grown on demand (never shrinks)
   void *h_stage[4];
   size_t h_stage_cap[4];
-  void *d_scratch[12];
-  size_t d_scratch_cap[12];
+  void *d_scratch[16];
+  size_t d_scratch_cap[16];
+  // per-kernel-class device timing (r1c_profile*): event pairs around the launches
+  int prof_on;
+  int prof_mc_slot;  // != 0: the MC launches belong to this slot (sub-pel path)
+  struct {
+    cudaEvent_t ev[2][R1C_PROF_RING];
+    int n;            // pairs recorded since the last read
+    int created;
+    double ms_carry;  // time of pairs already folded (ring wrapped)
+    int64_t launches;
+  } prof[R1C_PROF_SLOTS];
+  // whole-frame motion estimation (me_frame.cu): job lists of the last
+  // (frame size, parameters) seen, resident on the device
+  struct {
+    int valid;
+    int32_t key[10];
+    void *d_sbjobs, *d_map, *d_subjobs;
+    int64_t n_sb, n_blocks;
+  } frame_me;
 };
 
 // Device-side view of a plane: pointer to plane coordinate (0,0) + geometry.
@@ -66,6 +85,10 @@ int r1c_stage_host(r1c_ctx *ctx, int slot, size_t bytes, void **out);
 int r1c_scratch_dev(r1c_ctx *ctx, int slot, size_t bytes, void **out);
 int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
                          int64_t n, int bit_depth);
+
+// scoped event pair around a kernel launch (no-op unless r1c_profile(ctx, 1))
+void r1c_prof_begin(r1c_ctx *ctx, int slot);
+void r1c_prof_end(r1c_ctx *ctx, int slot);
 
 #define R1C_CUDA(ctx, call)                                                              \
   do {                                                                                   \

@@ -44,8 +44,17 @@ extern "C" void r1c_destroy(r1c_ctx *ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (int i = 0; i < 4; i++)
     if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
-  for (int i = 0; i < 12; i++)
+  for (int i = 0; i < 16; i++)
     if (ctx->d_scratch[i]) cudaFree(ctx->d_scratch[i]);
+  for (int s = 0; s < R1C_PROF_SLOTS; s++)
+    if (ctx->prof[s].created)
+      for (int i = 0; i < R1C_PROF_RING; i++) {
+        cudaEventDestroy(ctx->prof[s].ev[0][i]);
+        cudaEventDestroy(ctx->prof[s].ev[1][i]);
+      }
+  if (ctx->frame_me.d_sbjobs) cudaFree(ctx->frame_me.d_sbjobs);
+  if (ctx->frame_me.d_map) cudaFree(ctx->frame_me.d_map);
+  if (ctx->frame_me.d_subjobs) cudaFree(ctx->frame_me.d_subjobs);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
 }
@@ -59,6 +68,61 @@ extern "C" const char *r1c_last_error(const r1c_ctx *ctx) { return ctx ? ctx->er
 extern "C" void *r1c_stream(r1c_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 extern "C" int r1c_device(const r1c_ctx *ctx) { return ctx ? ctx->device : -1; }
 extern "C" int64_t r1c_launch_count(const r1c_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+// ---- per-kernel-class timing ---------------------------------------------------
+static void prof_fold(r1c_ctx *ctx, int slot) {
+  auto &p = ctx->prof[slot];
+  if (p.n == 0) return;
+  cudaEventSynchronize(p.ev[1][p.n - 1]);
+  for (int i = 0; i < p.n; i++) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, p.ev[0][i], p.ev[1][i]) == cudaSuccess) p.ms_carry += ms;
+  }
+  p.n = 0;
+}
+void r1c_prof_begin(r1c_ctx *ctx, int slot) {
+  if (!ctx->prof_on) return;
+  auto &p = ctx->prof[slot];
+  if (!p.created) {
+    for (int i = 0; i < R1C_PROF_RING; i++) {
+      cudaEventCreate(&p.ev[0][i]);
+      cudaEventCreate(&p.ev[1][i]);
+    }
+    p.created = 1;
+  }
+  if (p.n == R1C_PROF_RING) prof_fold(ctx, slot);
+  cudaEventRecord(p.ev[0][p.n], ctx->stream);
+}
+void r1c_prof_end(r1c_ctx *ctx, int slot) {
+  if (!ctx->prof_on) return;
+  auto &p = ctx->prof[slot];
+  cudaEventRecord(p.ev[1][p.n], ctx->stream);
+  p.n++;
+  p.launches++;
+}
+extern "C" int r1c_profile(r1c_ctx *ctx, int enable) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int s = 0; s < R1C_PROF_SLOTS; s++) {
+    prof_fold(ctx, s);
+    ctx->prof[s].ms_carry = 0;
+    ctx->prof[s].launches = 0;
+  }
+  ctx->prof_on = enable != 0;
+  return R1C_OK;
+}
+extern "C" int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches) {
+  if (!ctx || slot < 0 || slot >= R1C_PROF_SLOTS) return R1C_ERR_ARG;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  prof_fold(ctx, slot);
+  if (ms) *ms = ctx->prof[slot].ms_carry;
+  if (launches) *launches = ctx->prof[slot].launches;
+  ctx->prof[slot].ms_carry = 0;
+  ctx->prof[slot].launches = 0;
+  return R1C_OK;
+}
 
 int r1c_stage_host(r1c_ctx *ctx, int slot, size_t bytes, void **out) {
   if (bytes > ctx->h_stage_cap[slot]) {
@@ -184,6 +248,13 @@ extern "C" int r1c_plane_upload(r1c_ctx *ctx, r1c_plane *p, const void *host) {
   size_t bytes = (size_t)p->cfg.stride * p->cfg.alloc_height * p->px_bytes;
   R1C_CUDA(ctx, cudaMemcpyAsync(p->d_data, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return R1C_OK;
+}
+
+extern "C" int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *p, const void *host) {
+  if (!ctx || !p || !host) return R1C_ERR_ARG;
+  size_t bytes = (size_t)p->cfg.stride * p->cfg.alloc_height * p->px_bytes;
+  R1C_CUDA(ctx, cudaMemcpyAsync(p->d_data, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
   return R1C_OK;
 }
 

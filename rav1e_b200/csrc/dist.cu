@@ -76,6 +76,7 @@ int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plan
   a.n = n;
   const int wpb = 8;
   unsigned grid = (unsigned)((n + wpb - 1) / wpb);
+  r1c_prof_begin(ctx, R1C_PROF_DIST);
   if (org->px_bytes == 1) {
     if (use_satd) satd_kernel<1><<<grid, wpb * 32, 0, ctx->stream>>>(a);
     else sad_kernel<1><<<grid, wpb * 32, 0, ctx->stream>>>(a);
@@ -83,6 +84,7 @@ int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plan
     if (use_satd) satd_kernel<2><<<grid, wpb * 32, 0, ctx->stream>>>(a);
     else sad_kernel<2><<<grid, wpb * 32, 0, ctx->stream>>>(a);
   }
+  r1c_prof_end(ctx, R1C_PROF_DIST);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }

@@ -349,6 +349,7 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
   a.n = n;
   a.bit_depth = bit_depth;
   const int grid = grid_for(ctx);
+  r1c_prof_begin(ctx, ctx->prof_mc_slot ? ctx->prof_mc_slot : R1C_PROF_MC);
   if (src->px_bytes == 1) {
     if (kind == 0) mc_kernel<1, 0><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
     else if (kind == 1) mc_kernel<1, 1><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
@@ -358,6 +359,7 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
     else if (kind == 1) mc_kernel<2, 1><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
     else mc_kernel<2, 2><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
   }
+  r1c_prof_end(ctx, ctx->prof_mc_slot ? ctx->prof_mc_slot : R1C_PROF_MC);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }
@@ -485,8 +487,10 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
   a.offs = d_offs;
   a.n = n;
   a.bit_depth = bit_depth;
+  r1c_prof_begin(ctx, R1C_PROF_MC);
   if (dst->px_bytes == 1) avg_kernel<1><<<grid_for(ctx), MC_THREADS, 0, ctx->stream>>>(a);
   else avg_kernel<2><<<grid_for(ctx), MC_THREADS, 0, ctx->stream>>>(a);
+  r1c_prof_end(ctx, R1C_PROF_MC);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }

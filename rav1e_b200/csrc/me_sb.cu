@@ -422,6 +422,7 @@ int launch_sb(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1
   a.rstride = ((winW * PB + 3) & ~3) + 4;
   const size_t smem = (size_t)64 * 64 * PB + (size_t)winH * a.rstride + 2 * 16 * 5 * 16 * 4;
   R1C_REQUIRE(ctx, smem <= 220 * 1024, R1C_ERR_ARG, "search range %dx%d needs %zu bytes of shared memory", p->range_x, p->range_y, smem);
+  r1c_prof_begin(ctx, R1C_PROF_ME_SB);
   if (PB == 1) {
     R1C_CUDA(ctx, cudaFuncSetAttribute(me_sb_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     me_sb_kernel<1><<<(unsigned)n, SB_THREADS, smem, ctx->stream>>>(a);
@@ -429,6 +430,7 @@ int launch_sb(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1
     R1C_CUDA(ctx, cudaFuncSetAttribute(me_sb_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     me_sb_kernel<2><<<(unsigned)n, SB_THREADS, smem, ctx->stream>>>(a);
   }
+  r1c_prof_end(ctx, R1C_PROF_ME_SB);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }

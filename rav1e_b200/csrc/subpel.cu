@@ -229,11 +229,15 @@ int prepare(r1c_ctx *ctx, SubArgs &a, int ncand) {
 }
 
 int run_costs(r1c_ctx *ctx, const r1c_plane *ref, SubArgs &a) {
+  ctx->prof_mc_slot = R1C_PROF_SUBPEL_MC;
   int rc = r1c_mc_put_dense_dev(ctx, (void *)a.dense, ref, a.mcjobs, a.n * a.ncand, a.bit_depth);
+  ctx->prof_mc_slot = 0;
   if (rc) return rc;
   const unsigned grid = (unsigned)((a.n * a.ncand + 7) / 8);
+  r1c_prof_begin(ctx, R1C_PROF_SUBPEL_COST);
   if (ref->px_bytes == 1) cost_kernel<1><<<grid, 256, 0, ctx->stream>>>(a);
   else cost_kernel<2><<<grid, 256, 0, ctx->stream>>>(a);
+  r1c_prof_end(ctx, R1C_PROF_SUBPEL_COST);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }

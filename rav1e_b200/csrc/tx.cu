@@ -56,7 +56,10 @@ static int launch(r1c_ctx *ctx, int tx_size, int tx_type, int bit_depth, FhtArgs
   a.sh1 = sh[1];
   a.sh2 = sh[2];
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  return fn(ctx, a, fused_pb);
+  r1c_prof_begin(ctx, R1C_PROF_TX);
+  const int rc = fn(ctx, a, fused_pb);
+  r1c_prof_end(ctx, R1C_PROF_TX);
+  return rc;
 }
 }  // namespace tx
 

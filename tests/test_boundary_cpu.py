@@ -110,3 +110,20 @@ def test_no_context_without_gpu(lib):
     from rav1e_b200 import api
     with pytest.raises(api.Rav1eCudaError):
         api.Context(0)  # no CPU fallback: must fail loudly
+
+
+def test_frame_me_layout_matches_oracle(lib):
+    """pure host arithmetic: result layout of r1c_frame_me vs the oracle's"""
+    from oracle import r1o
+    from rav1e_b200 import api
+    L = r1o.lib()
+    for (w, h, mask) in [(1920, 1080, api.ALL_SIZES_TO_64), (200, 152, api.ALL_SIZES_TO_64), (64, 64, 0b1001)]:
+        p = api.make_frame_me_params(w, h, 8, 8, 1, bsize_mask=mask)
+        off, cols, rows = (C.c_int64 * 22)(), (C.c_int32 * 22)(), (C.c_int32 * 22)()
+        total = L.r1o_frame_me_layout(w, h, mask, C.byref(off), C.byref(cols), C.byref(rows))
+        assert api.frame_me_count(p) == total
+        for b in range(22):
+            o, c, r_ = api.frame_me_layout(p, b)
+            assert (o, c, r_) == (off[b], cols[b], rows[b]), b
+    assert api.frame_me_count(api.make_frame_me_params(1922, 1080, 8, 8, 1)) == -1
+    assert api.frame_me_count(api.make_frame_me_params(64, 64, 8, 8, 1, bsize_mask=0)) == -1

@@ -490,3 +490,55 @@ def test_subpel_cost_and_telescopic(r, ctx, oracle, pb, bd, use_satd, hp):
         want = oracle_telescopic(oracle, o_org, o_ref, jobs[i],
                                  (int(start[i]["mv"]["row"]), int(start[i]["mv"]["col"])), int(start[i]["cost"]), bd)
         assert ((int(ref[i]["mv"]["row"]), int(ref[i]["mv"]["col"])), int(ref[i]["cost"])) == want, i
+
+
+# ------------------------------------------------- whole-frame motion search ----
+def _frame_pair(r, oracle, ctx, W, H, pb, bd, seed):
+    rng = np.random.default_rng(seed)
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    noisy = np.roll(o_ref.visible, (3, -5), axis=(0, 1)).astype(np.int64) + rng.integers(-3, 4, size=(H, W))
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.clip(noisy, 0, (1 << bd) - 1))
+    return o_org, d_org, o_ref, d_ref
+
+
+@pytest.mark.parametrize("pb,bd,refine,use_satd,hp", [(1, 8, 1, 1, 0), (1, 8, 0, 0, 0), (2, 10, 1, 1, 1), (1, 8, 1, 0, 0)])
+def test_frame_me_matches_per_block_motion_estimation(r, ctx, oracle, pb, bd, refine, use_satd, hp):
+    """r1c_frame_me == motion_estimation (src/me.rs:193-271) block by block, every size,
+    borders and the partial last superblock row included"""
+    W, H = 200, 152
+    o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, W, H, pb, bd, 900 + bd + refine + use_satd)
+    params = r.make_frame_me_params(W, H, 14, 10, 77, refine=refine, use_satd=use_satd, allow_hp=hp)
+    got = r.frame_me(ctx, d_org, d_ref, params, bd)
+    mv, cost = oracle.frame_me(o_org, o_ref, 14, 10, 77, params.bsize_mask, refine, use_satd, hp, bd)
+    assert got.size == cost.size == r.frame_me_count(params) > 5000
+    assert np.array_equal(got["cost"], cost)
+    assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
+
+
+def test_frame_me_sharded_rows_equal_whole_frame(r, ctx, oracle):
+    """multi-GPU sharding by superblock row: the shards of two 'ranks' fill one result
+    array identical to the whole-frame call; untouched entries keep their values"""
+    W, H = 192, 200
+    o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, W, H, 1, 8, 77)
+    mask = (1 << r.BLOCK["BLOCK_8X8"]) | (1 << r.BLOCK["BLOCK_16X16"]) | (1 << r.BLOCK["BLOCK_64X64"]) | 1
+    whole = r.frame_me(ctx, d_org, d_ref, r.make_frame_me_params(W, H, 9, 9, 31, bsize_mask=mask), 8)
+    part = np.zeros(whole.size, dtype=r.ME_RESULT)
+    part["cost"] = 4242
+    p0 = r.make_frame_me_params(W, H, 9, 9, 31, bsize_mask=mask, sb_rows=(0, 2))
+    r.frame_me(ctx, d_org, d_ref, p0, 8, part)
+    assert (part["cost"] == 4242).any() and not np.array_equal(part, whole)
+    p1 = r.make_frame_me_params(W, H, 9, 9, 31, bsize_mask=mask, sb_rows=(2, 4))
+    r.frame_me(ctx, d_org, d_ref, p1, 8, part)
+    assert np.array_equal(part, whole)
+    with pytest.raises(r.Rav1eCudaError):
+        r.frame_me(ctx, d_org, d_ref, r.make_frame_me_params(W + 4, H, 9, 9, 31), 8)
+
+
+def test_profile_hooks_count_launches(r, ctx, oracle):
+    o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, 128, 128, 1, 8, 5)
+    ctx.check(ctx.lib.r1c_profile(ctx.h, 1))
+    r.frame_me(ctx, d_org, d_ref, r.make_frame_me_params(128, 128, 8, 8, 10), 8)
+    ms, n = C.c_double(), C.c_int64()
+    ctx.check(ctx.lib.r1c_profile_read(ctx.h, 0, C.byref(ms), C.byref(n)))
+    ctx.check(ctx.lib.r1c_profile(ctx.h, 0))
+    assert n.value == 1 and ms.value > 0
