@@ -83,6 +83,10 @@ static inline bool region_in_plane(const r1c_plane_cfg &c, int64_t x, int64_t y,
 int r1c_set_err(r1c_ctx *ctx, int code, const char *fmt, ...);
 int r1c_stage_host(r1c_ctx *ctx, int slot, size_t bytes, void **out);
 int r1c_scratch_dev(r1c_ctx *ctx, int slot, size_t bytes, void **out);
+// me_sb2.cu: superblock search for 8-bit planes; *handled = 0 -> caller falls back to me_sb.cu
+int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p,
+                   const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results, const int2 *d_map, int64_t n_map,
+                   int *handled);
 int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
                          int64_t n, int bit_depth);
 

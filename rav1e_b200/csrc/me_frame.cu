@@ -186,8 +186,6 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
   if (rc) return rc;
   const int64_t n_sb = ctx->frame_me.n_sb, n = ctx->frame_me.n_blocks;
   if (n_sb == 0 || n == 0) return R1C_OK;
-  void *d_sbres;
-  if ((rc = r1c_scratch_dev(ctx, 12, (size_t)n_sb * R1C_SB_RESULTS * sizeof(r1c_me_result), &d_sbres))) return rc;
   r1c_sb_params sp;
   sp.w_in_b = p->width / 4;
   sp.h_in_b = p->height / 4;
@@ -196,15 +194,29 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
   sp.step = 1;
   sp.lambda = p->lambda;
   sp.allow_high_precision_mv = p->allow_high_precision_mv;
-  if ((rc = r1c_me_sb_batch_dev(ctx, org, ref, &sp, (const r1c_sb_job *)ctx->frame_me.d_sbjobs, n_sb, bit_depth,
-                                (r1c_me_result *)d_sbres)))
-    return rc;
+  R1C_REQUIRE(ctx, org->px_bytes == ref->px_bytes && bit_depth_ok(bit_depth, org->px_bytes), R1C_ERR_ARG,
+              "frame_me: bit_depth %d vs %d-byte pixels", bit_depth, org->px_bytes);
   const bool whole = p->sb_row_hi == 0;
   const unsigned grid = (unsigned)((n + 255) / 256);
+  void *d_sbres = nullptr;
+  int direct = 0;
+  if (whole || !p->refine) {  // the search can scatter straight into the frame layout
+    if ((rc = r1c_sb2_search(ctx, org, ref, &sp, (const r1c_sb_job *)ctx->frame_me.d_sbjobs, n_sb, d_results,
+                             (const int2 *)ctx->frame_me.d_map, n, &direct)))
+      return rc;
+  }
+  if (!direct) {
+    if ((rc = r1c_scratch_dev(ctx, 12, (size_t)n_sb * R1C_SB_RESULTS * sizeof(r1c_me_result), &d_sbres))) return rc;
+    if ((rc = r1c_me_sb_batch_dev(ctx, org, ref, &sp, (const r1c_sb_job *)ctx->frame_me.d_sbjobs, n_sb, bit_depth,
+                                  (r1c_me_result *)d_sbres)))
+      return rc;
+  }
   if (whole || !p->refine) {
-    gather_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_sbres, (const int2 *)ctx->frame_me.d_map, n,
-                                                 d_results, 1);
-    R1C_LAUNCH_CHECK(ctx);
+    if (!direct) {
+      gather_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_sbres, (const int2 *)ctx->frame_me.d_map, n,
+                                                   d_results, 1);
+      R1C_LAUNCH_CHECK(ctx);
+    }
     if (p->refine)  // whole frame: job i <-> frame slot i, refine in place
       return r1c_subpel_refine_batch_dev(ctx, org, ref, (const r1c_subpel_job *)ctx->frame_me.d_subjobs, n, bit_depth,
                                          d_results);

@@ -403,6 +403,11 @@ int launch_sb(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1
               const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results) {
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  {
+    int handled = 0;
+    const int rc2 = r1c_sb2_search(ctx, org, ref, p, d_jobs, n, d_results, nullptr, 0, &handled);
+    if (rc2 || handled) return rc2;
+  }
   static bool table_done[64] = {false};
   if (!table_done[ctx->device & 63]) {
     BigBlk t[65];

@@ -1,0 +1,603 @@
+// me_sb2.cu -- whole-superblock full search, second generation (8-bit planes).
+//
+// Same contract as me_sb.cu (the result of the reference's full_search,
+// src/me.rs:943-990, for every block of every size inside a 64x64 region against
+// FullSearch::full_pixel_me's window, src/me.rs:533-546), restructured around
+// what bounds it on sm_100a: the integer ALU pipe and shared-memory loads.
+//
+//  * Work item = (superblock, chunk of candidate rows); 512 threads: warp w owns
+//    the 16x16 quadrant w, lane l owns one SLOT per iteration.  A slot is a pair
+//    of vertically adjacent candidates (dx, dy) / (dx, dy + 1): they share 15 of
+//    their 16 reference rows and every org row, so the pair costs 17 x 4 LDS.32
+//    + 16 LDS.128 for 128 VABSDIFF4.
+//  * The reference window is staged four times, shifted by 0..3 bytes, so every
+//    16-byte row segment of every candidate starts on a word: no funnel shifts
+//    in the inner loop (SHF shares the half-rate ALU pipe with VABSDIFF4).
+//  * Running minimum of the 44 blocks up to 8x8 / 4x16 / 16x4 (SAD < 2^14) is ONE
+//    32-bit key  (sad + rl >> 8) << 17 | (rl & 255) << 9 | seq  -> IMAD + VIMNMX
+//    per update; `seq` numbers the thread's candidates in raster order, so the
+//    minimum key is the FIRST minimum of the reference's strict-`<` raster scan.
+//    The larger blocks keep (cost32, seq) pairs.  rl = rate * lambda.
+//  * Blocks spanning quadrants: five partial sums per (quadrant, candidate) go
+//    through a double-buffered shared-memory exchange (one barrier / iteration).
+//  * Each work item writes 849 partial keys  cost << 32 | raster index;
+//    sb2_finalize_kernel takes the minimum over the chunks (lexicographic =
+//    raster tie-break), turns it into (mv, cost) and scatters it either to the
+//    [job][849] layout of r1c_me_sb_batch or straight to a caller-supplied map
+//    (whole-frame layout of r1c_frame_me).
+// INT-bound: per (pixel, candidate) 1/4 VABSDIFF4; planes are read once per work
+// item from L2.  Falls back to me_sb.cu for 16-bit planes, step 2, huge lambda
+// or windows too small / too large for this layout.
+#include <stdlib.h>
+
+#include "me_common.cuh"
+
+namespace {
+
+constexpr int T2 = 512;
+constexpr int SEQ_BITS = 9;
+constexpr int KSHIFT = 8 + SEQ_BITS;  // sad field of the 32-bit key
+constexpr uint32_t NONE32 = 0xffffffffu;
+constexpr int NSLOT = 849;
+
+struct Sb2Args {
+  PlaneView org, ref;
+  r1c_sb_params p;
+  const r1c_sb_job *jobs;
+  unsigned long long *partial;  // [n * split][849]
+  long long n;
+  int split;  // chunks of candidate rows per superblock
+  int rpc;    // candidate rows per chunk (even)
+  int rsw;    // words per staged window row
+  int csz;    // words per shifted copy ( == 8 mod 32 )
+  int M;      // ceil(NX / 32)
+};
+
+__host__ __device__ inline int sb2_count(int b) {
+  const int w = blk_w_of(b), h = blk_h_of(b);
+  return (w > 64 || h > 64) ? 0 : (64 / w) * (64 / h);
+}
+__host__ __device__ inline int sb2_offset(int b) {
+  int o = 0;
+  for (int i = 0; i < b; i++) o += sb2_count(i);
+  return o;
+}
+
+// the 65 blocks that span more than one 16x16 quadrant (same table as me_sb.cu)
+struct BigBlk2 {
+  unsigned char bsize, qx0, qy0, nqx, nqy, part, lx, ly;  // lx, ly in units of 4 px
+};
+__constant__ BigBlk2 c_big2[80];
+
+__device__ __forceinline__ uint32_t rate1(int diff, int allow_hp) {
+  const int d = allow_hp ? (int)(int16_t)diff : ((int)(int16_t)diff >> 1);
+  if (d == 0) return 0;
+  const uint32_t a = (uint32_t)(d < 0 ? -d : d) & 0xffffu;
+  return 2u * (uint32_t)(32 - __clz(a));
+}
+
+struct Geo2 {
+  int QX, QY;  // absolute position of the warp's quadrant
+  int RX, RY;  // region origin
+  int W4, H4;
+};
+// legality of MV offset (ox, oy) for a block at (bx, by) of size (bw, bh): the
+// window of full_pixel_me after get_mv_range (src/me.rs:64-80, 533-546)
+__device__ __forceinline__ bool mv_ok(const Geo2 &g, int bx, int by, int bw, int bh, int ox, int oy) {
+  return (bx + ox + bw >= -16) && (bx + ox <= g.W4 + 16) && (by + oy + bh >= -16) && (by + oy <= g.H4 + 16);
+}
+
+// in-quadrant aggregation + running minima of one candidate
+template <bool MASKED>
+__device__ __forceinline__ void quad_update(const uint32_t (&cell)[4][4], uint32_t rck, uint32_t rl, uint32_t seq,
+                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
+                                            uint32_t (&xs)[5], const Geo2 &g, int ox, int oy) {
+#define K_UPD(BI, SAD, LX, LY, BW, BH)                                                     \
+  do {                                                                                     \
+    uint32_t key_ = (SAD) * (1u << KSHIFT) + rck;                                          \
+    if (MASKED) key_ = mv_ok(g, g.QX + (LX), g.QY + (LY), BW, BH, ox, oy) ? key_ : NONE32; \
+    best[BI] = min(best[BI], key_);                                                        \
+  } while (0)
+#define P_UPD(PI, SAD, LX, LY, BW, BH)                                                  \
+  do {                                                                                  \
+    uint32_t c_ = (SAD) * 256u + rl;                                                    \
+    if (MASKED) c_ = mv_ok(g, g.QX + (LX), g.QY + (LY), BW, BH, ox, oy) ? c_ : NONE32;  \
+    if (c_ < pc[PI]) {                                                                  \
+      pc[PI] = c_;                                                                      \
+      ps[PI] = seq;                                                                     \
+    }                                                                                   \
+  } while (0)
+  uint32_t v48[2][4], h84[4][2], s88[2][2];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int k = 0; k < 4; k++) K_UPD(i * 4 + k, cell[i][k], 4 * k, 4 * i, 4, 4);
+#pragma unroll
+  for (int i = 0; i < 2; i++)
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      v48[i][k] = cell[2 * i][k] + cell[2 * i + 1][k];
+      K_UPD(16 + i * 4 + k, v48[i][k], 4 * k, 8 * i, 4, 8);
+    }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      h84[i][k] = cell[i][2 * k] + cell[i][2 * k + 1];
+      K_UPD(24 + i * 2 + k, h84[i][k], 8 * k, 4 * i, 8, 4);
+    }
+#pragma unroll
+  for (int i = 0; i < 2; i++)
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      s88[i][k] = v48[i][2 * k] + v48[i][2 * k + 1];
+      K_UPD(32 + i * 2 + k, s88[i][k], 8 * k, 8 * i, 8, 8);
+    }
+#pragma unroll
+  for (int k = 0; k < 4; k++) K_UPD(36 + k, v48[0][k] + v48[1][k], 4 * k, 0, 4, 16);
+#pragma unroll
+  for (int i = 0; i < 4; i++) K_UPD(40 + i, h84[i][0] + h84[i][1], 0, 4 * i, 16, 4);
+  const uint32_t c816l = s88[0][0] + s88[1][0], c816r = s88[0][1] + s88[1][1];
+  const uint32_t c168t = s88[0][0] + s88[0][1], c168b = s88[1][0] + s88[1][1];
+  const uint32_t c1616 = c816l + c816r;
+  P_UPD(0, c816l, 0, 0, 8, 16);
+  P_UPD(1, c816r, 8, 0, 8, 16);
+  P_UPD(2, c168t, 0, 0, 16, 8);
+  P_UPD(3, c168b, 0, 8, 16, 8);
+  P_UPD(4, c1616, 0, 0, 16, 16);
+  xs[0] = c1616;
+  xs[1] = c816l;
+  xs[2] = c816r;
+  xs[3] = c168t;
+  xs[4] = c168b;
+#undef K_UPD
+#undef P_UPD
+}
+
+struct Chunk {
+  int NX, NYc, NP, NS, iters;
+  int row0;        // first candidate row of the chunk
+  int cxlo, cylo;  // MV offset of candidate (0, 0) of the whole window
+};
+
+template <bool MASKED>
+__device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
+                                           const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
+                                           uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
+                                           uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
+  const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
+  const int qx = q & 3, qy = q >> 2;
+  const int sdx = 32 % ck.NX, sj = 32 / ck.NX;
+  const int hp = a.p.allow_high_precision_mv;
+  const int M2 = 2 * a.M;
+  // slot of this lane: f = it * 32 + lane = j * NX + dx
+  int f = lane, j = lane / ck.NX, dx = lane - j * ck.NX;
+  const uint32_t *orow = s_org + (qy * 16) * 16 + qx * 4;
+  for (int it = 0; it < ck.iters; it++) {
+    const int dyA = min(2 * j, ck.NYc - 2);
+    const uint32_t *rp = s_ref + (dx & 3) * a.csz + (qy * 16 + dyA) * a.rsw + qx * 4 + (dx >> 2);
+    // ---- 2 x 16 cell SADs: candidate A = (dx, dyA), B = (dx, dyA + 1) ----------------
+    uint32_t cA[4][4], cB[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) cA[i][k] = cB[i][k] = 0;
+    uint4 oprev = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int r = 0; r < 17; r++) {
+      const uint32_t w0 = rp[r * a.rsw + 0], w1 = rp[r * a.rsw + 1], w2 = rp[r * a.rsw + 2], w3 = rp[r * a.rsw + 3];
+      if (r >= 1) {
+        const int i = (r - 1) >> 2;
+        cB[i][0] = me::sad4_acc(oprev.x, w0, cB[i][0]);
+        cB[i][1] = me::sad4_acc(oprev.y, w1, cB[i][1]);
+        cB[i][2] = me::sad4_acc(oprev.z, w2, cB[i][2]);
+        cB[i][3] = me::sad4_acc(oprev.w, w3, cB[i][3]);
+      }
+      if (r < 16) {
+        const uint4 o = *(const uint4 *)(orow + r * 16);
+        const int i = r >> 2;
+        cA[i][0] = me::sad4_acc(o.x, w0, cA[i][0]);
+        cA[i][1] = me::sad4_acc(o.y, w1, cA[i][1]);
+        cA[i][2] = me::sad4_acc(o.z, w2, cA[i][2]);
+        cA[i][3] = me::sad4_acc(o.w, w3, cA[i][3]);
+        oprev = o;
+      }
+    }
+    // ---- rate terms ---------------------------------------------------------------------
+    const int ox = ck.cxlo + dx, oyA = ck.cylo + ck.row0 + dyA;
+    const int mvc = 8 * ox, mvrA = 8 * oyA, mvrB = mvrA + 8;
+    const uint32_t rc0 = rate1(mvc - job.pmv[0].col, hp), rc1 = rate1(mvc - job.pmv[1].col, hp) + 1;
+    const uint32_t rA = min(rate1(mvrA - job.pmv[0].row, hp) + rc0, rate1(mvrA - job.pmv[1].row, hp) + rc1);
+    const uint32_t rB = min(rate1(mvrB - job.pmv[0].row, hp) + rc0, rate1(mvrB - job.pmv[1].row, hp) + rc1);
+    const uint32_t rlA = rA * a.p.lambda, rlB = rB * a.p.lambda;
+    const uint32_t seqA = (uint32_t)(j * M2 + (dx >> 5)), seqB = seqA + (uint32_t)a.M;
+    const uint32_t rckA = ((rlA >> 8) << KSHIFT) | ((rlA & 255u) << SEQ_BITS) | seqA;
+    const uint32_t rckB = ((rlB >> 8) << KSHIFT) | ((rlB & 255u) << SEQ_BITS) | seqB;
+
+    uint32_t xsA[5], xsB[5];
+    quad_update<MASKED>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
+    quad_update<MASKED>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
+
+    // ---- exchange of the quadrant partial sums: xb[part][quadrant][A lanes | B lanes] ---
+    uint32_t *xb = s_x + (it & 1) * (5 * 16 * 64);
+#pragma unroll
+    for (int p = 0; p < 5; p++) {
+      xb[(p * 16 + q) * 64 + lane] = xsA[p];
+      xb[(p * 16 + q) * 64 + 32 + lane] = xsB[p];
+    }
+    __syncthreads();
+    // ---- the 65 blocks spanning quadrants: (block = q + 16 * rd, this lane's A and B) ---
+#pragma unroll
+    for (int rd = 0; rd < 5; rd++) {
+      const int bi = q + 16 * rd;  // warp-uniform
+      if (bi < 65) {
+        const BigBlk2 bb = c_big2[bi];
+        uint32_t sA = 0, sB = 0;
+        for (int yy = 0; yy < bb.nqy; yy++)
+          for (int xx = 0; xx < bb.nqx; xx++) {
+            const uint32_t *src = xb + ((bb.part * 16) + (bb.qy0 + yy) * 4 + bb.qx0 + xx) * 64 + lane;
+            sA += src[0];
+            sB += src[32];
+          }
+        uint32_t cAv = sA * 256u + rlA, cBv = sB * 256u + rlB;
+        if (MASKED) {
+          const int bw = blk_w_of(bb.bsize), bh = blk_h_of(bb.bsize);
+          const int bx = g.RX + bb.lx * 4, by = g.RY + bb.ly * 4;
+          cAv = mv_ok(g, bx, by, bw, bh, ox, oyA) ? cAv : NONE32;
+          cBv = mv_ok(g, bx, by, bw, bh, ox, oyA + 1) ? cBv : NONE32;
+        }
+        if (cAv < bc[rd]) {
+          bc[rd] = cAv;
+          bs[rd] = seqA;
+        }
+        if (cBv < bc[rd]) {
+          bc[rd] = cBv;
+          bs[rd] = seqB;
+        }
+      }
+    }
+    // ---- next slot; a lane that runs out of slots repeats its last one (same keys) ----
+    if (f + 32 < ck.NS) {
+      f += 32;
+      dx += sdx;
+      j += sj;
+      if (dx >= ck.NX) {
+        dx -= ck.NX;
+        j++;
+      }
+    }
+  }
+}
+
+// (seq, lane) -> raster index of the candidate inside the WHOLE window
+__device__ __forceinline__ uint32_t decode_ridx(const Sb2Args &a, const Chunk &ck, uint32_t seq, int lane) {
+  const int M2 = 2 * a.M;
+  const int j = (int)seq / M2, rem = (int)seq - j * M2;
+  const int isB = rem >= a.M, k = rem - (isB ? a.M : 0);
+  const int d0 = (((lane - j * ck.NX) % 32) + 32) % 32;
+  const int dx = d0 + 32 * k;
+  const int dy = min(2 * j, ck.NYc - 2) + isB;
+  return (uint32_t)((ck.row0 + dy) * ck.NX + dx);
+}
+
+// lexicographic (cost, raster index) minimum over the warp -> 64-bit partial key
+__device__ __forceinline__ unsigned long long warp_best(uint32_t cost, uint32_t ridx) {
+  const uint32_t cmin = __reduce_min_sync(0xffffffffu, cost);
+  const uint32_t rmin = __reduce_min_sync(0xffffffffu, cost == cmin ? ridx : NONE32);
+  return cmin == NONE32 ? ~0ull : (((unsigned long long)cmin << 32) | rmin);
+}
+
+template <int DUMMY>
+__global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const long long wi = blockIdx.x;
+  const long long ji = wi / a.split;
+  const int chunk = (int)(wi - ji * a.split);
+  const r1c_sb_job job = a.jobs[ji];
+  const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
+  const int Rx = a.p.range_x, Ry = a.p.range_y;
+  const int cx = job.cmv.col / 8, cy = job.cmv.row / 8;  // truncating, like the reference
+
+  Chunk ck;
+  ck.NX = 2 * Rx + 1;
+  const int NY = 2 * Ry + 1;
+  ck.row0 = chunk * a.rpc;
+  ck.NYc = min(a.rpc, NY - ck.row0);
+  ck.NP = (ck.NYc + 1) >> 1;
+  ck.NS = ck.NP * ck.NX;
+  ck.iters = (ck.NS + 31) >> 5;
+  ck.cxlo = cx - Rx;
+  ck.cylo = cy - Ry;
+
+  uint32_t *s_org = (uint32_t *)smem;                      // [64][16] words
+  uint32_t *s_ref = s_org + 64 * 16;                       // 4 copies of csz words
+  uint32_t *s_x = s_ref + 4 * a.csz;                       // 2 x [5][16][64]
+  const int nrows = ck.NYc + 63;
+
+  // ---- stage the org region and copy 0 of the window (clamped into the allocation:
+  //      pixels outside it never belong to a legal candidate) ---------------------------
+  {
+    const uint8_t *po = (const uint8_t *)a.org.p0, *pr = (const uint8_t *)a.ref.p0;
+    const int oxmin = -a.org.xorigin, oxmax = a.org.alloc_w - a.org.xorigin - 1;
+    const int oymin = -a.org.yorigin, oymax = a.org.alloc_h - a.org.yorigin - 1;
+    for (int i = tid; i < 64 * 64; i += T2) {
+      const int y = min(max(job.po_y + (i >> 6), oymin), oymax), x = min(max(job.po_x + (i & 63), oxmin), oxmax);
+      ((uint8_t *)s_org)[i] = po[(long long)y * a.org.stride + x];
+    }
+    const int rxmin = -a.ref.xorigin, rxmax = a.ref.alloc_w - a.ref.xorigin - 1;
+    const int rymin = -a.ref.yorigin, rymax = a.ref.alloc_h - a.ref.yorigin - 1;
+    const int x0 = job.po_x + ck.cxlo, y0 = job.po_y + ck.cylo + ck.row0;
+    const int rowb = a.rsw * 4;
+    for (int i = tid; i < nrows * rowb; i += T2) {
+      const int wy = i / rowb, wx = i - wy * rowb;
+      const int y = min(max(y0 + wy, rymin), rymax), x = min(max(x0 + wx, rxmin), rxmax);
+      ((uint8_t *)s_ref)[(size_t)wy * rowb + wx] = pr[(long long)y * a.ref.stride + x];
+    }
+  }
+  __syncthreads();
+  // ---- copies 1..3: the same rows shifted left by 1..3 bytes ------------------------------
+  for (int i = tid; i < nrows * a.rsw; i += T2) {
+    const int wx = i % a.rsw;
+    const uint32_t lo = s_ref[i], hi = (wx + 1 < a.rsw) ? s_ref[i + 1] : 0u;
+    s_ref[a.csz + i] = __funnelshift_r(lo, hi, 8);
+    s_ref[2 * a.csz + i] = __funnelshift_r(lo, hi, 16);
+    s_ref[3 * a.csz + i] = __funnelshift_r(lo, hi, 24);
+  }
+  __syncthreads();
+
+  Geo2 g;
+  g.RX = job.po_x;
+  g.RY = job.po_y;
+  g.QX = job.po_x + (q & 3) * 16;
+  g.QY = job.po_y + (q >> 2) * 16;
+  g.W4 = a.p.w_in_b * 4;
+  g.H4 = a.p.h_in_b * 4;
+  // every candidate of the chunk is legal for every block of the region (the most
+  // restrictive blocks are the 4x4s on the region's edges)
+  const int oylo = ck.cylo + ck.row0, oyhi = oylo + ck.NYc - 1;
+  const bool fast = (job.po_x + 60 + ck.cxlo + 4 >= -16) && (job.po_x + cx + Rx <= g.W4 + 16) &&
+                    (job.po_x + ck.cxlo + 4 >= -16) && (job.po_x + 60 + cx + Rx <= g.W4 + 16) &&
+                    (job.po_y + oylo + 4 >= -16) && (job.po_y + 60 + oyhi <= g.H4 + 16) &&
+                    (job.po_y + 60 + oylo + 4 >= -16) && (job.po_y + oyhi <= g.H4 + 16);
+
+  uint32_t best[44], pc[5], ps[5], bc[5], bs[5];
+#pragma unroll
+  for (int i = 0; i < 44; i++) best[i] = NONE32;
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    pc[i] = bc[i] = NONE32;
+    ps[i] = bs[i] = 0;
+  }
+  if (fast) sb2_search<false>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  else sb2_search<true>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+
+  // ---- reduce over the 32 lanes and write the partial keys ------------------------------
+  unsigned long long *out = a.partial + wi * NSLOT;
+  const int qx16 = (q & 3) * 16, qy16 = (q >> 2) * 16;
+#pragma unroll
+  for (int bi = 0; bi < 49; bi++) {
+    uint32_t cost, seq;
+    if (bi < 44) {
+      cost = best[bi] == NONE32 ? NONE32 : (best[bi] >> SEQ_BITS);
+      seq = best[bi] & ((1u << SEQ_BITS) - 1);
+    } else {
+      cost = pc[bi - 44];
+      seq = ps[bi - 44];
+    }
+    const unsigned long long key = warp_best(cost, decode_ridx(a, ck, seq, lane));
+    if (lane == 0) {
+      int bsize, lx, ly;
+      if (bi < 16) { bsize = R1C_BLOCK_4X4; lx = 4 * (bi & 3); ly = 4 * (bi >> 2); }
+      else if (bi < 24) { bsize = R1C_BLOCK_4X8; lx = 4 * ((bi - 16) & 3); ly = 8 * ((bi - 16) >> 2); }
+      else if (bi < 32) { bsize = R1C_BLOCK_8X4; lx = 8 * ((bi - 24) & 1); ly = 4 * ((bi - 24) >> 1); }
+      else if (bi < 36) { bsize = R1C_BLOCK_8X8; lx = 8 * ((bi - 32) & 1); ly = 8 * ((bi - 32) >> 1); }
+      else if (bi < 40) { bsize = R1C_BLOCK_4X16; lx = 4 * (bi - 36); ly = 0; }
+      else if (bi < 44) { bsize = R1C_BLOCK_16X4; lx = 0; ly = 4 * (bi - 40); }
+      else if (bi < 46) { bsize = R1C_BLOCK_8X16; lx = 8 * (bi - 44); ly = 0; }
+      else if (bi < 48) { bsize = R1C_BLOCK_16X8; lx = 0; ly = 8 * (bi - 46); }
+      else { bsize = R1C_BLOCK_16X16; lx = 0; ly = 0; }
+      const int bw = blk_w_of(bsize), bh = blk_h_of(bsize);
+      out[sb2_offset(bsize) + ((qy16 + ly) / bh) * (64 / bw) + (qx16 + lx) / bw] = key;
+    }
+  }
+#pragma unroll
+  for (int rd = 0; rd < 5; rd++) {
+    const int bi = q + 16 * rd;
+    if (bi < 65) {
+      const unsigned long long key = warp_best(bc[rd], decode_ridx(a, ck, bs[rd], lane));
+      if (lane == 0) {
+        const BigBlk2 bb = c_big2[bi];
+        const int bw = blk_w_of(bb.bsize), bh = blk_h_of(bb.bsize);
+        out[sb2_offset(bb.bsize) + ((bb.ly * 4) / bh) * (64 / bw) + (bb.lx * 4) / bw] = key;
+      }
+    }
+  }
+}
+
+// min over the chunks -> (mv, cost); entries of blocks that do not exist in the frame or
+// are not in the job's mask are left untouched
+struct FinArgs {
+  const unsigned long long *partial;
+  const r1c_sb_job *jobs;
+  r1c_me_result *results;
+  const int2 *map;  // optional: (source slot, destination index)
+  long long n_out;
+  int split, NX, Rx, Ry, W4, H4;
+};
+__global__ void sb2_finalize_kernel(FinArgs a) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n_out) return;
+  const long long src = a.map ? a.map[i].x : i;
+  const long long dst = a.map ? a.map[i].y : i;
+  const long long ji = src / NSLOT;
+  const int slot = (int)(src - ji * NSLOT);
+  const r1c_sb_job job = a.jobs[ji];
+  int bsize = 0, off = 0;
+  for (int b = 0; b < R1C_BLOCK_SIZES_ALL; b++) {
+    const int c = sb2_count(b);
+    if (slot < off + c) {
+      bsize = b;
+      break;
+    }
+    off += c;
+  }
+  if (!((job.bsize_mask >> bsize) & 1u)) return;
+  const int bw = blk_w_of(bsize), bh = blk_h_of(bsize);
+  const int k = slot - off, rx = (k % (64 / bw)) * bw, ry = (k / (64 / bw)) * bh;
+  if (job.po_x + rx + bw > a.W4 || job.po_y + ry + bh > a.H4) return;
+  unsigned long long key = ~0ull;
+  for (int c = 0; c < a.split; c++) {
+    const unsigned long long v = a.partial[(ji * a.split + c) * NSLOT + slot];
+    key = v < key ? v : key;
+  }
+  r1c_me_result r;
+  r.reserved = 0;
+  if (key == ~0ull) {
+    r.mv.row = 0;
+    r.mv.col = 0;
+    r.cost = ~0ull;
+  } else {
+    const uint32_t ridx = (uint32_t)key;
+    const int dy = (int)(ridx / (uint32_t)a.NX), dx = (int)(ridx - (uint32_t)dy * a.NX);
+    r.mv.row = (int16_t)(8 * (job.cmv.row / 8 - a.Ry + dy));
+    r.mv.col = (int16_t)(8 * (job.cmv.col / 8 - a.Rx + dx));
+    r.cost = key >> 32;
+  }
+  a.results[dst] = r;
+}
+
+void build_big_table2(BigBlk2 *t) {
+  int n = 0;
+  auto add = [&](int bsize, int part_mode) {
+    const int bw = blk_w_of(bsize), bh = blk_h_of(bsize);
+    for (int y = 0; y < 64; y += bh)
+      for (int x = 0; x < 64; x += bw) {
+        BigBlk2 b;
+        b.bsize = (unsigned char)bsize;
+        b.qx0 = (unsigned char)(x / 16);
+        b.qy0 = (unsigned char)(y / 16);
+        b.nqx = (unsigned char)(bw >= 16 ? bw / 16 : 1);
+        b.nqy = (unsigned char)(bh >= 16 ? bh / 16 : 1);
+        b.part = 0;
+        if (part_mode == 1) b.part = (unsigned char)(1 + ((x / 8) & 1));  // 8 wide: 8x16 left / right halves
+        if (part_mode == 2) b.part = (unsigned char)(3 + ((y / 8) & 1));  // 8 high: 16x8 top / bottom halves
+        b.lx = (unsigned char)(x / 4);
+        b.ly = (unsigned char)(y / 4);
+        t[n++] = b;
+      }
+  };
+  // heaviest first (warp q takes blocks q, q + 16, ...: spreads the 16-load blocks)
+  add(R1C_BLOCK_64X64, 0);
+  add(R1C_BLOCK_32X64, 0);
+  add(R1C_BLOCK_64X32, 0);
+  add(R1C_BLOCK_32X32, 0);
+  add(R1C_BLOCK_16X64, 0);
+  add(R1C_BLOCK_64X16, 0);
+  add(R1C_BLOCK_16X32, 0);
+  add(R1C_BLOCK_32X16, 0);
+  add(R1C_BLOCK_8X32, 1);
+  add(R1C_BLOCK_32X8, 2);
+  for (; n < 80; n++) memset(&t[n], 0, sizeof(BigBlk2));
+}
+
+}  // namespace
+
+// layout parameters of the kernel for a search range; false when this kernel cannot
+// take the job (the caller falls back to me_sb.cu)
+struct Sb2Plan {
+  int split, rpc, rsw, csz, M;
+  size_t smem;
+};
+static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, int64_t n, Sb2Plan *pl) {
+  if (px_bytes != 1 || p->step != 1) return false;
+  if (p->lambda > 60000u) return false;  // rl >> 8 must stay below 2^14 (rate <= 65)
+  const int NX = 2 * p->range_x + 1, NY = 2 * p->range_y + 1;
+  if (p->range_y < 1 || NX > 255) return false;
+  const int M = (NX + 31) / 32;
+  const int winW = 64 + 2 * p->range_x;
+  const int rsw = (winW + 3) / 4;  // a copy row holds bytes [p, p + 4 * rsw)
+  const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
+  for (int split = 1; split <= 16; split++) {
+    const int rpc = 2 * ((NY + 2 * split - 1) / (2 * split));
+    const int chunks = (NY + rpc - 1) / rpc;
+    if (chunks != split) continue;
+    const int last = NY - (split - 1) * rpc;
+    if (last < 2) continue;
+    const int NP = rpc / 2;
+    if (NP * 2 * M > (1 << SEQ_BITS)) continue;  // seq field
+    if ((long long)(last + 1) / 2 * NX < 32) continue;  // every lane needs a slot of its own
+    const int nrows = rpc + 63;
+    int csz = nrows * rsw;
+    csz += ((8 - (csz & 31)) + 32) & 31;
+    const size_t smem = (size_t)64 * 64 + (size_t)4 * csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    if (smem > 220 * 1024) continue;
+    // enough work items to balance the SMs: stop once the tail is small
+    pl->split = split;
+    pl->rpc = rpc;
+    pl->rsw = rsw;
+    pl->csz = csz;
+    pl->M = M;
+    pl->smem = smem;
+    const long long items = n * split;
+    const long long waves = (items + sms - 1) / sms;
+    if ((double)items / (double)(waves * sms) > 0.93 || items >= 8ll * sms) return true;
+  }
+  return pl->split > 0 && pl->smem > 0;
+}
+
+// search + finalize.  d_map == nullptr: results is the [n][849] layout.
+int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p,
+                   const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results, const int2 *d_map, int64_t n_map,
+                   int *handled) {
+  *handled = 0;
+  Sb2Plan pl = {};
+  const char *force = getenv("R1C_ME_SB_V1");
+  if ((force && force[0] == '1') || !sb2_plan(ctx, p, org->px_bytes, n, &pl)) return R1C_OK;
+  *handled = 1;
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  static bool table_done[64] = {false};
+  if (!table_done[ctx->device & 63]) {
+    BigBlk2 t[80];
+    build_big_table2(t);
+    R1C_CUDA(ctx, cudaMemcpyToSymbol(c_big2, t, sizeof t));
+    table_done[ctx->device & 63] = true;
+  }
+  void *d_partial;
+  int rc = r1c_scratch_dev(ctx, 15, (size_t)n * pl.split * NSLOT * sizeof(unsigned long long), &d_partial);
+  if (rc) return rc;
+  Sb2Args a;
+  a.org = make_view(org);
+  a.ref = make_view(ref);
+  a.p = *p;
+  a.jobs = d_jobs;
+  a.partial = (unsigned long long *)d_partial;
+  a.n = n;
+  a.split = pl.split;
+  a.rpc = pl.rpc;
+  a.rsw = pl.rsw;
+  a.csz = pl.csz;
+  a.M = pl.M;
+  R1C_CUDA(ctx, cudaFuncSetAttribute(me_sb2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  r1c_prof_begin(ctx, R1C_PROF_ME_SB);
+  me_sb2_kernel<0><<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
+  r1c_prof_end(ctx, R1C_PROF_ME_SB);
+  R1C_LAUNCH_CHECK(ctx);
+  FinArgs fa;
+  fa.partial = a.partial;
+  fa.jobs = d_jobs;
+  fa.results = d_results;
+  fa.map = d_map;
+  fa.n_out = d_map ? n_map : n * NSLOT;
+  fa.split = pl.split;
+  fa.NX = 2 * p->range_x + 1;
+  fa.Rx = p->range_x;
+  fa.Ry = p->range_y;
+  fa.W4 = p->w_in_b * 4;
+  fa.H4 = p->h_in_b * 4;
+  if (fa.n_out > 0) {
+    sb2_finalize_kernel<<<(unsigned)((fa.n_out + 255) / 256), 256, 0, ctx->stream>>>(fa);
+    R1C_LAUNCH_CHECK(ctx);
+  }
+  return R1C_OK;
+}
