@@ -49,7 +49,7 @@ struct Sb2Args {
   int split;  // chunks of candidate rows per superblock
   int rpc;    // candidate rows per chunk (even)
   int rsw;    // words per staged window row
-  int csz;    // words per shifted copy ( == 8 mod 32 )
+  int csz;    // words of the staged window: rows * rsw * 4 byte phases
   int M;      // ceil(NX / 32)
 };
 
@@ -62,12 +62,6 @@ __host__ __device__ inline int sb2_offset(int b) {
   for (int i = 0; i < b; i++) o += sb2_count(i);
   return o;
 }
-
-// the 65 blocks that span more than one 16x16 quadrant (same table as me_sb.cu)
-struct BigBlk2 {
-  unsigned char bsize, qx0, qy0, nqx, nqy, part, lx, ly;  // lx, ly in units of 4 px
-};
-__constant__ BigBlk2 c_big2[80];
 
 __device__ __forceinline__ uint32_t rate1(int diff, int allow_hp) {
   const int d = allow_hp ? (int)(int16_t)diff : ((int)(int16_t)diff >> 1);
@@ -160,22 +154,83 @@ struct Chunk {
   int cxlo, cylo;  // MV offset of candidate (0, 0) of the whole window
 };
 
+// running minimum of one block spanning quadrants, for this lane's candidates A and B
 template <bool MASKED>
+__device__ __forceinline__ void big_upd(uint32_t &bc, uint32_t &bs, uint32_t sA, uint32_t sB, uint32_t rlA,
+                                        uint32_t rlB, uint32_t seqA, uint32_t seqB, const Geo2 &g, int lx, int ly,
+                                        int bw, int bh, int ox, int oyA) {
+  uint32_t cA = sA * 256u + rlA, cB = sB * 256u + rlB;
+  if (MASKED) {
+    cA = mv_ok(g, g.RX + lx, g.RY + ly, bw, bh, ox, oyA) ? cA : NONE32;
+    cB = mv_ok(g, g.RX + lx, g.RY + ly, bw, bh, ox, oyA + 1) ? cB : NONE32;
+  }
+  const bool la = cA < bc;
+  bc = la ? cA : bc;
+  bs = la ? seqA : bs;
+  const bool lb = cB < bc;
+  bc = lb ? cB : bc;
+  bs = lb ? seqB : bs;
+}
+
+// The 65 blocks that span quadrants, split over the 16 warps by role (q = warp):
+//   q 0..3   column c = q      : 16x32 top / bottom, 16x64, and the 32x32 block c
+//   q 4..7   column c = q - 4  : 8x32 left-top, left-bottom, right-top, right-bottom
+//   q 8..11  row r = q - 8     : 32x16 left / right, 64x16, and 32x64 left / right (r = 0, 1)
+//                                or 64x32 top / bottom (r = 2, 3)
+//   q 12..15 row r = q - 12    : 32x8 top-left, top-right, bottom-left, bottom-right;
+//                                q 12 also the 64x64
+// slot s of role q <-> (bsize, lx, ly): big_slot().  X(part, quadrant) = exchanged sums.
+struct BigSlot {
+  int bsize, lx, ly;
+};
+__host__ __device__ inline BigSlot big_slot(int q, int s) {
+  BigSlot b = {-1, 0, 0};
+  if (q < 4) {
+    const int c = q;
+    if (s == 0) b = {R1C_BLOCK_16X32, 16 * c, 0};
+    else if (s == 1) b = {R1C_BLOCK_16X32, 16 * c, 32};
+    else if (s == 2) b = {R1C_BLOCK_16X64, 16 * c, 0};
+    else if (s == 3) b = {R1C_BLOCK_32X32, 32 * (c & 1), 32 * (c >> 1)};
+  } else if (q < 8) {
+    const int c = q - 4;
+    if (s < 4) b = {R1C_BLOCK_8X32, 16 * c + 8 * (s >> 1), 32 * (s & 1)};
+  } else if (q < 12) {
+    const int r = q - 8;
+    if (s == 0) b = {R1C_BLOCK_32X16, 0, 16 * r};
+    else if (s == 1) b = {R1C_BLOCK_32X16, 32, 16 * r};
+    else if (s == 2) b = {R1C_BLOCK_64X16, 0, 16 * r};
+    else if (s == 3) {
+      if (r < 2) b = {R1C_BLOCK_32X64, 32 * r, 0};
+      else b = {R1C_BLOCK_64X32, 0, 32 * (r - 2)};
+    }
+  } else {
+    const int r = q - 12;
+    if (s < 4) b = {R1C_BLOCK_32X8, 32 * (s & 1), 16 * r + 8 * (s >> 1)};
+    else if (s == 4 && q == 12) b = {R1C_BLOCK_64X64, 0, 0};
+  }
+  return b;
+}
+
+template <bool MASKED, int RSW>
 __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
                                            const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                            uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
   const int qx = q & 3, qy = q >> 2;
+  const int rsw = RSW ? RSW : a.rsw;
   const int sdx = 32 % ck.NX, sj = 32 / ck.NX;
   const int hp = a.p.allow_high_precision_mv;
   const int M2 = 2 * a.M;
   // slot of this lane: f = it * 32 + lane = j * NX + dx
   int f = lane, j = lane / ck.NX, dx = lane - j * ck.NX;
   const uint32_t *orow = s_org + (qy * 16) * 16 + qx * 4;
+  // role of this warp in the cross-quadrant phase
+  const int rg = q >> 2, ri = q & 3;
   for (int it = 0; it < ck.iters; it++) {
     const int dyA = min(2 * j, ck.NYc - 2);
-    const uint32_t *rp = s_ref + (dx & 3) * a.csz + (qy * 16 + dyA) * a.rsw + qx * 4 + (dx >> 2);
+    // window word (row, w) of byte phase p lives at s_ref[(row * rsw + w) * 4 + p]
+    const uint32_t *rp = s_ref + (((qy * 16 + dyA) * rsw + qx * 4 + (dx >> 2)) << 2) + (dx & 3);
     // ---- 2 x 16 cell SADs: candidate A = (dx, dyA), B = (dx, dyA + 1) ----------------
     uint32_t cA[4][4], cB[4][4];
 #pragma unroll
@@ -185,7 +240,8 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
     uint4 oprev = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int r = 0; r < 17; r++) {
-      const uint32_t w0 = rp[r * a.rsw + 0], w1 = rp[r * a.rsw + 1], w2 = rp[r * a.rsw + 2], w3 = rp[r * a.rsw + 3];
+      const uint32_t *rr = rp + r * rsw * 4;
+      const uint32_t w0 = rr[0], w1 = rr[4], w2 = rr[8], w3 = rr[12];
       if (r >= 1) {
         const int i = (r - 1) >> 2;
         cB[i][0] = me::sad4_acc(oprev.x, w0, cB[i][0]);
@@ -226,35 +282,73 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
       xb[(p * 16 + q) * 64 + 32 + lane] = xsB[p];
     }
     __syncthreads();
-    // ---- the 65 blocks spanning quadrants: (block = q + 16 * rd, this lane's A and B) ---
+    // ---- blocks spanning quadrants, by warp role ----------------------------------------
+    {
+      const uint32_t *xl = xb + lane;
+#define XA(PART, QUAD) xl[((PART) * 16 + (QUAD)) * 64]
+#define XB(PART, QUAD) xl[((PART) * 16 + (QUAD)) * 64 + 32]
+#define BIG(S, SA, SB, LX, LY, BW, BH) \
+  big_upd<MASKED>(bc[S], bs[S], SA, SB, rlA, rlB, seqA, seqB, g, LX, LY, BW, BH, ox, oyA)
+      if (rg == 0) {  // column ri: 16x16 sums of its four quadrants
+        const int c = ri;
+        const uint32_t a0 = XA(0, c), a1 = XA(0, c + 4), a2 = XA(0, c + 8), a3 = XA(0, c + 12);
+        const uint32_t b0 = XB(0, c), b1 = XB(0, c + 4), b2 = XB(0, c + 8), b3 = XB(0, c + 12);
+        const uint32_t at = a0 + a1, ab = a2 + a3, bt = b0 + b1, bb = b2 + b3;
+        BIG(0, at, bt, 16 * c, 0, 16, 32);
+        BIG(1, ab, bb, 16 * c, 32, 16, 32);
+        BIG(2, at + ab, bt + bb, 16 * c, 0, 16, 64);
+        const int q0 = (c >> 1) * 8 + (c & 1) * 2;  // 32x32 block c
+        const uint32_t sA = XA(0, q0) + XA(0, q0 + 1) + XA(0, q0 + 4) + XA(0, q0 + 5);
+        const uint32_t sB = XB(0, q0) + XB(0, q0 + 1) + XB(0, q0 + 4) + XB(0, q0 + 5);
+        BIG(3, sA, sB, 32 * (c & 1), 32 * (c >> 1), 32, 32);
+      } else if (rg == 1) {  // column ri: 8x16 halves -> 8x32
+        const int c = ri;
 #pragma unroll
-    for (int rd = 0; rd < 5; rd++) {
-      const int bi = q + 16 * rd;  // warp-uniform
-      if (bi < 65) {
-        const BigBlk2 bb = c_big2[bi];
+        for (int h = 0; h < 2; h++) {
+          const uint32_t a0 = XA(1 + h, c), a1 = XA(1 + h, c + 4), a2 = XA(1 + h, c + 8), a3 = XA(1 + h, c + 12);
+          const uint32_t b0 = XB(1 + h, c), b1 = XB(1 + h, c + 4), b2 = XB(1 + h, c + 8), b3 = XB(1 + h, c + 12);
+          BIG(2 * h, a0 + a1, b0 + b1, 16 * c + 8 * h, 0, 8, 32);
+          BIG(2 * h + 1, a2 + a3, b2 + b3, 16 * c + 8 * h, 32, 8, 32);
+        }
+      } else if (rg == 2) {  // row ri
+        const int r = ri;
+        const uint32_t a0 = XA(0, 4 * r), a1 = XA(0, 4 * r + 1), a2 = XA(0, 4 * r + 2), a3 = XA(0, 4 * r + 3);
+        const uint32_t b0 = XB(0, 4 * r), b1 = XB(0, 4 * r + 1), b2 = XB(0, 4 * r + 2), b3 = XB(0, 4 * r + 3);
+        const uint32_t al = a0 + a1, ar = a2 + a3, bl = b0 + b1, br = b2 + b3;
+        BIG(0, al, bl, 0, 16 * r, 32, 16);
+        BIG(1, ar, br, 32, 16 * r, 32, 16);
+        BIG(2, al + ar, bl + br, 0, 16 * r, 64, 16);
+        // r < 2: 32x64 half r (quadrant columns 2r, 2r+1); else 64x32 half r-2 (rows 2(r-2), +1)
+        const int q0 = r < 2 ? 2 * r : 8 * (r - 2), st = r < 2 ? 4 : 1, st2 = r < 2 ? 1 : 4;
         uint32_t sA = 0, sB = 0;
-        for (int yy = 0; yy < bb.nqy; yy++)
-          for (int xx = 0; xx < bb.nqx; xx++) {
-            const uint32_t *src = xb + ((bb.part * 16) + (bb.qy0 + yy) * 4 + bb.qx0 + xx) * 64 + lane;
-            sA += src[0];
-            sB += src[32];
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          sA += XA(0, q0 + t * st) + XA(0, q0 + t * st + st2);
+          sB += XB(0, q0 + t * st) + XB(0, q0 + t * st + st2);
+        }
+        BIG(3, sA, sB, r < 2 ? 32 * r : 0, r < 2 ? 0 : 32 * (r - 2), r < 2 ? 32 : 64, r < 2 ? 64 : 32);
+      } else {  // row ri: 16x8 halves -> 32x8
+        const int r = ri;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const uint32_t a0 = XA(3 + h, 4 * r), a1 = XA(3 + h, 4 * r + 1), a2 = XA(3 + h, 4 * r + 2), a3 = XA(3 + h, 4 * r + 3);
+          const uint32_t b0 = XB(3 + h, 4 * r), b1 = XB(3 + h, 4 * r + 1), b2 = XB(3 + h, 4 * r + 2), b3 = XB(3 + h, 4 * r + 3);
+          BIG(2 * h, a0 + a1, b0 + b1, 0, 16 * r + 8 * h, 32, 8);
+          BIG(2 * h + 1, a2 + a3, b2 + b3, 32, 16 * r + 8 * h, 32, 8);
+        }
+        if (r == 0) {  // 64x64
+          uint32_t sA = 0, sB = 0;
+#pragma unroll
+          for (int t = 0; t < 16; t++) {
+            sA += XA(0, t);
+            sB += XB(0, t);
           }
-        uint32_t cAv = sA * 256u + rlA, cBv = sB * 256u + rlB;
-        if (MASKED) {
-          const int bw = blk_w_of(bb.bsize), bh = blk_h_of(bb.bsize);
-          const int bx = g.RX + bb.lx * 4, by = g.RY + bb.ly * 4;
-          cAv = mv_ok(g, bx, by, bw, bh, ox, oyA) ? cAv : NONE32;
-          cBv = mv_ok(g, bx, by, bw, bh, ox, oyA + 1) ? cBv : NONE32;
-        }
-        if (cAv < bc[rd]) {
-          bc[rd] = cAv;
-          bs[rd] = seqA;
-        }
-        if (cBv < bc[rd]) {
-          bc[rd] = cBv;
-          bs[rd] = seqB;
+          BIG(4, sA, sB, 0, 0, 64, 64);
         }
       }
+#undef XA
+#undef XB
+#undef BIG
     }
     // ---- next slot; a lane that runs out of slots repeats its last one (same keys) ----
     if (f + 32 < ck.NS) {
@@ -270,11 +364,11 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
 }
 
 // (seq, lane) -> raster index of the candidate inside the WHOLE window
-__device__ __forceinline__ uint32_t decode_ridx(const Sb2Args &a, const Chunk &ck, uint32_t seq, int lane) {
-  const int M2 = 2 * a.M;
-  const int j = (int)seq / M2, rem = (int)seq - j * M2;
-  const int isB = rem >= a.M, k = rem - (isB ? a.M : 0);
-  const int d0 = (((lane - j * ck.NX) % 32) + 32) % 32;
+__device__ __forceinline__ uint32_t decode_ridx(const Chunk &ck, uint32_t seq, int lane, int M, uint32_t inv_m2) {
+  const int j = (int)((seq * inv_m2) >> 16);  // seq / (2M): exact for seq < 512, 2M <= 16
+  const int rem = (int)seq - j * 2 * M;
+  const int isB = rem >= M, k = rem - (isB ? M : 0);
+  const int d0 = (lane - j * ck.NX) & 31;
   const int dx = d0 + 32 * k;
   const int dy = min(2 * j, ck.NYc - 2) + isB;
   return (uint32_t)((ck.row0 + dy) * ck.NX + dx);
@@ -287,7 +381,7 @@ __device__ __forceinline__ unsigned long long warp_best(uint32_t cost, uint32_t 
   return cmin == NONE32 ? ~0ull : (((unsigned long long)cmin << 32) | rmin);
 }
 
-template <int DUMMY>
+template <int RSW>
 __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   extern __shared__ __align__(16) unsigned char smem[];
   const long long wi = blockIdx.x;
@@ -297,6 +391,7 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
   const int Rx = a.p.range_x, Ry = a.p.range_y;
   const int cx = job.cmv.col / 8, cy = job.cmv.row / 8;  // truncating, like the reference
+  const int rsw = RSW ? RSW : a.rsw;
 
   Chunk ck;
   ck.NX = 2 * Rx + 1;
@@ -309,12 +404,12 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   ck.cxlo = cx - Rx;
   ck.cylo = cy - Ry;
 
-  uint32_t *s_org = (uint32_t *)smem;                      // [64][16] words
-  uint32_t *s_ref = s_org + 64 * 16;                       // 4 copies of csz words
-  uint32_t *s_x = s_ref + 4 * a.csz;                       // 2 x [5][16][64]
+  uint32_t *s_org = (uint32_t *)smem;  // [64][16] words
+  uint32_t *s_ref = s_org + 64 * 16;   // [nrows][rsw][4 byte phases]
+  uint32_t *s_x = s_ref + a.csz;       // 2 x [5][16][64]
   const int nrows = ck.NYc + 63;
 
-  // ---- stage the org region and copy 0 of the window (clamped into the allocation:
+  // ---- stage the org region and phase 0 of the window (clamped into the allocation:
   //      pixels outside it never belong to a legal candidate) ---------------------------
   {
     const uint8_t *po = (const uint8_t *)a.org.p0, *pr = (const uint8_t *)a.ref.p0;
@@ -327,22 +422,28 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     const int rxmin = -a.ref.xorigin, rxmax = a.ref.alloc_w - a.ref.xorigin - 1;
     const int rymin = -a.ref.yorigin, rymax = a.ref.alloc_h - a.ref.yorigin - 1;
     const int x0 = job.po_x + ck.cxlo, y0 = job.po_y + ck.cylo + ck.row0;
-    const int rowb = a.rsw * 4;
-    for (int i = tid; i < nrows * rowb; i += T2) {
-      const int wy = i / rowb, wx = i - wy * rowb;
-      const int y = min(max(y0 + wy, rymin), rymax), x = min(max(x0 + wx, rxmin), rxmax);
-      ((uint8_t *)s_ref)[(size_t)wy * rowb + wx] = pr[(long long)y * a.ref.stride + x];
+    // one thread = one word (4 pixels) of one row
+    for (int wy = q; wy < nrows; wy += T2 / 32) {
+      const int y = min(max(y0 + wy, rymin), rymax);
+      const uint8_t *row = pr + (long long)y * a.ref.stride;
+      for (int w = lane; w < rsw; w += 32) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) v |= (uint32_t)row[min(max(x0 + 4 * w + b, rxmin), rxmax)] << (8 * b);
+        s_ref[(wy * rsw + w) << 2] = v;
+      }
     }
   }
   __syncthreads();
-  // ---- copies 1..3: the same rows shifted left by 1..3 bytes ------------------------------
-  for (int i = tid; i < nrows * a.rsw; i += T2) {
-    const int wx = i % a.rsw;
-    const uint32_t lo = s_ref[i], hi = (wx + 1 < a.rsw) ? s_ref[i + 1] : 0u;
-    s_ref[a.csz + i] = __funnelshift_r(lo, hi, 8);
-    s_ref[2 * a.csz + i] = __funnelshift_r(lo, hi, 16);
-    s_ref[3 * a.csz + i] = __funnelshift_r(lo, hi, 24);
-  }
+  // ---- phases 1..3: the same row shifted left by 1..3 bytes ------------------------------
+  for (int wy = q; wy < nrows; wy += T2 / 32)
+    for (int w = lane; w < rsw; w += 32) {
+      const int i = wy * rsw + w;
+      const uint32_t lo = s_ref[i << 2], hi = (w + 1 < rsw) ? s_ref[(i + 1) << 2] : 0u;
+      s_ref[(i << 2) + 1] = __funnelshift_r(lo, hi, 8);
+      s_ref[(i << 2) + 2] = __funnelshift_r(lo, hi, 16);
+      s_ref[(i << 2) + 3] = __funnelshift_r(lo, hi, 24);
+    }
   __syncthreads();
 
   Geo2 g;
@@ -368,12 +469,13 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     pc[i] = bc[i] = NONE32;
     ps[i] = bs[i] = 0;
   }
-  if (fast) sb2_search<false>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
-  else sb2_search<true>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  if (fast) sb2_search<false, RSW>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  else sb2_search<true, RSW>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
 
   // ---- reduce over the 32 lanes and write the partial keys ------------------------------
   unsigned long long *out = a.partial + wi * NSLOT;
   const int qx16 = (q & 3) * 16, qy16 = (q >> 2) * 16;
+  const uint32_t inv_m2 = (65536u + 2 * a.M - 1) / (2 * a.M);
 #pragma unroll
   for (int bi = 0; bi < 49; bi++) {
     uint32_t cost, seq;
@@ -384,7 +486,7 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
       cost = pc[bi - 44];
       seq = ps[bi - 44];
     }
-    const unsigned long long key = warp_best(cost, decode_ridx(a, ck, seq, lane));
+    const unsigned long long key = warp_best(cost, decode_ridx(ck, seq, lane, a.M, inv_m2));
     if (lane == 0) {
       int bsize, lx, ly;
       if (bi < 16) { bsize = R1C_BLOCK_4X4; lx = 4 * (bi & 3); ly = 4 * (bi >> 2); }
@@ -401,14 +503,13 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     }
   }
 #pragma unroll
-  for (int rd = 0; rd < 5; rd++) {
-    const int bi = q + 16 * rd;
-    if (bi < 65) {
-      const unsigned long long key = warp_best(bc[rd], decode_ridx(a, ck, bs[rd], lane));
+  for (int s = 0; s < 5; s++) {
+    const BigSlot b = big_slot(q, s);
+    if (b.bsize >= 0) {  // warp-uniform
+      const unsigned long long key = warp_best(bc[s], decode_ridx(ck, bs[s], lane, a.M, inv_m2));
       if (lane == 0) {
-        const BigBlk2 bb = c_big2[bi];
-        const int bw = blk_w_of(bb.bsize), bh = blk_h_of(bb.bsize);
-        out[sb2_offset(bb.bsize) + ((bb.ly * 4) / bh) * (64 / bw) + (bb.lx * 4) / bw] = key;
+        const int bw = blk_w_of(b.bsize), bh = blk_h_of(b.bsize);
+        out[sb2_offset(b.bsize) + (b.ly / bh) * (64 / bw) + b.lx / bw] = key;
       }
     }
   }
@@ -466,40 +567,6 @@ __global__ void sb2_finalize_kernel(FinArgs a) {
   a.results[dst] = r;
 }
 
-void build_big_table2(BigBlk2 *t) {
-  int n = 0;
-  auto add = [&](int bsize, int part_mode) {
-    const int bw = blk_w_of(bsize), bh = blk_h_of(bsize);
-    for (int y = 0; y < 64; y += bh)
-      for (int x = 0; x < 64; x += bw) {
-        BigBlk2 b;
-        b.bsize = (unsigned char)bsize;
-        b.qx0 = (unsigned char)(x / 16);
-        b.qy0 = (unsigned char)(y / 16);
-        b.nqx = (unsigned char)(bw >= 16 ? bw / 16 : 1);
-        b.nqy = (unsigned char)(bh >= 16 ? bh / 16 : 1);
-        b.part = 0;
-        if (part_mode == 1) b.part = (unsigned char)(1 + ((x / 8) & 1));  // 8 wide: 8x16 left / right halves
-        if (part_mode == 2) b.part = (unsigned char)(3 + ((y / 8) & 1));  // 8 high: 16x8 top / bottom halves
-        b.lx = (unsigned char)(x / 4);
-        b.ly = (unsigned char)(y / 4);
-        t[n++] = b;
-      }
-  };
-  // heaviest first (warp q takes blocks q, q + 16, ...: spreads the 16-load blocks)
-  add(R1C_BLOCK_64X64, 0);
-  add(R1C_BLOCK_32X64, 0);
-  add(R1C_BLOCK_64X32, 0);
-  add(R1C_BLOCK_32X32, 0);
-  add(R1C_BLOCK_16X64, 0);
-  add(R1C_BLOCK_64X16, 0);
-  add(R1C_BLOCK_16X32, 0);
-  add(R1C_BLOCK_32X16, 0);
-  add(R1C_BLOCK_8X32, 1);
-  add(R1C_BLOCK_32X8, 2);
-  for (; n < 80; n++) memset(&t[n], 0, sizeof(BigBlk2));
-}
-
 }  // namespace
 
 // layout parameters of the kernel for a search range; false when this kernel cannot
@@ -527,9 +594,8 @@ static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, i
     if (NP * 2 * M > (1 << SEQ_BITS)) continue;  // seq field
     if ((long long)(last + 1) / 2 * NX < 32) continue;  // every lane needs a slot of its own
     const int nrows = rpc + 63;
-    int csz = nrows * rsw;
-    csz += ((8 - (csz & 31)) + 32) & 31;
-    const size_t smem = (size_t)64 * 64 + (size_t)4 * csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    const int csz = nrows * rsw * 4;
+    const size_t smem = (size_t)64 * 64 + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
     if (smem > 220 * 1024) continue;
     // enough work items to balance the SMs: stop once the tail is small
     pl->split = split;
@@ -556,13 +622,6 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   *handled = 1;
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  static bool table_done[64] = {false};
-  if (!table_done[ctx->device & 63]) {
-    BigBlk2 t[80];
-    build_big_table2(t);
-    R1C_CUDA(ctx, cudaMemcpyToSymbol(c_big2, t, sizeof t));
-    table_done[ctx->device & 63] = true;
-  }
   void *d_partial;
   int rc = r1c_scratch_dev(ctx, 15, (size_t)n * pl.split * NSLOT * sizeof(unsigned long long), &d_partial);
   if (rc) return rc;
@@ -578,9 +637,10 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   a.rsw = pl.rsw;
   a.csz = pl.csz;
   a.M = pl.M;
-  R1C_CUDA(ctx, cudaFuncSetAttribute(me_sb2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  auto kern = pl.rsw == 48 ? me_sb2_kernel<48> : me_sb2_kernel<0>;  // 48: the +-64 px window
+  R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   r1c_prof_begin(ctx, R1C_PROF_ME_SB);
-  me_sb2_kernel<0><<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
+  kern<<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
   r1c_prof_end(ctx, R1C_PROF_ME_SB);
   R1C_LAUNCH_CHECK(ctx);
   FinArgs fa;
