@@ -1,0 +1,141 @@
+"""bench_kernels.py -- the other kernel classes of BASELINE.json's metric, timed on
+device-resident data and reported next to the headline ME line (bench.py "kernels"):
+
+  mc_4k10  (configs[2]) 4K 10-bit luma: put_8tap of the frame tiled by every one of
+           the 19 block sizes, random 1/16 fracs (all four (col, row) cases), the ten
+           filter pairs of the asm set, integer offsets +-32; and the compound path
+           prep_8tap x2 + mc_avg.  Mpix/s = output pixels / time; HBM-bound,
+           4 B/px (put, prep) and 6 B/px (avg) algorithmic.
+  tx_4k10  (configs[3]) 4K 10-bit 4:2:0 residual (12.4 M samples): forward_transform
+           DCT_DCT of the frame tiled by every TxSize; 6 B/coeff algorithmic.
+
+Inputs are larger than L2 in aggregate and L2 is flushed between timed launches.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+SIZES_TO_64 = [b for b in range(22) if b not in (13, 14, 15)]
+FILTER_PAIRS = [(0, 0), (0, 1), (0, 2), (1, 0), (1, 1), (1, 2), (2, 0), (2, 1), (2, 2), (3, 3)]
+
+
+def _hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def _timed(torch, ext, flush, fn, reps):
+    """reps launches of fn, each event-bracketed on the library stream after an untimed L2 flush"""
+    evs = []
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(ext):
+            flush.zero_()
+            a.record(ext)
+        fn()
+        b.record(ext)
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / reps
+
+
+def mc_jobs(r, rng, lib, W, H):
+    jobs = []
+    for b in SIZES_TO_64:
+        bw, bh = lib.r1c_block_width(b), lib.r1c_block_height(b)
+        xs, ys = np.meshgrid(np.arange(0, W - bw + 1, bw), np.arange(0, H - bh + 1, bh))
+        n = xs.size
+        j = np.zeros(n, dtype=r.MC_JOB)
+        j["dst_x"], j["dst_y"] = xs.ravel(), ys.ravel()
+        j["src_x"] = j["dst_x"] + rng.integers(-32, 33, size=n)
+        j["src_y"] = j["dst_y"] + rng.integers(-32, 33, size=n)
+        j["w"], j["h"] = bw, bh
+        j["col_frac"] = rng.integers(0, 16, size=n)
+        j["row_frac"] = rng.integers(0, 16, size=n)
+        fp = np.array(FILTER_PAIRS)[rng.integers(0, len(FILTER_PAIRS), size=n)]
+        j["mode_x"], j["mode_y"] = fp[:, 0], fp[:, 1]
+        jobs.append(j)
+    return jobs
+
+
+def run(ctx, r, torch, ext, flush, reps=3):
+    lib = ctx.lib
+    hbm, hbm_how = _hbm_peak()
+    out = {}
+    rng = np.random.default_rng(3)
+    # ------------------------------------------------------------------ MC, 4K 10-bit luma
+    W, H, BD = 3840, 2160, 10
+    src = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
+    dst = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
+    host = rng.integers(0, 1024, size=src.shape, dtype=np.uint16)
+    src.upload(host)
+    per_size = mc_jobs(r, rng, lib, W, H)
+    put_ms = prep_ms = avg_ms = 0.0
+    px_total = 0
+    tmp1 = torch.empty(W * H, dtype=torch.int16, device="cuda")
+    tmp2 = torch.empty(W * H, dtype=torch.int16, device="cuda")
+    for j in per_size:
+        n = j.size
+        area = int(j["w"][0]) * int(j["h"][0])
+        j["tmp_off"] = np.arange(n, dtype=np.int64) * area
+        d_jobs = torch.from_numpy(j.view(np.uint8).copy()).cuda()
+        aj = np.zeros(n, dtype=r.AVG_JOB)
+        aj["dst_x"], aj["dst_y"], aj["w"], aj["h"], aj["tmp_off"] = j["dst_x"], j["dst_y"], j["w"], j["h"], j["tmp_off"]
+        d_aj = torch.from_numpy(aj.view(np.uint8).copy()).cuda()
+        px_total += n * area
+
+        def f_put():
+            ctx.check(lib.r1c_put_8tap_batch_dev(ctx.h, dst.h, src.h, d_jobs.data_ptr(), n, BD))
+
+        def f_prep():
+            ctx.check(lib.r1c_prep_8tap_batch_dev(ctx.h, tmp1.data_ptr(), src.h, d_jobs.data_ptr(), n, BD))
+
+        def f_avg():
+            ctx.check(lib.r1c_mc_avg_batch_dev(ctx.h, dst.h, tmp1.data_ptr(), tmp2.data_ptr(), d_aj.data_ptr(), n, BD))
+        f_put()
+        ctx.check(lib.r1c_prep_8tap_batch_dev(ctx.h, tmp2.data_ptr(), src.h, d_jobs.data_ptr(), n, BD))
+        f_prep()
+        f_avg()
+        ctx.sync()
+        put_ms += _timed(torch, ext, flush, f_put, reps)
+        prep_ms += _timed(torch, ext, flush, f_prep, reps)
+        avg_ms += _timed(torch, ext, flush, f_avg, reps)
+    for name, ms, bpp in (("put_8tap", put_ms, 4), ("prep_8tap", prep_ms, 4), ("mc_avg", avg_ms, 6)):
+        gbs = px_total * bpp / (ms / 1e3) / 1e9
+        out["mc_4k10_" + name] = {
+            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, random fracs / filter pairs / +-32 px",
+            "value": px_total / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "pixels": px_total,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                         "alg_bytes_per_px": bpp, "peak_source": hbm_how}}
+    del tmp1, tmp2
+    # ---------------------------------------------------- forward transforms, 4K 10-bit 4:2:0
+    n_samples = 3840 * 2160 * 3 // 2
+    res = torch.from_numpy(rng.integers(-1023, 1024, size=n_samples, dtype=np.int16)).cuda()
+    coef = torch.empty(n_samples, dtype=torch.int32, device="cuda")
+    tx_ms = 0.0
+    coeffs = 0
+    per = {}
+    for ts in range(19):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        n = n_samples // (w * h)
+
+        def f_tx():
+            ctx.check(lib.r1c_fwd_txfm_batch_dev(ctx.h, ts, 0, BD, res.data_ptr(), coef.data_ptr(), n))
+        f_tx()
+        ctx.sync()
+        ms = _timed(torch, ext, flush, f_tx, reps)
+        tx_ms += ms
+        coeffs += n * w * h
+        per["%dx%d" % (w, h)] = round(n * w * h * 6 / (ms / 1e3) / 1e9 / hbm, 3)
+    gbs = coeffs * 6 / (tx_ms / 1e3) / 1e9
+    out["tx_4k10_fwd_dct_dct"] = {
+        "workload": "4K 10-bit 4:2:0 residual (12.4 M samples) tiled by each of the 19 TxSize, DCT_DCT",
+        "value": coeffs / 1e6 / (tx_ms / 1e3), "unit": "Mcoeff/s", "ms": tx_ms, "coeffs": coeffs,
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                     "alg_bytes_per_coeff": 6, "peak_source": hbm_how, "frac_by_tx_size": per}}
+    return out

@@ -1,0 +1,82 @@
+"""N > 1 path on CPU: world_size-2 gloo run of the superblock-row sharding + gather
+(rav1e_b200.shard).  The compute inside each rank is the oracle (no GPU here); what
+is under test is the partition and the merge: shards are disjoint, cover every
+block, and the gathered array equals the whole-frame result."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+W, H, RNG, LAM = 128, 200, 6, 21
+
+
+def _planes(r1o):
+    rng = np.random.default_rng(11)
+    o_ref = r1o.OPlane(W, H, 0, 0, 88, 88, 1)
+    o_org = r1o.OPlane(W, H, 0, 0, 88, 88, 1)
+    o_ref.visible[...] = rng.integers(0, 256, size=(H, W))
+    o_org.visible[...] = np.roll(o_ref.visible, (2, -1), axis=(0, 1))
+    o_ref.pad()
+    o_org.pad()
+    return o_org, o_ref
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from oracle import r1o
+    from rav1e_b200 import api, shard
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mask = (1 << api.BLOCK["BLOCK_8X8"]) | (1 << api.BLOCK["BLOCK_16X16"]) | (1 << api.BLOCK["BLOCK_64X64"])
+    lo, hi = shard.split_sb_rows(H, world)[rank]
+    slots = shard.shard_slots(W, H, mask, lo, hi)
+    o_org, o_ref = _planes(r1o)
+    mv, cost = r1o.frame_me(o_org, o_ref, RNG, RNG, LAM, mask, 0, 0, 0, 8, idx=slots)
+    local = np.zeros(cost.size, dtype=api.ME_RESULT)
+    local["mv"]["row"], local["mv"]["col"], local["cost"] = mv[:, 0], mv[:, 1], cost
+    merged = shard.gather_frame_results(local, slots, cost.size, dist)
+    if rank == 0:
+        q.put((merged["mv"]["row"].copy(), merged["mv"]["col"].copy(), merged["cost"].copy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sb_row_split_is_a_partition():
+    sys.path.insert(0, ROOT)
+    from rav1e_b200 import api, shard
+    for world in (1, 2, 3, 4, 8):
+        parts = shard.split_sb_rows(1080, world)
+        assert parts[0][0] == 0 and parts[-1][1] == 17
+        assert all(parts[i][1] == parts[i + 1][0] for i in range(world - 1))
+        sl = [shard.shard_slots(1920, 1080, api.ALL_SIZES_TO_64, lo, hi) for lo, hi in parts]
+        allidx = np.sort(np.concatenate(sl))
+        p = api.make_frame_me_params(1920, 1080, 8, 8, 1)
+        assert np.array_equal(allidx, np.arange(api.frame_me_count(p)))
+    assert shard.split_frames(5, 2) == [[0, 2, 4], [1, 3]]
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_gloo_gather_equals_whole_frame():
+    import torch.multiprocessing as mp
+    sys.path.insert(0, ROOT)
+    from oracle import r1o
+    from rav1e_b200 import api
+    r1o.build()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    row, col, cost = q.get(timeout=240)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    mask = (1 << api.BLOCK["BLOCK_8X8"]) | (1 << api.BLOCK["BLOCK_16X16"]) | (1 << api.BLOCK["BLOCK_64X64"])
+    o_org, o_ref = _planes(r1o)
+    mv, want = r1o.frame_me(o_org, o_ref, RNG, RNG, LAM, mask, 0, 0, 0, 8)
+    assert np.array_equal(cost, want) and np.array_equal(row, mv[:, 0]) and np.array_equal(col, mv[:, 1])
