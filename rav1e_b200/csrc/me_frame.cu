@@ -56,6 +56,12 @@ __global__ void gather_kernel(const r1c_me_result *__restrict__ src, const int2 
   const uint4 v = *(const uint4 *)(src + m.x);
   *(uint4 *)(dst + (to_frame_layout ? (long long)m.y : i)) = v;
 }
+__global__ void gather_frame_kernel(const r1c_me_result *__restrict__ src, const int2 *__restrict__ map, long long n,
+                                    r1c_me_result *__restrict__ dst) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  *(uint4 *)(dst + i) = *(const uint4 *)(src + map[i].y);
+}
 __global__ void scatter_kernel(const r1c_me_result *__restrict__ src, const int2 *__restrict__ map, long long n,
                                r1c_me_result *__restrict__ dst) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -198,40 +204,38 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
               "frame_me: bit_depth %d vs %d-byte pixels", bit_depth, org->px_bytes);
   const bool whole = p->sb_row_hi == 0;
   const unsigned grid = (unsigned)((n + 255) / 256);
-  void *d_sbres = nullptr;
+  const r1c_sb_job *d_sbs = (const r1c_sb_job *)ctx->frame_me.d_sbjobs;
+  const int2 *d_map = (const int2 *)ctx->frame_me.d_map;
+  const r1c_subpel_job *d_sub = (const r1c_subpel_job *)ctx->frame_me.d_subjobs;
+  // 1. full-pel search, scattered straight into the frame layout when me_sb2 takes it
   int direct = 0;
-  if (whole || !p->refine) {  // the search can scatter straight into the frame layout
-    if ((rc = r1c_sb2_search(ctx, org, ref, &sp, (const r1c_sb_job *)ctx->frame_me.d_sbjobs, n_sb, d_results,
-                             (const int2 *)ctx->frame_me.d_map, n, &direct)))
-      return rc;
-  }
+  if ((rc = r1c_sb2_search(ctx, org, ref, &sp, d_sbs, n_sb, d_results, d_map, n, &direct))) return rc;
   if (!direct) {
+    void *d_sbres;
     if ((rc = r1c_scratch_dev(ctx, 12, (size_t)n_sb * R1C_SB_RESULTS * sizeof(r1c_me_result), &d_sbres))) return rc;
-    if ((rc = r1c_me_sb_batch_dev(ctx, org, ref, &sp, (const r1c_sb_job *)ctx->frame_me.d_sbjobs, n_sb, bit_depth,
-                                  (r1c_me_result *)d_sbres)))
-      return rc;
+    if ((rc = r1c_me_sb_batch_dev(ctx, org, ref, &sp, d_sbs, n_sb, bit_depth, (r1c_me_result *)d_sbres))) return rc;
+    gather_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_sbres, d_map, n, d_results, 1);
+    R1C_LAUNCH_CHECK(ctx);
   }
-  if (whole || !p->refine) {
-    if (!direct) {
-      gather_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_sbres, (const int2 *)ctx->frame_me.d_map, n,
-                                                   d_results, 1);
-      R1C_LAUNCH_CHECK(ctx);
-    }
-    if (p->refine)  // whole frame: job i <-> frame slot i, refine in place
-      return r1c_subpel_refine_batch_dev(ctx, org, ref, (const r1c_subpel_job *)ctx->frame_me.d_subjobs, n, bit_depth,
-                                         d_results);
-    return R1C_OK;
+  if (!p->refine) return R1C_OK;
+  // 2. SATD re-evaluation + telescopic sub-pel: fused kernel (8-bit), else the generic path
+  {
+    Layout l;
+    make_layout(p, &l);
+    long long off[R1C_BLOCK_SIZES_ALL];
+    for (int b = 0; b < R1C_BLOCK_SIZES_ALL; b++) off[b] = l.off[b];
+    int fused = 0;
+    if ((rc = r1c_refine_frame(ctx, org, ref, p, off, l.cols, l.rows, d_sbs, n_sb, d_results, &fused))) return rc;
+    if (fused) return R1C_OK;
   }
+  if (whole)  // job i <-> frame slot i: refine in place
+    return r1c_subpel_refine_batch_dev(ctx, org, ref, d_sub, n, bit_depth, d_results);
   void *d_compact;
   if ((rc = r1c_scratch_dev(ctx, 13, (size_t)n * sizeof(r1c_me_result), &d_compact))) return rc;
-  gather_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_sbres, (const int2 *)ctx->frame_me.d_map, n,
-                                               (r1c_me_result *)d_compact, 0);
+  gather_frame_kernel<<<grid, 256, 0, ctx->stream>>>(d_results, d_map, n, (r1c_me_result *)d_compact);
   R1C_LAUNCH_CHECK(ctx);
-  if ((rc = r1c_subpel_refine_batch_dev(ctx, org, ref, (const r1c_subpel_job *)ctx->frame_me.d_subjobs, n, bit_depth,
-                                        (r1c_me_result *)d_compact)))
-    return rc;
-  scatter_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_compact, (const int2 *)ctx->frame_me.d_map, n,
-                                                d_results);
+  if ((rc = r1c_subpel_refine_batch_dev(ctx, org, ref, d_sub, n, bit_depth, (r1c_me_result *)d_compact))) return rc;
+  scatter_kernel<<<grid, 256, 0, ctx->stream>>>((const r1c_me_result *)d_compact, d_map, n, d_results);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }
