@@ -29,6 +29,13 @@ def _hbm_peak():
         return 6650.0, "fallback"
 
 
+def _kernel_ms(ctx, slot):
+    """summed duration / launches of one kernel class since the last read (r1c_profile hooks)"""
+    ms, n = C.c_double(), C.c_int64()
+    ctx.check(ctx.lib.r1c_profile_read(ctx.h, slot, C.byref(ms), C.byref(n)))
+    return ms.value, n.value
+
+
 def _timed(torch, ext, flush, fn, reps):
     """reps launches of fn, each event-bracketed on the library stream after an untimed L2 flush"""
     evs = []
@@ -46,7 +53,8 @@ def _timed(torch, ext, flush, fn, reps):
 
 def mc_jobs(r, rng, lib, W, H):
     jobs = []
-    for b in SIZES_TO_64:
+    only = os.environ.get("R1C_BENCH_SIZES")  # profiling aid: restrict to some BlockSize values
+    for b in ([int(v) for v in only.split(",")] if only else SIZES_TO_64):
         bw, bh = lib.r1c_block_width(b), lib.r1c_block_height(b)
         xs, ys = np.meshgrid(np.arange(0, W - bw + 1, bw), np.arange(0, H - bh + 1, bh))
         n = xs.size
@@ -76,7 +84,9 @@ def run(ctx, r, torch, ext, flush, reps=3):
     src.upload(host)
     per_size = mc_jobs(r, rng, lib, W, H)
     put_ms = prep_ms = avg_ms = 0.0
+    kput = kprep = kavg = 0.0
     px_total = 0
+    ctx.check(lib.r1c_profile(ctx.h, 1))
     tmp1 = torch.empty(W * H, dtype=torch.int16, device="cuda")
     tmp2 = torch.empty(W * H, dtype=torch.int16, device="cuda")
     for j in per_size:
@@ -102,17 +112,57 @@ def run(ctx, r, torch, ext, flush, reps=3):
         f_prep()
         f_avg()
         ctx.sync()
+        _kernel_ms(ctx, 3)
         put_ms += _timed(torch, ext, flush, f_put, reps)
+        kput += _kernel_ms(ctx, 3)[0] / reps
         prep_ms += _timed(torch, ext, flush, f_prep, reps)
+        kprep += _kernel_ms(ctx, 3)[0] / reps
         avg_ms += _timed(torch, ext, flush, f_avg, reps)
-    for name, ms, bpp in (("put_8tap", put_ms, 4), ("prep_8tap", prep_ms, 4), ("mc_avg", avg_ms, 6)):
+        kavg += _kernel_ms(ctx, 3)[0] / reps
+    for name, call_ms, ms, bpp in (("put_8tap", put_ms, kput, 4), ("prep_8tap", prep_ms, kprep, 4),
+                                   ("mc_avg", avg_ms, kavg, 6)):
         gbs = px_total * bpp / (ms / 1e3) / 1e9
         out["mc_4k10_" + name] = {
             "workload": "4K 10-bit luma tiled by each of the 19 block sizes, random fracs / filter pairs / +-32 px",
-            "value": px_total / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "pixels": px_total,
+            "value": px_total / 1e6 / (call_ms / 1e3), "unit": "Mpix/s", "ms": call_ms, "pixels": px_total,
+            "kernel_ms": ms, "note": "value / ms = whole _dev call (item count + prefix sum + kernel); "
+                                     "roofline = the main kernel alone (19 launches, CUDA events inside the library)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_px": bpp, "peak_source": hbm_how}}
     del tmp1, tmp2
+    # ------------------------------------------ SAD / SATD, 4K 10-bit luma, one job per block
+    org = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
+    org.upload(rng.integers(0, 1024, size=src.shape, dtype=np.uint16))
+    d_out = torch.empty(W * H // 16, dtype=torch.int32, device="cuda")
+    sad_ms = satd_ms = 0.0
+    dist_px = 0
+    for j in per_size:
+        n = j.size
+        dj = np.zeros(n, dtype=r.DIST_JOB)
+        dj["org_x"], dj["org_y"], dj["ref_x"], dj["ref_y"] = j["dst_x"], j["dst_y"], j["src_x"], j["src_y"]
+        dj["bsize"] = [b for b in SIZES_TO_64 if lib.r1c_block_width(b) == int(j["w"][0])
+                       and lib.r1c_block_height(b) == int(j["h"][0])][0]
+        d_dj = torch.from_numpy(dj.view(np.uint8).copy()).cuda()
+        dist_px += n * int(j["w"][0]) * int(j["h"][0])
+        for satd in (0, 1):
+            def f_dist():
+                ctx.check(lib.r1c_dist_batch_dev(ctx.h, satd, org.h, src.h, d_dj.data_ptr(), n, BD, d_out.data_ptr()))
+            f_dist()
+            ctx.sync()
+            _kernel_ms(ctx, 5)
+            _timed(torch, ext, flush, f_dist, reps)
+            ms = _kernel_ms(ctx, 5)[0] / reps
+            if satd:
+                satd_ms += ms
+            else:
+                sad_ms += ms
+    for name, ms in (("sad", sad_ms), ("satd", satd_ms)):
+        gbs = dist_px * 4 / (ms / 1e3) / 1e9
+        out["dist_4k10_" + name] = {
+            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, one job per block, reference offset +-32 px",
+            "value": dist_px / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "pixels": dist_px,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                         "alg_bytes_per_px": 4, "peak_source": hbm_how}}
     # ---------------------------------------------------- forward transforms, 4K 10-bit 4:2:0
     n_samples = 3840 * 2160 * 3 // 2
     res = torch.from_numpy(rng.integers(-1023, 1024, size=n_samples, dtype=np.int16)).cuda()
@@ -120,7 +170,8 @@ def run(ctx, r, torch, ext, flush, reps=3):
     tx_ms = 0.0
     coeffs = 0
     per = {}
-    for ts in range(19):
+    only = os.environ.get("R1C_BENCH_TXSIZES")
+    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
         w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
         n = n_samples // (w * h)
 
@@ -128,7 +179,9 @@ def run(ctx, r, torch, ext, flush, reps=3):
             ctx.check(lib.r1c_fwd_txfm_batch_dev(ctx.h, ts, 0, BD, res.data_ptr(), coef.data_ptr(), n))
         f_tx()
         ctx.sync()
-        ms = _timed(torch, ext, flush, f_tx, reps)
+        _kernel_ms(ctx, 4)
+        _timed(torch, ext, flush, f_tx, reps)
+        ms = _kernel_ms(ctx, 4)[0] / reps
         tx_ms += ms
         coeffs += n * w * h
         per["%dx%d" % (w, h)] = round(n * w * h * 6 / (ms / 1e3) / 1e9 / hbm, 3)
@@ -138,4 +191,5 @@ def run(ctx, r, torch, ext, flush, reps=3):
         "value": coeffs / 1e6 / (tx_ms / 1e3), "unit": "Mcoeff/s", "ms": tx_ms, "coeffs": coeffs,
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                      "alg_bytes_per_coeff": 6, "peak_source": hbm_how, "frac_by_tx_size": per}}
+    ctx.check(lib.r1c_profile(ctx.h, 0))
     return out

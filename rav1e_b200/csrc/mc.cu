@@ -66,10 +66,19 @@ __device__ __forceinline__ int filter_bank(int mode, int length) {
 
 __device__ __forceinline__ int rshift_round(int v, int bit) { return (v + ((1 << bit) >> 1)) >> bit; }
 
-template <typename JOB>
-__global__ void count_items_kernel(const JOB *jobs, long long n, long long *counts) {
+template <typename JOB, int ROWS_PER_ITEM>
+__global__ void count_items_kernel(const JOB *jobs, long long n, long long *counts, long long *minmax) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) counts[i] = items_of(jobs[i].w, jobs[i].h);
+  if (i < n) {
+    const long long c = ROWS_PER_ITEM == 1 ? (long long)((jobs[i].w + 3) >> 2) * jobs[i].h : items_of(jobs[i].w, jobs[i].h);
+    counts[i] = c;
+    // min / max items per job: equal -> the kernels index jobs by division instead of searching
+    const long long wmin = __reduce_min_sync(__activemask(), (unsigned)c), wmax = __reduce_max_sync(__activemask(), (unsigned)c);
+    if ((threadIdx.x & 31) == 0 || i == 0) {
+      atomicMin(minmax, wmin);
+      atomicMin(minmax + 1, -wmax);  // kept negated so one memset initialises both
+    }
+  }
   if (i == n) counts[i] = 0;
 }
 
@@ -124,138 +133,234 @@ struct McArgs {
   int bit_depth;
 };
 
+// ---- packed-arithmetic strip walker -------------------------------------------------
+// Taps are s8 (every filter row with frac != 0 has |tap| <= 126), so an 8-tap sum is
+// 2 DP4A on u8 pixels or 4 DP2A on u16 pixels / i16 intermediates:
+//   t0 = taps 0..3, t1 = taps 4..7, one s8 per byte.
+__device__ __forceinline__ int dp4a_u8s8(uint32_t px, uint32_t taps, int acc) {
+  int d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(px), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_lo_u(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.lo.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_u(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.hi.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_lo_s(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_s(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ uint32_t pack_taps4(const short *f) {
+  return ((uint32_t)(uint8_t)(int8_t)f[0]) | ((uint32_t)(uint8_t)(int8_t)f[1] << 8) |
+         ((uint32_t)(uint8_t)(int8_t)f[2] << 16) | ((uint32_t)(uint8_t)(int8_t)f[3] << 24);
+}
+
+// raw aligned words of one source row of a strip (pixels x0-3 .. x0+ncols+3), `first` =
+// address of pixel x0-3.  Only words holding a needed pixel are loaded.
+template <int PB>
+struct RowWords {
+  uint32_t w[PB == 1 ? 4 : 6];
+};
+template <int PB>
+__device__ __forceinline__ void load_row_words(const uint8_t *first, uint32_t need, RowWords<PB> &rw) {
+  constexpr int NW = PB == 1 ? 4 : 6;
+  const uint32_t *wp = (const uint32_t *)((uintptr_t)first & ~(uintptr_t)3);
+#pragma unroll
+  for (int i = 0; i < NW; i++) rw.w[i] = ((need >> i) & 1u) ? __ldg(wp + i) : 0u;
+}
+// bit i set = aligned word i of a row holds a pixel the job really reads: pixels
+// [x0-3, x0+ncols+4) with a horizontal filter, [x0, x0+ncols) without
+template <int PB>
+__device__ __forceinline__ uint32_t need_mask(const uint8_t *first, int ncols, bool has_h) {
+  const int misb = (int)((uintptr_t)first & 3);
+  const int lo = has_h ? 0 : 3, hi = has_h ? ncols + 7 : 3 + ncols;
+  const int wlo = (misb + lo * PB) >> 2, whi = (misb + hi * PB + 3) >> 2;
+  return ((1u << whi) - 1u) & ~((1u << wlo) - 1u);
+}
+// horizontal 8-tap sums (+ rnd) of the 4 columns of the strip.  `mis` = misalignment of the
+// row start inside its first word: bytes (PB 1) or 0 / 1 pixel (PB 2); the same for every
+// row of an item (strides are multiples of 4 bytes).
+template <int PB>
+__device__ __forceinline__ void hsum_words(const RowWords<PB> &rw, uint32_t mis, uint32_t t0, uint32_t t1, int rnd,
+                                           int (&s)[4]) {
+  if (PB == 1) {
+    const uint32_t sh = mis * 8;
+    const uint32_t a = __funnelshift_r(rw.w[0], rw.w[1], sh), b = __funnelshift_r(rw.w[1], rw.w[2], sh),
+                   c = __funnelshift_r(rw.w[2], rw.w[3], sh);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t lo = k ? __funnelshift_r(a, b, 8 * k) : a, hi = k ? __funnelshift_r(b, c, 8 * k) : b;
+      s[k] = dp4a_u8s8(hi, t1, dp4a_u8s8(lo, t0, rnd));
+    }
+  } else {
+    // realign so that pixel x0-3 is the low half of v[0], then q = the odd-phase pairs
+    const uint32_t sh = mis * 16;
+    uint32_t v[6], q[5];
+#pragma unroll
+    for (int i = 0; i < 6; i++) v[i] = __funnelshift_r(rw.w[i], i < 5 ? rw.w[i + 1] : 0u, sh);
+#pragma unroll
+    for (int i = 0; i < 5; i++) q[i] = __byte_perm(v[i], v[i + 1], 0x5432);  // (hi(v[i]), lo(v[i+1]))
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t *pp = (k & 1) ? &q[k >> 1] : &v[k >> 1];
+      s[k] = dp2a_hi_u(pp[3], t1, dp2a_lo_u(pp[2], t1, dp2a_hi_u(pp[1], t0, dp2a_lo_u(pp[0], t0, rnd))));
+    }
+  }
+}
+
+template <int PB, int KIND>
+__device__ __forceinline__ void store_strip_row(const McArgs &a, const r1c_mc_job &j, int orow, int x0, int ncols,
+                                                const int (&outv)[4]) {
+  if (KIND == 0 || KIND == 2) {
+    uint8_t *d = KIND == 0 ? a.dst0 + ((long long)(j.dst_y + orow) * a.dst_stride + j.dst_x + x0) * PB
+                           : (uint8_t *)a.tmp + ((long long)j.tmp_off + (long long)orow * j.w + x0) * PB;
+    if (PB == 1) {
+      if (ncols == 4 && (((uintptr_t)d) & 3) == 0) {
+        *(uint32_t *)d = (uint32_t)outv[0] | ((uint32_t)outv[1] << 8) | ((uint32_t)outv[2] << 16) | ((uint32_t)outv[3] << 24);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+          if (c < ncols) d[c] = (uint8_t)outv[c];
+      }
+    } else {
+      uint16_t *d16 = (uint16_t *)d;
+      if (ncols == 4 && (((uintptr_t)d) & 7) == 0) {
+        uint2 v;
+        v.x = (uint32_t)outv[0] | ((uint32_t)outv[1] << 16);
+        v.y = (uint32_t)outv[2] | ((uint32_t)outv[3] << 16);
+        *(uint2 *)d = v;
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+          if (c < ncols) d16[c] = (uint16_t)outv[c];
+      }
+    }
+  } else {
+    int16_t *t = a.tmp + j.tmp_off + (long long)orow * j.w + x0;
+    if (ncols == 4 && (((uintptr_t)t) & 7) == 0) {
+      uint2 v;
+      v.x = ((uint32_t)outv[0] & 0xffff) | ((uint32_t)outv[1] << 16);
+      v.y = ((uint32_t)outv[2] & 0xffff) | ((uint32_t)outv[3] << 16);
+      *(uint2 *)t = v;
+    } else {
+#pragma unroll
+      for (int c = 0; c < 4; c++)
+        if (c < ncols) t[c] = (int16_t)outv[c];
+    }
+  }
+}
+
+// halved taps as s8 x 4 (every SUBPEL_FILTERS entry is even; frac 0 = the unit tap 128 -> 64)
+__device__ __forceinline__ void half_taps(int bank, int frac, uint32_t &t0, uint32_t &t1) {
+  const short *f = c_filters[bank][frac & 15];
+  short h[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) h[k] = (short)(f[k] >> 1);
+  t0 = pack_taps4(h);
+  t1 = pack_taps4(h + 4);
+}
+
+// One strip (4 columns) of rows [r0, r1) of a job.  ONE code path for the four
+// (col_frac, row_frac) cases of put_8tap_ref / prep_8tap_ref (src/mc.rs:224-306,
+// 326-386): a zero frac is the unit filter (tap 128), for which the separable
+// formula  mid = round_shift(sum_x, 7-ib) as i16;  out = round_shift(sum_y, 7+ib | 7)
+// reproduces the reference's 1-D and copy cases bit for bit (128 * px >> (7-ib) =
+// px << ib exactly; round_shift(128 * mid, 7+ib) = round_shift(mid, ib)).  Taps are
+// halved to fit s8 (all are even), so every shift drops by one:
+// round_shift(2 S, s) = (S + 2^(s-2)) >> (s-1).  Lanes of a warp therefore never
+// diverge on the case; rows / words a case does not read are not loaded.
+template <int PB, int KIND>
+__device__ __forceinline__ void walk_strip(const McArgs &a, const r1c_mc_job &j, int x0, int ncols, int r0, int r1,
+                                           int ib, int maxv) {
+  const bool has_h = j.col_frac != 0, has_v = j.row_frac != 0;
+  uint32_t tx0, tx1, ty0, ty1;
+  half_taps(filter_bank(j.mode_x, j.w), j.col_frac, tx0, tx1);
+  half_taps(filter_bank(j.mode_y, j.h), j.row_frac, ty0, ty1);
+  const uint8_t *src = (const uint8_t *)a.src.p0 + ((long long)j.src_y * a.src.stride + j.src_x + x0) * PB;
+  const long long sstride = (long long)a.src.stride * PB;
+  const int hsh = 6 - ib, hrnd = 1 << (5 - ib);
+  const int vshift = (KIND == 1 ? 7 : 7 + ib) - 1, vrnd = 1 << (vshift - 1);
+  const uint8_t *hfirst = src - 3 * PB;  // pixel x0-3 of row 0
+  const uint32_t mis = PB == 1 ? (uint32_t)((uintptr_t)hfirst & 3) : (uint32_t)(((uintptr_t)hfirst >> 1) & 1);
+  const uint32_t need = need_mask<PB>(hfirst, ncols, has_h);
+  const int nrows = r1 - r0 + 7;            // source rows r0-3 .. r1+3
+  const int ilo = has_v ? 0 : 3, ihi = has_v ? nrows : nrows - 4;  // rows really read
+  RowWords<PB> nxt;
+  load_row_words<PB>(hfirst + (long long)(r0 - 3) * sstride, ilo == 0 ? need : 0u, nxt);
+  // vertical stage on packed pairs of consecutive intermediate rows:
+  //   pr[c][slot] = (mid[i-1], mid[i]) as two i16; out(i-7) = taps . mids(i-7 .. i)
+  uint32_t pr[4][8];
+  int prev[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int c = 0; c < 4; c++)
+#pragma unroll
+    for (int k = 0; k < 8; k++) pr[c][k] = 0;
+  for (int ib8 = 0; ib8 < nrows; ib8 += 8) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      const int i = ib8 + u;
+      if (i < nrows) {
+        const RowWords<PB> cur = nxt;
+        if (i + 1 < nrows)
+          load_row_words<PB>(hfirst + (long long)(r0 - 3 + i + 1) * sstride, (i + 1 >= ilo && i + 1 < ihi) ? need : 0u, nxt);
+        int sum[4], mid[4];
+        hsum_words<PB>(cur, mis, tx0, tx1, hrnd, sum);
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          mid[c] = sum[c] >> hsh;
+          pr[c][(u + 7) & 7] = __byte_perm((uint32_t)prev[c], (uint32_t)mid[c], 0x5410);
+          prev[c] = mid[c];
+        }
+        if (i >= 7) {
+          int outv[4];
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            int v = dp2a_lo_s(pr[c][(u + 1) & 7], ty0, vrnd);
+            v = dp2a_hi_s(pr[c][(u + 3) & 7], ty0, v);
+            v = dp2a_lo_s(pr[c][(u + 5) & 7], ty1, v);
+            v = dp2a_hi_s(pr[c][(u + 7) & 7], ty1, v);
+            v >>= vshift;
+            outv[c] = KIND == 1 ? (int)(int16_t)v : min(max(v, 0), maxv);
+          }
+          store_strip_row<PB, KIND>(a, j, r0 + i - 7, x0, ncols, outv);
+        }
+      }
+    }
+  }
+}
+
 // KIND 0 = put (clamped pixels into the dst plane), 1 = prep (i16, dense w*h at tmp_off),
 // 2 = put into a dense w*h pixel block at tmp_off (pixels; used by the sub-pel search)
 template <int PB, int KIND>
 __global__ void __launch_bounds__(MC_THREADS) mc_kernel(McArgs a) {
   const long long total = a.offs[a.n];
+  const int ipj = a.offs[a.n + 1] == -a.offs[a.n + 2] ? (int)a.offs[a.n + 1] : 0;  // min == max items per job
   const int ib = a.bit_depth == 12 ? 2 : 4;
   const int maxv = (1 << a.bit_depth) - 1;
   for (long long item = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item < total;
        item += (long long)gridDim.x * MC_THREADS) {
-    const long long ji = find_job(a.offs, a.n, item);
+    // every job with the same number of items (the usual batch): no search
+    const long long ji = ipj ? (long long)((unsigned long long)item / (unsigned)ipj) : find_job(a.offs, a.n, item);
     const r1c_mc_job j = a.jobs[ji];
-    const int local = (int)(item - a.offs[ji]);
+    const int local = ipj ? (int)(item - ji * ipj) : (int)(item - a.offs[ji]);
     const int nstrips = (j.w + 3) >> 2;
     const int seg = local / nstrips, strip = local - seg * nstrips;
     const int x0 = strip * 4;
     const int ncols = min(4, j.w - x0);
     const int r0 = seg * SEG_ROWS, r1 = min((int)j.h, r0 + SEG_ROWS);
-    const bool has_h = j.col_frac != 0, has_v = j.row_frac != 0;
-
-    int xf[8], yf[8];
-    {
-      const short *fx = c_filters[filter_bank(j.mode_x, j.w)][j.col_frac & 15];
-      const short *fy = c_filters[filter_bank(j.mode_y, j.h)][j.row_frac & 15];
-#pragma unroll
-      for (int k = 0; k < 8; k++) {
-        xf[k] = fx[k];
-        yf[k] = fy[k];
-      }
-    }
-    const uint8_t *src = (const uint8_t *)a.src.p0 + ((long long)j.src_y * a.src.stride + j.src_x) * PB;
-    const long long sstride = (long long)a.src.stride * PB;
-    const int vshift = has_h ? (KIND == 1 ? 7 : 7 + ib) : (KIND == 1 ? 7 - ib : 7);
-
-    int win[4][8];  // win[c][k]: horizontally processed value of row (current - 7 + k)
-#pragma unroll
-    for (int c = 0; c < 4; c++)
-#pragma unroll
-      for (int k = 0; k < 8; k++) win[c][k] = 0;
-
-    const int row_first = has_v ? r0 - 3 : r0;
-    const int row_last = has_v ? r1 + 4 : r1;  // exclusive
-    for (int rb = row_first; rb < row_last; rb += 8) {
-#pragma unroll
-      for (int u = 0; u < 8; u++) {
-        const int r = rb + u;  // source row relative to the block origin
-        if (r < row_last) {
-          int px[11];
-          if (has_h) load_strip_row<PB, true>(src + r * sstride, x0, ncols, px);
-          else load_strip_row<PB, false>(src + r * sstride, x0, ncols, px);
-          int hv[4];  // value entering the vertical stage (or the output when !has_v)
-#pragma unroll
-          for (int c = 0; c < 4; c++) {
-            if (has_h) {
-              int s = 0;
-#pragma unroll
-              for (int k = 0; k < 8; k++) s += xf[k] * px[c + k];
-              hv[c] = rshift_round(s, 7 - ib);  // i32; cast to i16 where the reference does
-            } else {
-              hv[c] = px[c + 3];
-            }
-          }
-          int outv[4];
-          bool emit = false;
-          int orow = 0;
-          if (has_v) {
-            // slot (u) of the rotating window receives this row; the window is
-            // complete once 8 rows are in: rows r-7 .. r produce output row r-4
-#pragma unroll
-            for (int c = 0; c < 4; c++) win[c][u] = has_h ? (int)(int16_t)hv[c] : hv[c];
-            orow = r - 4;
-            if (orow >= r0) {
-              emit = true;
-#pragma unroll
-              for (int c = 0; c < 4; c++) {
-                int s = 0;
-#pragma unroll
-                for (int k = 0; k < 8; k++) s += yf[k] * win[c][(u + 1 + k) & 7];
-                s = rshift_round(s, vshift);
-                outv[c] = KIND == 1 ? (int)(int16_t)s : min(max(s, 0), maxv);
-              }
-            }
-          } else {
-            emit = true;
-            orow = r;
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-              if (has_h) outv[c] = KIND == 1 ? (int)(int16_t)hv[c] : min(max(rshift_round(hv[c], ib), 0), maxv);
-              else outv[c] = KIND == 1 ? (int)(int16_t)((int16_t)hv[c] << ib) : hv[c];
-            }
-          }
-          if (emit) {
-            if (KIND == 0 || KIND == 2) {
-              uint8_t *d = KIND == 0 ? a.dst0 + ((long long)(j.dst_y + orow) * a.dst_stride + j.dst_x + x0) * PB
-                                     : (uint8_t *)a.tmp + ((long long)j.tmp_off + (long long)orow * j.w + x0) * PB;
-              if (PB == 1) {
-                if (ncols == 4 && (((uintptr_t)d) & 3) == 0) {
-                  *(uint32_t *)d = (uint32_t)outv[0] | ((uint32_t)outv[1] << 8) | ((uint32_t)outv[2] << 16) | ((uint32_t)outv[3] << 24);
-                } else {
-#pragma unroll
-                  for (int c = 0; c < 4; c++)
-                    if (c < ncols) d[c] = (uint8_t)outv[c];
-                }
-              } else {
-                uint16_t *d16 = (uint16_t *)d;
-                if (ncols == 4 && (((uintptr_t)d) & 7) == 0) {
-                  uint2 v;
-                  v.x = (uint32_t)outv[0] | ((uint32_t)outv[1] << 16);
-                  v.y = (uint32_t)outv[2] | ((uint32_t)outv[3] << 16);
-                  *(uint2 *)d = v;
-                } else {
-#pragma unroll
-                  for (int c = 0; c < 4; c++)
-                    if (c < ncols) d16[c] = (uint16_t)outv[c];
-                }
-              }
-            } else {
-              int16_t *t = a.tmp + j.tmp_off + (long long)orow * j.w + x0;
-              if (ncols == 4 && (((uintptr_t)t) & 7) == 0) {
-                uint2 v;
-                v.x = ((uint32_t)outv[0] & 0xffff) | ((uint32_t)outv[1] << 16);
-                v.y = ((uint32_t)outv[2] & 0xffff) | ((uint32_t)outv[3] << 16);
-                *(uint2 *)t = v;
-              } else {
-#pragma unroll
-                for (int c = 0; c < 4; c++)
-                  if (c < ncols) t[c] = (int16_t)outv[c];
-              }
-            }
-          }
-        }
-      }
-    }
+    walk_strip<PB, KIND>(a, j, x0, ncols, r0, r1, ib, maxv);
   }
 }
 
@@ -275,39 +380,55 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   const long long total = a.offs[a.n];
   const int ib = a.bit_depth == 12 ? 2 : 4;
   const int maxv = (1 << a.bit_depth) - 1;
+  const int ipj = a.offs[a.n + 1] == -a.offs[a.n + 2] ? (int)a.offs[a.n + 1] : 0;  // min == max items per job
+  // item = 4 pixels of one row: fully parallel, 8-byte loads / stores
   for (long long item = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item < total;
        item += (long long)gridDim.x * MC_THREADS) {
-    const long long ji = find_job(a.offs, a.n, item);
+    const long long ji = ipj ? (long long)((unsigned long long)item / (unsigned)ipj) : find_job(a.offs, a.n, item);
     const r1c_avg_job j = a.jobs[ji];
-    const int local = (int)(item - a.offs[ji]);
+    const int local = ipj ? (int)(item - ji * ipj) : (int)(item - a.offs[ji]);
     const int nstrips = (j.w + 3) >> 2;
-    const int seg = local / nstrips, strip = local - seg * nstrips;
+    const int r = local / nstrips, strip = local - r * nstrips;
     const int x0 = strip * 4, ncols = min(4, j.w - x0);
-    const int r0 = seg * SEG_ROWS, r1 = min((int)j.h, r0 + SEG_ROWS);
-    for (int r = r0; r < r1; r++) {
-      const long long o = (long long)j.tmp_off + (long long)r * j.w + x0;
-      uint8_t *d = a.dst0 + ((long long)(j.dst_y + r) * a.dst_stride + j.dst_x + x0) * PB;
+    const long long o = (long long)j.tmp_off + (long long)r * j.w + x0;
+    uint8_t *d = a.dst0 + ((long long)(j.dst_y + r) * a.dst_stride + j.dst_x + x0) * PB;
+    int v[4];
+    if (ncols == 4 && (o & 3) == 0) {
+      const uint2 p = __ldg((const uint2 *)(a.t1 + o)), q = __ldg((const uint2 *)(a.t2 + o));
+      v[0] = (int)(int16_t)p.x + (int)(int16_t)q.x;
+      v[1] = ((int)p.x >> 16) + ((int)q.x >> 16);
+      v[2] = (int)(int16_t)p.y + (int)(int16_t)q.y;
+      v[3] = ((int)p.y >> 16) + ((int)q.y >> 16);
+    } else {
 #pragma unroll
-      for (int c = 0; c < 4; c++) {
+      for (int c = 0; c < 4; c++) v[c] = c < ncols ? (int)a.t1[o + c] + (int)a.t2[o + c] : 0;
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
+    if (ncols == 4 && ((uintptr_t)d & (4 * PB - 1)) == 0) {
+      if (PB == 1) *(uint32_t *)d = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+      else *(uint2 *)d = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
+    } else {
+#pragma unroll
+      for (int c = 0; c < 4; c++)
         if (c < ncols) {
-          int v = rshift_round((int)a.t1[o + c] + (int)a.t2[o + c], ib + 1);
-          v = min(max(v, 0), maxv);
-          if (PB == 1) d[c] = (uint8_t)v;
-          else ((uint16_t *)d)[c] = (uint16_t)v;
+          if (PB == 1) d[c] = (uint8_t)v[c];
+          else ((uint16_t *)d)[c] = (uint16_t)v[c];
         }
-      }
     }
   }
 }
 
-template <typename JOB>
+template <typename JOB, int ROWS_PER_ITEM>
 int build_offsets(r1c_ctx *ctx, const JOB *d_jobs, int64_t n, long long **d_offs_out) {
   void *d_counts, *d_offs, *d_tmp;
   int rc;
-  const size_t bytes = (size_t)(n + 1) * sizeof(long long);
+  const size_t bytes = (size_t)(n + 3) * sizeof(long long);  // offs[n+1], offs[n+2] = min / max items per job
   if ((rc = r1c_scratch_dev(ctx, 2, bytes, &d_counts))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 3, bytes, &d_offs))) return rc;
-  count_items_kernel<JOB><<<(unsigned)((n + 1 + 255) / 256), 256, 0, ctx->stream>>>(d_jobs, n, (long long *)d_counts);
+  long long *minmax = (long long *)d_offs + n + 1;
+  R1C_CUDA(ctx, cudaMemsetAsync(minmax, 0x7f, 2 * sizeof(long long), ctx->stream));
+  count_items_kernel<JOB, ROWS_PER_ITEM><<<(unsigned)((n + 1 + 255) / 256), 256, 0, ctx->stream>>>(d_jobs, n, (long long *)d_counts, minmax);
   R1C_LAUNCH_CHECK(ctx);
   size_t tmp_bytes = 0;
   R1C_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, (long long *)d_counts, (long long *)d_offs, (int)(n + 1), ctx->stream));
@@ -325,14 +446,22 @@ int check_mc(r1c_ctx *ctx, const r1c_plane *src, int bit_depth, int64_t n, const
   return R1C_OK;
 }
 
-int grid_for(r1c_ctx *ctx) { return ctx->sm_count * 8; }
+// persistent grids: exactly the CTAs that are resident at once
+template <typename K>
+int grid_for(r1c_ctx *ctx, K kern) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MC_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+  return ctx->sm_count * per_sm;
+}
 
 int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_plane *src,
               const r1c_mc_job *d_jobs, int64_t n, int bit_depth) {
   if (n == 0) return R1C_OK;
+  // the u16 horizontal filter pairs pixels on 32-bit words: rows must keep the parity
+  R1C_REQUIRE(ctx, ((src->cfg.stride * src->px_bytes) & 3) == 0, R1C_ERR_ARG, "plane rows must be a multiple of 4 bytes");
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   long long *d_offs;
-  int rc = build_offsets(ctx, d_jobs, n, &d_offs);
+  int rc = build_offsets<r1c_mc_job, 0>(ctx, d_jobs, n, &d_offs);
   if (rc) return rc;
   McArgs a;
   a.src = make_view(src);
@@ -348,16 +477,15 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
   a.offs = d_offs;
   a.n = n;
   a.bit_depth = bit_depth;
-  const int grid = grid_for(ctx);
   r1c_prof_begin(ctx, ctx->prof_mc_slot ? ctx->prof_mc_slot : R1C_PROF_MC);
   if (src->px_bytes == 1) {
-    if (kind == 0) mc_kernel<1, 0><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
-    else if (kind == 1) mc_kernel<1, 1><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
-    else mc_kernel<1, 2><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
+    if (kind == 0) mc_kernel<1, 0><<<grid_for(ctx, mc_kernel<1, 0>), MC_THREADS, 0, ctx->stream>>>(a);
+    else if (kind == 1) mc_kernel<1, 1><<<grid_for(ctx, mc_kernel<1, 1>), MC_THREADS, 0, ctx->stream>>>(a);
+    else mc_kernel<1, 2><<<grid_for(ctx, mc_kernel<1, 2>), MC_THREADS, 0, ctx->stream>>>(a);
   } else {
-    if (kind == 0) mc_kernel<2, 0><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
-    else if (kind == 1) mc_kernel<2, 1><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
-    else mc_kernel<2, 2><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
+    if (kind == 0) mc_kernel<2, 0><<<grid_for(ctx, mc_kernel<2, 0>), MC_THREADS, 0, ctx->stream>>>(a);
+    else if (kind == 1) mc_kernel<2, 1><<<grid_for(ctx, mc_kernel<2, 1>), MC_THREADS, 0, ctx->stream>>>(a);
+    else mc_kernel<2, 2><<<grid_for(ctx, mc_kernel<2, 2>), MC_THREADS, 0, ctx->stream>>>(a);
   }
   r1c_prof_end(ctx, ctx->prof_mc_slot ? ctx->prof_mc_slot : R1C_PROF_MC);
   R1C_LAUNCH_CHECK(ctx);
@@ -475,7 +603,7 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   long long *d_offs;
-  int rc = build_offsets(ctx, d_jobs, n, &d_offs);
+  int rc = build_offsets<r1c_avg_job, 1>(ctx, d_jobs, n, &d_offs);
   if (rc) return rc;
   AvgArgs a;
   PlaneView dv = make_view(dst);
@@ -488,8 +616,8 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
   a.n = n;
   a.bit_depth = bit_depth;
   r1c_prof_begin(ctx, R1C_PROF_MC);
-  if (dst->px_bytes == 1) avg_kernel<1><<<grid_for(ctx), MC_THREADS, 0, ctx->stream>>>(a);
-  else avg_kernel<2><<<grid_for(ctx), MC_THREADS, 0, ctx->stream>>>(a);
+  if (dst->px_bytes == 1) avg_kernel<1><<<grid_for(ctx, avg_kernel<1>), MC_THREADS, 0, ctx->stream>>>(a);
+  else avg_kernel<2><<<grid_for(ctx, avg_kernel<2>), MC_THREADS, 0, ctx->stream>>>(a);
   r1c_prof_end(ctx, R1C_PROF_MC);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
