@@ -110,7 +110,7 @@ int64_t r1c_launch_count(const r1c_ctx *ctx);
 #define R1C_PROF_SUBPEL_COST 2 /* SAD / SATD of the predicted candidates      */
 #define R1C_PROF_MC 3         /* put / prep / avg batch kernels               */
 #define R1C_PROF_TX 4         /* forward transform kernels                    */
-#define R1C_PROF_DIST 5       /* SAD / SATD batch kernels                     */
+#define R1C_PROF_DIST 5       /* SAD / SATD / RDO distortion batch kernels    */
 #define R1C_PROF_SLOTS 6
 int r1c_profile(r1c_ctx *ctx, int enable);
 int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches);
@@ -212,6 +212,49 @@ int r1c_prep_8tap_batch_dev(r1c_ctx *ctx, int16_t *d_tmp, const r1c_plane *src,
 int r1c_mc_avg_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_tmp1,
                          const int16_t *d_tmp2, const r1c_avg_job *d_jobs, int64_t n,
                          int bit_depth);
+
+/* ------------------------------------------------------------------------
+ * RDO distortion.
+ *   r1c_sse_wxh_batch    sse_wxh, src/rdo.rs:286-335: SSE per importance block
+ *                        (8x8 luma px, decimated with src1's plane) times the
+ *                        f64 distortion bias, truncated to u64 per block, summed
+ *   r1c_cdef_dist_batch  cdef_dist_wxh, src/rdo.rs:219-283 (w, h multiples of 8,
+ *                        non-subsampled planes)
+ *   bias                 compute_distortion_bias, src/rdo.rs:477-508, from
+ *                        fi.block_importances (src/encoder.rs:719) at the frame
+ *                        block offset of (src_x, src_y) in src1's plane;
+ *                        block_importances == NULL gives bias 1.0 (raw sums)
+ *   r1c_tx_dist_batch    tx-domain distortion, src/encoder.rs:1210-1224: block i
+ *                        reads coeffs + i*W*H and rcoeffs + i*min(W,32)*min(H,32)
+ * Results are Distortion values (u64), bit-identical to the reference's f64
+ * arithmetic (no fused multiply-add, IEEE div / sqrt).
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int32_t src_x, src_y; /* region origin in src1 (the input plane), >= 0 */
+  int32_t rec_x, rec_y; /* region origin in src2 (the reconstruction)    */
+  int32_t w, h;         /* pixels of these planes                        */
+} r1c_rdo_job;
+typedef struct {
+  int32_t w_in_imp_b; /* fi.w_in_imp_b: row pitch of block_importances     */
+  int32_t n_imp;      /* elements in block_importances                     */
+  int32_t w_in_b;     /* fi.w_in_b, fi.h_in_b: frame size in 4x4 units     */
+  int32_t h_in_b;
+} r1c_bias_params;
+int r1c_sse_wxh_batch(r1c_ctx *ctx, const r1c_plane *src1, const r1c_plane *src2,
+                      const r1c_rdo_job *jobs, int64_t n, int bit_depth,
+                      const float *block_importances, const r1c_bias_params *bp, uint64_t *out);
+int r1c_cdef_dist_batch(r1c_ctx *ctx, const r1c_plane *src1, const r1c_plane *src2,
+                        const r1c_rdo_job *jobs, int64_t n, int bit_depth,
+                        const float *block_importances, const r1c_bias_params *bp, uint64_t *out);
+/* kind 0 = sse_wxh, 1 = cdef_dist_wxh; every pointer is device memory except bp */
+int r1c_rdo_dist_batch_dev(r1c_ctx *ctx, int kind, const r1c_plane *src1, const r1c_plane *src2,
+                           const r1c_rdo_job *d_jobs, int64_t n, int bit_depth,
+                           const float *d_block_importances, const r1c_bias_params *bp,
+                           uint64_t *d_out);
+int r1c_tx_dist_batch(r1c_ctx *ctx, const int32_t *coeffs, const int32_t *rcoeffs, int tx_size,
+                      int64_t n, uint64_t *out);
+int r1c_tx_dist_batch_dev(r1c_ctx *ctx, const int32_t *d_coeffs, const int32_t *d_rcoeffs,
+                          int tx_size, int64_t n, uint64_t *d_out);
 
 /* ------------------------------------------------------------------------
  * Forward transforms: forward_transform, src/transform/mod.rs:556-566 ->

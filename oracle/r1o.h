@@ -143,6 +143,18 @@ uint64_t r1o_subpel_cost(const void *org0, const r1o_plane_cfg *org_cfg,
                          int use_satd, int allow_hp, const int64_t range[4],
                          int bit_depth, int px_bytes);
 
+/* ---- RDO distortion (r1o_rdo.c; src/rdo.rs:219-335,477-530, src/encoder.rs:1210-1224) ---- */
+double r1o_distortion_bias(const float *importances, int64_t w_in_imp_b, int64_t w_in_b, int64_t h_in_b,
+                           int64_t bo_x, int64_t bo_y, int64_t width_mi, int64_t height_mi);
+uint64_t r1o_sse_wxh(const void *src1, int64_t stride1, int64_t x1, int64_t y1, const void *src2, int64_t stride2,
+                     int64_t x2, int64_t y2, int64_t w, int64_t h, int xdec, int ydec, int px_bytes,
+                     const float *importances, int64_t w_in_imp_b, int64_t w_in_b, int64_t h_in_b);
+uint64_t r1o_cdef_dist_wxh(const void *src1, int64_t stride1, int64_t x1, int64_t y1, const void *src2,
+                           int64_t stride2, int64_t x2, int64_t y2, int64_t w, int64_t h, int bit_depth,
+                           int px_bytes, const float *importances, int64_t w_in_imp_b, int64_t w_in_b,
+                           int64_t h_in_b);
+uint64_t r1o_tx_dist(const int32_t *coeffs, const int32_t *rcoeffs, int tx_size);
+
 #ifdef __cplusplus
 }
 #endif

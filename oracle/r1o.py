@@ -87,6 +87,15 @@ def lib():
         L.r1o_frame_me.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i, i, i, i, u32, u32, i, i, i, i, i,
                                    vp, i64, vp, vp]
         L.r1o_frame_me.restype = i64
+        dbl = C.c_double
+        L.r1o_distortion_bias.argtypes = [vp, i64, i64, i64, i64, i64, i64, i64]
+        L.r1o_distortion_bias.restype = dbl
+        L.r1o_sse_wxh.argtypes = [vp, i64, i64, i64, vp, i64, i64, i64, i64, i64, i, i, i, vp, i64, i64, i64]
+        L.r1o_sse_wxh.restype = u64
+        L.r1o_cdef_dist_wxh.argtypes = [vp, i64, i64, i64, vp, i64, i64, i64, i64, i64, i, i, vp, i64, i64, i64]
+        L.r1o_cdef_dist_wxh.restype = u64
+        L.r1o_tx_dist.argtypes = [vp, vp, i]
+        L.r1o_tx_dist.restype = u64
         _lib = L
     return _lib
 
@@ -133,6 +142,36 @@ def sad(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
 def satd(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
     return lib().r1o_satd(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
                           org.px_bytes)
+
+
+def _imp(block_importances):
+    if block_importances is None:
+        return None, None
+    a = np.ascontiguousarray(block_importances, dtype=np.float32)
+    return a, _p(a)
+
+
+def sse_wxh(src1: OPlane, x1, y1, src2: OPlane, x2, y2, w, h, block_importances=None, w_in_imp_b=0, w_in_b=0,
+            h_in_b=0):
+    """sse_wxh, src/rdo.rs:286-335 (bias from block_importances; None -> 1.0)"""
+    _keep, ip = _imp(block_importances)
+    return lib().r1o_sse_wxh(src1.origin_ptr(), src1.cfg.stride, x1, y1, src2.origin_ptr(), src2.cfg.stride, x2, y2,
+                             w, h, src1.cfg.xdec, src1.cfg.ydec, src1.px_bytes, ip, w_in_imp_b, w_in_b, h_in_b)
+
+
+def cdef_dist_wxh(src1: OPlane, x1, y1, src2: OPlane, x2, y2, w, h, bit_depth, block_importances=None, w_in_imp_b=0,
+                  w_in_b=0, h_in_b=0):
+    """cdef_dist_wxh, src/rdo.rs:256-283"""
+    _keep, ip = _imp(block_importances)
+    return lib().r1o_cdef_dist_wxh(src1.origin_ptr(), src1.cfg.stride, x1, y1, src2.origin_ptr(), src2.cfg.stride,
+                                   x2, y2, w, h, bit_depth, src1.px_bytes, ip, w_in_imp_b, w_in_b, h_in_b)
+
+
+def tx_dist(coeffs, rcoeffs, tx_size):
+    """tx-domain distortion of one block, src/encoder.rs:1210-1224"""
+    c = np.ascontiguousarray(coeffs, dtype=np.int32)
+    r = np.ascontiguousarray(rcoeffs, dtype=np.int32)
+    return lib().r1o_tx_dist(_p(c), _p(r), tx_size)
 
 
 def fht(residual, tx_size, tx_type, bit_depth):

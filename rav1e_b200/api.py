@@ -30,6 +30,8 @@ MC_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("src_x", "<i4"), ("src_y
 AVG_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                     ("tmp_off", "<i4")])
 TX_JOB = np.dtype([("in_x", "<i4"), ("in_y", "<i4"), ("pred_x", "<i4"), ("pred_y", "<i4")])
+RDO_JOB = np.dtype([("src_x", "<i4"), ("src_y", "<i4"), ("rec_x", "<i4"), ("rec_y", "<i4"),
+                    ("w", "<i4"), ("h", "<i4")])
 ME_RESULT = np.dtype([("mv", MV), ("reserved", "<u4"), ("cost", "<u8")])
 FS_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("x_lo", "<i4"),
                    ("x_hi", "<i4"), ("y_lo", "<i4"), ("y_hi", "<i4"), ("step", "<i4"),
@@ -42,7 +44,7 @@ SUBPEL_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("lam
                        ("mvy_min", "<i4"), ("mvy_max", "<i4"), ("use_satd", "<i4"),
                        ("allow_high_precision_mv", "<i4")])
 STRUCT_PAIRS = [(DIST_JOB, capi.DistJob), (MC_JOB, capi.McJob), (AVG_JOB, capi.AvgJob),
-                (TX_JOB, capi.TxJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
+                (TX_JOB, capi.TxJob), (RDO_JOB, capi.RdoJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
                 (SB_JOB, capi.SbJob), (SUBPEL_JOB, capi.SubpelJob), (MV, capi.Mv)]
 
 BLOCK = {n: i for i, n in enumerate(capi.BLOCK_SIZES)}
@@ -245,6 +247,44 @@ def mc_avg(ctx, dst, dst_xy, tmp1, tmp2, width, height, bit_depth):
 # ------------------------------------------------------------ forward transform --
 def fwd_txfm_valid(tx_size, tx_type):
     return bool(capi.load().r1c_fwd_txfm_valid(tx_size, tx_type))
+
+
+def _bias_args(block_importances, w_in_imp_b, w_in_b, h_in_b):
+    if block_importances is None:
+        return None, None, None
+    imp = _arr(block_importances, np.float32)
+    bp = capi.BiasParams(int(w_in_imp_b), int(imp.size), int(w_in_b), int(h_in_b))
+    return imp, bp, C.byref(bp)
+
+
+def sse_wxh(ctx, src1, src2, jobs, bit_depth, block_importances=None, w_in_imp_b=0, w_in_b=0, h_in_b=0,
+            cdef=False):
+    """sse_wxh (src/rdo.rs:286-335) or, with cdef=True, cdef_dist_wxh (:256-283) of every RDO_JOB;
+    the bias closure is compute_distortion_bias (:477-508) over block_importances (None: bias 1.0).
+    Returns the u64 Distortion per job."""
+    jobs = _arr(jobs, RDO_JOB)
+    out = np.empty(jobs.size, dtype=np.uint64)
+    imp, _keep, bp = _bias_args(block_importances, w_in_imp_b, w_in_b, h_in_b)
+    fn = ctx.lib.r1c_cdef_dist_batch if cdef else ctx.lib.r1c_sse_wxh_batch
+    ctx.check(fn(ctx.h, src1.h, src2.h, _p(jobs), jobs.size, bit_depth, _p(imp) if imp is not None else None,
+                 bp, _p(out)))
+    return out
+
+
+def cdef_dist_wxh(ctx, src1, src2, jobs, bit_depth, block_importances=None, w_in_imp_b=0, w_in_b=0, h_in_b=0):
+    return sse_wxh(ctx, src1, src2, jobs, bit_depth, block_importances, w_in_imp_b, w_in_b, h_in_b, cdef=True)
+
+
+def tx_distortion(ctx, coeffs, rcoeffs, tx_size):
+    """tx-domain distortion of encode_tx_block (src/encoder.rs:1210-1224); coeffs (N, H*W) int32,
+    rcoeffs (N, min(H,32)*min(W,32)) int32 -> (N,) uint64"""
+    coeffs, rcoeffs = _arr(coeffs, np.int32), _arr(rcoeffs, np.int32)
+    w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)
+    n = coeffs.size // (w * h)
+    assert n * w * h == coeffs.size and n * min(w, 32) * min(h, 32) == rcoeffs.size
+    out = np.empty(n, dtype=np.uint64)
+    ctx.check(ctx.lib.r1c_tx_dist_batch(ctx.h, _p(coeffs), _p(rcoeffs), tx_size, n, _p(out)))
+    return out
 
 
 def forward_transform(ctx, residual, tx_size, tx_type, bit_depth):

@@ -63,6 +63,14 @@ class TxJob(C.Structure):
                 ("pred_y", C.c_int32)]
 
 
+class RdoJob(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("src_x", "src_y", "rec_x", "rec_y", "w", "h")]
+
+
+class BiasParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("w_in_imp_b", "n_imp", "w_in_b", "h_in_b")]
+
+
 class Mv(C.Structure):
     _fields_ = [("row", C.c_int16), ("col", C.c_int16)]
 
@@ -138,6 +146,11 @@ SIGNATURES = {
     "r1c_forward_transform": (_i, [_vp, _vp, _vp, _i, _i, _i]),
     "r1c_fwd_txfm_batch": (_i, [_vp, _i, _i, _i, _vp, _vp, _i64]),
     "r1c_fwd_txfm_batch_dev": (_i, [_vp, _i, _i, _i, _vp, _vp, _i64]),
+    "r1c_sse_wxh_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _vp, _vp]),
+    "r1c_cdef_dist_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _vp, _vp]),
+    "r1c_rdo_dist_batch_dev": (_i, [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp, _vp, _vp]),
+    "r1c_tx_dist_batch": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
+    "r1c_tx_dist_batch_dev": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
     "r1c_diff_fwd_txfm_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_diff_fwd_txfm_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_mv_range": (None, [_i64, _i64, _i64, _i64, _i, _i, _P(_i64 * 4)]),

@@ -542,3 +542,77 @@ def test_profile_hooks_count_launches(r, ctx, oracle):
     ctx.check(ctx.lib.r1c_profile_read(ctx.h, 0, C.byref(ms), C.byref(n)))
     ctx.check(ctx.lib.r1c_profile(ctx.h, 0))
     assert n.value == 1 and ms.value > 0
+
+
+# ------------------------------------------------------------ RDO distortion ----
+def _rdo_jobs(r, rng, W, H, n, mult, max_log=5):
+    """random regions on the MI grid of a W x H plane, sizes `mult` * 2^k up to 128"""
+    jobs = np.zeros(n, dtype=r.RDO_JOB)
+    for i in range(n):
+        w = min(mult << int(rng.integers(0, max_log + 1)), 128, W)
+        h = min(mult << int(rng.integers(0, max_log + 1)), 128, H)
+        x = int(rng.integers(0, (W - w) // mult + 1)) * mult
+        y = int(rng.integers(0, (H - h) // mult + 1)) * mult
+        jobs[i] = (x, y, x, y, w, h)
+    return jobs
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_sse_wxh_and_cdef_dist_match_oracle(r, ctx, oracle, pb, bd):
+    rng = np.random.default_rng(1200 + bd)
+    W, H = 256, 192
+    o1, d1 = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, xpad=16, ypad=16)
+    o2, d2 = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, xpad=48, ypad=32)  # different stride
+    w_in_b, h_in_b = W // 4, H // 4
+    w_imp = w_in_b // 2
+    imp = (rng.random(w_imp * (h_in_b // 2)) * 5).astype(np.float32)
+    for cdef in (False, True):
+        jobs = _rdo_jobs(r, rng, W, H, 400, 8 if cdef else 4, 4 if cdef else 5)
+        for use_imp in (False, True):
+            kw = dict(block_importances=imp, w_in_imp_b=w_imp, w_in_b=w_in_b, h_in_b=h_in_b) if use_imp else {}
+            got = r.sse_wxh(ctx, d1, d2, jobs, bd, cdef=cdef, **kw)
+            for j, g in zip(jobs, got):
+                a = (o1, int(j["src_x"]), int(j["src_y"]), o2, int(j["rec_x"]), int(j["rec_y"]), int(j["w"]), int(j["h"]))
+                okw = {k: v for k, v in kw.items()}
+                want = oracle.cdef_dist_wxh(*a, bd, **okw) if cdef else oracle.sse_wxh(*a, **okw)
+                assert int(g) == want, (cdef, use_imp, j)
+    # frame edge: the importance sum stops at w_in_b / h_in_b but divides by the full area
+    jobs = np.array([(W - 8, H - 8, W - 8, H - 8, 8, 8)], dtype=r.RDO_JOB)
+    got = r.sse_wxh(ctx, d1, d2, jobs, bd, imp, w_imp, w_in_b - 1, h_in_b - 1)
+    assert int(got[0]) == oracle.sse_wxh(o1, W - 8, H - 8, o2, W - 8, H - 8, 8, 8, imp, w_imp, w_in_b - 1, h_in_b - 1)
+
+
+def test_sse_wxh_chroma_plane_and_errors(r, ctx, oracle):
+    rng = np.random.default_rng(31)
+    o1, d1 = twin_plane(r, oracle, ctx, 128, 96, 2, 10, rng, xpad=8, ypad=8, xdec=1, ydec=1)
+    o2, d2 = twin_plane(r, oracle, ctx, 128, 96, 2, 10, rng, xpad=8, ypad=8, xdec=1, ydec=1)
+    w_in_b, h_in_b = 64, 48  # luma 256 x 192
+    imp = (rng.random(32 * 24) * 3).astype(np.float32)
+    jobs = _rdo_jobs(r, rng, 128, 96, 300, 4, 4)
+    got = r.sse_wxh(ctx, d1, d2, jobs, 10, imp, 32, w_in_b, h_in_b)
+    for j, g in zip(jobs, got):
+        want = oracle.sse_wxh(o1, int(j["src_x"]), int(j["src_y"]), o2, int(j["rec_x"]), int(j["rec_y"]), int(j["w"]),
+                              int(j["h"]), imp, 32, w_in_b, h_in_b)
+        assert int(g) == want, j
+    with pytest.raises(r.Rav1eCudaError):  # cdef_dist is luma-only
+        r.cdef_dist_wxh(ctx, d1, d2, jobs[:1], 10)
+    with pytest.raises(r.Rav1eCudaError):  # not a multiple of MI_SIZE
+        r.sse_wxh(ctx, d1, d2, np.array([(0, 0, 0, 0, 6, 8)], dtype=r.RDO_JOB), 10)
+    with pytest.raises(r.Rav1eCudaError):  # leaves the plane
+        r.sse_wxh(ctx, d1, d2, np.array([(120, 90, 120, 90, 64, 64)], dtype=r.RDO_JOB), 10)
+    assert r.sse_wxh(ctx, d1, d2, np.zeros(0, dtype=r.RDO_JOB), 10).size == 0
+
+
+def test_tx_distortion_matches_oracle(r, ctx, oracle):
+    rng = np.random.default_rng(8)
+    L = oracle.lib()
+    for ts in range(19):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        n = 37
+        # large magnitudes: the i32 square wraps like the reference's release build
+        c = rng.integers(-(1 << 17), 1 << 17, size=(n, w * h)).astype(np.int32)
+        rc = rng.integers(-(1 << 17), 1 << 17, size=(n, coded)).astype(np.int32)
+        got = r.tx_distortion(ctx, c, rc, ts)
+        for i in range(n):
+            assert int(got[i]) == oracle.tx_dist(c[i], rc[i], ts), (ts, i)

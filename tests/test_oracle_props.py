@@ -223,3 +223,94 @@ def test_full_search_finds_shift_and_first_min(oracle):
                                       C.byref(flat.cfg), -200, 40, 28, 36, 8, 8, 32, 32, 1, 0,
                                       C.byref(pmv), 0, 1, C.byref(best), C.byref(cost))
     assert rc == -1
+
+
+# ------------------------------------------------------------- RDO distortion -----
+def _np_bias(imp, w_in_imp_b, w_in_b, h_in_b, bo_x, bo_y, wmi, hmi):
+    """compute_distortion_bias restated independently with numpy float32 scalars (src/rdo.rs:477-508)"""
+    total = np.float32(0)
+    for y in range(bo_y, min(bo_y + hmi, h_in_b)):
+        for x in range(bo_x, min(bo_x + wmi, w_in_b)):
+            total = np.float32(total + imp[y // 2 * w_in_imp_b + x // 2])
+    mean = np.float32(total / np.float32(wmi * hmi))
+    return float(np.float32(mean / np.float32(3))) + 0.65
+
+
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10), (2, 12)])
+def test_sse_wxh_and_cdef_dist_against_numpy(oracle, pb, bd):
+    rng = np.random.default_rng(900 + bd)
+    W, H = 96, 64
+    a = oracle.OPlane(W, H, 0, 0, 16, 16, pb)
+    b = oracle.OPlane(W, H, 0, 0, 16, 16, pb)
+    a.data[...] = rng.integers(0, 1 << bd, a.data.shape)
+    b.data[...] = np.clip(a.data.astype(np.int64) + rng.integers(-40, 41, a.data.shape), 0, (1 << bd) - 1)
+    w_in_b, h_in_b = W // 4, H // 4
+    w_imp = w_in_b // 2
+    imp = (rng.random(w_imp * (h_in_b // 2)) * 4).astype(np.float32)
+    for (x, y, w, h) in [(0, 0, 4, 4), (8, 4, 4, 16), (16, 8, 16, 8), (32, 0, 64, 64), (88, 56, 8, 8), (4, 4, 8, 8)]:
+        va, vb = a.visible[y:y + h, x:x + w].astype(np.int64), b.visible[y:y + h, x:x + w].astype(np.int64)
+        assert oracle.sse_wxh(a, x, y, b, x, y, w, h) == int(((va - vb) ** 2).sum())
+        bw, bh = min(w, 8), min(h, 8)
+        want = 0
+        for by in range(h // bh):
+            for bx in range(w // bw):
+                d = va[by * bh:(by + 1) * bh, bx * bw:(bx + 1) * bw] - vb[by * bh:(by + 1) * bh, bx * bw:(bx + 1) * bw]
+                bias = _np_bias(imp, w_imp, w_in_b, h_in_b, (x + bx * bw) // 4, (y + by * bh) // 4, bw // 4, bh // 4)
+                want += int(float(int((d * d).sum())) * bias)
+        assert oracle.sse_wxh(a, x, y, b, x, y, w, h, imp, w_imp, w_in_b, h_in_b) == want
+        if w % 8 == 0 and h % 8 == 0 and x % 8 == 0 and y % 8 == 0:
+            cs = bd - 8
+            want = 0
+            for by in range(h // 8):
+                for bx in range(w // 8):
+                    s = va[by * 8:by * 8 + 8, bx * 8:bx * 8 + 8]
+                    d = vb[by * 8:by * 8 + 8, bx * 8:bx * 8 + 8]
+                    ss, sd = int(s.sum()), int(d.sum())
+                    s2, d2, sdx = int((s * s).sum()), int((d * d).sum()), int((s * d).sum())
+                    svar = float(s2 - ((ss * ss + 32) >> 6))
+                    dvar = float(d2 - ((sd * sd + 32) >> 6))
+                    boost = (4033.0 / 16384.0) * (svar + dvar + float(16384 << (2 * cs))) / np.sqrt(
+                        float(16265089 << (4 * cs)) + svar * dvar)
+                    value = int(float(d2 + s2 - 2 * sdx) * float(boost) + 0.5)
+                    bias = _np_bias(imp, w_imp, w_in_b, h_in_b, (x + bx * 8) // 4, (y + by * 8) // 4, 2, 2)
+                    want += int(float(value) * bias)
+            assert oracle.cdef_dist_wxh(a, x, y, b, x, y, w, h, bd, imp, w_imp, w_in_b, h_in_b) == want
+            assert oracle.cdef_dist_wxh(a, x, y, a, x, y, w, h, bd) == 0
+
+
+def test_sse_wxh_chroma_uses_decimated_importance_blocks(oracle):
+    """4:2:0 chroma: an importance block is 4x4 chroma px and covers 2x2 MI of the frame (src/rdo.rs:296-301)"""
+    rng = np.random.default_rng(77)
+    a = oracle.OPlane(32, 32, 1, 1, 8, 8, 1)
+    b = oracle.OPlane(32, 32, 1, 1, 8, 8, 1)
+    a.data[...] = rng.integers(0, 256, a.data.shape)
+    b.data[...] = rng.integers(0, 256, b.data.shape)
+    w_in_b = h_in_b = 16
+    imp = (rng.random(8 * 8) * 2).astype(np.float32)
+    x, y, w, h = 8, 4, 8, 8  # chroma px
+    want = 0
+    for by in range(2):
+        for bx in range(2):
+            d = (a.visible[y + by * 4:y + by * 4 + 4, x + bx * 4:x + bx * 4 + 4].astype(np.int64) -
+                 b.visible[y + by * 4:y + by * 4 + 4, x + bx * 4:x + bx * 4 + 4])
+            bias = _np_bias(imp, 8, w_in_b, h_in_b, (x + bx * 4) // 2, (y + by * 4) // 2, 2, 2)
+            want += int(float(int((d * d).sum())) * bias)
+    assert oracle.sse_wxh(a, x, y, b, x, y, w, h, imp, 8, w_in_b, h_in_b) == want
+
+
+def test_tx_dist_scaling_and_coded_area(oracle):
+    rng = np.random.default_rng(5)
+    L = oracle.lib()
+    for ts in range(19):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        c = rng.integers(-20000, 20000, w * h)
+        rc = rng.integers(-20000, 20000, coded)
+        bits = 2 * (3 - ((w * h > 256) + (w * h > 1024)))
+        want = (int(((c[:coded] - rc) ** 2).sum()) + (1 << (bits - 1))) >> bits
+        assert oracle.tx_dist(c, rc, ts) == want
+    # the i32 product wraps, then sign-extends into the u64 sum (src/encoder.rs:1215-1217)
+    c = np.array([70000] + [0] * 15)
+    rc = np.array([-70000] + [0] * 15)
+    wrapped = ((140000 * 140000 + 2 ** 31) % 2 ** 32) - 2 ** 31
+    assert oracle.tx_dist(c, rc, 0) == ((wrapped % 2 ** 64) + 32) >> 6
