@@ -384,6 +384,24 @@ int r1c_subpel_refine_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane 
 int r1c_subpel_refine_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                                 const r1c_subpel_job *d_jobs, int64_t n, int bit_depth,
                                 r1c_me_result *d_results);
+/* diamond_me_search (src/me.rs:693-785) with get_best_predictor (:655-691), the
+ * search of DiamondSearch::{full_pixel_me, sub_pixel_me, me_ss2} (:391-520):
+ * the best of `n_pred` predictor MVs per job (predictors[job*n_pred + k]; pad a
+ * shorter list by repeating an entry -- ties keep the first) becomes the centre,
+ * then 4-point diamonds of radius 16 -> 8 on the full-pel path (candidate block
+ * at po + mv/8, truncating) or, with `subpixel`, 4 -> 2 (-> 1 with
+ * allow_high_precision_mv) through predict_inter.  Pattern order (1,0),(0,1),
+ * (-1,0),(0,-1) in (row, col), strict `<`, centre kept on ties.  The predictor
+ * lists themselves (get_subset_predictors, :82-174) depend on the encoder's
+ * neighbour state and are built by the caller.  results[i] is output only. */
+int r1c_diamond_search_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                             const r1c_subpel_job *jobs, int64_t n, int subpixel,
+                             const r1c_mv *predictors, int n_pred, int bit_depth,
+                             r1c_me_result *results);
+int r1c_diamond_search_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                 const r1c_subpel_job *d_jobs, int64_t n, int subpixel,
+                                 int allow_high_precision_mv, const r1c_mv *d_predictors,
+                                 int n_pred, int bit_depth, r1c_me_result *d_results);
 
 /* ------------------------------------------------------------------------
  * Whole-frame motion estimation: MotionEstimation::motion_estimation for

@@ -87,6 +87,12 @@ def lib():
         L.r1o_frame_me.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i, i, i, i, u32, u32, i, i, i, i, i,
                                    vp, i64, vp, vp]
         L.r1o_frame_me.restype = i64
+        L.r1o_fullpel_cost.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i, i, Mv, P(Mv * 2), u32, i, i,
+                                       P(i64 * 4), i]
+        L.r1o_fullpel_cost.restype = u64
+        L.r1o_diamond_search.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i, i, vp, i, P(Mv * 2), u32, i, i,
+                                         P(i64 * 4), i, i, i, P(Mv), P(u64)]
+        L.r1o_diamond_search.restype = i
         dbl = C.c_double
         L.r1o_distortion_bias.argtypes = [vp, i64, i64, i64, i64, i64, i64, i64]
         L.r1o_distortion_bias.restype = dbl
@@ -142,6 +148,20 @@ def sad(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
 def satd(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
     return lib().r1o_satd(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
                           org.px_bytes)
+
+
+def diamond_search(org: OPlane, ref: OPlane, po, blk_w, blk_h, predictors, pmv, lambda_, use_satd, allow_hp, mv_range,
+                   subpixel, bit_depth):
+    """diamond_me_search + get_best_predictor, src/me.rs:655-785 -> ((row, col), cost, iterations)"""
+    pred = np.ascontiguousarray(np.asarray(predictors, dtype=np.int16).reshape(-1, 2))  # (row, col)
+    pm = (Mv * 2)(Mv(*pmv[0]), Mv(*pmv[1]))
+    rng = (C.c_int64 * 4)(*mv_range)
+    mv, cost = Mv(0, 0), C.c_uint64(0)
+    it = lib().r1o_diamond_search(org.origin_ptr(), C.byref(org.cfg), ref.origin_ptr(), C.byref(ref.cfg), po[0], po[1],
+                                  blk_w, blk_h, _p(pred), pred.shape[0], C.byref(pm), lambda_, int(use_satd),
+                                  int(allow_hp), C.byref(rng), int(subpixel), bit_depth, org.px_bytes, C.byref(mv),
+                                  C.byref(cost))
+    return (mv.row, mv.col), cost.value, it
 
 
 def _imp(block_importances):

@@ -100,3 +100,75 @@ uint64_t r1o_subpel_cost(const void *org0, const r1o_plane_cfg *ocfg, const void
   uint32_t rate = r1 < r2 + 1 ? r1 : r2 + 1;
   return 256ull * d + (uint64_t)rate * lambda;
 }
+
+/* get_mv_rd_cost with tmp_plane_opt = None (full-pel path), src/me.rs:794-799,826-836:
+ * the reference block sits at po + mv / 8 (division truncating toward zero). */
+uint64_t r1o_fullpel_cost(const void *org0, const r1o_plane_cfg *ocfg, const void *ref0,
+                          const r1o_plane_cfg *rcfg, int64_t po_x, int64_t po_y, int blk_w,
+                          int blk_h, r1o_mv cand, const r1o_mv pmv[2], uint32_t lambda,
+                          int use_satd, int allow_hp, const int64_t range[4], int pb) {
+  if (cand.col < range[0] || cand.col > range[1]) return UINT64_MAX;
+  if (cand.row < range[2] || cand.row > range[3]) return UINT64_MAX;
+  const int64_t rx = po_x + cand.col / 8, ry = po_y + cand.row / 8;
+  if (!region_ok(rcfg, rx, ry, blk_w, blk_h)) return UINT64_MAX; /* the reference would panic */
+  const void *org = px_ptr(org0, ocfg, po_x, po_y, pb);
+  const void *rp = px_ptr(ref0, rcfg, rx, ry, pb);
+  uint32_t d = use_satd ? r1o_satd(org, ocfg->stride, rp, rcfg->stride, blk_w, blk_h, pb)
+                        : r1o_sad(org, ocfg->stride, rp, rcfg->stride, blk_w, blk_h, pb);
+  uint32_t r1 = r1o_mv_rate(cand, pmv[0], allow_hp);
+  uint32_t r2 = r1o_mv_rate(cand, pmv[1], allow_hp);
+  uint32_t rate = r1 < r2 + 1 ? r1 : r2 + 1;
+  return 256ull * d + (uint64_t)rate * lambda;
+}
+
+/* diamond_me_search, src/me.rs:693-785, with get_best_predictor :655-691.
+ * subpixel: radius 4 -> 2 (1 with high-precision MVs), candidates through predict_inter;
+ * else radius 16 -> 8 on the full-pel path.  Returns the number of diamond iterations. */
+int r1o_diamond_search(const void *org0, const r1o_plane_cfg *ocfg, const void *ref0,
+                       const r1o_plane_cfg *rcfg, int64_t po_x, int64_t po_y, int blk_w, int blk_h,
+                       const r1o_mv *predictors, int n_pred, const r1o_mv pmv[2], uint32_t lambda,
+                       int use_satd, int allow_hp, const int64_t range[4], int subpixel, int bd,
+                       int pb, r1o_mv *center_mv, uint64_t *center_cost) {
+  static const int16_t pattern[4][2] = {{1, 0}, {0, 1}, {-1, 0}, {0, -1}}; /* (row, col) */
+  int16_t radius = subpixel ? 4 : 16;
+  const int16_t radius_end = subpixel ? (allow_hp ? 1 : 2) : 8;
+#define R1O_COST(mv)                                                                                          \
+  (subpixel ? r1o_subpel_cost(org0, ocfg, ref0, rcfg, po_x, po_y, blk_w, blk_h, (mv), pmv, lambda, use_satd, \
+                              allow_hp, range, bd, pb)                                                       \
+            : r1o_fullpel_cost(org0, ocfg, ref0, rcfg, po_x, po_y, blk_w, blk_h, (mv), pmv, lambda, use_satd, \
+                               allow_hp, range, pb))
+  r1o_mv c = {0, 0};
+  uint64_t cc = UINT64_MAX;
+  for (int k = 0; k < n_pred; k++) {
+    uint64_t cost = R1O_COST(predictors[k]);
+    if (cost < cc) {
+      c = predictors[k];
+      cc = cost;
+    }
+  }
+  int iters = 0;
+  for (;;) {
+    uint64_t best = UINT64_MAX;
+    r1o_mv best_mv = {0, 0};
+    iters++;
+    for (int k = 0; k < 4; k++) {
+      r1o_mv cand = {(int16_t)(c.row + radius * pattern[k][0]), (int16_t)(c.col + radius * pattern[k][1])};
+      uint64_t cost = R1O_COST(cand);
+      if (cost < best) {
+        best = cost;
+        best_mv = cand;
+      }
+    }
+    if (cc <= best) {
+      if (radius == radius_end) break;
+      radius /= 2;
+    } else {
+      c = best_mv;
+      cc = best;
+    }
+  }
+#undef R1O_COST
+  *center_mv = c;
+  *center_cost = cc;
+  return iters;
+}

@@ -392,6 +392,17 @@ def subpel_refine_batch(ctx, plane_org, plane_ref, jobs, results, bit_depth):
     return results
 
 
+def diamond_search_batch(ctx, plane_org, plane_ref, jobs, predictors, bit_depth, subpixel=False):
+    """diamond_me_search + get_best_predictor (src/me.rs:655-785) for every SUBPEL_JOB;
+    predictors: MV array (n, n_pred).  Returns ME_RESULT (centre MV, cost) per job."""
+    jobs = _arr(jobs, SUBPEL_JOB)
+    predictors = _arr(predictors, MV).reshape(jobs.size, -1)
+    out = np.zeros(jobs.size, dtype=ME_RESULT)
+    ctx.check(ctx.lib.r1c_diamond_search_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs), jobs.size, int(subpixel),
+                                               _p(predictors), predictors.shape[1], bit_depth, _p(out)))
+    return out
+
+
 # ----------------------------------------------------- whole-frame motion search --
 ALL_SIZES_TO_64 = sum(1 << b for b in range(22) if b not in (13, 14, 15))
 

@@ -163,6 +163,8 @@ SIGNATURES = {
     "r1c_subpel_cost_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _vp]),
     "r1c_subpel_refine_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_subpel_refine_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
+    "r1c_diamond_search_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _i, _i, _vp]),
+    "r1c_diamond_search_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _vp, _i, _i, _vp]),
     "r1c_frame_me_count": (_i64, [_P(FrameMeParams)]),
     "r1c_frame_me_offset": (_i64, [_P(FrameMeParams), _i, _P(C.c_int32), _P(C.c_int32)]),
     "r1c_frame_me": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),

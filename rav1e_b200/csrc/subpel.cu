@@ -28,6 +28,7 @@ struct SubArgs {
   const r1c_subpel_job *jobs;
   long long n;
   int ncand;
+  int ncand_alloc;             // candidates the dense buffer was laid out for (>= ncand)
   const r1c_mv *cand;          // n * ncand
   const long long *area_off;   // exclusive prefix sum of block areas, n + 1 entries
   r1c_mc_job *mcjobs;          // n * ncand
@@ -277,6 +278,194 @@ int refine_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r
   return R1C_OK;
 }
 
+// ---- diamond_me_search (src/me.rs:693-785) -----------------------------------------
+// State per job: results[i] = (center_mv, center_mv_cost), radius[i] (0 = finished).
+// One iteration = candidate generation, the cost kernels above, and the pick rule;
+// the host reads back one counter per iteration (jobs still searching).
+
+// get_mv_rd_cost without a temp plane (src/me.rs:826-836): block at po + mv / 8, truncating
+template <int PB>
+__global__ void __launch_bounds__(256) fullpel_cost_kernel(SubArgs a, const int *radius) {
+  const int lane = threadIdx.x & 31;
+  const long long p = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (p >= a.n * a.ncand) return;
+  const long long i = p / a.ncand;
+  unsigned long long cost = ~0ull;
+  if (!radius || radius[i] != 0) {
+    const r1c_subpel_job j = a.jobs[i];
+    const r1c_mv mv = a.cand[p];
+    const int bw = blk_w_of(j.bsize), bh = blk_h_of(j.bsize);
+    const int rx = j.po_x + mv.col / 8, ry = j.po_y + mv.row / 8;
+    const bool inside = rx >= -a.ref.xorigin && ry >= -a.ref.yorigin && a.ref.xorigin + rx + bw <= a.ref.alloc_w &&
+                        a.ref.yorigin + ry + bh <= a.ref.alloc_h;
+    if (mv_in_range(j, mv) && inside) {
+      const uint8_t *po = (const uint8_t *)a.org.p0 + ((long long)j.po_y * a.org.stride + j.po_x) * PB;
+      const uint8_t *pr = (const uint8_t *)a.ref.p0 + ((long long)ry * a.ref.stride + rx) * PB;
+      const uint32_t d = j.use_satd ? distdev::satd_block_warp<PB>(po, a.org.stride * PB, pr, a.ref.stride * PB, bw, bh, lane)
+                                    : distdev::sad_warp<PB>(po, a.org.stride * PB, pr, a.ref.stride * PB, bw, bh, lane);
+      const uint32_t rate = me::mv_rate2(mv, j.pmv[0], j.pmv[1], j.allow_high_precision_mv);
+      cost = 256ull * d + (unsigned long long)rate * j.lambda;
+    }
+  }
+  if (lane == 0) a.costs[p] = cost;
+}
+
+// the 4 diamond candidates around the centre, pattern order (1,0),(0,1),(-1,0),(0,-1) in (row, col)
+__global__ void gen_diamond_kernel(SubArgs a, r1c_mv *cand_out, const int *radius, int subpixel) {
+  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= a.n * 4) return;
+  const long long i = p >> 2;
+  const int k = (int)(p & 3);
+  const int pr = k == 0 ? 1 : (k == 2 ? -1 : 0), pc = k == 1 ? 1 : (k == 3 ? -1 : 0);
+  const int rad = radius[i];
+  const r1c_subpel_job j = a.jobs[i];
+  const r1c_mv c0 = a.results[i].mv;
+  r1c_mv mv;
+  mv.row = (int16_t)(c0.row + rad * pr);
+  mv.col = (int16_t)(c0.col + rad * pc);
+  cand_out[p] = mv;
+  if (subpixel) {
+    const long long area = a.area_off[i + 1] - a.area_off[i];
+    r1c_mc_job m = make_mc_job(a.ref, j, mv, a.area_off[i] * a.ncand_alloc + k * area, true);
+    const bool valid = rad != 0 && mv_in_range(j, mv) && mc_footprint_ok(a.ref, m, blk_w_of(j.bsize), blk_h_of(j.bsize));
+    if (!valid) {
+      m.w = 0;
+      m.h = 0;
+    }
+    a.mcjobs[p] = m;
+  }
+}
+
+// the predictor list as put_8tap jobs (sub-pel get_best_predictor)
+__global__ void gen_pred_jobs_kernel(SubArgs a) {
+  const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= a.n * a.ncand) return;
+  const long long i = p / a.ncand;
+  const int k = (int)(p - i * a.ncand);
+  const r1c_subpel_job j = a.jobs[i];
+  const r1c_mv mv = a.cand[p];
+  const long long area = a.area_off[i + 1] - a.area_off[i];
+  r1c_mc_job m = make_mc_job(a.ref, j, mv, a.area_off[i] * a.ncand_alloc + k * area, true);
+  if (!(mv_in_range(j, mv) && mc_footprint_ok(a.ref, m, blk_w_of(j.bsize), blk_h_of(j.bsize)))) {
+    m.w = 0;
+    m.h = 0;
+  }
+  a.mcjobs[p] = m;
+}
+
+// get_best_predictor, src/me.rs:655-691: first strict minimum over the predictors
+__global__ void best_predictor_kernel(SubArgs a, int *radius, int radius0) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  r1c_me_result r;
+  r.mv.row = 0;
+  r.mv.col = 0;
+  r.reserved = 0;
+  r.cost = ~0ull;
+  for (int k = 0; k < a.ncand; k++) {
+    const unsigned long long c = a.costs[i * a.ncand + k];
+    if (c < r.cost) {
+      r.cost = c;
+      r.mv = a.cand[i * a.ncand + k];
+    }
+  }
+  a.results[i] = r;
+  radius[i] = radius0;
+}
+
+// src/me.rs:737-781: best of the 4 (strict <), then keep / shrink / move
+__global__ void diamond_pick_kernel(SubArgs a, const r1c_mv *cand, int *radius, int radius_end, int *active) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  int rad = radius[i];
+  if (rad == 0) return;
+  unsigned long long best = ~0ull;
+  r1c_mv best_mv;
+  best_mv.row = 0;
+  best_mv.col = 0;
+  for (int k = 0; k < 4; k++) {
+    const unsigned long long c = a.costs[i * 4 + k];
+    if (c < best) {
+      best = c;
+      best_mv = cand[i * 4 + k];
+    }
+  }
+  r1c_me_result r = a.results[i];
+  if (r.cost <= best) {
+    rad = rad == radius_end ? 0 : rad / 2;
+    radius[i] = rad;
+  } else {
+    r.mv = best_mv;
+    r.cost = best;
+    a.results[i] = r;
+  }
+  if (rad != 0) atomicAdd(active, 1);
+}
+
+int run_fullpel_costs(r1c_ctx *ctx, const r1c_plane *ref, SubArgs &a, const int *radius) {
+  const unsigned grid = (unsigned)((a.n * a.ncand + 7) / 8);
+  r1c_prof_begin(ctx, R1C_PROF_SUBPEL_COST);
+  if (ref->px_bytes == 1) fullpel_cost_kernel<1><<<grid, 256, 0, ctx->stream>>>(a, radius);
+  else fullpel_cost_kernel<2><<<grid, 256, 0, ctx->stream>>>(a, radius);
+  r1c_prof_end(ctx, R1C_PROF_SUBPEL_COST);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
+
+// d_pred: n * n_pred predictors; d_results: out
+int diamond_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_subpel_job *d_jobs, int64_t n,
+                int subpixel, int allow_hp, const r1c_mv *d_pred, int n_pred, int bit_depth, r1c_me_result *d_results) {
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  SubArgs a = {};
+  a.org = make_view(org);
+  a.ref = make_view(ref);
+  a.jobs = d_jobs;
+  a.n = n;
+  a.results = d_results;
+  a.bit_depth = bit_depth;
+  const int nalloc = n_pred > 4 ? n_pred : 4;
+  int rc = prepare(ctx, a, nalloc);
+  if (rc) return rc;
+  a.ncand_alloc = nalloc;
+  void *d_cand, *d_state;
+  if ((rc = r1c_scratch_dev(ctx, 11, (size_t)n * 4 * sizeof(r1c_mv), &d_cand))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 12, (size_t)(n + 1) * sizeof(int), &d_state))) return rc;
+  int *radius = (int *)d_state, *active = (int *)d_state + n;
+  // get_best_predictor
+  a.cand = d_pred;
+  a.ncand = n_pred;
+  if (subpixel) {
+    gen_pred_jobs_kernel<<<(unsigned)((n * n_pred + 255) / 256), 256, 0, ctx->stream>>>(a);
+    R1C_LAUNCH_CHECK(ctx);
+    if ((rc = run_costs(ctx, ref, a))) return rc;
+  } else if ((rc = run_fullpel_costs(ctx, ref, a, nullptr))) {
+    return rc;
+  }
+  const int radius0 = subpixel ? 4 : 16, radius_end = subpixel ? (allow_hp ? 1 : 2) : 8;
+  best_predictor_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a, radius, radius0);
+  R1C_LAUNCH_CHECK(ctx);
+  a.cand = (const r1c_mv *)d_cand;
+  a.ncand = 4;
+  int *h_active;
+  if ((rc = r1c_stage_host(ctx, 3, sizeof(int), (void **)&h_active))) return rc;
+  for (int it = 0;; it++) {
+    R1C_REQUIRE(ctx, it < 100000, R1C_ERR_CUDA, "diamond search did not converge");
+    R1C_CUDA(ctx, cudaMemsetAsync(active, 0, sizeof(int), ctx->stream));
+    gen_diamond_kernel<<<(unsigned)((n * 4 + 255) / 256), 256, 0, ctx->stream>>>(a, (r1c_mv *)d_cand, radius, subpixel);
+    R1C_LAUNCH_CHECK(ctx);
+    if (subpixel) rc = run_costs(ctx, ref, a);
+    else rc = run_fullpel_costs(ctx, ref, a, radius);
+    if (rc) return rc;
+    diamond_pick_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(a, (const r1c_mv *)d_cand, radius, radius_end, active);
+    R1C_LAUNCH_CHECK(ctx);
+    R1C_CUDA(ctx, cudaMemcpyAsync(h_active, active, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (*h_active == 0) break;
+  }
+  return R1C_OK;
+}
+
 int validate_jobs(r1c_ctx *ctx, const r1c_plane *org, const r1c_subpel_job *jobs, int64_t n, long long *total_px,
                   int *hp) {
   long long t = 0;
@@ -372,6 +561,48 @@ extern "C" int r1c_subpel_refine_batch(r1c_ctx *ctx, const r1c_plane *org, const
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
   R1C_CUDA(ctx, cudaMemcpyAsync(d_res, h_res, rb, cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = refine_dev(ctx, org, ref, (const r1c_subpel_job *)d_jobs, n, bit_depth, (r1c_me_result *)d_res, hp))) return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(h_res, d_res, rb, cudaMemcpyDeviceToHost, ctx->stream));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(results, h_res, rb);
+  return R1C_OK;
+}
+
+extern "C" int r1c_diamond_search_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                            const r1c_subpel_job *d_jobs, int64_t n, int subpixel,
+                                            int allow_high_precision_mv, const r1c_mv *d_predictors, int n_pred,
+                                            int bit_depth, r1c_me_result *d_results) {
+  int rc = check_sub(ctx, org, ref, bit_depth, n);
+  if (rc) return rc;
+  R1C_REQUIRE(ctx, n_pred >= 1 && n_pred <= 64 && (n == 0 || (d_jobs && d_predictors && d_results)), R1C_ERR_ARG, "bad predictor list");
+  return diamond_dev(ctx, org, ref, d_jobs, n, subpixel != 0, allow_high_precision_mv != 0, d_predictors, n_pred, bit_depth, d_results);
+}
+
+extern "C" int r1c_diamond_search_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                        const r1c_subpel_job *jobs, int64_t n, int subpixel, const r1c_mv *predictors,
+                                        int n_pred, int bit_depth, r1c_me_result *results) {
+  int rc = check_sub(ctx, org, ref, bit_depth, n);
+  if (rc) return rc;
+  R1C_REQUIRE(ctx, n_pred >= 1 && n_pred <= 64 && (n == 0 || (jobs && predictors && results)), R1C_ERR_ARG, "bad predictor list");
+  if (n == 0) return R1C_OK;
+  long long total_px;
+  int hp;
+  if ((rc = validate_jobs(ctx, org, jobs, n, &total_px, &hp))) return rc;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  void *h_jobs, *h_pred, *h_res, *d_jobs, *d_pred, *d_res;
+  const size_t jb = (size_t)n * sizeof(r1c_subpel_job), pb = (size_t)n * n_pred * sizeof(r1c_mv), rb = (size_t)n * sizeof(r1c_me_result);
+  if ((rc = r1c_stage_host(ctx, 0, jb, &h_jobs))) return rc;
+  if ((rc = r1c_stage_host(ctx, 1, pb, &h_pred))) return rc;
+  if ((rc = r1c_stage_host(ctx, 2, rb, &h_res))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 0, jb, &d_jobs))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 1, pb, &d_pred))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 13, rb, &d_res))) return rc;
+  memcpy(h_jobs, jobs, jb);
+  memcpy(h_pred, predictors, pb);
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_pred, h_pred, pb, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = diamond_dev(ctx, org, ref, (const r1c_subpel_job *)d_jobs, n, subpixel != 0, hp, (const r1c_mv *)d_pred, n_pred, bit_depth,
+                        (r1c_me_result *)d_res)))
+    return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_res, d_res, rb, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(results, h_res, rb);

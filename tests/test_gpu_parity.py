@@ -616,3 +616,51 @@ def test_tx_distortion_matches_oracle(r, ctx, oracle):
         got = r.tx_distortion(ctx, c, rc, ts)
         for i in range(n):
             assert int(got[i]) == oracle.tx_dist(c[i], rc[i], ts), (ts, i)
+
+
+# ---------------------------------------------------------- diamond search -----
+@pytest.mark.parametrize("pb,bd,subpixel,use_satd,hp", [(1, 8, 0, 0, 0), (1, 8, 1, 1, 0), (2, 10, 0, 1, 0), (2, 10, 1, 0, 1),
+                                                         (2, 12, 1, 1, 1)])
+def test_diamond_search_matches_oracle(r, ctx, oracle, pb, bd, subpixel, use_satd, hp):
+    """diamond_me_search + get_best_predictor (src/me.rs:655-785): full-pel (radius 16 -> 8) and sub-pel
+    (4 -> 2 / 1) variants, predictor lists with out-of-range entries and duplicates"""
+    rng = np.random.default_rng(1500 + bd + 2 * subpixel + use_satd)
+    W, H = 192, 128
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    noisy = np.roll(o_ref.visible, (5, -9), axis=(0, 1)).astype(np.int64) + rng.integers(-2, 3, size=(H, W))
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.clip(noisy, 0, (1 << bd) - 1))
+    L = oracle.lib()
+    n, n_pred = 80, 5
+    jobs = np.zeros(n, dtype=r.SUBPEL_JOB)
+    pred = np.zeros((n, n_pred), dtype=r.MV)
+    for i in range(n):
+        b = int(rng.choice([0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 16, 17, 18, 19, 20, 21]))
+        bw, bh = L.r1o_block_width(b), L.r1o_block_height(b)
+        po = (int(rng.integers(0, (W - bw) // 4 + 1)) * 4, int(rng.integers(0, (H - bh) // 4 + 1)) * 4)
+        rngv = (C.c_int64 * 4)()
+        L.r1o_mv_range(W // 4, H // 4, po[0] // 4, po[1] // 4, bw, bh, C.byref(rngv))
+        jobs[i]["po_x"], jobs[i]["po_y"], jobs[i]["bsize"] = po[0], po[1], b
+        jobs[i]["lambda_"] = int(rng.choice([0, 40, 900]))
+        jobs[i]["pmv"][0] = (int(rng.integers(-30, 30)), int(rng.integers(-30, 30)))
+        jobs[i]["pmv"][1] = (int(rng.integers(-30, 30)), int(rng.integers(-30, 30)))
+        jobs[i]["mvx_min"], jobs[i]["mvx_max"], jobs[i]["mvy_min"], jobs[i]["mvy_max"] = tuple(rngv)
+        jobs[i]["use_satd"], jobs[i]["allow_high_precision_mv"] = use_satd, hp
+        pred[i, 0] = (0, 0)
+        for k in range(1, n_pred - 1):  # sub-pel valued predictors also reach the full-pel path (mv / 8 truncates)
+            pred[i, k] = (int(rng.integers(-80, 81)), int(rng.integers(-80, 81)))
+        pred[i, n_pred - 1] = pred[i, 1]  # padding by repetition
+        if i % 7 == 0:
+            pred[i, 2] = (int(rngv[3]) + 8, 0)  # out of the legal range: u64::MAX, never chosen
+    got = r.diamond_search_batch(ctx, d_org, d_ref, jobs, pred, bd, subpixel=bool(subpixel))
+    moved = 0
+    for i in range(n):
+        j = jobs[i]
+        bw, bh = L.r1o_block_width(int(j["bsize"])), L.r1o_block_height(int(j["bsize"]))
+        mv, cost, iters = oracle.diamond_search(
+            o_org, o_ref, (int(j["po_x"]), int(j["po_y"])), bw, bh, [(int(p["row"]), int(p["col"])) for p in pred[i]],
+            [(int(j["pmv"][0]["row"]), int(j["pmv"][0]["col"])), (int(j["pmv"][1]["row"]), int(j["pmv"][1]["col"]))],
+            int(j["lambda_"]), use_satd, hp, (int(j["mvx_min"]), int(j["mvx_max"]), int(j["mvy_min"]), int(j["mvy_max"])),
+            subpixel, bd)
+        assert ((int(got[i]["mv"]["row"]), int(got[i]["mv"]["col"])), int(got[i]["cost"])) == (mv, cost), i
+        moved += iters > (3 if subpixel and hp else 2)
+    assert moved > n // 4  # the search really walks (not only the shrink steps)

@@ -314,3 +314,30 @@ def test_tx_dist_scaling_and_coded_area(oracle):
     rc = np.array([-70000] + [0] * 15)
     wrapped = ((140000 * 140000 + 2 ** 31) % 2 ** 32) - 2 ** 31
     assert oracle.tx_dist(c, rc, 0) == ((wrapped % 2 ** 64) + 32) >> 6
+
+
+def test_diamond_search_walks_to_the_shift(oracle):
+    """diamond_me_search (src/me.rs:693-785): on a smooth plane shifted by (+16, -24) px the full-pel diamond
+    started at (0, 0) ends on the true shift; the sub-pel stage then stays there (cost 0 with lambda 0)"""
+    rng = np.random.default_rng(3)
+    W, H = 192, 128
+    yy, xx = np.mgrid[0:H, 0:W]
+    v = np.rint(127 + 60 * np.sin(2 * np.pi * xx / 300) + 60 * np.sin(2 * np.pi * yy / 260) + rng.integers(0, 2, size=(H, W)))
+    ref = oracle.OPlane(W, H, 0, 0, 88, 88, 1)
+    ref.visible[...] = v.astype(np.uint8)
+    ref.pad()
+    org = oracle.OPlane(W, H, 0, 0, 88, 88, 1)
+    org.visible[...] = np.roll(ref.visible, (-16, 24), axis=(0, 1))  # org(y, x) = ref(y + 16, x - 24)
+    org.pad()
+    mv_range = (-8 * 64, 8 * 64, -8 * 64, 8 * 64)
+    pmv = [(0, 0), (0, 0)]
+    mv, cost, iters = oracle.diamond_search(org, ref, (64, 48), 32, 32, [(0, 0)], pmv, 0, False, False, mv_range, False, 8)
+    start = oracle.diamond_search(org, ref, (64, 48), 32, 32, [(0, 0)], pmv, 0, False, False, (0, 0, 0, 0), False, 8)[1]
+    # a 4-neighbour descent may stop one pixel off on a diagonal valley
+    assert abs(mv[0] - 16 * 8) <= 8 and abs(mv[1] + 24 * 8) <= 8 and cost < start // 10 and iters > 3
+    mv2, cost2, _ = oracle.diamond_search(org, ref, (64, 48), 32, 32, [mv, (16 * 8, -24 * 8)], pmv, 0, True, False, mv_range,
+                                          True, 8)
+    assert mv2 == (16 * 8, -24 * 8) and cost2 == 0  # get_best_predictor picks the exact shift, the diamond keeps it
+    # every predictor outside the range: the reference would assert; the restatement returns u64::MAX
+    mv3, cost3, _ = oracle.diamond_search(org, ref, (64, 48), 32, 32, [(9999, 0)], pmv, 0, False, False, (-8, 8, -8, 8), False, 8)
+    assert cost3 >= (1 << 64) - 1 or mv3 != (9999, 0)
