@@ -29,6 +29,8 @@ import time
 
 import numpy as np
 
+import bench_kernels
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -156,6 +158,9 @@ def run_cpu(seconds_target, steps=1, warmup=0):
     o_ref.pad()
     mask, layout = oracle_layout(r1o)
     rng = np.random.default_rng(7)
+    # all the host cores this process may use (torchrun exports OMP_NUM_THREADS=1: override it)
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    r1o.lib().r1o_set_num_threads(avail)
     cores = r1o.lib().r1o_num_threads()
     # calibrate on a tiny sample, then size the sample for the time target
     frac = 1.0 / 4000
@@ -184,7 +189,7 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    v, cores, sample, ms = run_cpu(6.0, steps=args.steps, warmup=min(args.warmup, 1))
+    v, cores, sample, ms = run_cpu(10.0, steps=args.steps, warmup=min(args.warmup, 1))
     line = {
         "impl": "reference", "metric": "Mpix/s", "value": v, "unit": "Mpix/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -262,7 +267,7 @@ def main():
     n_res = r.frame_me_count(params)
     d_res = torch.empty(n_res * 16, dtype=torch.uint8, device="cuda")
     h_res = np.zeros(n_res, dtype=r.ME_RESULT)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    flush = torch.zeros(512 << 20, dtype=torch.uint8, device="cuda")  # each half > 126 MB L2
 
     def step_dev():
         ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, d_res.data_ptr()))
@@ -285,7 +290,7 @@ def main():
         barrier()
         for a, b in evs:
             with torch.cuda.stream(ext):
-                flush.zero_()
+                bench_kernels.flush_l2(torch, flush)
                 a.record(ext)
             fn()
             b.record(ext)
@@ -308,7 +313,7 @@ def main():
     ms_total = timed(step_dev, K)
     launches = ctx.launches - l0
     prof = {}
-    for name, slot in (("me_sb_kernel", 0), ("subpel_mc", 1), ("subpel_cost", 2)):
+    for name, slot in (("me_sb2_kernel", 0), ("subpel_mc_generic", 1), ("me_refine_kernel", 2)):
         ms, n = C.c_double(), C.c_int64()
         ctx.check(lib.r1c_profile_read(ctx.h, slot, C.byref(ms), C.byref(n)))
         prof[name] = (ms.value, n.value)
@@ -328,29 +333,39 @@ def main():
     if rank == 0:
         ipeak, ipeak_how, ipk = int_peak()
         hpeak, hpeak_how = hbm_peak()
-        sb_ms = prof["me_sb_kernel"][0] / max(1, prof["me_sb_kernel"][1])
+        sb_ms = prof["me_sb2_kernel"][0] / max(1, prof["me_sb2_kernel"][1])
         n_sb = ((W + 63) // 64) * ((H + 63) // 64)
         win = (64 + 2 * RANGE) ** 2 + 64 * 64
         alg_bytes = n_sb * (win * PB + 849 * 16)  # window + org region per superblock, results out
         achieved = ALG_INT_OPS / (sb_ms / 1e3) / 1e9  # G int-ops/s
-        roof = {"bound": "int32_alu", "kernel": "me_sb_kernel<1>", "achieved": achieved, "peak": ipeak,
+        roof = {"bound": "int32_alu", "kernel": "me_sb2_kernel<48> (superblock full search, every size from one 4x4 SAD layer)", "achieved": achieved, "peak": ipeak,
                 "unit": "Gop/s", "frac": achieved / ipeak, "traffic": None,
                 "peak_source": ipeak_how,
                 "alg_ops_per_launch": ALG_INT_OPS, "ms_per_launch": sb_ms,
-                "share_of_step": prof["me_sb_kernel"][0] / ms_total,
+                "share_of_step": prof["me_sb2_kernel"][0] / ms_total,
                 "hbm": {"achieved": alg_bytes / (sb_ms / 1e3) / 1e9, "peak": hpeak, "unit": "GB/s",
                         "frac": alg_bytes / (sb_ms / 1e3) / 1e9 / hpeak, "alg_bytes_per_launch": alg_bytes,
                         "peak_source": hpeak_how},
                 "packed_simd": {"vabsdiff4_peak_Ginstr_s": ipk.get("vabsdiff4_acc"),
                                 "note": "1 VABSDIFF4.ACC = 8 byte-ops; packed peak = 8 x this"},
                 "other_kernels_ms_per_step": {k: v[0] / K for k, v in prof.items()}}
+        # second kernel of the step: fused sub-pel tail.  Integer work per pixel of every block: SATD re-evaluation
+        # (1 diff + 6 Hadamard + 2 abs/add = 9) + 24 candidates x (8 + 8 filter MACs + 9) = 609 lane-ops
+        rf_ms = prof["me_refine_kernel"][0] / max(1, prof["me_refine_kernel"][1])
+        rf_ops = 19 * W * H * (9 + 24 * 25)
+        if rf_ms > 0:
+            roof["me_refine_kernel"] = {"bound": "int32_alu", "achieved": rf_ops / (rf_ms / 1e3) / 1e9, "peak": ipeak,
+                                        "unit": "Gop/s", "frac": rf_ops / (rf_ms / 1e3) / 1e9 / ipeak,
+                                        "alg_ops_per_launch": rf_ops, "ms_per_launch": rf_ms,
+                                        "share_of_step": prof["me_refine_kernel"][0] / ms_total,
+                                        "note": "MACs counted as one op each; the kernel issues them as DP4A (4 MACs)"}
         line = {
             "metric": "Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K, "warmup": W_,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
             "config": {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE,
                        "lambda": LAMBDA, "blocks_per_frame": int(n_res),
-                       "l2": "flushed between steps (256 MiB memset, untimed)",
+                       "l2": "flushed between steps (256 MiB written, then 256 MiB read back, untimed)",
                        "sharding": "one frame pair per GPU, no collective"},
             "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / K,
@@ -364,7 +379,6 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample}
         if world == 1 and not args.no_extras:
             try:
-                import bench_kernels
                 line["kernels"] = bench_kernels.run(ctx, r, torch, ext, flush)
             except Exception as e:  # the headline line must still print
                 line["kernels"] = {"error": repr(e)}

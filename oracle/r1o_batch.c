@@ -8,6 +8,8 @@
 #include <omp.h>
 
 int r1o_num_threads(void) { return omp_get_max_threads(); }
+/* launchers such as torchrun export OMP_NUM_THREADS=1; the timed CPU baseline asks for the cores explicitly */
+void r1o_set_num_threads(int n) { omp_set_num_threads(n > 0 ? n : omp_get_num_procs()); }
 
 /* jobs: n x {org_x, org_y, ref_x, ref_y, bsize} int32 */
 void r1o_dist_batch(int use_satd, const void *org0, const r1o_plane_cfg *ocfg, const void *ref0,

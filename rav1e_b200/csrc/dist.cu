@@ -29,40 +29,127 @@ __device__ __forceinline__ bool job_in_bounds(const PlaneView &v, int x, int y, 
          v.yorigin + y + h <= v.alloc_h;
 }
 
-template <int PB>
-__global__ void __launch_bounds__(256) sad_kernel(DistArgs a) {
-  const int lane = threadIdx.x & 31;
-  long long job = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+// ---- lane-per-tile kernels ------------------------------------------------------------
+// A lane owns whole S x S tiles (S = 4 when the block has a side of 4, else 8): it loads
+// the S rows of both planes with word loads, and for SATD keeps the S*S differences in
+// registers, where the 2-D Hadamard needs no shuffles (6 add/sub per pixel).  G lanes
+// share a block and stride over its tiles; G is picked from the length of the job list
+// (long lists = small blocks = one lane per block, so a warp works on 32 blocks and the
+// per-block set-up is paid once per warp instead of once per 64 pixels).
+
+template <int PB, int S, bool VEC>
+__device__ __forceinline__ uint32_t tile_sad(const uint8_t *po, int so, const uint8_t *pr, int sr) {
+  constexpr int NW = S * PB / 4;
+  uint32_t acc = 0;
+#pragma unroll
+  for (int r = 0; r < S; r++) {
+    uint32_t x[NW], y[NW];
+    ld_row<NW, VEC>(po + r * so, x);
+    ld_row<NW, VEC>(pr + r * sr, y);
+#pragma unroll
+    for (int i = 0; i < NW; i++) {
+      if (PB == 1) {
+        acc = sad4_acc(x[i], y[i], acc);
+      } else {
+        acc = absdiff_acc(x[i] & 0xffffu, y[i] & 0xffffu, acc);
+        acc = absdiff_acc(x[i] >> 16, y[i] >> 16, acc);
+      }
+    }
+  }
+  return acc;
+}
+
+template <int PB, int S, bool VEC>
+__device__ __forceinline__ uint32_t tile_satd(const uint8_t *po, int so, const uint8_t *pr, int sr) {
+  int d[S][S];
+#pragma unroll
+  for (int r = 0; r < S; r++) {
+    load_diff_row<PB, S, VEC>(po + r * so, pr + r * sr, d[r]);
+    hadamard_regs<S>(d[r]);  // horizontal
+  }
+#pragma unroll
+  for (int m = 1; m < S; m <<= 1)  // vertical
+#pragma unroll
+    for (int r = 0; r < S; r++)
+      if ((r & m) == 0) {
+#pragma unroll
+        for (int c = 0; c < S; c++) {
+          const int u = d[r][c], v = d[r | m][c];
+          d[r][c] = u + v;
+          d[r | m][c] = u - v;
+        }
+      }
+  uint32_t acc = 0;
+#pragma unroll
+  for (int r = 0; r < S; r++)
+#pragma unroll
+    for (int c = 0; c < S; c++) acc += (uint32_t)abs(d[r][c]);
+  return acc;
+}
+
+template <int PB, int G, int SATD, bool VEC>
+__global__ void __launch_bounds__(128) dist_kernel(DistArgs a) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long job = gid / G;
+  const int sub = (int)(gid % G);
+  const unsigned mask = G == 32 ? 0xffffffffu : (G == 1 ? 0u : (((1u << G) - 1u) << ((threadIdx.x & 31) & ~(G - 1))));
   if (job >= a.n) return;
   const r1c_dist_job j = a.jobs[job];
   const int w = blk_w_of(j.bsize), h = blk_h_of(j.bsize);
   if (!job_in_bounds(a.org, j.org_x, j.org_y, w, h) || !job_in_bounds(a.ref, j.ref_x, j.ref_y, w, h)) {
-    if (lane == 0) a.out[job] = 0xFFFFFFFFu;
+    if (sub == 0) a.out[job] = 0xFFFFFFFFu;
     return;
   }
   const uint8_t *po = (const uint8_t *)a.org.p0 + ((long long)j.org_y * a.org.stride + j.org_x) * PB;
   const uint8_t *pr = (const uint8_t *)a.ref.p0 + ((long long)j.ref_y * a.ref.stride + j.ref_x) * PB;
   const int so = a.org.stride * PB, sr = a.ref.stride * PB;
-  const uint32_t acc = sad_warp<PB>(po, so, pr, sr, w, h, lane);
-  if (lane == 0) a.out[job] = acc;
+  const bool small = w == 4 || h == 4;  // get_satd_ref's tile rule (src/dist.rs:287); SAD uses the same tiling
+  const int ls = small ? 2 : 3;
+  const int tx = w >> ls, ntiles = tx * (h >> ls);
+  unsigned long long acc = 0;  // 256 tiles x 8*8*64*4095 exceeds u32
+  for (int t = sub; t < ntiles; t += G) {
+    const int ty = t / tx, txi = t - ty * tx;
+    const uint8_t *o = po + (long long)(ty << ls) * so + (txi << ls) * PB;
+    const uint8_t *r = pr + (long long)(ty << ls) * sr + (txi << ls) * PB;
+    if (small) acc += SATD ? tile_satd<PB, 4, VEC>(o, so, r, sr) : tile_sad<PB, 4, VEC>(o, so, r, sr);
+    else acc += SATD ? tile_satd<PB, 8, VEC>(o, so, r, sr) : tile_sad<PB, 8, VEC>(o, so, r, sr);
+  }
+  if (G > 1) {
+#pragma unroll
+    for (int m = G >> 1; m; m >>= 1) acc += __shfl_xor_sync(mask, acc, m);
+  }
+  if (sub == 0) a.out[job] = SATD ? (uint32_t)((acc + ((1ull << ls) >> 1)) >> ls) : (uint32_t)acc;
+}
+
+template <int PB, int G>
+void launch_dist_g(r1c_ctx *ctx, int use_satd, bool vec, const DistArgs &a) {
+  const unsigned grid = (unsigned)((a.n * G + 127) / 128);
+  if (vec) {
+    if (use_satd) dist_kernel<PB, G, 1, true><<<grid, 128, 0, ctx->stream>>>(a);
+    else dist_kernel<PB, G, 0, true><<<grid, 128, 0, ctx->stream>>>(a);
+  } else {
+    if (use_satd) dist_kernel<PB, G, 1, false><<<grid, 128, 0, ctx->stream>>>(a);
+    else dist_kernel<PB, G, 0, false><<<grid, 128, 0, ctx->stream>>>(a);
+  }
 }
 
 template <int PB>
-__global__ void __launch_bounds__(256) satd_kernel(DistArgs a) {
-  const int lane = threadIdx.x & 31;
-  long long job = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (job >= a.n) return;
-  const r1c_dist_job j = a.jobs[job];
-  const int w = blk_w_of(j.bsize), h = blk_h_of(j.bsize);
-  if (!job_in_bounds(a.org, j.org_x, j.org_y, w, h) || !job_in_bounds(a.ref, j.ref_x, j.ref_y, w, h)) {
-    if (lane == 0) a.out[job] = 0xFFFFFFFFu;
-    return;
-  }
-  const uint8_t *po = (const uint8_t *)a.org.p0 + ((long long)j.org_y * a.org.stride + j.org_x) * PB;
-  const uint8_t *pr = (const uint8_t *)a.ref.p0 + ((long long)j.ref_y * a.ref.stride + j.ref_x) * PB;
-  const int so = a.org.stride * PB, sr = a.ref.stride * PB;
-  const uint32_t v = satd_block_warp<PB>(po, so, pr, sr, w, h, lane);
-  if (lane == 0) a.out[job] = v;
+void launch_dist_pb(r1c_ctx *ctx, int use_satd, bool vec, const DistArgs &a) {
+  // lanes per block from the list length: enough lanes to fill the GPU (~150 K threads), and a long
+  // list means small blocks (a frame tiled by 8x8 has >= 30 K of them), which one lane handles whole
+  const long long want = (long long)ctx->sm_count * 1024 / (a.n > 0 ? a.n : 1);
+  if (want < 2) launch_dist_g<PB, 1>(ctx, use_satd, vec, a);
+  else if (want < 4) launch_dist_g<PB, 2>(ctx, use_satd, vec, a);
+  else if (want < 8) launch_dist_g<PB, 4>(ctx, use_satd, vec, a);
+  else if (want < 16) launch_dist_g<PB, 8>(ctx, use_satd, vec, a);
+  else if (want < 32) launch_dist_g<PB, 16>(ctx, use_satd, vec, a);
+  else launch_dist_g<PB, 32>(ctx, use_satd, vec, a);
+}
+
+// vector loads are legal when both allocations start and end on 16-byte boundaries
+static bool planes_vec_ok(const r1c_plane *p) {
+  const size_t bytes = (size_t)p->cfg.stride * p->cfg.alloc_height * p->px_bytes;
+  return (((uintptr_t)p->d_data) & 15) == 0 && (bytes & 15) == 0;
 }
 
 int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
@@ -74,16 +161,10 @@ int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plan
   a.jobs = d_jobs;
   a.out = d_out;
   a.n = n;
-  const int wpb = 8;
-  unsigned grid = (unsigned)((n + wpb - 1) / wpb);
   r1c_prof_begin(ctx, R1C_PROF_DIST);
-  if (org->px_bytes == 1) {
-    if (use_satd) satd_kernel<1><<<grid, wpb * 32, 0, ctx->stream>>>(a);
-    else sad_kernel<1><<<grid, wpb * 32, 0, ctx->stream>>>(a);
-  } else {
-    if (use_satd) satd_kernel<2><<<grid, wpb * 32, 0, ctx->stream>>>(a);
-    else sad_kernel<2><<<grid, wpb * 32, 0, ctx->stream>>>(a);
-  }
+  const bool vec = planes_vec_ok(org) && planes_vec_ok(ref);
+  if (org->px_bytes == 1) launch_dist_pb<1>(ctx, use_satd, vec, a);
+  else launch_dist_pb<2>(ctx, use_satd, vec, a);
   r1c_prof_end(ctx, R1C_PROF_DIST);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;

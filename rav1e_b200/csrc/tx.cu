@@ -55,6 +55,13 @@ static int launch(r1c_ctx *ctx, int tx_size, int tx_type, int bit_depth, FhtArgs
   a.sh0 = sh[0];
   a.sh1 = sh[1];
   a.sh2 = sh[2];
+  // every table has entry 0 >= 0 (left shift) and entry 1 <= 0 (rounding right shift)
+  a.ls0 = sh[0];
+  a.rs1 = -sh[1];
+  a.rnd1 = (1 << a.rs1) >> 1;
+  a.ls2 = sh[2] > 0 ? sh[2] : 0;
+  a.rs2 = sh[2] < 0 ? -sh[2] : 0;
+  a.rnd2 = (1 << a.rs2) >> 1;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   r1c_prof_begin(ctx, R1C_PROF_TX);
   const int rc = fn(ctx, a, fused_pb);

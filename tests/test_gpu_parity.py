@@ -92,6 +92,22 @@ def test_sad_satd_batch_random(r, ctx, oracle, pb, bd):
                      flat.ctypes.data, n, pb, want_satd.ctypes.data)
     assert np.array_equal(r.sad_batch(ctx, d_org, d_ref, jobs, bd), want_sad)
     assert np.array_equal(r.satd_batch(ctx, d_org, d_ref, jobs, bd), want_satd)
+    # the lanes-per-block choice follows the list length (32 / 4 / 1 lanes): same answers for any mix of sizes
+    for reps in (3, 6, 12, 20, 30):  # 16, 8, 4, 2, 1 lanes per block on a 148-SM part
+        big = np.tile(jobs, reps)
+        assert np.array_equal(r.sad_batch(ctx, d_org, d_ref, big, bd), np.tile(want_sad, reps))
+        assert np.array_equal(r.satd_batch(ctx, d_org, d_ref, big, bd), np.tile(want_satd, reps))
+    # planes wrapped around memory that is only pixel-aligned take the word-load path (no 16-byte vectors)
+    import torch
+    raw_o = torch.zeros(o_org.data.nbytes + 64, dtype=torch.uint8, device="cuda")
+    raw_r = torch.zeros(o_ref.data.nbytes + 64, dtype=torch.uint8, device="cuda")
+    off = 4  # word aligned, not 16-byte aligned
+    raw_o[off:off + o_org.data.nbytes] = torch.from_numpy(o_org.data.view(np.uint8).reshape(-1)).cuda()
+    raw_r[off:off + o_ref.data.nbytes] = torch.from_numpy(o_ref.data.view(np.uint8).reshape(-1)).cuda()
+    w_org = r.Plane(ctx, 0, 0, px_bytes=pb, cfg=d_org.cfg, device_ptr=raw_o.data_ptr() + off)
+    w_ref = r.Plane(ctx, 0, 0, px_bytes=pb, cfg=d_ref.cfg, device_ptr=raw_r.data_ptr() + off)
+    assert np.array_equal(r.sad_batch(ctx, w_org, w_ref, jobs, bd), want_sad)
+    assert np.array_equal(r.satd_batch(ctx, w_org, w_ref, np.tile(jobs, 12), bd), np.tile(want_satd, 12))
 
 
 def test_satd_extreme_amplitude(r, ctx, oracle):

@@ -13,5 +13,5 @@ import rav1e_b200 as r  # noqa: E402
 
 ctx = r.Context(0)
 ext = torch.cuda.ExternalStream(ctx.stream, device=0)
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+flush = torch.zeros(512 << 20, dtype=torch.uint8, device="cuda")
 print(json.dumps(bench_kernels.run(ctx, r, torch, ext, flush, reps=int(sys.argv[1]) if len(sys.argv) > 1 else 3)))
