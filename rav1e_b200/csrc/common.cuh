@@ -121,13 +121,14 @@ void r1c_prof_end(r1c_ctx *ctx, int slot);
   } while (0)
 
 // BlockSize -> (w, h), order of src/partition.rs:116-140
+// (log2(side) - 2 packed 4 bits per BlockSize: no table in local / constant memory)
 __host__ __device__ inline int blk_w_of(int b) {
-  const unsigned char t[22] = {4, 4, 8, 8, 8, 16, 16, 16, 32, 32, 32, 64, 64, 64, 128, 128, 4, 16, 8, 32, 16, 64};
-  return t[b];
+  const unsigned long long lo = 0x5544433322211100ull, hi = 0x423120ull;
+  return 4 << (unsigned)((b < 16 ? lo >> (4 * b) : hi >> (4 * (b - 16))) & 15);
 }
 __host__ __device__ inline int blk_h_of(int b) {
-  const unsigned char t[22] = {4, 8, 4, 8, 16, 8, 16, 32, 16, 32, 64, 32, 64, 128, 64, 128, 16, 4, 32, 8, 64, 16};
-  return t[b];
+  const unsigned long long lo = 0x5454343232121010ull, hi = 0x241302ull;
+  return 4 << (unsigned)((b < 16 ? lo >> (4 * b) : hi >> (4 * (b - 16))) & 15);
 }
 
 static inline bool bit_depth_ok(int bd, int px_bytes) {

@@ -219,42 +219,63 @@ __device__ __forceinline__ bool mv_in_range(const RefArgs &a, int bx, int by, in
   return mv.col >= xmin && mv.col <= xmax && mv.row >= ymin && mv.row <= ymax;
 }
 
-// all tile jobs of one class for one step.  step == 0: the full-pel SATD re-evaluation
-// (one candidate: the block's best_mv through the full-pel path).
+// all tiles of one class for one step.  step == 0: the full-pel SATD re-evaluation
+// (one candidate: the block's best_mv through the full-pel path).  A group of S threads
+// takes a tile, decodes it and loads its org column ONCE, then walks the candidates
+// (per-job set-up was a third of the instructions when every (tile, candidate) pair was
+// a job of its own).
 template <int S>
 __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, const uint32_t *tiles, int t_lo,
                                           int t_hi, int step, int ncand, int RX, int RY, int wx0, int wy0) {
   constexpr int GROUPS = RT / S;
   const int tid = threadIdx.x, lane = tid & 31, c = tid & (S - 1), grp = tid / S;
   const int nt = t_hi - t_lo;
-  const int njobs = nt * ncand;
-  const int rounds = (njobs + GROUPS - 1) / GROUPS;
+  const int rounds = (nt + GROUPS - 1) / GROUPS;
+  const bool satd = a.use_satd != 0;
   for (int rd = 0; rd < rounds; rd++) {
-    const int job = rd * GROUPS + grp;
-    int d[S];
+    const int t = rd * GROUPS + grp;
+    bool tile_live = t < nt;
+    int slot = 0, bw = 8, bh = 8, bx = 0, by = 0, tx = 0, ty = 0;
+    int oc[S];
 #pragma unroll
-    for (int i = 0; i < S; i++) d[i] = 0;
-    bool live = job < njobs;
-    int slot = 0, k = 0;
-    if (live) {
-      k = job / nt;
-      const uint32_t e = tiles[t_lo + (job - k * nt)];
+    for (int y = 0; y < S; y++) oc[y] = 0;
+    r1c_mv center = {0, 0}, best = {0, 0};
+    if (tile_live) {
+      const uint32_t e = tiles[t_lo + t];
       slot = e & 1023;
       const int bsize = (e >> 10) & 31;
-      const int bw = blk_w_of(bsize), bh = blk_h_of(bsize);
-      const int bx = RX + 4 * ((e >> 15) & 15), by = RY + 4 * ((e >> 19) & 15);
-      const int tx = 4 * ((e >> 23) & 15), ty = 4 * ((e >> 27) & 15);
-      live = a.off[bsize] >= 0 && bx + bw <= a.W && by + bh <= a.H;
-      if (live) {
+      bw = blk_w_of(bsize);
+      bh = blk_h_of(bsize);
+      bx = RX + 4 * ((e >> 15) & 15);
+      by = RY + 4 * ((e >> 19) & 15);
+      tx = 4 * ((e >> 23) & 15);
+      ty = 4 * ((e >> 27) & 15);
+      tile_live = a.off[bsize] >= 0 && bx + bw <= a.W && by + bh <= a.H;
+      if (tile_live) {
         const Blk b = sh.blk[slot];
+        center = b.center;
+        best = b.mv;
+        const uint8_t *o = sh.org + (by - RY + ty) * 64 + (bx - RX + tx + c);
+#pragma unroll
+        for (int y = 0; y < S; y++) oc[y] = (int)o[y * 64];
+      }
+    }
+    const int tbx = (bw <= 4 ? 16 : 0), tby = (bh <= 4 ? 16 : 0);
+#pragma unroll 1
+    for (int k = 0; k < ncand; k++) {
+      int d[S];
+#pragma unroll
+      for (int i = 0; i < S; i++) d[i] = 0;
+      bool live = tile_live;
+      if (live) {
         int cf = 0, rf = 0, sx, sy;
         r1c_mv mv;
         if (step == 0) {  // full-pel path: ref block at po + mv / 8, truncating (src/me.rs:828-836)
-          mv = b.mv;
+          mv = best;
           sx = bx + mv.col / 8;
           sy = by + mv.row / 8;
         } else {  // predict_inter's get_params (src/predict.rs:267-284), luma
-          mv = step_cand(b.center, step, k);
+          mv = step_cand(center, step, k);
           const int ro = (int)mv.row >> 3, co = (int)mv.col >> 3;
           rf = ((int)mv.row - (ro << 3)) << 1;
           cf = ((int)mv.col - (co << 3)) << 1;
@@ -268,17 +289,16 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
           int wx = sx + tx + c - wx0, wy = sy + ty - wy0;
           wx = min(max(wx, 3), a.winW - 5);
           wy = min(max(wy, 3), a.winH - S - 4);
-          const uint2 txw = sh.taps[(bw <= 4 ? 16 : 0) + cf], tyw = sh.taps[(bh <= 4 ? 16 : 0) + rf];
+          const uint2 txw = sh.taps[tbx + cf], tyw = sh.taps[tby + rf];
           int out[S];
           predict_column<S>(sh.win, a.wstride, wx, wy, cf, rf, txw, tyw, out);
-          const uint8_t *o = sh.org + (by - RY + ty) * 64 + (bx - RX + tx + c);
 #pragma unroll
-          for (int y = 0; y < S; y++) d[y] = (int)o[y * 64] - out[y];
+          for (int y = 0; y < S; y++) d[y] = oc[y] - out[y];
         }
       }
+      const uint32_t acc = tile_dist<S>(d, lane, satd);
+      if (live && c == 0) atomicAdd(&sh.dist[slot * 8 + k], acc);
     }
-    const uint32_t acc = tile_dist<S>(d, lane, a.use_satd != 0);
-    if (live && c == 0) atomicAdd(&sh.dist[slot * 8 + k], acc);
   }
 }
 
