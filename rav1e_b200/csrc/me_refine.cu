@@ -176,6 +176,43 @@ __device__ __forceinline__ uint32_t tile_dist(int (&d)[S], int lane, bool satd) 
   return acc;
 }
 
+// Two candidates of the same tile at once: x = d1 * 65536 + d0 is carried through the
+// (linear) Hadamard as ONE integer per coefficient -- plain 32-bit adds / subs act on both
+// halves, and since |coef| <= 64 * 255 < 2^15 the halves separate again exactly
+// (lo = sign-extended low 16 bits, hi = (x - lo) >> 16).  Half the butterflies and shuffles
+// per candidate.  Must be called by all 32 lanes.
+template <int S>
+__device__ __forceinline__ void tile_dist2(const int (&d0)[S], const int (&d1)[S], int lane, bool satd, uint32_t &a0,
+                                           uint32_t &a1) {
+  a0 = 0;
+  a1 = 0;
+  if (satd) {
+    int x[S];
+#pragma unroll
+    for (int i = 0; i < S; i++) x[i] = d1[i] * 65536 + d0[i];
+    distdev::hadamard_regs<S>(x);
+    distdev::hadamard_lanes<S>(x, lane);
+#pragma unroll
+    for (int i = 0; i < S; i++) {
+      const int lo = (int)(short)x[i];
+      const int hi = (x[i] - lo) >> 16;
+      a0 += (uint32_t)abs(lo);
+      a1 += (uint32_t)abs(hi);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < S; i++) {
+      a0 += (uint32_t)abs(d0[i]);
+      a1 += (uint32_t)abs(d1[i]);
+    }
+  }
+#pragma unroll
+  for (int m = 1; m < S; m <<= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, m);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, m);
+  }
+}
+
 struct Shared {
   const uint8_t *win, *org;
   uint32_t *dist;   // [NSLOT][8]
@@ -261,43 +298,56 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
       }
     }
     const int tbx = (bw <= 4 ? 16 : 0), tby = (bh <= 4 ? 16 : 0);
-#pragma unroll 1
-    for (int k = 0; k < ncand; k++) {
-      int d[S];
+    // differences of candidate k in this thread's column (zeros when the candidate is not evaluated)
+    auto eval = [&](int k, int (&d)[S]) -> bool {
 #pragma unroll
       for (int i = 0; i < S; i++) d[i] = 0;
-      bool live = tile_live;
-      if (live) {
-        int cf = 0, rf = 0, sx, sy;
-        r1c_mv mv;
-        if (step == 0) {  // full-pel path: ref block at po + mv / 8, truncating (src/me.rs:828-836)
-          mv = best;
-          sx = bx + mv.col / 8;
-          sy = by + mv.row / 8;
-        } else {  // predict_inter's get_params (src/predict.rs:267-284), luma
-          mv = step_cand(center, step, k);
-          const int ro = (int)mv.row >> 3, co = (int)mv.col >> 3;
-          rf = ((int)mv.row - (ro << 3)) << 1;
-          cf = ((int)mv.col - (co << 3)) << 1;
-          sx = max(min(bx + co - 3, a.ref.width), -a.ref.xorigin) + 3;
-          sy = max(min(by + ro - 3, a.ref.height), -a.ref.yorigin) + 3;
-        }
-        live = mv_in_range(a, bx, by, bw, bh, mv);
-        if (live) {
-          // window coordinates of this thread's column; clamped for memory safety only
-          // (a legal MV of the search range never leaves the staged window)
-          int wx = sx + tx + c - wx0, wy = sy + ty - wy0;
-          wx = min(max(wx, 3), a.winW - 5);
-          wy = min(max(wy, 3), a.winH - S - 4);
-          const uint2 txw = sh.taps[tbx + cf], tyw = sh.taps[tby + rf];
-          int out[S];
-          predict_column<S>(sh.win, a.wstride, wx, wy, cf, rf, txw, tyw, out);
+      if (!tile_live) return false;
+      int cf = 0, rf = 0, sx, sy;
+      r1c_mv mv;
+      if (step == 0) {  // full-pel path: ref block at po + mv / 8, truncating (src/me.rs:828-836)
+        mv = best;
+        sx = bx + mv.col / 8;
+        sy = by + mv.row / 8;
+      } else {  // predict_inter's get_params (src/predict.rs:267-284), luma
+        mv = step_cand(center, step, k);
+        const int ro = (int)mv.row >> 3, co = (int)mv.col >> 3;
+        rf = ((int)mv.row - (ro << 3)) << 1;
+        cf = ((int)mv.col - (co << 3)) << 1;
+        sx = max(min(bx + co - 3, a.ref.width), -a.ref.xorigin) + 3;
+        sy = max(min(by + ro - 3, a.ref.height), -a.ref.yorigin) + 3;
+      }
+      if (!mv_in_range(a, bx, by, bw, bh, mv)) return false;
+      // window coordinates of this thread's column; clamped for memory safety only
+      // (a legal MV of the search range never leaves the staged window)
+      int wx = sx + tx + c - wx0, wy = sy + ty - wy0;
+      wx = min(max(wx, 3), a.winW - 5);
+      wy = min(max(wy, 3), a.winH - S - 4);
+      const uint2 txw = sh.taps[tbx + cf], tyw = sh.taps[tby + rf];
+      int out[S];
+      predict_column<S>(sh.win, a.wstride, wx, wy, cf, rf, txw, tyw, out);
 #pragma unroll
-          for (int y = 0; y < S; y++) d[y] = oc[y] - out[y];
+      for (int y = 0; y < S; y++) d[y] = oc[y] - out[y];
+      return true;
+    };
+    if (ncand == 1) {
+      int d[S];
+      const bool live = eval(0, d);
+      const uint32_t acc = tile_dist<S>(d, lane, satd);
+      if (live && c == 0) atomicAdd(&sh.dist[slot * 8], acc);
+    } else {
+#pragma unroll 1
+      for (int k = 0; k < ncand; k += 2) {  // candidates in pairs through one packed Hadamard
+        int d0[S], d1[S];
+        const bool live0 = eval(k, d0);
+        const bool live1 = eval(k + 1, d1);
+        uint32_t a0, a1;
+        tile_dist2<S>(d0, d1, lane, satd, a0, a1);
+        if (c == 0) {
+          if (live0) atomicAdd(&sh.dist[slot * 8 + k], a0);
+          if (live1) atomicAdd(&sh.dist[slot * 8 + k + 1], a1);
         }
       }
-      const uint32_t acc = tile_dist<S>(d, lane, satd);
-      if (live && c == 0) atomicAdd(&sh.dist[slot * 8 + k], acc);
     }
   }
 }
