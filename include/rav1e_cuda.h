@@ -357,6 +357,35 @@ int r1c_me_sb_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref
                         const r1c_sb_params *params, const r1c_sb_job *d_jobs, int64_t n,
                         int bit_depth, r1c_me_result *d_results);
 
+/* The full-pel stages of FullSearch motion estimation on the frame pyramid, batched over
+ * blocks (window arithmetic of the reference on the host, searches = r1c_full_search_batch):
+ *   ss4: estimate_motion_ss4, src/me.rs:1023-1075 -- quarter-res planes, window
+ *        +-192*me_range_scale x +-64*me_range_scale luma px clipped by get_mv_range, >> 2;
+ *        lambda = (me_lambda*256/16*0.125) as u32; result = best_mv * 4
+ *   ss2: estimate_motion_ss2 + FullSearch::me_ss2, :280-333, 597-650 -- half-res planes,
+ *        +-16 px around each of <= 3 predictor MVs (pmv_valid[i*3+k] != 0), best carried
+ *        across the rounds; lambda = (me_lambda*256/4*0.125) as u32; result = best_mv * 2
+ *   full: estimate_motion + FullSearch::full_pixel_me, :335-385, 522-565 -- +-16 px, step 2,
+ *        around each of <= 7 candidate MVs; lambda = (me_lambda*256*0.5) as u32
+ * jobs[i] = the block's offset in 4x4 units BEFORE adjust_bo (:993-1003) and its BlockSize;
+ * a block without any valid predictor keeps MotionVector::default(). */
+typedef struct {
+  int32_t bo_x, bo_y;
+  int32_t bsize;
+} r1c_block_job;
+int r1c_estimate_motion_ss4_batch(r1c_ctx *ctx, const r1c_plane *org_qres, const r1c_plane *ref_qres,
+                                  int w_in_b, int h_in_b, const r1c_block_job *jobs, int64_t n,
+                                  int me_range_scale, double me_lambda, int allow_high_precision_mv,
+                                  int bit_depth, r1c_mv *out);
+int r1c_estimate_motion_ss2_batch(r1c_ctx *ctx, const r1c_plane *org_hres, const r1c_plane *ref_hres,
+                                  int w_in_b, int h_in_b, const r1c_block_job *jobs, int64_t n,
+                                  const r1c_mv *pmvs, const uint8_t *pmv_valid, double me_lambda,
+                                  int allow_high_precision_mv, int bit_depth, r1c_mv *out);
+int r1c_estimate_motion_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, int w_in_b,
+                              int h_in_b, const r1c_block_job *jobs, int64_t n, const r1c_mv *cmvs,
+                              const uint8_t *cmv_valid, double me_lambda, int allow_high_precision_mv,
+                              int bit_depth, r1c_mv *out);
+
 /* Sub-pel candidate costs (get_mv_rd_cost with a temp plane, src/me.rs:787-838):
  * predict_inter (put_8tap, REGULAR/REGULAR = fi.default_filter) of the block at
  * each candidate MV, then SAD|SATD + rate.  n_cand candidates per job, laid out

@@ -94,6 +94,11 @@ def lib():
                                          P(i64 * 4), i, i, i, P(Mv), P(u64)]
         L.r1o_diamond_search.restype = i
         dbl = C.c_double
+        L.r1o_estimate_motion_ss4.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i64, i64, i, i, i, dbl, i, i, P(Mv)]
+        L.r1o_estimate_motion_ss4.restype = i
+        for f in (L.r1o_estimate_motion_ss2, L.r1o_estimate_motion):
+            f.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i64, i64, i64, i64, i, i, vp, vp, dbl, i, i, P(Mv)]
+            f.restype = i
         L.r1o_distortion_bias.argtypes = [vp, i64, i64, i64, i64, i64, i64, i64]
         L.r1o_distortion_bias.restype = dbl
         L.r1o_sse_wxh.argtypes = [vp, i64, i64, i64, vp, i64, i64, i64, i64, i64, i, i, i, vp, i64, i64, i64]
@@ -162,6 +167,30 @@ def diamond_search(org: OPlane, ref: OPlane, po, blk_w, blk_h, predictors, pmv, 
                                   int(allow_hp), C.byref(rng), int(subpixel), bit_depth, org.px_bytes, C.byref(mv),
                                   C.byref(cost))
     return (mv.row, mv.col), cost.value, it
+
+
+def estimate_motion_ss4(org_q: OPlane, ref_q: OPlane, w_in_b, h_in_b, bo, blk_w, blk_h, me_range_scale, me_lambda, allow_hp):
+    """estimate_motion_ss4, src/me.rs:1023-1075 -> (row, col)"""
+    mv = Mv(0, 0)
+    rc = lib().r1o_estimate_motion_ss4(org_q.origin_ptr(), C.byref(org_q.cfg), ref_q.origin_ptr(), C.byref(ref_q.cfg), w_in_b,
+                                       h_in_b, bo[0], bo[1], blk_w, blk_h, me_range_scale, float(me_lambda), int(allow_hp),
+                                       org_q.px_bytes, C.byref(mv))
+    assert rc == 0
+    return mv.row, mv.col
+
+
+def estimate_motion_pred(org: OPlane, ref: OPlane, w_in_b, h_in_b, bo, blk_w, blk_h, preds, valid, me_lambda, allow_hp, ss2):
+    """estimate_motion_ss2 (ss2=True, 3 pmvs, half-res planes, src/me.rs:280-333,597-650) or estimate_motion with
+    FullSearch::full_pixel_me (7 cmvs, :335-385,522-565) -> (row, col)"""
+    slots = 3 if ss2 else 7
+    p = np.ascontiguousarray(np.asarray(preds, dtype=np.int16).reshape(slots, 2))
+    v = np.ascontiguousarray(np.asarray(valid, dtype=np.uint8).reshape(slots))
+    mv = Mv(0, 0)
+    fn = lib().r1o_estimate_motion_ss2 if ss2 else lib().r1o_estimate_motion
+    rc = fn(org.origin_ptr(), C.byref(org.cfg), ref.origin_ptr(), C.byref(ref.cfg), w_in_b, h_in_b, bo[0], bo[1], blk_w, blk_h,
+            _p(p), _p(v), float(me_lambda), int(allow_hp), org.px_bytes, C.byref(mv))
+    assert rc == 0
+    return mv.row, mv.col
 
 
 def _imp(block_importances):

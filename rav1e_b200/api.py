@@ -30,6 +30,7 @@ MC_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("src_x", "<i4"), ("src_y
 AVG_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                     ("tmp_off", "<i4")])
 TX_JOB = np.dtype([("in_x", "<i4"), ("in_y", "<i4"), ("pred_x", "<i4"), ("pred_y", "<i4")])
+BLOCK_JOB = np.dtype([("bo_x", "<i4"), ("bo_y", "<i4"), ("bsize", "<i4")])
 RDO_JOB = np.dtype([("src_x", "<i4"), ("src_y", "<i4"), ("rec_x", "<i4"), ("rec_y", "<i4"),
                     ("w", "<i4"), ("h", "<i4")])
 ME_RESULT = np.dtype([("mv", MV), ("reserved", "<u4"), ("cost", "<u8")])
@@ -44,7 +45,7 @@ SUBPEL_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("lam
                        ("mvy_min", "<i4"), ("mvy_max", "<i4"), ("use_satd", "<i4"),
                        ("allow_high_precision_mv", "<i4")])
 STRUCT_PAIRS = [(DIST_JOB, capi.DistJob), (MC_JOB, capi.McJob), (AVG_JOB, capi.AvgJob),
-                (TX_JOB, capi.TxJob), (RDO_JOB, capi.RdoJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
+                (TX_JOB, capi.TxJob), (RDO_JOB, capi.RdoJob), (BLOCK_JOB, capi.BlockJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
                 (SB_JOB, capi.SbJob), (SUBPEL_JOB, capi.SubpelJob), (MV, capi.Mv)]
 
 BLOCK = {n: i for i, n in enumerate(capi.BLOCK_SIZES)}
@@ -390,6 +391,30 @@ def subpel_refine_batch(ctx, plane_org, plane_ref, jobs, results, bit_depth):
     ctx.check(ctx.lib.r1c_subpel_refine_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs),
                                               jobs.size, bit_depth, _p(results)))
     return results
+
+
+def estimate_motion_ss4_batch(ctx, org_qres, ref_qres, w_in_b, h_in_b, jobs, me_range_scale, me_lambda, bit_depth,
+                              allow_hp=False):
+    """estimate_motion_ss4 (src/me.rs:1023-1075) for every BLOCK_JOB -> MV array (already x 4)"""
+    jobs = _arr(jobs, BLOCK_JOB)
+    out = np.zeros(jobs.size, dtype=MV)
+    ctx.check(ctx.lib.r1c_estimate_motion_ss4_batch(ctx.h, org_qres.h, ref_qres.h, w_in_b, h_in_b, _p(jobs), jobs.size,
+                                                    me_range_scale, float(me_lambda), int(allow_hp), bit_depth, _p(out)))
+    return out
+
+
+def estimate_motion_batch(ctx, org, ref, w_in_b, h_in_b, jobs, preds, valid, me_lambda, bit_depth, allow_hp=False, ss2=False):
+    """ss2=True: estimate_motion_ss2 / FullSearch::me_ss2 on half-res planes, preds (n, 3); else estimate_motion /
+    FullSearch::full_pixel_me on the full-res planes, preds (n, 7).  valid: same shape, non-zero = Some(mv)."""
+    jobs = _arr(jobs, BLOCK_JOB)
+    slots = 3 if ss2 else 7
+    preds = _arr(preds, MV).reshape(jobs.size, slots)
+    valid = _arr(valid, np.uint8).reshape(jobs.size, slots)
+    out = np.zeros(jobs.size, dtype=MV)
+    fn = ctx.lib.r1c_estimate_motion_ss2_batch if ss2 else ctx.lib.r1c_estimate_motion_batch
+    ctx.check(fn(ctx.h, org.h, ref.h, w_in_b, h_in_b, _p(jobs), jobs.size, _p(preds), _p(valid), float(me_lambda),
+                 int(allow_hp), bit_depth, _p(out)))
+    return out
 
 
 def diamond_search_batch(ctx, plane_org, plane_ref, jobs, predictors, bit_depth, subpixel=False):

@@ -63,6 +63,10 @@ class TxJob(C.Structure):
                 ("pred_y", C.c_int32)]
 
 
+class BlockJob(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("bo_x", "bo_y", "bsize")]
+
+
 class RdoJob(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("src_x", "src_y", "rec_x", "rec_y", "w", "h")]
 
@@ -163,6 +167,9 @@ SIGNATURES = {
     "r1c_subpel_cost_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _vp]),
     "r1c_subpel_refine_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_subpel_refine_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
+    "r1c_estimate_motion_ss4_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _i, C.c_double, _i, _i, _vp]),
+    "r1c_estimate_motion_ss2_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, C.c_double, _i, _i, _vp]),
+    "r1c_estimate_motion_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, C.c_double, _i, _i, _vp]),
     "r1c_diamond_search_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _i, _i, _vp]),
     "r1c_diamond_search_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _vp, _i, _i, _vp]),
     "r1c_frame_me_count": (_i64, [_P(FrameMeParams)]),

@@ -680,3 +680,70 @@ def test_diamond_search_matches_oracle(r, ctx, oracle, pb, bd, subpixel, use_sat
         assert ((int(got[i]["mv"]["row"]), int(got[i]["mv"]["col"])), int(got[i]["cost"])) == (mv, cost), i
         moved += iters > (3 if subpixel and hp else 2)
     assert moved > n // 4  # the search really walks (not only the shrink steps)
+
+
+# ------------------------------------------------ pyramid stages of FullSearch ----
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+def test_estimate_motion_pyramid_matches_oracle(r, ctx, oracle, pb, bd):
+    """estimate_motion_ss4 (quarter res), estimate_motion_ss2 (half res, <= 3 pmvs) and estimate_motion with
+    FullSearch::full_pixel_me (full res, <= 7 cmvs, step 2) on a frame pyramid built by downsample_from"""
+    rng = np.random.default_rng(1700 + bd)
+    W, H = 256, 192
+    planes = {}
+    for name, shift in (("ref", (0, 0)), ("org", (6, -10))):
+        o0 = oracle.OPlane(W, H, 0, 0, 88, 88, pb)
+        if name == "ref":
+            v = rng.integers(0, 1 << bd, size=(H, W)).astype(np.float64)
+            for _ in range(4):
+                v = (v + np.roll(v, 1, 0) + np.roll(v, 1, 1) + np.roll(v, -1, 0) + np.roll(v, -1, 1)) / 5
+            base = np.clip(np.rint(v), 0, (1 << bd) - 1)
+            o0.visible[...] = base.astype(o0.dtype)
+        else:
+            o0.visible[...] = np.clip(np.roll(base, shift, axis=(0, 1)) + rng.integers(-2, 3, size=(H, W)), 0,
+                                      (1 << bd) - 1).astype(o0.dtype)
+        o0.pad()
+        levels = [o0]
+        for lvl in (1, 2):  # hres / qres: Plane::new(w/2, h/2, 1, 1, pad/2, pad/2) ..., src/encoder.rs:361-376
+            o = oracle.OPlane(W >> lvl, H >> lvl, lvl, lvl, 88 >> lvl, 88 >> lvl, pb)
+            assert oracle.lib().r1o_plane_downsample(o.data.ctypes.data, C.byref(o.cfg), levels[-1].data.ctypes.data,
+                                                     C.byref(levels[-1].cfg), pb) == 0
+            o.pad(W, H)
+            levels.append(o)
+        planes[name] = [(o, r.Plane(ctx, int(o.cfg.width), int(o.cfg.height), int(o.cfg.xdec), int(o.cfg.ydec), int(o.cfg.xpad),
+                                    int(o.cfg.ypad), pb).upload(o.data)) for o in levels]
+    w_in_b, h_in_b = W // 4, H // 4
+    L = oracle.lib()
+    me_lambda = 1.37
+    # ss4: 64x64 / 32x32 / 16x16 blocks (quarter-res 16x16 / 8x8 / 4x4), offsets incl. ones adjust_bo pulls back inside
+    jobs = np.array([(bx, by, b) for b in (12, 9, 6) for by in range(0, h_in_b + 4, 8) for bx in range(0, w_in_b + 4, 8)],
+                    dtype=r.BLOCK_JOB)
+    got = r.estimate_motion_ss4_batch(ctx, planes["org"][2][1], planes["ref"][2][1], w_in_b, h_in_b, jobs, 1, me_lambda, bd)
+    hits = 0
+    for j, g in zip(jobs, got):
+        bw, bh = L.r1o_block_width(int(j["bsize"])), L.r1o_block_height(int(j["bsize"]))
+        want = oracle.estimate_motion_ss4(planes["org"][2][0], planes["ref"][2][0], w_in_b, h_in_b, (int(j["bo_x"]), int(j["bo_y"])),
+                                          bw, bh, 1, me_lambda, False)
+        assert (int(g["row"]), int(g["col"])) == want, j
+        hits += abs(want[0] + 48) <= 32 and abs(want[1] - 80) <= 32  # org(y, x) = ref(y - 6, x + 10)
+    assert hits > jobs.size // 2
+    # ss2 and full res: predictors around the ss4 result, some slots empty, one block with none
+    for ss2 in (True, False):
+        slots = 3 if ss2 else 7
+        jobs = np.array([(bx, by, b) for b in (12, 9, 6, 3) for by in range(0, h_in_b, 16) for bx in range(0, w_in_b + 4, 16)],
+                        dtype=r.BLOCK_JOB)
+        preds = np.zeros((jobs.size, slots), dtype=r.MV)
+        valid = np.zeros((jobs.size, slots), dtype=np.uint8)
+        for i in range(jobs.size):
+            for s in range(slots):
+                preds[i, s] = (-48 + int(rng.integers(-40, 41)), 80 + int(rng.integers(-40, 41)))
+                valid[i, s] = i > 0 and rng.integers(0, 4) != 0
+        lvl = 1 if ss2 else 0
+        got = r.estimate_motion_batch(ctx, planes["org"][lvl][1], planes["ref"][lvl][1], w_in_b, h_in_b, jobs, preds, valid,
+                                      me_lambda, bd, ss2=ss2)
+        for i, (j, g) in enumerate(zip(jobs, got)):
+            bw, bh = L.r1o_block_width(int(j["bsize"])), L.r1o_block_height(int(j["bsize"]))
+            want = oracle.estimate_motion_pred(planes["org"][lvl][0], planes["ref"][lvl][0], w_in_b, h_in_b,
+                                               (int(j["bo_x"]), int(j["bo_y"])), bw, bh,
+                                               [(int(p["row"]), int(p["col"])) for p in preds[i]], valid[i], me_lambda, False, ss2)
+            assert (int(g["row"]), int(g["col"])) == want, (ss2, j)
+        assert (int(got[0]["row"]), int(got[0]["col"])) == (0, 0)  # no predictor: MotionVector::default()
