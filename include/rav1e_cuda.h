@@ -386,6 +386,27 @@ int r1c_estimate_motion_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plan
                               const uint8_t *cmv_valid, double me_lambda, int allow_high_precision_mv,
                               int bit_depth, r1c_mv *out);
 
+/* The motion-vector field: FrameMotionVectors (src/me.rs:32-62) = cols x rows r1c_mv in 4x4
+ * units, row-major, owned by the caller.
+ *   save_block_motion      src/encoder.rs:1432-1444: mvs[i] written to every cell block i covers
+ *                          (jobs of one call must not overlap: the reference is sequential)
+ *   get_subset_predictors  src/me.rs:82-174: per block the zero MV, its coarse MVs (cmvs[i*7 + k],
+ *                          k < n_cmvs[i]) quantised to full-pel, EPZS subsets A/B from `field` and
+ *                          C from `prev_field` (NULL = no reference frame); predictors[i*17 ..]
+ *                          holds counts[i] entries in the reference's order, the rest repeats the
+ *                          last one (the layout r1c_diamond_search_batch takes with n_pred = 17). */
+int r1c_save_block_motion_batch(r1c_ctx *ctx, r1c_mv *field, int cols, int rows,
+                                const r1c_block_job *jobs, const r1c_mv *mvs, int64_t n);
+int r1c_save_block_motion_batch_dev(r1c_ctx *ctx, r1c_mv *d_field, int cols, int rows,
+                                    const r1c_block_job *d_jobs, const r1c_mv *d_mvs, int64_t n);
+int r1c_subset_predictors_batch(r1c_ctx *ctx, const r1c_mv *field, const r1c_mv *prev_field, int cols,
+                                int rows, const r1c_block_job *jobs, int64_t n, const r1c_mv *cmvs,
+                                const uint8_t *n_cmvs, r1c_mv *predictors, int32_t *counts);
+int r1c_subset_predictors_batch_dev(r1c_ctx *ctx, const r1c_mv *d_field, const r1c_mv *d_prev_field,
+                                    int cols, int rows, const r1c_block_job *d_jobs, int64_t n,
+                                    const r1c_mv *d_cmvs, const uint8_t *d_n_cmvs,
+                                    r1c_mv *d_predictors, int32_t *d_counts);
+
 /* Sub-pel candidate costs (get_mv_rd_cost with a temp plane, src/me.rs:787-838):
  * predict_inter (put_8tap, REGULAR/REGULAR = fi.default_filter) of the block at
  * each candidate MV, then SAD|SATD + rate.  n_cand candidates per job, laid out

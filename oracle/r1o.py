@@ -193,6 +193,73 @@ def estimate_motion_pred(org: OPlane, ref: OPlane, w_in_b, h_in_b, bo, blk_w, bl
     return mv.row, mv.col
 
 
+def _tdiv(a, b):
+    """Rust integer `/`: truncation toward zero"""
+    q = abs(a) // abs(b)
+    return q if (a >= 0) == (b > 0) else -q
+
+
+def _i16(v):
+    return ((v + 32768) & 0xFFFF) - 32768
+
+
+def save_block_motion(field, bo, blk_w, blk_h, mv):
+    """save_block_motion, src/encoder.rs:1432-1444; field: int16 array (rows, cols, 2) as (row, col)"""
+    rows, cols = field.shape[:2]
+    for y in range(bo[1], min(bo[1] + blk_h // 4, rows)):
+        for x in range(bo[0], min(bo[0] + blk_w // 4, cols)):
+            field[y, x] = mv
+
+
+def get_subset_predictors(bo, cmvs, field, prev_field):
+    """get_subset_predictors, src/me.rs:82-174 (tile == frame) -> list of (row, col)"""
+    def fullpel(m):
+        return (_tdiv(m[0], 8) * 8, _tdiv(m[1], 8) * 8)
+
+    rows, cols = field.shape[:2]
+    x, y = bo
+    preds = [(0, 0)] + [fullpel(m) for m in cmvs]
+    med = []
+    if x > 0:
+        left = tuple(int(v) for v in field[y, x - 1])
+        med.append(left)
+        if left != (0, 0):
+            preds.append(left)
+    if y > 0:
+        top = tuple(int(v) for v in field[y - 1, x])
+        med.append(top)
+        if top != (0, 0):
+            preds.append(top)
+        if x < cols - 1:
+            tr = tuple(int(v) for v in field[y - 1, x + 1])
+            med.append(tr)
+            if tr != (0, 0):
+                preds.append(tr)
+    if med:
+        sr, sc = 0, 0
+        for m in med:
+            sr, sc = _i16(sr + m[0]), _i16(sc + m[1])
+        q = fullpel((_tdiv(sr, len(med)), _tdiv(sc, len(med))))
+        if q != (0, 0):
+            preds.append(q)
+    if prev_field is not None:
+        cand = []
+        if x > 0:
+            cand.append(prev_field[y, x - 1])
+        if y > 0:
+            cand.append(prev_field[y - 1, x])
+        if x < cols - 1:
+            cand.append(prev_field[y, x + 1])
+        if y < rows - 1:
+            cand.append(prev_field[y + 1, x])
+        cand.append(prev_field[y, x])
+        for m in cand:
+            m = (int(m[0]), int(m[1]))
+            if m != (0, 0):
+                preds.append(m)
+    return preds
+
+
 def _imp(block_importances):
     if block_importances is None:
         return None, None

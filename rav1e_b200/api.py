@@ -417,6 +417,29 @@ def estimate_motion_batch(ctx, org, ref, w_in_b, h_in_b, jobs, preds, valid, me_
     return out
 
 
+def save_block_motion(ctx, field, jobs, mvs):
+    """save_block_motion (src/encoder.rs:1432-1444) for every BLOCK_JOB; field: MV array (rows, cols), updated in place"""
+    jobs = _arr(jobs, BLOCK_JOB)
+    mvs = _arr(mvs, MV)
+    assert field.dtype == MV and field.flags.c_contiguous and field.ndim == 2 and mvs.size == jobs.size
+    ctx.check(ctx.lib.r1c_save_block_motion_batch(ctx.h, _p(field), field.shape[1], field.shape[0], _p(jobs), _p(mvs), jobs.size))
+    return field
+
+
+def get_subset_predictors(ctx, field, prev_field, jobs, cmvs, n_cmvs):
+    """get_subset_predictors (src/me.rs:82-174) -> (predictors (n, 17) MV, counts (n,))"""
+    jobs = _arr(jobs, BLOCK_JOB)
+    cmvs = _arr(cmvs, MV).reshape(jobs.size, 7)
+    n_cmvs = _arr(n_cmvs, np.uint8)
+    field = _arr(field, MV)
+    pf = _arr(prev_field, MV) if prev_field is not None else None
+    out = np.zeros((jobs.size, 17), dtype=MV)
+    cnt = np.zeros(jobs.size, dtype=np.int32)
+    ctx.check(ctx.lib.r1c_subset_predictors_batch(ctx.h, _p(field), _p(pf) if pf is not None else None, field.shape[1],
+                                                  field.shape[0], _p(jobs), jobs.size, _p(cmvs), _p(n_cmvs), _p(out), _p(cnt)))
+    return out, cnt
+
+
 def diamond_search_batch(ctx, plane_org, plane_ref, jobs, predictors, bit_depth, subpixel=False):
     """diamond_me_search + get_best_predictor (src/me.rs:655-785) for every SUBPEL_JOB;
     predictors: MV array (n, n_pred).  Returns ME_RESULT (centre MV, cost) per job."""

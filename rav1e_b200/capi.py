@@ -170,6 +170,10 @@ SIGNATURES = {
     "r1c_estimate_motion_ss4_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _i, C.c_double, _i, _i, _vp]),
     "r1c_estimate_motion_ss2_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, C.c_double, _i, _i, _vp]),
     "r1c_estimate_motion_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, C.c_double, _i, _i, _vp]),
+    "r1c_save_block_motion_batch": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i64]),
+    "r1c_save_block_motion_batch_dev": (_i, [_vp, _vp, _i, _i, _vp, _vp, _i64]),
+    "r1c_subset_predictors_batch": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "r1c_subset_predictors_batch_dev": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i64, _vp, _vp, _vp, _vp]),
     "r1c_diamond_search_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp, _i, _i, _vp]),
     "r1c_diamond_search_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _vp, _i, _i, _vp]),
     "r1c_frame_me_count": (_i64, [_P(FrameMeParams)]),

@@ -747,3 +747,66 @@ def test_estimate_motion_pyramid_matches_oracle(r, ctx, oracle, pb, bd):
                                                [(int(p["row"]), int(p["col"])) for p in preds[i]], valid[i], me_lambda, False, ss2)
             assert (int(g["row"]), int(g["col"])) == want, (ss2, j)
         assert (int(got[0]["row"]), int(got[0]["col"])) == (0, 0)  # no predictor: MotionVector::default()
+
+
+# ------------------------------------------------------------ MV field ---------
+def test_mv_field_save_and_subset_predictors(r, ctx, oracle):
+    """save_block_motion (src/encoder.rs:1432-1444) and get_subset_predictors (src/me.rs:82-174) on a 48 x 32 MI field,
+    then the predictor lists straight into the diamond search (n_pred = 17)"""
+    rng = np.random.default_rng(1900)
+    cols, rows = 48, 32
+    L = oracle.lib()
+    field = np.zeros((rows, cols), dtype=r.MV)
+    want = np.zeros((rows, cols, 2), dtype=np.int16)
+    # non-overlapping blocks: a 16x16-px grid with random block sizes that fit a cell, some hanging over the field edge
+    jobs, mvs = [], []
+    for by in range(0, rows, 4):
+        for bx in range(0, cols, 4):
+            b = int(rng.choice([0, 1, 2, 3, 4, 5, 6, 16, 17]))
+            if bx == cols - 4 and by == rows - 4:
+                b = 12  # 64x64 clipped by the field
+            jobs.append((bx, by, b))
+            mvs.append((int(rng.integers(-300, 301)), int(rng.integers(-300, 301))) if rng.integers(0, 5) else (0, 0))
+    jobs = np.array(jobs, dtype=r.BLOCK_JOB)
+    mvs = np.array(mvs, dtype=r.MV)
+    r.save_block_motion(ctx, field, jobs, mvs)
+    for j, m in zip(jobs, mvs):
+        oracle.save_block_motion(want, (int(j["bo_x"]), int(j["bo_y"])), L.r1o_block_width(int(j["bsize"])),
+                                 L.r1o_block_height(int(j["bsize"])), (int(m["row"]), int(m["col"])))
+    assert np.array_equal(field["row"], want[..., 0]) and np.array_equal(field["col"], want[..., 1])
+    prev = np.zeros((rows, cols), dtype=r.MV)
+    prev["row"] = rng.integers(-200, 201, size=(rows, cols)) * (rng.integers(0, 3, size=(rows, cols)) > 0)
+    prev["col"] = rng.integers(-200, 201, size=(rows, cols)) * (rng.integers(0, 3, size=(rows, cols)) > 0)
+    prev3 = np.stack([prev["row"], prev["col"]], axis=-1)
+    pj = np.array([(x, y, 3) for y in range(rows) for x in range(cols)], dtype=r.BLOCK_JOB)  # every cell incl. all borders
+    cm = np.zeros((pj.size, 7), dtype=r.MV)
+    cm["row"] = rng.integers(-500, 501, size=cm.shape)
+    cm["col"] = rng.integers(-500, 501, size=cm.shape)
+    ncm = rng.integers(0, 8, size=pj.size).astype(np.uint8)
+    for use_prev in (True, False):
+        got, cnt = r.get_subset_predictors(ctx, field, prev if use_prev else None, pj, cm, ncm)
+        for i, j in enumerate(pj):
+            w = oracle.get_subset_predictors((int(j["bo_x"]), int(j["bo_y"])), [(int(m["row"]), int(m["col"])) for m in cm[i, :ncm[i]]],
+                                             want, prev3 if use_prev else None)
+            assert cnt[i] == len(w) <= 17, i
+            g = [(int(m["row"]), int(m["col"])) for m in got[i]]
+            assert g[:len(w)] == w and all(m == w[-1] for m in g[len(w):]), i
+    # chain: predictor lists -> diamond search
+    o_ref, d_ref = twin_plane(r, oracle, ctx, cols * 4, rows * 4, 1, 8, rng, smooth=True)
+    o_org, d_org = twin_plane(r, oracle, ctx, cols * 4, rows * 4, 1, 8, data=np.roll(o_ref.visible, (2, -3), axis=(0, 1)))
+    sel = np.arange(0, pj.size, 37)
+    sj = np.zeros(sel.size, dtype=r.SUBPEL_JOB)
+    for k, i in enumerate(sel):
+        rngv = (C.c_int64 * 4)()
+        L.r1o_mv_range(cols, rows, int(pj[i]["bo_x"]), int(pj[i]["bo_y"]), 8, 8, C.byref(rngv))
+        po = (min(int(pj[i]["bo_x"]) * 4, cols * 4 - 8), min(int(pj[i]["bo_y"]) * 4, rows * 4 - 8))
+        sj[k]["po_x"], sj[k]["po_y"], sj[k]["bsize"], sj[k]["lambda_"] = po[0], po[1], 3, 50
+        sj[k]["mvx_min"], sj[k]["mvx_max"], sj[k]["mvy_min"], sj[k]["mvy_max"] = tuple(rngv)
+    got, cnt = r.get_subset_predictors(ctx, field, prev, pj[sel], cm[sel], ncm[sel])
+    res = r.diamond_search_batch(ctx, d_org, d_ref, sj, got, 8, subpixel=False)
+    for k in range(sel.size):
+        j = sj[k]
+        mv, cost, _ = oracle.diamond_search(o_org, o_ref, (int(j["po_x"]), int(j["po_y"])), 8, 8,
+                                            [(int(m["row"]), int(m["col"])) for m in got[k, :cnt[k]]], [(0, 0), (0, 0)], 50, False, False,
+                                            (int(j["mvx_min"]), int(j["mvx_max"]), int(j["mvy_min"]), int(j["mvy_max"])), False, 8)
+        assert ((int(res[k]["mv"]["row"]), int(res[k]["mv"]["col"])), int(res[k]["cost"])) == (mv, cost), k

@@ -341,3 +341,22 @@ def test_diamond_search_walks_to_the_shift(oracle):
     # every predictor outside the range: the reference would assert; the restatement returns u64::MAX
     mv3, cost3, _ = oracle.diamond_search(org, ref, (64, 48), 32, 32, [(9999, 0)], pmv, 0, False, False, (-8, 8, -8, 8), False, 8)
     assert cost3 >= (1 << 64) - 1 or mv3 != (9999, 0)
+
+
+def test_subset_predictors_and_save_block_motion(oracle):
+    """get_subset_predictors (src/me.rs:82-174): zero MV first, coarse MVs quantised toward zero, zero neighbours dropped,
+    median of the available neighbours; save_block_motion (src/encoder.rs:1432-1444) clips at the field edge"""
+    f = np.zeros((4, 6, 2), dtype=np.int16)
+    oracle.save_block_motion(f, (4, 2), 16, 16, (-13, 27))  # 4x4 MI block hanging over both edges
+    assert (f[2:, 4:] == (-13, 27)).all() and (f[:2] == 0).all() and (f[:, :4] == 0).all()
+    prev = np.zeros((4, 6, 2), dtype=np.int16)
+    prev[1, 1] = (5, 5)
+    p = oracle.get_subset_predictors((0, 0), [(-9, 15)], f, prev)
+    assert p == [(0, 0), (-8, 8)]  # corner: no neighbours, prev right / bottom / co-located are zero
+    f[1, 0] = (16, -8)
+    f[0, 1] = (0, 0)
+    f[0, 2] = (-24, 40)
+    p = oracle.get_subset_predictors((1, 1), [], f, prev)
+    # left (16,-8), top zero (dropped but in the median), top-right (-24,40); median = (-8/3, 32/3) -> (-2, 10) -> (0, 8);
+    # then the co-located previous MV
+    assert p == [(0, 0), (16, -8), (-24, 40), (0, 8), (5, 5)]
