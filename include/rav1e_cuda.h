@@ -170,6 +170,16 @@ int r1c_satd_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
 int r1c_dist_batch_dev(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
                        const r1c_dist_job *d_jobs, int64_t n, int bit_depth, uint32_t *d_out);
 
+/* compute_lookahead_intra_costs, src/api/internal.rs:680-765: out[y*w_in_imp_b + x] = get_satd of the
+ * 8x8 importance block (x, y) of the input luma plane against its DC_PRED prediction.  The
+ * reference hands predict_intra the block's own rectangle as tile_rect, so the variant is always
+ * NONE and the prediction is pred_dc_128 = 128 << (bit_depth - 8) for every block
+ * (src/predict.rs:176-184,206-212,623-633); reproduced as is. */
+int r1c_lookahead_intra_costs(r1c_ctx *ctx, const r1c_plane *input, int w_in_imp_b, int h_in_imp_b,
+                              int bit_depth, uint32_t *out);
+int r1c_lookahead_intra_costs_dev(r1c_ctx *ctx, const r1c_plane *input, int w_in_imp_b, int h_in_imp_b,
+                                  int bit_depth, uint32_t *d_out);
+
 /* ------------------------------------------------------------------------
  * Motion compensation: put_8tap / prep_8tap / mc_avg, src/mc.rs:410-706
  * (semantics of the `_ref` functions :213-408).

@@ -290,6 +290,18 @@ def tx_dist(coeffs, rcoeffs, tx_size):
     return lib().r1o_tx_dist(_p(c), _p(r), tx_size)
 
 
+def lookahead_intra_costs(plane: OPlane, w_in_imp_b, h_in_imp_b, bit_depth):
+    """compute_lookahead_intra_costs, src/api/internal.rs:680-765: tile_rect = the block itself -> PredictionVariant::NONE
+    -> pred_dc_128 (src/predict.rs:176-184,623-633), then get_satd of the 8x8 block"""
+    flat = OPlane(8, 8, 0, 0, 0, 0, plane.px_bytes)
+    flat.data[...] = 128 << (bit_depth - 8)
+    out = np.zeros((h_in_imp_b, w_in_imp_b), dtype=np.uint32)
+    for y in range(h_in_imp_b):
+        for x in range(w_in_imp_b):
+            out[y, x] = satd(plane, x * 8, y * 8, flat, 0, 0, 8, 8)
+    return out
+
+
 def fht(residual, tx_size, tx_type, bit_depth):
     residual = np.ascontiguousarray(residual, dtype=np.int16)
     out = np.empty(residual.size, dtype=np.int32)

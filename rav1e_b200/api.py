@@ -192,6 +192,13 @@ def satd_batch(ctx, plane_org, plane_ref, jobs, bit_depth):
 
 
 # ------------------------------------------------------- motion compensation --
+def lookahead_intra_costs(ctx, plane, w_in_imp_b, h_in_imp_b, bit_depth):
+    """compute_lookahead_intra_costs (src/api/internal.rs:680-765) -> uint32 (h_in_imp_b, w_in_imp_b)"""
+    out = np.zeros((h_in_imp_b, w_in_imp_b), dtype=np.uint32)
+    ctx.check(ctx.lib.r1c_lookahead_intra_costs(ctx.h, plane.h, w_in_imp_b, h_in_imp_b, bit_depth, _p(out)))
+    return out
+
+
 def mv_params(rec_cfg, po, mv):
     """get_params of predict_inter: -> (row_frac, col_frac, src_x, src_y)"""
     lib = capi.load()

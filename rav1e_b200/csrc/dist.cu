@@ -152,6 +152,52 @@ static bool planes_vec_ok(const r1c_plane *p) {
   return (((uintptr_t)p->d_data) & 15) == 0 && (bytes & 15) == 0;
 }
 
+// compute_lookahead_intra_costs, src/api/internal.rs:680-765: SATD of every 8x8 importance block of the
+// input luma plane against its DC_PRED prediction.  The reference passes the block's own rectangle as
+// `tile_rect` (:730-735), so predict_intra sees x = y = 0, picks PredictionVariant::NONE (src/predict.rs:176-184,
+// 206-212) and the prediction is pred_dc_128 for EVERY block: the constant 128 << (bit_depth - 8) (:623-633).
+// One lane per block (the lane-per-tile SATD above with a constant second operand).
+template <int PB, bool VEC>
+__global__ void __launch_bounds__(128) intra_cost_kernel(PlaneView v, int w_imp, int h_imp, int base, uint32_t *out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= w_imp * h_imp) return;
+  const int by = i / w_imp, bx = i - by * w_imp;
+  const uint8_t *p = (const uint8_t *)v.p0 + ((long long)(by * 8) * v.stride + bx * 8) * PB;
+  const int sb = v.stride * PB;
+  int d[8][8];
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    constexpr int NW = 8 * PB / 4;
+    uint32_t x[NW];
+    ld_row<NW, VEC>(p + r * sb, x);
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const uint32_t w = x[k * PB / 4];
+      const int px = PB == 1 ? (int)((w >> (8 * (k & 3))) & 0xff) : (int)((w >> (16 * (k & 1))) & 0xffff);
+      d[r][k] = px - base;
+    }
+    hadamard_regs<8>(d[r]);
+  }
+#pragma unroll
+  for (int m = 1; m < 8; m <<= 1)
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+      if ((r & m) == 0) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+          const int u = d[r][c], w2 = d[r | m][c];
+          d[r][c] = u + w2;
+          d[r | m][c] = u - w2;
+        }
+      }
+  uint32_t acc = 0;
+#pragma unroll
+  for (int r = 0; r < 8; r++)
+#pragma unroll
+    for (int c = 0; c < 8; c++) acc += (uint32_t)abs(d[r][c]);
+  out[i] = (acc + 4) >> 3;
+}
+
 int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
                 const r1c_dist_job *d_jobs, int64_t n, uint32_t *d_out) {
   if (n == 0) return R1C_OK;
@@ -235,4 +281,48 @@ extern "C" int r1c_satd(r1c_ctx *ctx, const r1c_plane *org, int ox, int oy, cons
                         int rx, int ry, int bsize, int bit_depth, uint32_t *out) {
   r1c_dist_job j = {ox, oy, rx, ry, bsize};
   return dist_batch_host(ctx, 1, org, ref, &j, 1, bit_depth, out);
+}
+
+extern "C" int r1c_lookahead_intra_costs_dev(r1c_ctx *ctx, const r1c_plane *input, int w_in_imp_b, int h_in_imp_b,
+                                             int bit_depth, uint32_t *d_out) {
+  if (!ctx || !input) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, bit_depth_ok(bit_depth, input->px_bytes), R1C_ERR_ARG, "bit_depth %d does not match %d-byte pixels", bit_depth, input->px_bytes);
+  R1C_REQUIRE(ctx, w_in_imp_b >= 0 && h_in_imp_b >= 0 && (long long)w_in_imp_b * h_in_imp_b < (1ll << 30) && d_out, R1C_ERR_ARG, "bad importance-block grid");
+  R1C_REQUIRE(ctx, region_in_plane(input->cfg, 0, 0, (int64_t)w_in_imp_b * 8, (int64_t)h_in_imp_b * 8), R1C_ERR_BOUNDS,
+              "the importance-block grid leaves the allocated plane");
+  const int n = w_in_imp_b * h_in_imp_b;
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  const PlaneView v = make_view(input);
+  const int base = 128 << (bit_depth - 8);
+  const bool vec = planes_vec_ok(input);
+  const unsigned grid = (unsigned)((n + 127) / 128);
+  r1c_prof_begin(ctx, R1C_PROF_DIST);
+  if (input->px_bytes == 1) {
+    if (vec) intra_cost_kernel<1, true><<<grid, 128, 0, ctx->stream>>>(v, w_in_imp_b, h_in_imp_b, base, d_out);
+    else intra_cost_kernel<1, false><<<grid, 128, 0, ctx->stream>>>(v, w_in_imp_b, h_in_imp_b, base, d_out);
+  } else {
+    if (vec) intra_cost_kernel<2, true><<<grid, 128, 0, ctx->stream>>>(v, w_in_imp_b, h_in_imp_b, base, d_out);
+    else intra_cost_kernel<2, false><<<grid, 128, 0, ctx->stream>>>(v, w_in_imp_b, h_in_imp_b, base, d_out);
+  }
+  r1c_prof_end(ctx, R1C_PROF_DIST);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
+
+extern "C" int r1c_lookahead_intra_costs(r1c_ctx *ctx, const r1c_plane *input, int w_in_imp_b, int h_in_imp_b, int bit_depth,
+                                         uint32_t *out) {
+  if (!ctx || !input) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, w_in_imp_b >= 0 && h_in_imp_b >= 0 && (long long)w_in_imp_b * h_in_imp_b < (1ll << 30) && out, R1C_ERR_ARG, "bad importance-block grid");
+  const size_t ob = (size_t)w_in_imp_b * h_in_imp_b * sizeof(uint32_t);
+  if (ob == 0) return R1C_OK;
+  void *d_out, *h_out;
+  int rc;
+  if ((rc = r1c_scratch_dev(ctx, 1, ob, &d_out))) return rc;
+  if ((rc = r1c_stage_host(ctx, 1, ob, &h_out))) return rc;
+  if ((rc = r1c_lookahead_intra_costs_dev(ctx, input, w_in_imp_b, h_in_imp_b, bit_depth, (uint32_t *)d_out))) return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(h_out, d_out, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(out, h_out, ob);
+  return R1C_OK;
 }

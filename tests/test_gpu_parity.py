@@ -810,3 +810,16 @@ def test_mv_field_save_and_subset_predictors(r, ctx, oracle):
                                             [(int(m["row"]), int(m["col"])) for m in got[k, :cnt[k]]], [(0, 0), (0, 0)], 50, False, False,
                                             (int(j["mvx_min"]), int(j["mvx_max"]), int(j["mvy_min"]), int(j["mvy_max"])), False, 8)
         assert ((int(res[k]["mv"]["row"]), int(res[k]["mv"]["col"])), int(res[k]["cost"])) == (mv, cost), k
+
+
+@pytest.mark.parametrize("pb,bd", BD)
+def test_lookahead_intra_costs(r, ctx, oracle, pb, bd):
+    """compute_lookahead_intra_costs (src/api/internal.rs:680-765): SATD of every 8x8 block vs pred_dc_128"""
+    rng = np.random.default_rng(2100 + bd)
+    W, H = 200, 120  # w_in_b = 50, h_in_b = 30 -> 25 x 15 importance blocks
+    o, d = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    w_imp, h_imp = (W // 4) // 2, (H // 4) // 2
+    got = r.lookahead_intra_costs(ctx, d, w_imp, h_imp, bd)
+    assert np.array_equal(got, oracle.lookahead_intra_costs(o, w_imp, h_imp, bd))
+    with pytest.raises(r.Rav1eCudaError):
+        r.lookahead_intra_costs(ctx, d, 1000, 1000, bd)
