@@ -95,6 +95,7 @@ def run(ctx, r, torch, ext, flush, reps=3):
     put_ms = prep_ms = avg_ms = 0.0
     kput = kprep = kavg = 0.0
     px_total = 0
+    by_size = {"put_8tap": {}, "prep_8tap": {}, "mc_avg": {}}
     ctx.check(lib.r1c_profile(ctx.h, 1))
     tmp1 = torch.empty(W * H, dtype=torch.int16, device="cuda")
     tmp2 = torch.empty(W * H, dtype=torch.int16, device="cuda")
@@ -122,19 +123,26 @@ def run(ctx, r, torch, ext, flush, reps=3):
         f_avg()
         ctx.sync()
         _kernel_ms(ctx, 3)
+        key = "%dx%d" % (int(j["w"][0]), int(j["h"][0]))
         put_ms += _timed(torch, ext, flush, f_put, reps)
-        kput += _kernel_ms(ctx, 3)[0] / reps
+        k = _kernel_ms(ctx, 3)[0] / reps
+        kput += k
+        by_size["put_8tap"][key] = round(k * 1e3, 1)
         prep_ms += _timed(torch, ext, flush, f_prep, reps)
-        kprep += _kernel_ms(ctx, 3)[0] / reps
+        k = _kernel_ms(ctx, 3)[0] / reps
+        kprep += k
+        by_size["prep_8tap"][key] = round(k * 1e3, 1)
         avg_ms += _timed(torch, ext, flush, f_avg, reps)
-        kavg += _kernel_ms(ctx, 3)[0] / reps
+        k = _kernel_ms(ctx, 3)[0] / reps
+        kavg += k
+        by_size["mc_avg"][key] = round(k * 1e3, 1)
     for name, call_ms, ms, bpp in (("put_8tap", put_ms, kput, 4), ("prep_8tap", prep_ms, kprep, 4),
                                    ("mc_avg", avg_ms, kavg, 6)):
         gbs = px_total * bpp / (ms / 1e3) / 1e9
         out["mc_4k10_" + name] = {
             "workload": "4K 10-bit luma tiled by each of the 19 block sizes, random fracs / filter pairs / +-32 px",
             "value": px_total / 1e6 / (call_ms / 1e3), "unit": "Mpix/s", "ms": call_ms, "pixels": px_total,
-            "kernel_ms": ms, "note": "value / ms = whole _dev call (item count + prefix sum + kernel); "
+            "kernel_ms": ms, "kernel_us_by_block_size": by_size[name], "note": "value / ms = whole _dev call (item count + prefix sum + kernel); "
                                      "roofline = the main kernel alone (19 launches, CUDA events inside the library)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_px": bpp, "peak_source": hbm_how}}

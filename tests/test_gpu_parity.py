@@ -295,6 +295,40 @@ def test_put_8tap_and_avg(r, ctx, oracle, pb, bd):
     assert (d_dst.download()[8:8 + 256, o_dst.cfg.xorigin:o_dst.cfg.xorigin + 384] == (1 << bd) - 1).all()
 
 
+@pytest.mark.parametrize("pb,bd", BD)
+def test_mc_one_block_size_lists(r, ctx, oracle, pb, bd):
+    """job lists of ONE block size take the two-pass tile kernel (mc_tile_kernel): put into disjoint tiles, prep,
+    all four frac cases, every block size incl. segments of 16 rows (h > 16) and short lists / ragged batches"""
+    rng = np.random.default_rng(2300 + bd)
+    W, H = 384, 256
+    o_src, d_src = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, xpad=24, ypad=24)
+    L = oracle.lib()
+    for (w, h) in SIZES_MC[:22] + [(12, 12), (8, 24)]:  # (8, 24): 24 % 16 != 0 -> strip kernel, still one size
+        xs, ys = np.meshgrid(np.arange(0, W - w + 1, w), np.arange(0, H - h + 1, h))
+        keep = rng.permutation(xs.size)[: int(rng.integers(1, min(xs.size, 150) + 1))]
+        n = keep.size
+        jobs = np.zeros(n, dtype=r.MC_JOB)
+        for i, k in enumerate(keep):
+            case = i % 4
+            cf = 0 if case in (0, 1) else int(rng.integers(1, 16))
+            rf = 0 if case in (0, 2) else int(rng.integers(1, 16))
+            jobs[i] = (int(xs.flat[k]), int(ys.flat[k]), int(rng.integers(-24 + 3, W + 24 - w - 4)),
+                       int(rng.integers(-24 + 3, H + 24 - h - 4)), w, h, cf, rf, int(rng.integers(0, 4)), int(rng.integers(0, 4)),
+                       i * w * h)
+        o_dst, d_dst = twin_plane(r, oracle, ctx, W, H, pb, bd, pad=False, xpad=8, ypad=8)
+        r.put_8tap_batch(ctx, d_dst, d_src, jobs, bd)
+        got = np.full(n * w * h + 3, -777, np.int16)
+        r.prep_8tap_batch(ctx, got, d_src, jobs, bd)
+        want = np.full(n * w * h + 3, -777, np.int16)
+        for j in jobs:
+            a = (o_src.ptr(int(j["src_x"]), int(j["src_y"])), o_src.cfg.stride, w, h, int(j["col_frac"]), int(j["row_frac"]),
+                 int(j["mode_x"]), int(j["mode_y"]), bd, pb)
+            L.r1o_put_8tap(o_dst.ptr(int(j["dst_x"]), int(j["dst_y"])), o_dst.cfg.stride, *a)
+            L.r1o_prep_8tap(want[int(j["tmp_off"]):].ctypes.data, *a)
+        assert np.array_equal(d_dst.download(), o_dst.data), (w, h)
+        assert np.array_equal(got, want), (w, h)
+
+
 def test_mc_errors(r, ctx, oracle):
     rng = np.random.default_rng(9)
     _, d = twin_plane(r, oracle, ctx, 64, 64, 1, 8, rng, xpad=8, ypad=8)
