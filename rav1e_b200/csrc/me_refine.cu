@@ -46,8 +46,8 @@ __constant__ signed char c_taps[2][16][8] = {
      {0, 0, -12, 110, 38, -8, 0, 0}, {0, 0, -12, 102, 48, -10, 0, 0}, {0, 0, -14, 94, 58, -10, 0, 0}, {0, 0, -12, 84, 66, -10, 0, 0},
      {0, 0, -12, 76, 76, -12, 0, 0}, {0, 0, -10, 66, 84, -12, 0, 0}, {0, 0, -10, 58, 94, -14, 0, 0}, {0, 0, -10, 48, 102, -12, 0, 0},
      {0, 0, -8, 38, 110, -12, 0, 0}, {0, 0, -6, 28, 116, -10, 0, 0}, {0, 0, -4, 18, 122, -8, 0, 0}, {0, 0, -2, 8, 126, -4, 0, 0}}};
-// (frac 0 never reaches a filter: the unit tap 128 does not fit s8 and the
-//  reference copies instead, src/mc.rs:224-231.)
+// (row 0 is a placeholder: the unit tap 128 does not fit s8; the kernel keeps HALVED taps in shared
+//  memory, where frac 0 is the unit tap 64 -- the reference copies instead, src/mc.rs:224-231.)
 
 // tile list of a full superblock, the same for every superblock: one u32 per
 // S x S tile = slot | bsize << 10 | bx4 << 15 | by4 << 19 | tx4 << 23 | ty4 << 27
@@ -105,59 +105,27 @@ __device__ __forceinline__ int hsum8(const uint8_t *row, int b, uint32_t tlo, ui
   const uint32_t sh = (uint32_t)(b & 3) * 8;
   const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
   const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
-  return dp4a_us(hi, thi, dp4a_us(lo, tlo, 0));
+  return dp4a_us(hi, thi, dp4a_us(lo, tlo, 2));  // + 2: the rounding of the >> 2 that follows (halved taps)
 }
 
-// Predicted column of an S-row tile, put_8tap_ref semantics for bit depth 8
-// (intermediate_bits = 4, src/mc.rs:213-307).  `src` = window address of the tile's
-// top-left source pixel for THIS column (integer part of the MV applied).
-template <int S>
-__device__ __forceinline__ void predict_column(const uint8_t *win, int wstride, int wx, int wy, int cf, int rf,
-                                               uint2 tx, uint2 ty, int (&out)[S]) {
-  const uint8_t *base = win + wy * wstride;
-  if (rf == 0) {
-    if (cf == 0) {
-#pragma unroll
-      for (int r = 0; r < S; r++) out[r] = base[r * wstride + wx];
-    } else {
-#pragma unroll
-      for (int r = 0; r < S; r++) {
-        const int s = hsum8(base + r * wstride, wx - 3, tx.x, tx.y);
-        out[r] = min(max(rshift_round(rshift_round(s, 3), 4), 0), 255);
-      }
-    }
-    return;
-  }
-  int tap[8];
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    tap[k] = (int)(int8_t)(ty.x >> (8 * k));
-    tap[k + 4] = (int)(int8_t)(ty.y >> (8 * k));
-  }
-#pragma unroll
-  for (int y = 0; y < S; y++) out[y] = 0;
-  const uint8_t *top = base - 3 * wstride;
-  if (cf == 0) {
-#pragma unroll
-    for (int r = 0; r < S + 7; r++) {
-      const int mid = top[r * wstride + wx];
-#pragma unroll
-      for (int k = 0; k < 8; k++)
-        if (r - k >= 0 && r - k < S) out[r - k] += mid * tap[k];
-    }
-#pragma unroll
-    for (int y = 0; y < S; y++) out[y] = min(max(rshift_round(out[y], 7), 0), 255);
-  } else {
-#pragma unroll
-    for (int r = 0; r < S + 7; r++) {
-      const int mid = (int)(int16_t)rshift_round(hsum8(top + r * wstride, wx - 3, tx.x, tx.y), 3);
-#pragma unroll
-      for (int k = 0; k < 8; k++)
-        if (r - k >= 0 && r - k < S) out[r - k] += mid * tap[k];
-    }
-#pragma unroll
-    for (int y = 0; y < S; y++) out[y] = min(max(rshift_round(out[y], 11), 0), 255);
-  }
+// put_8tap_ref for bit depth 8 (intermediate_bits = 4, src/mc.rs:213-307) in ONE formula for its four
+// (col_frac, row_frac) cases.  Every REGULAR tap is even, so the filters are kept halved (s8) and frac 0
+// is the unit tap 64:
+//   mid = (sum px * htx + 2) >> 2            == round_shift(sum px * tx, 3), and px << 4 for col_frac 0
+//   out = clamp((sum mid * hty + 512) >> 10)  == round_shift(sum mid * ty, 11); round_shift(mid, 4) for
+//                                               row_frac 0; round_shift(sum px * ty, 7) for col_frac 0
+// which are exactly the reference's four branches (no branch here: the lanes of a warp hold different MVs).
+// The outer taps (0 and 7) of every row of both banks are zero: a candidate whose rows start `off` rows
+// below the first row of its group is the same 8 DP2A taps shifted by `off` bytes.
+__device__ __forceinline__ int dp2a_lo_ss(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_ss(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
 }
 
 // |Hadamard| sum of the S x S tile whose column `d` this thread holds (S threads =
@@ -298,54 +266,92 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
       }
     }
     const int tbx = (bw <= 4 ? 16 : 0), tby = (bh <= 4 ? 16 : 0);
-    // differences of candidate k in this thread's column (zeros when the candidate is not evaluated)
-    auto eval = [&](int k, int (&d)[S]) -> bool {
+    if (ncand == 1) {
+      // step 0, full-pel path: ref block at po + mv / 8, truncating (src/me.rs:828-836)
+      int d[S];
 #pragma unroll
       for (int i = 0; i < S; i++) d[i] = 0;
-      if (!tile_live) return false;
-      int cf = 0, rf = 0, sx, sy;
-      r1c_mv mv;
-      if (step == 0) {  // full-pel path: ref block at po + mv / 8, truncating (src/me.rs:828-836)
-        mv = best;
-        sx = bx + mv.col / 8;
-        sy = by + mv.row / 8;
-      } else {  // predict_inter's get_params (src/predict.rs:267-284), luma
-        mv = step_cand(center, step, k);
-        const int ro = (int)mv.row >> 3, co = (int)mv.col >> 3;
-        rf = ((int)mv.row - (ro << 3)) << 1;
-        cf = ((int)mv.col - (co << 3)) << 1;
-        sx = max(min(bx + co - 3, a.ref.width), -a.ref.xorigin) + 3;
-        sy = max(min(by + ro - 3, a.ref.height), -a.ref.yorigin) + 3;
-      }
-      if (!mv_in_range(a, bx, by, bw, bh, mv)) return false;
-      // window coordinates of this thread's column; clamped for memory safety only
-      // (a legal MV of the search range never leaves the staged window)
-      int wx = sx + tx + c - wx0, wy = sy + ty - wy0;
-      wx = min(max(wx, 3), a.winW - 5);
-      wy = min(max(wy, 3), a.winH - S - 4);
-      const uint2 txw = sh.taps[tbx + cf], tyw = sh.taps[tby + rf];
-      int out[S];
-      predict_column<S>(sh.win, a.wstride, wx, wy, cf, rf, txw, tyw, out);
+      const bool live = tile_live && mv_in_range(a, bx, by, bw, bh, best);
+      if (live) {
+        int wx = bx + best.col / 8 + tx + c - wx0, wy = by + best.row / 8 + ty - wy0;
+        wx = min(max(wx, 0), a.winW - 1);  // clamped for memory safety only
+        wy = min(max(wy, 0), a.winH - S);
+        const uint8_t *p = sh.win + wy * a.wstride + wx;
 #pragma unroll
-      for (int y = 0; y < S; y++) d[y] = oc[y] - out[y];
-      return true;
-    };
-    if (ncand == 1) {
-      int d[S];
-      const bool live = eval(0, d);
+        for (int y = 0; y < S; y++) d[y] = oc[y] - (int)p[y * a.wstride];
+      }
       const uint32_t acc = tile_dist<S>(d, lane, satd);
       if (live && c == 0) atomicAdd(&sh.dist[slot * 8], acc);
     } else {
-#pragma unroll 1
-      for (int k = 0; k < ncand; k += 2) {  // candidates in pairs through one packed Hadamard
-        int d0[S], d1[S];
-        const bool live0 = eval(k, d0);
-        const bool live1 = eval(k + 1, d1);
-        uint32_t a0, a1;
-        tile_dist2<S>(d0, d1, lane, satd, a0, a1);
-        if (c == 0) {
-          if (live0) atomicAdd(&sh.dist[slot * 8 + k], a0);
-          if (live1) atomicAdd(&sh.dist[slot * 8 + k + 1], a1);
+      // The 8 neighbours (i, j) of the centre, walked by column offset j: the (up to) three candidates of
+      // one j have the same col_frac and source column, and their source rows start 0..2 rows apart, so
+      // the S + 7 horizontally filtered rows are computed ONCE per j and every candidate is 4 DP2A per
+      // output on the shared (row n, row n+1) pairs.  Candidates leave in pairs through the packed Hadamard.
+      int dp[S];  // the candidate waiting for its pair partner
+      bool dp_live = false;
+      int dp_k = 0, arrived = 0;  // (compile-time after unrolling)
+#pragma unroll
+      for (int jg = 0; jg < 3; jg++) {
+        // predict_inter's get_params (src/predict.rs:267-284), luma, column part
+        const int mvc = (int)center.col + step * (jg - 1);
+        const int co = mvc >> 3, cf = (mvc - (co << 3)) << 1;
+        const int sx = max(min(bx + co - 3, a.ref.width), -a.ref.xorigin) + 3;
+        // window coordinates; clamped for memory safety only (a legal MV of the search range never
+        // leaves the staged window)
+        const int wx = min(max(sx + tx + c - wx0, 3), a.winW - 5);
+        const int mvr0 = (int)center.row - step;
+        const int sy0 = max(min(by + (mvr0 >> 3) - 3, a.ref.height), -a.ref.yorigin) + 3;
+        const int wyb = min(max(sy0 + ty - wy0, 3), a.winH - S - 5);  // rows wyb - 2 .. wyb + S + 4
+        uint32_t P[S + 6];  // P[n] = (mid[n + 1], mid[n + 2]), mid[n] = filtered window row wyb - 3 + n
+        {
+          const uint2 txw = sh.taps[tbx + cf];
+          const uint8_t *row = sh.win + (wyb - 2) * a.wstride;
+          int prev = hsum8(row, wx - 3, txw.x, txw.y) >> 2;
+#pragma unroll
+          for (int n = 0; n < S + 6; n++) {
+            row += a.wstride;
+            const int cur = hsum8(row, wx - 3, txw.x, txw.y) >> 2;
+            P[n] = __byte_perm((uint32_t)prev, (uint32_t)cur, 0x5410);
+            prev = cur;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+          if (i == 1 && jg == 1) continue;  // the centre itself
+          const int kk = 3 * i + jg, k = kk < 4 ? kk : kk - 1;
+          r1c_mv mv;
+          mv.row = (int16_t)((int)center.row + step * (i - 1));
+          mv.col = (int16_t)mvc;
+          const int ro = (int)mv.row >> 3, rf = ((int)mv.row - (ro << 3)) << 1;
+          const int sy = max(min(by + ro - 3, a.ref.height), -a.ref.yorigin) + 3;
+          const uint32_t sh8 = 8u * (uint32_t)min(max(sy + ty - wy0 - wyb, 0), 2);
+          const uint2 tyw = sh.taps[tby + rf];
+          // taps 1..8 of the filter moved down by `off` rows (byte shifts of the 64-bit tap word)
+          const uint32_t e0 = tyw.x << sh8, e1 = __funnelshift_l(tyw.x, tyw.y, sh8), e2 = __funnelshift_l(tyw.y, 0u, sh8);
+          const uint32_t f0 = __funnelshift_r(e0, e1, 8), f1 = __funnelshift_r(e1, e2, 8);
+          const bool live = tile_live && mv_in_range(a, bx, by, bw, bh, mv);
+          int d[S];
+#pragma unroll
+          for (int t = 0; t < S; t++) {
+            int v = dp2a_lo_ss(P[t], f0, 512);
+            v = dp2a_hi_ss(P[t + 2], f0, v);
+            v = dp2a_lo_ss(P[t + 4], f1, v);
+            v = dp2a_hi_ss(P[t + 6], f1, v);
+            d[t] = live ? oc[t] - min(max(v >> 10, 0), 255) : 0;
+          }
+          if ((arrived++ & 1) == 0) {
+#pragma unroll
+            for (int t = 0; t < S; t++) dp[t] = d[t];
+            dp_live = live;
+            dp_k = k;
+          } else {
+            uint32_t a0, a1;
+            tile_dist2<S>(dp, d, lane, satd, a0, a1);
+            if (c == 0) {
+              if (dp_live) atomicAdd(&sh.dist[slot * 8 + dp_k], a0);
+              if (live) atomicAdd(&sh.dist[slot * 8 + k], a1);
+            }
+          }
         }
       }
     }
@@ -388,13 +394,15 @@ __global__ void __launch_bounds__(RT, 2) me_refine_kernel(RefArgs a) {
       ((uint32_t *)s_win)[i] = v;
     }
     if (tid < 32) {
+      // halved taps; frac 0 = the unit tap 64 (see the unified formula above)
       const signed char *t = &c_taps[tid >> 4][tid & 15][0];
       uint32_t lo = 0, hi = 0;
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        lo |= (uint32_t)(uint8_t)t[k] << (8 * k);
-        hi |= (uint32_t)(uint8_t)t[k + 4] << (8 * k);
+        lo |= (uint32_t)(uint8_t)(signed char)(t[k] / 2) << (8 * k);
+        hi |= (uint32_t)(uint8_t)(signed char)(t[k + 4] / 2) << (8 * k);
       }
+      if ((tid & 15) == 0) lo = 64u << 24, hi = 0;
       s_taps[tid] = make_uint2(lo, hi);
     }
   }
