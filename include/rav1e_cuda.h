@@ -497,6 +497,8 @@ typedef struct {
  * (returns -1 for sizes outside the mask) */
 int64_t r1c_frame_me_count(const r1c_frame_me_params *p);
 int64_t r1c_frame_me_offset(const r1c_frame_me_params *p, int bsize, int32_t *cols, int32_t *rows);
+/* `results` is host memory; when it is page-locked (cudaHostAlloc / cudaHostRegister) the
+ * device writes into it directly, otherwise through the library's pinned stage + a memcpy. */
 int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                  const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results);
 int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,

@@ -248,19 +248,25 @@ extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane 
   Layout l;
   make_layout(p, &l);
   const size_t rb = (size_t)l.total * sizeof(r1c_me_result);
-  void *h_res, *d_res;
+  void *h_res = results, *d_res;
   int rc;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  if ((rc = r1c_stage_host(ctx, 3, rb, &h_res))) return rc;
+  // a page-locked result array is the DMA target itself; pageable memory goes through the pinned stage
+  cudaPointerAttributes attr;
+  const bool direct = cudaPointerGetAttributes(&attr, results) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+  if (!direct) {
+    (void)cudaGetLastError();
+    if ((rc = r1c_stage_host(ctx, 3, rb, &h_res))) return rc;
+  }
   if ((rc = r1c_scratch_dev(ctx, 14, rb, &d_res))) return rc;
   const bool whole = p->sb_row_hi == 0;
   if (!whole) {  // entries outside the shard keep the caller's values
-    memcpy(h_res, results, rb);
+    if (!direct) memcpy(h_res, results, rb);
     R1C_CUDA(ctx, cudaMemcpyAsync(d_res, h_res, rb, cudaMemcpyHostToDevice, ctx->stream));
   }
   if ((rc = r1c_frame_me_dev(ctx, org, ref, p, bit_depth, (r1c_me_result *)d_res))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_res, d_res, rb, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  memcpy(results, h_res, rb);
+  if (!direct) memcpy(results, h_res, rb);
   return R1C_OK;
 }
