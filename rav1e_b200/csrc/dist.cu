@@ -106,9 +106,10 @@ __global__ void __launch_bounds__(128) dist_kernel(DistArgs a) {
   const bool small = w == 4 || h == 4;  // get_satd_ref's tile rule (src/dist.rs:287); SAD uses the same tiling
   const int ls = small ? 2 : 3;
   const int tx = w >> ls, ntiles = tx * (h >> ls);
+  const int lg_tx = __ffs(tx) - 1;  // BlockSize widths are powers of two
   unsigned long long acc = 0;  // 256 tiles x 8*8*64*4095 exceeds u32
   for (int t = sub; t < ntiles; t += G) {
-    const int ty = t / tx, txi = t - ty * tx;
+    const int ty = t >> lg_tx, txi = t - (ty << lg_tx);
     const uint8_t *o = po + (long long)(ty << ls) * so + (txi << ls) * PB;
     const uint8_t *r = pr + (long long)(ty << ls) * sr + (txi << ls) * PB;
     if (small) acc += SATD ? tile_satd<PB, 4, VEC>(o, so, r, sr) : tile_sad<PB, 4, VEC>(o, so, r, sr);

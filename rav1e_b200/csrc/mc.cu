@@ -297,8 +297,13 @@ __device__ __forceinline__ void walk_strip(const McArgs &a, const r1c_mc_job &j,
   const uint32_t need = need_mask<PB>(hfirst, ncols, has_h);
   const int nrows = r1 - r0 + 7;            // source rows r0-3 .. r1+3
   const int ilo = has_v ? 0 : 3, ihi = has_v ? nrows : nrows - 4;  // rows really read
-  RowWords<PB> nxt;
-  load_row_words<PB>(hfirst + (long long)(r0 - 3) * sstride, ilo == 0 ? need : 0u, nxt);
+  // source rows are fetched PF rows ahead of their use: a thread walks its rows one after the other, and with a
+  // single row in flight every row paid a full DRAM latency (ncu: long-scoreboard stalls, 16 warps per SM)
+  constexpr int PF = 8;
+  RowWords<PB> ring[PF];
+  const uint8_t *rowp = hfirst + (long long)(r0 - 3) * sstride;
+#pragma unroll
+  for (int k = 0; k < PF; k++) load_row_words<PB>(rowp + k * sstride, (k >= ilo && k < ihi) ? need : 0u, ring[k]);
   // vertical stage on packed pairs of consecutive intermediate rows:
   //   pr[c][slot] = (mid[i-1], mid[i]) as two i16; out(i-7) = taps . mids(i-7 .. i)
   uint32_t pr[4][8];
@@ -312,9 +317,8 @@ __device__ __forceinline__ void walk_strip(const McArgs &a, const r1c_mc_job &j,
     for (int u = 0; u < 8; u++) {
       const int i = ib8 + u;
       if (i < nrows) {
-        const RowWords<PB> cur = nxt;
-        if (i + 1 < nrows)
-          load_row_words<PB>(hfirst + (long long)(r0 - 3 + i + 1) * sstride, (i + 1 >= ilo && i + 1 < ihi) ? need : 0u, nxt);
+        const RowWords<PB> cur = ring[u % PF];
+        load_row_words<PB>(rowp + (long long)(i + PF) * sstride, (i + PF >= ilo && i + PF < ihi) ? need : 0u, ring[u % PF]);
         int sum[4], mid[4];
         hsum_words<PB>(cur, mis, tx0, tx1, hrnd, sum);
 #pragma unroll
@@ -381,40 +385,74 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   const int ib = a.bit_depth == 12 ? 2 : 4;
   const int maxv = (1 << a.bit_depth) - 1;
   const int ipj = a.offs[a.n + 1] == -a.offs[a.n + 2] ? (int)a.offs[a.n + 1] : 0;  // min == max items per job
-  // item = 4 pixels of one row: fully parallel, 8-byte loads / stores
-  for (long long item = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item < total;
-       item += (long long)gridDim.x * MC_THREADS) {
-    const long long ji = ipj ? (long long)((unsigned long long)item / (unsigned)ipj) : find_job(a.offs, a.n, item);
-    const r1c_avg_job j = a.jobs[ji];
-    const int local = ipj ? (int)(item - ji * ipj) : (int)(item - a.offs[ji]);
-    const int nstrips = (j.w + 3) >> 2;
-    const int r = local / nstrips, strip = local - r * nstrips;
-    const int x0 = strip * 4, ncols = min(4, j.w - x0);
-    const long long o = (long long)j.tmp_off + (long long)r * j.w + x0;
-    uint8_t *d = a.dst0 + ((long long)(j.dst_y + r) * a.dst_stride + j.dst_x + x0) * PB;
-    int v[4];
-    if (ncols == 4 && (o & 3) == 0) {
-      const uint2 p = __ldg((const uint2 *)(a.t1 + o)), q = __ldg((const uint2 *)(a.t2 + o));
-      v[0] = (int)(int16_t)p.x + (int)(int16_t)q.x;
-      v[1] = ((int)p.x >> 16) + ((int)q.x >> 16);
-      v[2] = (int)(int16_t)p.y + (int)(int16_t)q.y;
-      v[3] = ((int)p.y >> 16) + ((int)q.y >> 16);
-    } else {
+  // item = 4 pixels of one row: fully parallel, 8-byte loads / stores.  A thread takes U items per trip and issues
+  // all their job reads, then all their loads, before the arithmetic: the kernel lasts only a few DRAM latencies, so
+  // the number of independent requests in flight per thread is what sets its bandwidth.
+  constexpr int U = 4;
+  const int lg_ipj = ipj > 0 && (ipj & (ipj - 1)) == 0 ? __ffs(ipj) - 1 : -1;  // every BlockSize: a shift
+  const long long stride = (long long)gridDim.x * MC_THREADS;
+  for (long long item0 = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item0 < total; item0 += U * stride) {
+    long long o[U];
+    uint8_t *d[U];
+    int ncols[U];
+    bool live[U], vec[U];
 #pragma unroll
-      for (int c = 0; c < 4; c++) v[c] = c < ncols ? (int)a.t1[o + c] + (int)a.t2[o + c] : 0;
+    for (int u = 0; u < U; u++) {
+      const long long item = item0 + u * stride;
+      live[u] = item < total;
+      const long long it = live[u] ? item : item0;
+      // (ncu: with a 64-bit division per item the kernel was bound by its ~250 instructions per item, not by memory)
+      const long long ji = lg_ipj >= 0 ? (it >> lg_ipj)
+                           : ipj      ? (long long)((unsigned long long)it / (unsigned)ipj)
+                                      : find_job(a.offs, a.n, it);
+      static_assert(sizeof(r1c_avg_job) == 16, "r1c_avg_job is read as one 16-byte word");
+      const uint4 jw = __ldg((const uint4 *)(a.jobs + ji));  // dst_x, dst_y, w | h << 16, tmp_off
+      const long long toff = (long long)(int)jw.w;
+      const int jx = (int)jw.x, jy = (int)jw.y, w = (int)(int16_t)(jw.z & 0xffffu);
+      const int local = ipj ? (int)(it - ji * ipj) : (int)(it - a.offs[ji]);
+      const int nstrips = (w + 3) >> 2;
+      const int r = (nstrips & (nstrips - 1)) == 0 ? local >> (__ffs(nstrips) - 1) : local / nstrips;
+      const int strip = local - r * nstrips;
+      const int x0 = strip * 4;
+      ncols[u] = min(4, w - x0);
+      o[u] = toff + (long long)r * w + x0;
+      d[u] = a.dst0 + ((long long)(jy + r) * a.dst_stride + jx + x0) * PB;
+      vec[u] = ncols[u] == 4 && (o[u] & 3) == 0;
     }
+    uint2 p[U], q[U];
 #pragma unroll
-    for (int c = 0; c < 4; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
-    if (ncols == 4 && ((uintptr_t)d & (4 * PB - 1)) == 0) {
-      if (PB == 1) *(uint32_t *)d = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
-      else *(uint2 *)d = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
-    } else {
+    for (int u = 0; u < U; u++)
+      if (live[u] && vec[u]) {
+        p[u] = __ldg((const uint2 *)(a.t1 + o[u]));
+        q[u] = __ldg((const uint2 *)(a.t2 + o[u]));
+      }
 #pragma unroll
-      for (int c = 0; c < 4; c++)
-        if (c < ncols) {
-          if (PB == 1) d[c] = (uint8_t)v[c];
-          else ((uint16_t *)d)[c] = (uint16_t)v[c];
-        }
+    for (int u = 0; u < U; u++) {
+      if (!live[u]) continue;
+      int v[4];
+      if (vec[u]) {
+        v[0] = (int)(int16_t)p[u].x + (int)(int16_t)q[u].x;
+        v[1] = ((int)p[u].x >> 16) + ((int)q[u].x >> 16);
+        v[2] = (int)(int16_t)p[u].y + (int)(int16_t)q[u].y;
+        v[3] = ((int)p[u].y >> 16) + ((int)q[u].y >> 16);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++) v[c] = c < ncols[u] ? (int)a.t1[o[u] + c] + (int)a.t2[o[u] + c] : 0;
+      }
+#pragma unroll
+      for (int c = 0; c < 4; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
+      uint8_t *dp = d[u];
+      if (ncols[u] == 4 && ((uintptr_t)dp & (4 * PB - 1)) == 0) {
+        if (PB == 1) *(uint32_t *)dp = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+        else *(uint2 *)dp = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+          if (c < ncols[u]) {
+            if (PB == 1) dp[c] = (uint8_t)v[c];
+            else ((uint16_t *)dp)[c] = (uint16_t)v[c];
+          }
+      }
     }
   }
 }
@@ -603,6 +641,7 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   long long *d_offs;
+  R1C_REQUIRE(ctx, ((uintptr_t)d_jobs & 15) == 0, R1C_ERR_ARG, "mc_avg: the job array must be 16-byte aligned");
   int rc = build_offsets<r1c_avg_job, 1>(ctx, d_jobs, n, &d_offs);
   if (rc) return rc;
   AvgArgs a;
