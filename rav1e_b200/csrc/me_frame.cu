@@ -209,7 +209,7 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
   const r1c_subpel_job *d_sub = (const r1c_subpel_job *)ctx->frame_me.d_subjobs;
   // 1. full-pel search, scattered straight into the frame layout when me_sb2 takes it
   int direct = 0;
-  if ((rc = r1c_sb2_search(ctx, org, ref, &sp, d_sbs, n_sb, d_results, d_map, n, &direct))) return rc;
+  if ((rc = r1c_sb2_search(ctx, org, ref, &sp, bit_depth, d_sbs, n_sb, d_results, d_map, n, &direct))) return rc;
   if (!direct) {
     void *d_sbres;
     if ((rc = r1c_scratch_dev(ctx, 12, (size_t)n_sb * R1C_SB_RESULTS * sizeof(r1c_me_result), &d_sbres))) return rc;

@@ -399,13 +399,13 @@ void build_big_table(BigBlk *t) {
   add(R1C_BLOCK_64X16, 0);
 }
 
-int launch_sb(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p,
+int launch_sb(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p, int bit_depth,
               const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results) {
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   {
     int handled = 0;
-    const int rc2 = r1c_sb2_search(ctx, org, ref, p, d_jobs, n, d_results, nullptr, 0, &handled);
+    const int rc2 = r1c_sb2_search(ctx, org, ref, p, bit_depth, d_jobs, n, d_results, nullptr, 0, &handled);
     if (rc2 || handled) return rc2;
   }
   static bool table_done[64] = {false};
@@ -469,7 +469,7 @@ extern "C" int r1c_me_sb_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c
   int rc = check_sb(ctx, org, ref, params, bit_depth, n);
   if (rc) return rc;
   R1C_REQUIRE(ctx, n == 0 || (d_jobs && d_results), R1C_ERR_ARG, "null job/result array");
-  return launch_sb(ctx, org, ref, params, d_jobs, n, d_results);
+  return launch_sb(ctx, org, ref, params, bit_depth, d_jobs, n, d_results);
 }
 
 extern "C" int r1c_me_sb_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
@@ -503,7 +503,7 @@ extern "C" int r1c_me_sb_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_pla
   memcpy(h_res, results, rb);  // entries the kernel does not emit keep the caller's values
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
   R1C_CUDA(ctx, cudaMemcpyAsync(d_res, h_res, rb, cudaMemcpyHostToDevice, ctx->stream));
-  if ((rc = launch_sb(ctx, org, ref, params, (const r1c_sb_job *)d_jobs, n, (r1c_me_result *)d_res))) return rc;
+  if ((rc = launch_sb(ctx, org, ref, params, bit_depth, (const r1c_sb_job *)d_jobs, n, (r1c_me_result *)d_res))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_res, d_res, rb, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(results, h_res, rb);

@@ -1,4 +1,4 @@
-// me_sb2.cu -- whole-superblock full search, second generation (8-bit planes).
+// me_sb2.cu -- whole-superblock full search, second generation (8-bit planes, and u16 planes up to 10 bits).
 //
 // Same contract as me_sb.cu (the result of the reference's full_search,
 // src/me.rs:943-990, for every block of every size inside a 64x64 region against
@@ -25,9 +25,14 @@
 //    raster tie-break), turns it into (mv, cost) and scatters it either to the
 //    [job][849] layout of r1c_me_sb_batch or straight to a caller-supplied map
 //    (whole-frame layout of r1c_frame_me).
-// INT-bound: per (pixel, candidate) 1/4 VABSDIFF4; planes are read once per work
-// item from L2.  Falls back to me_sb.cu for 16-bit planes, step 2, huge lambda
-// or windows too small / too large for this layout.
+//  * u16 planes (template PB = 2, bit depth <= 10): two pixels per window word, two pixel
+//    phases; |a - b| of a packed pair = VIMNMX.U16x2 max - min; a cell accumulates 8 pixels
+//    per 16-bit half and is folded once per candidate.  An 8x8 SAD needs 16 bits there, so
+//    the key keeps 6 bits of seq (12 candidate rows per chunk, 11 chunks for +-64) and 18
+//    bits of sad + rl >> 8; SAD * 256 + rl of a 64x64 block still fits 32 bits (not at 12 bits).
+// INT-bound: per (pixel, candidate) 1/4 VABSDIFF4 (u8) or 7/4 full-rate instructions (u16);
+// planes are read once per work item from L2.  Falls back to me_sb.cu for 12-bit planes,
+// step 2, huge lambda or windows too small / too large for this layout.
 #include <stdlib.h>
 
 #include "me_common.cuh"
@@ -35,8 +40,16 @@
 namespace {
 
 constexpr int T2 = 512;
-constexpr int SEQ_BITS = 9;
-constexpr int KSHIFT = 8 + SEQ_BITS;  // sad field of the 32-bit key
+// per pixel size: u8 planes (PB 1) and 10-bit u16 planes (PB 2)
+template <int PB>
+struct Px {
+  // The 8x8 SAD of the packed-key blocks is < 2^14 at 8 bits but needs 16 bits at 10: the 10-bit kernel has 6
+  // bits of `seq` (candidate rows are cut into more chunks) and 18 bits of sad + rl >> 8.
+  static constexpr int SEQ_BITS = PB == 1 ? 9 : 6;
+  static constexpr int KSHIFT = 8 + SEQ_BITS;  // sad field of the 32-bit key
+  static constexpr int PXW = 4 / PB;           // pixels per window word = phases of the staged window
+  static constexpr int NWQ = 4 * PB;           // words of a 16-pixel quadrant row
+};
 constexpr uint32_t NONE32 = 0xffffffffu;
 constexpr int NSLOT = 849;
 
@@ -82,7 +95,7 @@ __device__ __forceinline__ bool mv_ok(const Geo2 &g, int bx, int by, int bw, int
 }
 
 // in-quadrant aggregation + running minima of one candidate
-template <bool MASKED>
+template <bool MASKED, int KSHIFT>
 __device__ __forceinline__ void quad_update(const uint32_t (&cell)[4][4], uint32_t rck, uint32_t rl, uint32_t seq,
                                             uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                             uint32_t (&xs)[5], const Geo2 &g, int ox, int oy) {
@@ -211,53 +224,91 @@ __host__ __device__ inline BigSlot big_slot(int q, int s) {
   return b;
 }
 
-template <bool MASKED, int RSW>
+// |a - b| of two packed u16 pairs (10-bit pixels): max - min, no borrow between the halves
+__device__ __forceinline__ uint32_t absdiff2(uint32_t a, uint32_t b) { return __vmaxu2(a, b) - __vminu2(a, b); }
+
+template <bool MASKED, int RSW, int PB>
 __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
                                            const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                            uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
   const int qx = q & 3, qy = q >> 2;
+  constexpr int SEQ_BITS = Px<PB>::SEQ_BITS, KSHIFT = Px<PB>::KSHIFT, PXW = Px<PB>::PXW, NWQ = Px<PB>::NWQ;
   const int rsw = RSW ? RSW : a.rsw;
   const int sdx = 32 % ck.NX, sj = 32 / ck.NX;
   const int hp = a.p.allow_high_precision_mv;
   const int M2 = 2 * a.M;
   // slot of this lane: f = it * 32 + lane = j * NX + dx
   int f = lane, j = lane / ck.NX, dx = lane - j * ck.NX;
-  const uint32_t *orow = s_org + (qy * 16) * 16 + qx * 4;
+  const uint32_t *orow = s_org + (qy * 16) * (16 * PB) + qx * NWQ;
   // role of this warp in the cross-quadrant phase
   const int rg = q >> 2, ri = q & 3;
   for (int it = 0; it < ck.iters; it++) {
     const int dyA = min(2 * j, ck.NYc - 2);
-    // window word (row, w) of byte phase p lives at s_ref[(row * rsw + w) * 4 + p]
-    const uint32_t *rp = s_ref + (((qy * 16 + dyA) * rsw + qx * 4 + (dx >> 2)) << 2) + (dx & 3);
+    // window word (row, w) of pixel phase p lives at s_ref[(row * rsw + w) * PXW + p]
+    const uint32_t *rp = s_ref + ((qy * 16 + dyA) * rsw + qx * NWQ + dx / PXW) * PXW + dx % PXW;
     // ---- 2 x 16 cell SADs: candidate A = (dx, dyA), B = (dx, dyA + 1) ----------------
     uint32_t cA[4][4], cB[4][4];
 #pragma unroll
     for (int i = 0; i < 4; i++)
 #pragma unroll
       for (int k = 0; k < 4; k++) cA[i][k] = cB[i][k] = 0;
-    uint4 oprev = make_uint4(0, 0, 0, 0);
+    if (PB == 1) {
+      uint4 oprev = make_uint4(0, 0, 0, 0);
 #pragma unroll
-    for (int r = 0; r < 17; r++) {
-      const uint32_t *rr = rp + r * rsw * 4;
-      const uint32_t w0 = rr[0], w1 = rr[4], w2 = rr[8], w3 = rr[12];
-      if (r >= 1) {
-        const int i = (r - 1) >> 2;
-        cB[i][0] = me::sad4_acc(oprev.x, w0, cB[i][0]);
-        cB[i][1] = me::sad4_acc(oprev.y, w1, cB[i][1]);
-        cB[i][2] = me::sad4_acc(oprev.z, w2, cB[i][2]);
-        cB[i][3] = me::sad4_acc(oprev.w, w3, cB[i][3]);
+      for (int r = 0; r < 17; r++) {
+        const uint32_t *rr = rp + r * rsw * 4;
+        const uint32_t w0 = rr[0], w1 = rr[4], w2 = rr[8], w3 = rr[12];
+        if (r >= 1) {
+          const int i = (r - 1) >> 2;
+          cB[i][0] = me::sad4_acc(oprev.x, w0, cB[i][0]);
+          cB[i][1] = me::sad4_acc(oprev.y, w1, cB[i][1]);
+          cB[i][2] = me::sad4_acc(oprev.z, w2, cB[i][2]);
+          cB[i][3] = me::sad4_acc(oprev.w, w3, cB[i][3]);
+        }
+        if (r < 16) {
+          const uint4 o = *(const uint4 *)(orow + r * 16);
+          const int i = r >> 2;
+          cA[i][0] = me::sad4_acc(o.x, w0, cA[i][0]);
+          cA[i][1] = me::sad4_acc(o.y, w1, cA[i][1]);
+          cA[i][2] = me::sad4_acc(o.z, w2, cA[i][2]);
+          cA[i][3] = me::sad4_acc(o.w, w3, cA[i][3]);
+          oprev = o;
+        }
       }
-      if (r < 16) {
-        const uint4 o = *(const uint4 *)(orow + r * 16);
-        const int i = r >> 2;
-        cA[i][0] = me::sad4_acc(o.x, w0, cA[i][0]);
-        cA[i][1] = me::sad4_acc(o.y, w1, cA[i][1]);
-        cA[i][2] = me::sad4_acc(o.z, w2, cA[i][2]);
-        cA[i][3] = me::sad4_acc(o.w, w3, cA[i][3]);
-        oprev = o;
+    } else {
+      // u16 pixels: two per word, |a - b| on packed pairs (VIMNMX.U16x2 x2 + subtract); a cell accumulates
+      // 8 pixels in each 16-bit half (<= 8 * 4095) and is folded after the loop.  The quadrant row is taken
+      // in two 8-pixel halves to keep the live registers down; org words are the same address for the
+      // whole warp (broadcast), so B re-reads its row instead of keeping it.
+#pragma unroll
+      for (int r = 0; r < 17; r++) {
+#pragma unroll
+        for (int hf = 0; hf < 2; hf++) {
+          const uint32_t *rr = rp + (r * rsw + 4 * hf) * 2;
+          const uint32_t w0 = rr[0], w1 = rr[2], w2 = rr[4], w3 = rr[6];
+          if (r >= 1) {
+            const uint4 o = *(const uint4 *)(orow + (r - 1) * 32 + 4 * hf);
+            const int i = (r - 1) >> 2;
+            cB[i][2 * hf] += absdiff2(o.x, w0) + absdiff2(o.y, w1);
+            cB[i][2 * hf + 1] += absdiff2(o.z, w2) + absdiff2(o.w, w3);
+          }
+          if (r < 16) {
+            const uint4 o = *(const uint4 *)(orow + r * 32 + 4 * hf);
+            const int i = r >> 2;
+            cA[i][2 * hf] += absdiff2(o.x, w0) + absdiff2(o.y, w1);
+            cA[i][2 * hf + 1] += absdiff2(o.z, w2) + absdiff2(o.w, w3);
+          }
+        }
       }
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          cA[i][k] = (cA[i][k] & 0xffffu) + (cA[i][k] >> 16);
+          cB[i][k] = (cB[i][k] & 0xffffu) + (cB[i][k] >> 16);
+        }
     }
     // ---- rate terms ---------------------------------------------------------------------
     const int ox = ck.cxlo + dx, oyA = ck.cylo + ck.row0 + dyA;
@@ -271,8 +322,8 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
     const uint32_t rckB = ((rlB >> 8) << KSHIFT) | ((rlB & 255u) << SEQ_BITS) | seqB;
 
     uint32_t xsA[5], xsB[5];
-    quad_update<MASKED>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
-    quad_update<MASKED>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
+    quad_update<MASKED, KSHIFT>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
+    quad_update<MASKED, KSHIFT>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
 
     // ---- exchange of the quadrant partial sums: xb[part][quadrant][A lanes | B lanes] ---
     uint32_t *xb = s_x + (it & 1) * (5 * 16 * 64);
@@ -381,8 +432,9 @@ __device__ __forceinline__ unsigned long long warp_best(uint32_t cost, uint32_t 
   return cmin == NONE32 ? ~0ull : (((unsigned long long)cmin << 32) | rmin);
 }
 
-template <int RSW>
+template <int RSW, int PB>
 __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
+  constexpr int SEQ_BITS = Px<PB>::SEQ_BITS, PXW = Px<PB>::PXW;
   extern __shared__ __align__(16) unsigned char smem[];
   const long long wi = blockIdx.x;
   const long long ji = wi / a.split;
@@ -404,8 +456,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   ck.cxlo = cx - Rx;
   ck.cylo = cy - Ry;
 
-  uint32_t *s_org = (uint32_t *)smem;  // [64][16] words
-  uint32_t *s_ref = s_org + 64 * 16;   // [nrows][rsw][4 byte phases]
+  uint32_t *s_org = (uint32_t *)smem;       // [64][16 * PB] words
+  uint32_t *s_ref = s_org + 64 * 16 * PB;   // [nrows][rsw][PXW pixel phases]
   uint32_t *s_x = s_ref + a.csz;       // 2 x [5][16][64]
   const int nrows = ck.NYc + 63;
 
@@ -417,32 +469,35 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     const int oymin = -a.org.yorigin, oymax = a.org.alloc_h - a.org.yorigin - 1;
     for (int i = tid; i < 64 * 64; i += T2) {
       const int y = min(max(job.po_y + (i >> 6), oymin), oymax), x = min(max(job.po_x + (i & 63), oxmin), oxmax);
-      ((uint8_t *)s_org)[i] = po[(long long)y * a.org.stride + x];
+      if (PB == 1) ((uint8_t *)s_org)[i] = po[(long long)y * a.org.stride + x];
+      else ((uint16_t *)s_org)[i] = ((const uint16_t *)po)[(long long)y * a.org.stride + x];
     }
     const int rxmin = -a.ref.xorigin, rxmax = a.ref.alloc_w - a.ref.xorigin - 1;
     const int rymin = -a.ref.yorigin, rymax = a.ref.alloc_h - a.ref.yorigin - 1;
     const int x0 = job.po_x + ck.cxlo, y0 = job.po_y + ck.cylo + ck.row0;
-    // one thread = one word (4 pixels) of one row
+    // one thread = one word (4 / PB pixels) of one row
     for (int wy = q; wy < nrows; wy += T2 / 32) {
       const int y = min(max(y0 + wy, rymin), rymax);
-      const uint8_t *row = pr + (long long)y * a.ref.stride;
+      const uint8_t *row = pr + (long long)y * a.ref.stride * PB;
       for (int w = lane; w < rsw; w += 32) {
         uint32_t v = 0;
 #pragma unroll
-        for (int b = 0; b < 4; b++) v |= (uint32_t)row[min(max(x0 + 4 * w + b, rxmin), rxmax)] << (8 * b);
-        s_ref[(wy * rsw + w) << 2] = v;
+        for (int b = 0; b < PXW; b++) {
+          const int x = min(max(x0 + PXW * w + b, rxmin), rxmax);
+          v |= (PB == 1 ? (uint32_t)row[x] : (uint32_t)((const uint16_t *)row)[x]) << (8 * PB * b);
+        }
+        s_ref[(wy * rsw + w) * PXW] = v;
       }
     }
   }
   __syncthreads();
-  // ---- phases 1..3: the same row shifted left by 1..3 bytes ------------------------------
+  // ---- the other phases: the same row shifted left by 1..PXW-1 pixels --------------------
   for (int wy = q; wy < nrows; wy += T2 / 32)
     for (int w = lane; w < rsw; w += 32) {
       const int i = wy * rsw + w;
-      const uint32_t lo = s_ref[i << 2], hi = (w + 1 < rsw) ? s_ref[(i + 1) << 2] : 0u;
-      s_ref[(i << 2) + 1] = __funnelshift_r(lo, hi, 8);
-      s_ref[(i << 2) + 2] = __funnelshift_r(lo, hi, 16);
-      s_ref[(i << 2) + 3] = __funnelshift_r(lo, hi, 24);
+      const uint32_t lo = s_ref[i * PXW], hi = (w + 1 < rsw) ? s_ref[(i + 1) * PXW] : 0u;
+#pragma unroll
+      for (int ph = 1; ph < PXW; ph++) s_ref[i * PXW + ph] = __funnelshift_r(lo, hi, 8 * PB * ph);
     }
   __syncthreads();
 
@@ -469,8 +524,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     pc[i] = bc[i] = NONE32;
     ps[i] = bs[i] = 0;
   }
-  if (fast) sb2_search<false, RSW>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
-  else sb2_search<true, RSW>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
 
   // ---- reduce over the 32 lanes and write the partial keys ------------------------------
   unsigned long long *out = a.partial + wi * NSLOT;
@@ -575,14 +630,16 @@ struct Sb2Plan {
   int split, rpc, rsw, csz, M;
   size_t smem;
 };
-static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, int64_t n, Sb2Plan *pl) {
-  if (px_bytes != 1 || p->step != 1) return false;
+static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, int bit_depth, int64_t n, Sb2Plan *pl) {
+  // u16 planes up to 10 bits: packed-key SADs (8x8 <= 64 * 1023) and SAD * 256 + rl of a 64x64 block fit 32 bits
+  if ((px_bytes != 1 && !(px_bytes == 2 && bit_depth <= 10)) || p->step != 1) return false;
   if (p->lambda > 60000u) return false;  // rl >> 8 must stay below 2^14 (rate <= 65)
+  const int seq_bits = px_bytes == 1 ? Px<1>::SEQ_BITS : Px<2>::SEQ_BITS, pxw = 4 / px_bytes;
   const int NX = 2 * p->range_x + 1, NY = 2 * p->range_y + 1;
   if (p->range_y < 1 || NX > 255) return false;
   const int M = (NX + 31) / 32;
   const int winW = 64 + 2 * p->range_x;
-  const int rsw = (winW + 3) / 4;  // a copy row holds bytes [p, p + 4 * rsw)
+  const int rsw = (winW + pxw - 1) / pxw;  // a copy row holds pixels [p, p + pxw * rsw)
   const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
   for (int split = 1; split <= 16; split++) {
     const int rpc = 2 * ((NY + 2 * split - 1) / (2 * split));
@@ -591,11 +648,11 @@ static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, i
     const int last = NY - (split - 1) * rpc;
     if (last < 2) continue;
     const int NP = rpc / 2;
-    if (NP * 2 * M > (1 << SEQ_BITS)) continue;  // seq field
+    if (NP * 2 * M > (1 << seq_bits)) continue;  // seq field
     if ((long long)(last + 1) / 2 * NX < 32) continue;  // every lane needs a slot of its own
     const int nrows = rpc + 63;
-    const int csz = nrows * rsw * 4;
-    const size_t smem = (size_t)64 * 64 + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    const int csz = nrows * rsw * pxw;
+    const size_t smem = (size_t)64 * 64 * px_bytes + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
     if (smem > 220 * 1024) continue;
     // enough work items to balance the SMs: stop once the tail is small
     pl->split = split;
@@ -612,13 +669,14 @@ static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, i
 }
 
 // search + finalize.  d_map == nullptr: results is the [n][849] layout.
-int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p,
+int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p, int bit_depth,
                    const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results, const int2 *d_map, int64_t n_map,
                    int *handled) {
   *handled = 0;
   Sb2Plan pl = {};
   const char *force = getenv("R1C_ME_SB_V1");
-  if ((force && force[0] == '1') || !sb2_plan(ctx, p, org->px_bytes, n, &pl)) return R1C_OK;
+  if ((force && force[0] == '1') || org->px_bytes != ref->px_bytes || !sb2_plan(ctx, p, org->px_bytes, bit_depth, n, &pl))
+    return R1C_OK;
   *handled = 1;
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -637,7 +695,9 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   a.rsw = pl.rsw;
   a.csz = pl.csz;
   a.M = pl.M;
-  auto kern = pl.rsw == 48 ? me_sb2_kernel<48> : me_sb2_kernel<0>;  // 48: the +-64 px window
+  // 48 / 96 words per window row: the +-64 px window
+  auto kern = org->px_bytes == 1 ? (pl.rsw == 48 ? me_sb2_kernel<48, 1> : me_sb2_kernel<0, 1>)
+                                 : (pl.rsw == 96 ? me_sb2_kernel<96, 2> : me_sb2_kernel<0, 2>);
   R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   r1c_prof_begin(ctx, R1C_PROF_ME_SB);
   kern<<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);

@@ -471,6 +471,38 @@ def test_me_sb_matches_per_block_full_search(r, ctx, oracle, pb, bd, step, lam):
     assert n > 849 * 6
 
 
+@pytest.mark.parametrize("pb,bd,kind", [(2, 10, "extremes"), (2, 10, "smooth"), (1, 8, "extremes")])
+def test_me_sb_pm64_window(r, ctx, oracle, pb, bd, kind):
+    """the +-64 px window of the headline workload (the specialised kernel instances), 8- and 10-bit; `extremes` =
+    pixels at 0 / max only, so block SADs reach their largest values (key fields, 16-bit half accumulators)"""
+    rng = np.random.default_rng(77 + bd)
+    W, H = 256, 192
+    maxv = (1 << bd) - 1
+    if kind == "extremes":
+        ref_px = rng.integers(0, 2, size=(H, W)) * maxv
+        org_px = np.where(rng.random((H, W)) < 0.9, maxv - np.roll(ref_px, (3, -5), axis=(0, 1)), ref_px)
+    else:
+        ref_px = None
+    if ref_px is None:
+        o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+        noisy = np.roll(o_ref.visible, (-37, 51), axis=(0, 1)).astype(np.int64) + rng.integers(-3, 4, size=(H, W))
+        o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.clip(noisy, 0, maxv))
+    else:
+        o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, data=ref_px)
+        o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=org_px)
+    params = r.make_sb_params(W // 4, H // 4, 64, 64, 1, 160)
+    pos = [(64, 64), (192, 128)]  # interior, and the bottom-right corner (masked candidates)
+    jobs = np.zeros(len(pos), dtype=r.SB_JOB)
+    for i, (x, y) in enumerate(pos):
+        jobs[i]["po_x"], jobs[i]["po_y"], jobs[i]["bsize_mask"] = x, y, 0x3FFFFF
+        jobs[i]["pmv"][0] = (int(rng.integers(-200, 200)), int(rng.integers(-200, 200)))
+        jobs[i]["pmv"][1] = (int(rng.integers(-200, 200)), int(rng.integers(-200, 200)))
+    res = np.zeros(len(pos) * r.SB_RESULTS, dtype=r.ME_RESULT)
+    res["cost"] = 12345
+    out = r.me_sb_batch(ctx, d_org, d_ref, params, jobs, bd, res)
+    assert _check_sb(r, oracle, o_org, o_ref, params, jobs, out, W, H) == 849 * 2
+
+
 def test_me_sb_flat_ties_and_mask(r, ctx, oracle):
     o, d = twin_plane(r, oracle, ctx, 128, 128, 1, 8)  # all 128: every candidate ties at SAD 0
     params = r.make_sb_params(32, 32, 9, 7, 1, 0)
