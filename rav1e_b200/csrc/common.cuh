@@ -87,9 +87,9 @@ int r1c_scratch_dev(r1c_ctx *ctx, int slot, size_t bytes, void **out);
 int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p, int bit_depth,
                    const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results, const int2 *d_map, int64_t n_map,
                    int *handled);
-// me_refine.cu: fused sub-pel tail of r1c_frame_me for 8-bit planes
+// me_refine.cu: fused sub-pel tail of r1c_frame_me for 8-bit and 10-bit planes
 int r1c_refine_frame(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_frame_me_params *p,
-                     const long long *off, const int *cols, const int *rows, const r1c_sb_job *d_sbs, int64_t n_sb,
+                     int bit_depth, const long long *off, const int *cols, const int *rows, const r1c_sb_job *d_sbs, int64_t n_sb,
                      r1c_me_result *d_results, int *handled);
 int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
                          int64_t n, int bit_depth);

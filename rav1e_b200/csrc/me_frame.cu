@@ -225,7 +225,7 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
     long long off[R1C_BLOCK_SIZES_ALL];
     for (int b = 0; b < R1C_BLOCK_SIZES_ALL; b++) off[b] = l.off[b];
     int fused = 0;
-    if ((rc = r1c_refine_frame(ctx, org, ref, p, off, l.cols, l.rows, d_sbs, n_sb, d_results, &fused))) return rc;
+    if ((rc = r1c_refine_frame(ctx, org, ref, p, bit_depth, off, l.cols, l.rows, d_sbs, n_sb, d_results, &fused))) return rc;
     if (fused) return R1C_OK;
   }
   if (whole)  // job i <-> frame slot i: refine in place

@@ -1,5 +1,5 @@
 // me_refine.cu -- the tail of MotionEstimation::motion_estimation (src/me.rs:232-271)
-// for every block of a frame, fused into ONE kernel (8-bit planes):
+// for every block of a frame, fused into ONE kernel (8-bit planes; 10-bit u16 planes with PB = 2):
 //   * with use_satd: lowest_cost := SATD cost of the full-pel winner (get_mv_rd_cost
 //     with tmp_plane_opt = None, src/me.rs:235-252, 828-836);
 //   * telescopic_subpel_search (src/me.rs:858-941): steps 8, 4, 2 (and 1 with
@@ -30,7 +30,11 @@
 
 namespace {
 
-constexpr int RT = 256;        // threads per CTA
+// threads per CTA: 2 CTAs of 256 per SM for u8 planes; the u16 window (83 KB for +-64) leaves room for one CTA of 512
+template <int PB>
+struct Rc {
+  static constexpr int RT = PB == 1 ? 256 : 512;
+};
 constexpr int NSLOT = 849;     // blocks per superblock
 constexpr int SPLIT = 2;       // CTAs per superblock
 constexpr int MARGIN = 2;      // sub-pel steps move the MV by < 2 px in total
@@ -72,7 +76,7 @@ struct RefArgs {
   int W, H;          // frame size
   int range_x, range_y;  // full-pel search range the MVs come from (window = range + MARGIN)
   uint32_t lambda;
-  int use_satd, allow_hp;
+  int use_satd, allow_hp, bit_depth;
   int winW, winH, wstride;  // staged window (bytes per row = wstride, multiple of 4)
 };
 
@@ -99,16 +103,37 @@ __device__ __forceinline__ int dp4a_us(uint32_t px, uint32_t taps, int acc) {
   return d;
 }
 
-// horizontal 8-tap sum at window byte `b` of the row starting at `row` (bytes b .. b+7)
+// horizontal 8-tap sum (halved taps, + the rounding 2 of the >> 2 that follows) at window pixel `b` of the row
+// starting at `row` (pixels b .. b+7): u8 = 2 DP4A on funnel-shifted words, u16 = 4 DP2A on pixel pairs
+__device__ __forceinline__ int dp2a_lo_us(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.lo.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+__device__ __forceinline__ int dp2a_hi_us(uint32_t pair, uint32_t taps, int acc) {
+  int d;
+  asm("dp2a.hi.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pair), "r"(taps), "r"(acc));
+  return d;
+}
+template <int PB>
 __device__ __forceinline__ int hsum8(const uint8_t *row, int b, uint32_t tlo, uint32_t thi) {
-  const uint32_t *w = (const uint32_t *)row + (b >> 2);
-  const uint32_t sh = (uint32_t)(b & 3) * 8;
-  const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-  const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
-  return dp4a_us(hi, thi, dp4a_us(lo, tlo, 2));  // + 2: the rounding of the >> 2 that follows (halved taps)
+  if (PB == 1) {
+    const uint32_t *w = (const uint32_t *)row + (b >> 2);
+    const uint32_t sh = (uint32_t)(b & 3) * 8;
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+    const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+    return dp4a_us(hi, thi, dp4a_us(lo, tlo, 2));
+  } else {
+    const uint32_t *w = (const uint32_t *)row + (b >> 1);
+    const uint32_t sh = (uint32_t)(b & 1) * 16;
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+    const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh),
+                   v2 = __funnelshift_r(w2, w3, sh), v3 = __funnelshift_r(w3, w4, sh);
+    return dp2a_hi_us(v3, thi, dp2a_lo_us(v2, thi, dp2a_hi_us(v1, tlo, dp2a_lo_us(v0, tlo, 2))));
+  }
 }
 
-// put_8tap_ref for bit depth 8 (intermediate_bits = 4, src/mc.rs:213-307) in ONE formula for its four
+// put_8tap_ref for bit depths 8 and 10 (intermediate_bits = 4, src/mc.rs:213-307) in ONE formula for its four
 // (col_frac, row_frac) cases.  Every REGULAR tap is even, so the filters are kept halved (s8) and frac 0
 // is the unit tap 64:
 //   mid = (sum px * htx + 2) >> 2            == round_shift(sum px * tx, 3), and px << 4 for col_frac 0
@@ -229,10 +254,14 @@ __device__ __forceinline__ bool mv_in_range(const RefArgs &a, int bx, int by, in
 // takes a tile, decodes it and loads its org column ONCE, then walks the candidates
 // (per-job set-up was a third of the instructions when every (tile, candidate) pair was
 // a job of its own).
-template <int S>
+template <int S, int PB>
 __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, const uint32_t *tiles, int t_lo,
                                           int t_hi, int step, int ncand, int RX, int RY, int wx0, int wy0) {
-  constexpr int GROUPS = RT / S;
+  constexpr int GROUPS = Rc<PB>::RT / S;
+  // two candidates share one Hadamard as d1 * 65536 + d0 while |coef| < 2^15: always at 8 bits (64 * 255), at 10
+  // bits only for the 4x4 tiles (16 * 1023)
+  constexpr bool PAIR = PB == 1 || S == 4;
+  const int maxv = (1 << a.bit_depth) - 1;
   const int tid = threadIdx.x, lane = tid & 31, c = tid & (S - 1), grp = tid / S;
   const int nt = t_hi - t_lo;
   const int rounds = (nt + GROUPS - 1) / GROUPS;
@@ -260,9 +289,10 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
         const Blk b = sh.blk[slot];
         center = b.center;
         best = b.mv;
-        const uint8_t *o = sh.org + (by - RY + ty) * 64 + (bx - RX + tx + c);
+        const int oi = (by - RY + ty) * 64 + (bx - RX + tx + c);
 #pragma unroll
-        for (int y = 0; y < S; y++) oc[y] = (int)o[y * 64];
+        for (int y = 0; y < S; y++)
+          oc[y] = PB == 1 ? (int)sh.org[oi + y * 64] : (int)((const uint16_t *)sh.org)[oi + y * 64];
       }
     }
     const int tbx = (bw <= 4 ? 16 : 0), tby = (bh <= 4 ? 16 : 0);
@@ -276,9 +306,10 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
         int wx = bx + best.col / 8 + tx + c - wx0, wy = by + best.row / 8 + ty - wy0;
         wx = min(max(wx, 0), a.winW - 1);  // clamped for memory safety only
         wy = min(max(wy, 0), a.winH - S);
-        const uint8_t *p = sh.win + wy * a.wstride + wx;
+        const uint8_t *p = sh.win + wy * a.wstride + wx * PB;
 #pragma unroll
-        for (int y = 0; y < S; y++) d[y] = oc[y] - (int)p[y * a.wstride];
+        for (int y = 0; y < S; y++)
+          d[y] = oc[y] - (PB == 1 ? (int)p[y * a.wstride] : (int)*(const uint16_t *)(p + y * a.wstride));
       }
       const uint32_t acc = tile_dist<S>(d, lane, satd);
       if (live && c == 0) atomicAdd(&sh.dist[slot * 8], acc);
@@ -306,11 +337,11 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
         {
           const uint2 txw = sh.taps[tbx + cf];
           const uint8_t *row = sh.win + (wyb - 2) * a.wstride;
-          int prev = hsum8(row, wx - 3, txw.x, txw.y) >> 2;
+          int prev = hsum8<PB>(row, wx - 3, txw.x, txw.y) >> 2;
 #pragma unroll
           for (int n = 0; n < S + 6; n++) {
             row += a.wstride;
-            const int cur = hsum8(row, wx - 3, txw.x, txw.y) >> 2;
+            const int cur = hsum8<PB>(row, wx - 3, txw.x, txw.y) >> 2;
             P[n] = __byte_perm((uint32_t)prev, (uint32_t)cur, 0x5410);
             prev = cur;
           }
@@ -337,9 +368,12 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
             v = dp2a_hi_ss(P[t + 2], f0, v);
             v = dp2a_lo_ss(P[t + 4], f1, v);
             v = dp2a_hi_ss(P[t + 6], f1, v);
-            d[t] = live ? oc[t] - min(max(v >> 10, 0), 255) : 0;
+            d[t] = live ? oc[t] - min(max(v >> 10, 0), maxv) : 0;
           }
-          if ((arrived++ & 1) == 0) {
+          if (!PAIR) {
+            const uint32_t acc = tile_dist<S>(d, lane, satd);
+            if (live && c == 0) atomicAdd(&sh.dist[slot * 8 + k], acc);
+          } else if ((arrived++ & 1) == 0) {
 #pragma unroll
             for (int t = 0; t < S; t++) dp[t] = d[t];
             dp_live = live;
@@ -360,14 +394,16 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
 
 __device__ unsigned char g_owner[NSLOT];  // which CTA of the superblock owns a slot
 
-__global__ void __launch_bounds__(RT, 2) me_refine_kernel(RefArgs a) {
+template <int PB>
+__global__ void __launch_bounds__(Rc<PB>::RT, PB == 1 ? 2 : 1) me_refine_kernel(RefArgs a) {
+  constexpr int RT = Rc<PB>::RT;
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x;
   const int sbi = blockIdx.x / SPLIT, part = blockIdx.x - sbi * SPLIT;
   const int RX = a.sbs[sbi].po_x, RY = a.sbs[sbi].po_y;
   uint8_t *s_win = smem;
   uint8_t *s_org = s_win + (((size_t)a.winH * a.wstride + 15) & ~(size_t)15);
-  uint32_t *s_dist = (uint32_t *)(s_org + 64 * 64);
+  uint32_t *s_dist = (uint32_t *)(s_org + 64 * 64 * PB);
   Blk *s_blk = (Blk *)(s_dist + NSLOT * 8);
   uint2 *s_taps = (uint2 *)(s_blk + NSLOT);
   Shared sh = {s_win, s_org, s_dist, s_blk, s_taps};
@@ -380,17 +416,21 @@ __global__ void __launch_bounds__(RT, 2) me_refine_kernel(RefArgs a) {
     const int oxmax = a.org.alloc_w - a.org.xorigin - 1, oymax = a.org.alloc_h - a.org.yorigin - 1;
     for (int i = tid; i < 64 * 64; i += RT) {
       const int y = min(max(RY + (i >> 6), -a.org.yorigin), oymax), x = min(max(RX + (i & 63), -a.org.xorigin), oxmax);
-      s_org[i] = po[(long long)y * a.org.stride + x];
+      if (PB == 1) s_org[i] = po[(long long)y * a.org.stride + x];
+      else ((uint16_t *)s_org)[i] = ((const uint16_t *)po)[(long long)y * a.org.stride + x];
     }
     const int rxmax = a.ref.alloc_w - a.ref.xorigin - 1, rymax = a.ref.alloc_h - a.ref.yorigin - 1;
     const int wpr = a.wstride >> 2;
     for (int i = tid; i < a.winH * wpr; i += RT) {
       const int wy = i / wpr, w = i - wy * wpr;
       const int y = min(max(wy0 + wy, -a.ref.yorigin), rymax);
-      const uint8_t *row = pr + (long long)y * a.ref.stride;
+      const uint8_t *row = pr + (long long)y * a.ref.stride * PB;
       uint32_t v = 0;
 #pragma unroll
-      for (int b = 0; b < 4; b++) v |= (uint32_t)row[min(max(wx0 + 4 * w + b, -a.ref.xorigin), rxmax)] << (8 * b);
+      for (int b = 0; b < 4 / PB; b++) {
+        const int x = min(max(wx0 + (4 / PB) * w + b, -a.ref.xorigin), rxmax);
+        v |= (PB == 1 ? (uint32_t)row[x] : (uint32_t)((const uint16_t *)row)[x]) << (8 * PB * b);
+      }
       ((uint32_t *)s_win)[i] = v;
     }
     if (tid < 32) {
@@ -433,8 +473,8 @@ __global__ void __launch_bounds__(RT, 2) me_refine_kernel(RefArgs a) {
     const int ncand = s < 0 ? 1 : 8;
     for (int i = tid; i < NSLOT * 8; i += RT) s_dist[i] = 0;
     __syncthreads();
-    run_tiles<8>(a, sh, g_tiles8, a.tt.split8[part], a.tt.split8[part + 1], step, ncand, RX, RY, wx0, wy0);
-    run_tiles<4>(a, sh, g_tiles4, a.tt.split4[part], a.tt.split4[part + 1], step, ncand, RX, RY, wx0, wy0);
+    run_tiles<8, PB>(a, sh, g_tiles8, a.tt.split8[part], a.tt.split8[part + 1], step, ncand, RX, RY, wx0, wy0);
+    run_tiles<4, PB>(a, sh, g_tiles4, a.tt.split4[part], a.tt.split4[part + 1], step, ncand, RX, RY, wx0, wy0);
     __syncthreads();
     // ---- pick: strict `<` in candidate order (src/me.rs:934-937) ---------------------------
     for (int slot = tid; slot < NSLOT; slot += RT) {
@@ -529,21 +569,24 @@ static void build_tile_tables(uint32_t *t4, uint32_t *t8, unsigned char *owner, 
   }
 }
 
-// Sub-pel tail of r1c_frame_me for 8-bit planes.  d_results: frame layout (off / cols of
+// Sub-pel tail of r1c_frame_me for 8-bit and 10-bit planes.  d_results: frame layout (off / cols of
 // the mask), already holding the full-pel results of the superblocks in d_sbs.
 // *handled = 0 -> not applicable, the caller uses the generic path (subpel.cu).
 int r1c_refine_frame(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_frame_me_params *p,
-                     const long long *off, const int *cols, const int *rows, const r1c_sb_job *d_sbs, int64_t n_sb,
+                     int bit_depth, const long long *off, const int *cols, const int *rows, const r1c_sb_job *d_sbs, int64_t n_sb,
                      r1c_me_result *d_results, int *handled) {
   *handled = 0;
   const char *force = getenv("R1C_REFINE_GENERIC");
-  if ((force && force[0] == '1') || org->px_bytes != 1 || ref->px_bytes != 1) return R1C_OK;
+  const int pb = org->px_bytes;
+  // u16 planes up to 10 bits (intermediate_bits = 4 as at 8 bits; 12-bit uses 2 and stays on the generic path)
+  if ((force && force[0] == '1') || pb != ref->px_bytes || !(pb == 1 || (pb == 2 && bit_depth <= 10))) return R1C_OK;
   RefArgs a;
   a.winW = 64 + 2 * (p->range_x + MARGIN) + 7;
   a.winH = 64 + 2 * (p->range_y + MARGIN) + 7;
-  a.wstride = ((a.winW + 3) & ~3) + 8;
-  const size_t smem = (((size_t)a.winH * a.wstride + 15) & ~(size_t)15) + 64 * 64 + (size_t)NSLOT * 8 * 4 + (size_t)NSLOT * sizeof(Blk) + 32 * 8;
-  if (smem > 110 * 1024) return R1C_OK;
+  a.wstride = ((a.winW * pb + 3) & ~3) + 8;  // bytes
+  a.bit_depth = bit_depth;
+  const size_t smem = (((size_t)a.winH * a.wstride + 15) & ~(size_t)15) + 64 * 64 * pb + (size_t)NSLOT * 8 * 4 + (size_t)NSLOT * sizeof(Blk) + 32 * 8;
+  if (smem > (pb == 1 ? 110 : 220) * 1024) return R1C_OK;
   *handled = 1;
   if (n_sb == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -578,9 +621,10 @@ int r1c_refine_frame(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, c
   a.lambda = p->lambda;
   a.use_satd = p->use_satd;
   a.allow_hp = p->allow_high_precision_mv;
-  R1C_CUDA(ctx, cudaFuncSetAttribute(me_refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = pb == 1 ? me_refine_kernel<1> : me_refine_kernel<2>;
+  R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   r1c_prof_begin(ctx, R1C_PROF_SUBPEL_COST);
-  me_refine_kernel<<<(unsigned)(n_sb * SPLIT), RT, smem, ctx->stream>>>(a);
+  kern<<<(unsigned)(n_sb * SPLIT), pb == 1 ? Rc<1>::RT : Rc<2>::RT, smem, ctx->stream>>>(a);
   r1c_prof_end(ctx, R1C_PROF_SUBPEL_COST);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;

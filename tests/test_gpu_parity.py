@@ -583,7 +583,8 @@ def _frame_pair(r, oracle, ctx, W, H, pb, bd, seed):
     return o_org, d_org, o_ref, d_ref
 
 
-@pytest.mark.parametrize("pb,bd,refine,use_satd,hp", [(1, 8, 1, 1, 0), (1, 8, 0, 0, 0), (2, 10, 1, 1, 1), (1, 8, 1, 0, 0)])
+@pytest.mark.parametrize("pb,bd,refine,use_satd,hp", [(1, 8, 1, 1, 0), (1, 8, 0, 0, 0), (2, 10, 1, 1, 1), (1, 8, 1, 0, 0),
+                                                      (2, 10, 1, 0, 0), (2, 12, 1, 1, 0)])
 def test_frame_me_matches_per_block_motion_estimation(r, ctx, oracle, pb, bd, refine, use_satd, hp):
     """r1c_frame_me == motion_estimation (src/me.rs:193-271) block by block, every size,
     borders and the partial last superblock row included"""
@@ -593,6 +594,25 @@ def test_frame_me_matches_per_block_motion_estimation(r, ctx, oracle, pb, bd, re
     got = r.frame_me(ctx, d_org, d_ref, params, bd)
     mv, cost = oracle.frame_me(o_org, o_ref, 14, 10, 77, params.bsize_mask, refine, use_satd, hp, bd)
     assert got.size == cost.size == r.frame_me_count(params) > 5000
+    assert np.array_equal(got["cost"], cost)
+    assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
+
+
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+def test_frame_me_extreme_pixels(r, ctx, oracle, pb, bd):
+    """pixels at 0 / max only: the largest differences the sub-pel filters, the packed pair Hadamard (4x4 tiles at 10
+    bits, every tile at 8) and the distortion accumulators can see; filter overshoot is clamped on both sides"""
+    rng = np.random.default_rng(4100 + bd)
+    W, H = 136, 128
+    maxv = (1 << bd) - 1
+    blocks = rng.integers(0, 2, size=(H // 2 + 1, W // 2 + 1)) * maxv  # 2x2 checker noise: strong sub-pel response
+    ref_px = np.kron(blocks, np.ones((2, 2), dtype=np.int64))[:H, :W]
+    org_px = np.where(rng.random((H, W)) < 0.5, maxv - np.roll(ref_px, (1, -2), axis=(0, 1)), np.roll(ref_px, (1, -2), axis=(0, 1)))
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, data=ref_px)
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=org_px)
+    params = r.make_frame_me_params(W, H, 6, 6, 20, refine=1, use_satd=1, allow_hp=1)
+    got = r.frame_me(ctx, d_org, d_ref, params, bd)
+    mv, cost = oracle.frame_me(o_org, o_ref, 6, 6, 20, params.bsize_mask, 1, 1, 1, bd)
     assert np.array_equal(got["cost"], cost)
     assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
 
