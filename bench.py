@@ -46,37 +46,10 @@ ALG_HBM_BYTES_SB = None  # filled once the plane geometry is known
 
 # ----------------------------------------------------------------- synthetic frames --
 def synth_frame_pair(seed):
-    """SURVEY 8(d) cfg 1: cur = smooth random field; ref = cur moved by a random integer MV
-    per 64x64 superblock (+-48 px) plus +-4 noise, so minima are unique and non-trivial."""
-    rng = np.random.default_rng(seed)
-    big = rng.integers(0, 256, size=(H + 256, W + 256)).astype(np.float32)
-    for _ in range(2):  # separable box blur, radius 2
-        big = (np.roll(big, 2, 0) + np.roll(big, 1, 0) + big + np.roll(big, -1, 0) + np.roll(big, -2, 0)) / 5
-        big = (np.roll(big, 2, 1) + np.roll(big, 1, 1) + big + np.roll(big, -1, 1) + np.roll(big, -2, 1)) / 5
-    big = (big - big.mean()) * 3.0 + 128.0
-    cur = np.clip(np.rint(big[128:128 + H, 128:128 + W]), 0, 255).astype(np.uint8)
-    ref = np.empty_like(cur)
-    for sy in range(0, H, 64):
-        for sx in range(0, W, 64):
-            dy, dx = (int(v) for v in rng.integers(-48, 49, size=2))
-            h, w = min(64, H - sy), min(64, W - sx)
-            ref[sy:sy + h, sx:sx + w] = np.clip(np.rint(big[128 + sy + dy:128 + sy + dy + h,
-                                                            128 + sx + dx:128 + sx + dx + w]), 0, 255)
-    noise = rng.integers(-4, 5, size=ref.shape)
-    ref = np.clip(ref.astype(np.int16) + noise, 0, 255).astype(np.uint8)
-    return cur, ref
+    return bench_kernels.synth_frame_pair(seed, W, H)
 
 
-def padded(cfg, vis):
-    """whole allocation with Plane::pad semantics (edge replication) -- numpy, input prep only"""
-    a = np.empty((cfg.alloc_height, cfg.stride), dtype=vis.dtype)
-    yo, xo, h, w = cfg.yorigin, cfg.xorigin, cfg.height, cfg.width
-    a[yo:yo + h, xo:xo + w] = vis
-    a[yo:yo + h, :xo] = vis[:, :1]
-    a[yo:yo + h, xo + w:] = vis[:, -1:]
-    a[:yo, :] = a[yo:yo + 1, :]
-    a[yo + h:, :] = a[yo + h - 1:yo + h, :]
-    return a
+padded = bench_kernels.padded
 
 
 # ----------------------------------------------------------------------- clocks --

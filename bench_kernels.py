@@ -61,6 +61,44 @@ def _timed(torch, ext, flush, fn, reps):
     return sum(a.elapsed_time(b) for a, b in evs) / reps
 
 
+def synth_frame_pair(seed, W, H, bit_depth=8):
+    """SURVEY 8(d) cfg 1: cur = smooth random field; ref = cur moved by a random integer MV
+    per 64x64 superblock (+-48 px) plus +-4 noise, so minima are unique and non-trivial.
+    bit_depth > 8: the same field scaled to the deeper range (u16)."""
+    rng = np.random.default_rng(seed)
+    maxv = (1 << bit_depth) - 1
+    sc = 1 << (bit_depth - 8)
+    big = rng.integers(0, 256, size=(H + 256, W + 256)).astype(np.float32)
+    for _ in range(2):  # separable box blur, radius 2
+        big = (np.roll(big, 2, 0) + np.roll(big, 1, 0) + big + np.roll(big, -1, 0) + np.roll(big, -2, 0)) / 5
+        big = (np.roll(big, 2, 1) + np.roll(big, 1, 1) + big + np.roll(big, -1, 1) + np.roll(big, -2, 1)) / 5
+    big = ((big - big.mean()) * 3.0 + 128.0) * sc
+    dt = np.uint8 if bit_depth == 8 else np.uint16
+    cur = np.clip(np.rint(big[128:128 + H, 128:128 + W]), 0, maxv).astype(dt)
+    ref = np.empty_like(cur)
+    for sy in range(0, H, 64):
+        for sx in range(0, W, 64):
+            dy, dx = (int(v) for v in rng.integers(-48, 49, size=2))
+            h, w = min(64, H - sy), min(64, W - sx)
+            ref[sy:sy + h, sx:sx + w] = np.clip(np.rint(big[128 + sy + dy:128 + sy + dy + h,
+                                                            128 + sx + dx:128 + sx + dx + w]), 0, maxv)
+    noise = rng.integers(-4 * sc, 4 * sc + 1, size=ref.shape)
+    ref = np.clip(ref.astype(np.int32) + noise, 0, maxv).astype(dt)
+    return cur, ref
+
+
+def padded(cfg, vis):
+    """whole allocation with Plane::pad semantics (edge replication) -- numpy, input prep only"""
+    a = np.empty((cfg.alloc_height, cfg.stride), dtype=vis.dtype)
+    yo, xo, h, w = cfg.yorigin, cfg.xorigin, cfg.height, cfg.width
+    a[yo:yo + h, xo:xo + w] = vis
+    a[yo:yo + h, :xo] = vis[:, :1]
+    a[yo:yo + h, xo + w:] = vis[:, -1:]
+    a[:yo, :] = a[yo:yo + 1, :]
+    a[yo + h:, :] = a[yo + h - 1:yo + h, :]
+    return a
+
+
 def mc_jobs(r, rng, lib, W, H):
     jobs = []
     only = os.environ.get("R1C_BENCH_SIZES")  # profiling aid: restrict to some BlockSize values
@@ -210,4 +248,48 @@ def run(ctx, r, torch, ext, flush, reps=3):
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                      "alg_bytes_per_coeff": 6, "peak_source": hbm_how, "frac_by_tx_size": per}}
     ctx.check(lib.r1c_profile(ctx.h, 0))
+    del res, coef, org, src, dst, d_out
+    # -------------------------- whole-frame motion estimation on a 4K 10-bit frame pair (u16 planes)
+    if not os.environ.get("R1C_BENCH_SIZES") and not os.environ.get("R1C_BENCH_TXSIZES"):
+        out["me_4k10_fullsearch_pm64"] = me_frame_line(ctx, r, torch, ext, flush, 3840, 2160, 10, 64)
     return out
+
+
+def me_frame_line(ctx, r, torch, ext, flush, W, H, BD, RANGE, reps=2):
+    """r1c_frame_me_dev on a synthetic frame pair, planes resident: the headline workload at another frame size /
+    bit depth (same kernels; u16 planes take the packed-pair variants of me_sb2 / me_refine)"""
+    lib = ctx.lib
+    PB = 1 if BD == 8 else 2
+    cur, ref = synth_frame_pair(11, W, H, BD)
+    p_org = r.Plane(ctx, W, H, 0, 0, 88, 88, PB)
+    p_ref = r.Plane(ctx, W, H, 0, 0, 88, 88, PB)
+    p_org.upload(padded(p_org.cfg, cur))
+    p_ref.upload(padded(p_ref.cfg, ref))
+    params = r.make_frame_me_params(W, H, RANGE, RANGE, 160 << (BD - 8), refine=1, use_satd=1)
+    n_res = r.frame_me_count(params)
+    d_res = torch.empty(n_res * 16, dtype=torch.uint8, device="cuda")
+
+    def step():
+        ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, d_res.data_ptr()))
+    step()
+    ctx.sync()
+    ctx.check(lib.r1c_profile(ctx.h, 1))
+    l0 = ctx.launches
+    ms = _timed(torch, ext, flush, step, reps)
+    launches = (ctx.launches - l0) // reps
+    sb_ms = _kernel_ms(ctx, 0)[0] / reps
+    _kernel_ms(ctx, 1)
+    rf_ms = _kernel_ms(ctx, 2)[0] / reps
+    ctx.check(lib.r1c_profile(ctx.h, 0))
+    try:
+        ipeak = float(json.load(open(os.path.join(ROOT, "profiles", "int_peaks_r01.json")))["iadd"])
+        ihow = "measured (tools/int_peak.cu, IADD3 lane-ops/s)"
+    except Exception:
+        ipeak, ihow = 36000.0, "fallback"
+    ops = 2.0 * W * H * (2 * RANGE + 1) ** 2
+    return {"workload": "%dx%d %d-bit full-search ME +-%d, 19 sizes, SAD then SATD sub-pel (planes resident)" % (W, H, BD, RANGE),
+            "value": W * H / 1e3 / ms, "unit": "Mpix/s", "ms": ms, "launches_per_frame": launches,
+            "blocks_per_frame": int(n_res), "kernel_ms": {"me_sb2_kernel": sb_ms, "me_refine_kernel": rf_ms},
+            "roofline": {"bound": "int32_alu", "kernel": "me_sb2_kernel (u16 variant)", "achieved": ops / (sb_ms / 1e3) / 1e9 if sb_ms else None,
+                         "peak": ipeak, "unit": "Gop/s", "frac": ops / (sb_ms / 1e3) / 1e9 / ipeak if sb_ms else None,
+                         "alg_ops_per_launch": ops, "peak_source": ihow}}

@@ -19,11 +19,7 @@ RANGE = int(sys.argv[4]) if len(sys.argv) > 4 else 64
 REPS = int(sys.argv[5]) if len(sys.argv) > 5 else 3
 PB = 1 if BD == 8 else 2
 
-bench.W, bench.H = W, H
-cur, ref = bench.synth_frame_pair(1)
-if PB == 2:  # same content at the higher depth
-    cur = (cur.astype(np.uint16) << (BD - 8)) | 1
-    ref = (ref.astype(np.uint16) << (BD - 8)) | 2
+cur, ref = bench.bench_kernels.synth_frame_pair(1, W, H, BD)
 
 ctx = r.Context(0)
 p_org = r.Plane(ctx, W, H, 0, 0, 88, 88, PB)
