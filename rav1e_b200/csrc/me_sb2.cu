@@ -58,6 +58,7 @@ struct Sb2Args {
   r1c_sb_params p;
   const r1c_sb_job *jobs;
   unsigned long long *partial;  // [n * split][849]
+  uint32_t *bias;               // u16 planes: [n][849] sum of org over each block (written by chunk 0)
   long long n;
   int split;  // chunks of candidate rows per superblock
   int rpc;    // candidate rows per chunk (even)
@@ -70,10 +71,17 @@ __host__ __device__ inline int sb2_count(int b) {
   const int w = blk_w_of(b), h = blk_h_of(b);
   return (w > 64 || h > 64) ? 0 : (64 / w) * (64 / h);
 }
+// first slot of BlockSize b in the [849] layout = sum of sb2_count over the smaller enum values
+__constant__ short c_sb2_off[R1C_BLOCK_SIZES_ALL] = {0,   256, 384, 512, 576, 608, 640, 656, 664, 672, 676,
+                                                     678, 680, 681, 681, 681, 681, 745, 809, 825, 841, 845};
 __host__ __device__ inline int sb2_offset(int b) {
+#ifdef __CUDA_ARCH__
+  return c_sb2_off[b];
+#else
   int o = 0;
   for (int i = 0; i < b; i++) o += sb2_count(i);
   return o;
+#endif
 }
 
 __device__ __forceinline__ uint32_t rate1(int diff, int allow_hp) {
@@ -224,12 +232,22 @@ __host__ __device__ inline BigSlot big_slot(int q, int s) {
   return b;
 }
 
-// |a - b| of two packed u16 pairs (10-bit pixels): max - min, no borrow between the halves
-__device__ __forceinline__ uint32_t absdiff2(uint32_t a, uint32_t b) { return __vmaxu2(a, b) - __vminu2(a, b); }
+// u16 planes: sum |a - b| = 2 sum max(a, b) - sum a - sum b.  The inner loop only accumulates the packed maxima
+// (VIMNMX.U16x2 + a 3-input add per two words); sum b of a 4x4 cell at a window position is candidate-independent
+// work (a box filter of the staged window, kept negated as s16 in shared memory), and sum a of a block is the same
+// for all its candidates, so the running minima are taken on SAD + sum a and the constant leaves in the epilogue.
+__device__ __forceinline__ uint32_t max2(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
+// 2 * (lo16(c) + hi16(c)) + nb
+__device__ __forceinline__ uint32_t fold_cell(uint32_t c, int nb) {
+  uint32_t d;
+  asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(c), "r"(0x0202u), "r"((uint32_t)nb));
+  return d;
+}
 
 template <bool MASKED, int RSW, int PB>
 __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
                                            const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
+                                           const int16_t *s_nbox,
                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                            uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
@@ -278,10 +296,11 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
         }
       }
     } else {
-      // u16 pixels: two per word, |a - b| on packed pairs (VIMNMX.U16x2 x2 + subtract); a cell accumulates
-      // 8 pixels in each 16-bit half (<= 8 * 4095) and is folded after the loop.  The quadrant row is taken
+      // u16 pixels: two per word, packed maxima (VIMNMX.U16x2 + add, see max2); a cell accumulates 8 values
+      // in each 16-bit half (<= 8 * 1023) and is folded after the loop.  The quadrant row is taken
       // in two 8-pixel halves to keep the live registers down; org words are the same address for the
       // whole warp (broadcast), so B re-reads its row instead of keeping it.
+      uint4 oprev[2];
 #pragma unroll
       for (int r = 0; r < 17; r++) {
 #pragma unroll
@@ -289,25 +308,29 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
           const uint32_t *rr = rp + (r * rsw + 4 * hf) * 2;
           const uint32_t w0 = rr[0], w1 = rr[2], w2 = rr[4], w3 = rr[6];
           if (r >= 1) {
-            const uint4 o = *(const uint4 *)(orow + (r - 1) * 32 + 4 * hf);
+            const uint4 o = oprev[hf];
             const int i = (r - 1) >> 2;
-            cB[i][2 * hf] += absdiff2(o.x, w0) + absdiff2(o.y, w1);
-            cB[i][2 * hf + 1] += absdiff2(o.z, w2) + absdiff2(o.w, w3);
+            cB[i][2 * hf] += max2(o.x, w0) + max2(o.y, w1);
+            cB[i][2 * hf + 1] += max2(o.z, w2) + max2(o.w, w3);
           }
           if (r < 16) {
             const uint4 o = *(const uint4 *)(orow + r * 32 + 4 * hf);
             const int i = r >> 2;
-            cA[i][2 * hf] += absdiff2(o.x, w0) + absdiff2(o.y, w1);
-            cA[i][2 * hf + 1] += absdiff2(o.z, w2) + absdiff2(o.w, w3);
+            cA[i][2 * hf] += max2(o.x, w0) + max2(o.y, w1);
+            cA[i][2 * hf + 1] += max2(o.z, w2) + max2(o.w, w3);
+            oprev[hf] = o;
           }
         }
       }
+      // cell = 2 * sum max - box sum of the window at (candidate, cell) = SAD + sum org of the cell
+      const int bw = rsw * PXW;
+      const int16_t *nb = s_nbox + (qy * 16 + dyA) * bw + qx * 16 + dx;
 #pragma unroll
       for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-          cA[i][k] = (cA[i][k] & 0xffffu) + (cA[i][k] >> 16);
-          cB[i][k] = (cB[i][k] & 0xffffu) + (cB[i][k] >> 16);
+          cA[i][k] = fold_cell(cA[i][k], nb[4 * i * bw + 4 * k]);
+          cB[i][k] = fold_cell(cB[i][k], nb[(4 * i + 1) * bw + 4 * k]);
         }
     }
     // ---- rate terms ---------------------------------------------------------------------
@@ -460,6 +483,9 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   uint32_t *s_ref = s_org + 64 * 16 * PB;   // [nrows][rsw][PXW pixel phases]
   uint32_t *s_x = s_ref + a.csz;       // 2 x [5][16][64]
   const int nrows = ck.NYc + 63;
+  // u16 only: negated 4x4 box sums of the window [nrows - 3][rsw * PXW], summed-area table of org's 4x4 cells
+  uint32_t *s_sat = s_x + 2 * 5 * 16 * 64;  // [17][17]
+  int16_t *s_nbox = (int16_t *)(s_sat + 17 * 17 + 3);
 
   // ---- stage the org region and phase 0 of the window (clamped into the allocation:
   //      pixels outside it never belong to a legal candidate) ---------------------------
@@ -499,7 +525,67 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
 #pragma unroll
       for (int ph = 1; ph < PXW; ph++) s_ref[i * PXW + ph] = __funnelshift_r(lo, hi, 8 * PB * ph);
     }
+  if (PB == 2 && chunk == 0) {  // sums of org's 4x4 cells (-> s_x, free until the search starts)
+    if (tid < 256) {
+      const uint16_t *o = (const uint16_t *)s_org + (tid >> 4) * 4 * 64 + (tid & 15) * 4;
+      uint32_t sum = 0;
+#pragma unroll
+      for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) sum += o[r * 64 + c];
+      s_x[tid] = sum;
+    }
+  }
   __syncthreads();
+  if (PB == 2) {
+    // box(y, x) = sum of window pixels [y, y + 4) x [x, x + 4): a thread owns a column and a segment of rows and
+    // slides down it with the row sums h4 of the last four rows in a ring
+    const int bw = rsw * PXW, nby = nrows - 3;
+    const int nseg = max(1, T2 / bw), seg_rows = (nby + nseg - 1) / nseg;
+    for (int t = tid; t < bw * nseg; t += T2) {
+      const int sg = t / bw, x = t - sg * bw;
+      const int ylo = sg * seg_rows, yhi = min(nby, ylo + seg_rows);
+      if (x > bw - 4) continue;
+      const uint32_t *col = s_ref + (x >> 1) * PXW + (x & 1);
+      auto h4 = [&](int y) {
+        const uint32_t v = col[y * rsw * PXW] + col[(y * rsw + 1) * PXW];  // two pixel pairs, halves stay apart
+        return (int)((v & 0xffffu) + (v >> 16));
+      };
+      if (ylo < yhi) {
+        int h0 = h4(ylo), h1 = h4(ylo + 1), h2 = h4(ylo + 2);
+        for (int y = ylo; y < yhi; y++) {
+          const int h3 = h4(y + 3);
+          s_nbox[y * bw + x] = (int16_t)(-(h0 + h1 + h2 + h3));
+          h0 = h1;
+          h1 = h2;
+          h2 = h3;
+        }
+      }
+    }
+    // summed-area table of the cell sums: sat[Y][X] = sum of cells [0, Y) x [0, X); the minima are taken on
+    // 256 * (SAD + sum org of the block) + rl, and the block sums go to sb2_finalize_kernel once per superblock
+    if (chunk == 0) {
+      if (tid < 17 * 17) {
+        const int Y = tid / 17, X = tid - Y * 17;
+        uint32_t sum = 0;
+        for (int y = 0; y < Y; y++)
+          for (int x = 0; x < X; x++) sum += s_x[y * 16 + x];
+        s_sat[tid] = sum;
+      }
+      __syncthreads();
+      uint32_t *bias = a.bias + ji * NSLOT;
+      for (int b = 0; b < R1C_BLOCK_SIZES_ALL; b++) {
+        const int cnt = sb2_count(b);
+        if (cnt == 0) continue;
+        const int cw = blk_w_of(b) >> 2, ch = blk_h_of(b) >> 2, per_row = 16 / cw, off = sb2_offset(b);
+        for (int k = tid; k < cnt; k += T2) {
+          const int y0 = (k / per_row) * ch, x0 = (k % per_row) * cw, y1 = y0 + ch, x1 = x0 + cw;
+          bias[off + k] = s_sat[y1 * 17 + x1] - s_sat[y0 * 17 + x1] - s_sat[y1 * 17 + x0] + s_sat[y0 * 17 + x0];
+        }
+      }
+    }
+    __syncthreads();
+  }
 
   Geo2 g;
   g.RX = job.po_x;
@@ -524,8 +610,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     pc[i] = bc[i] = NONE32;
     ps[i] = bs[i] = 0;
   }
-  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
-  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, best, pc, ps, bc, bs, g);
+  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, best, pc, ps, bc, bs, g);
+  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, best, pc, ps, bc, bs, g);
 
   // ---- reduce over the 32 lanes and write the partial keys ------------------------------
   unsigned long long *out = a.partial + wi * NSLOT;
@@ -574,6 +660,7 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
 // are not in the job's mask are left untouched
 struct FinArgs {
   const unsigned long long *partial;
+  const uint32_t *bias;  // u16 planes: sum of org per block, taken off the cost (x 256); else nullptr
   const r1c_sb_job *jobs;
   r1c_me_result *results;
   const int2 *map;  // optional: (source slot, destination index)
@@ -617,7 +704,7 @@ __global__ void sb2_finalize_kernel(FinArgs a) {
     const int dy = (int)(ridx / (uint32_t)a.NX), dx = (int)(ridx - (uint32_t)dy * a.NX);
     r.mv.row = (int16_t)(8 * (job.cmv.row / 8 - a.Ry + dy));
     r.mv.col = (int16_t)(8 * (job.cmv.col / 8 - a.Rx + dx));
-    r.cost = key >> 32;
+    r.cost = (key >> 32) - (a.bias ? 256ull * a.bias[ji * NSLOT + slot] : 0ull);
   }
   a.results[dst] = r;
 }
@@ -652,7 +739,8 @@ static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, i
     if ((long long)(last + 1) / 2 * NX < 32) continue;  // every lane needs a slot of its own
     const int nrows = rpc + 63;
     const int csz = nrows * rsw * pxw;
-    const size_t smem = (size_t)64 * 64 * px_bytes + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    size_t smem = (size_t)64 * 64 * px_bytes + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    if (px_bytes == 2) smem += (size_t)(17 * 17 + 3) * 4 + (size_t)(nrows - 3) * rsw * pxw * 2;  // s_sat, s_nbox
     if (smem > 220 * 1024) continue;
     // enough work items to balance the SMs: stop once the tail is small
     pl->split = split;
@@ -681,7 +769,9 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   void *d_partial;
-  int rc = r1c_scratch_dev(ctx, 15, (size_t)n * pl.split * NSLOT * sizeof(unsigned long long), &d_partial);
+  const size_t partial_bytes = (size_t)n * pl.split * NSLOT * sizeof(unsigned long long);
+  const size_t bias_bytes = org->px_bytes == 2 ? (size_t)n * NSLOT * sizeof(uint32_t) : 0;
+  int rc = r1c_scratch_dev(ctx, 15, partial_bytes + bias_bytes, &d_partial);
   if (rc) return rc;
   Sb2Args a;
   a.org = make_view(org);
@@ -689,6 +779,7 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   a.p = *p;
   a.jobs = d_jobs;
   a.partial = (unsigned long long *)d_partial;
+  a.bias = bias_bytes ? (uint32_t *)((uint8_t *)d_partial + partial_bytes) : nullptr;
   a.n = n;
   a.split = pl.split;
   a.rpc = pl.rpc;
@@ -705,6 +796,7 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   R1C_LAUNCH_CHECK(ctx);
   FinArgs fa;
   fa.partial = a.partial;
+  fa.bias = a.bias;
   fa.jobs = d_jobs;
   fa.results = d_results;
   fa.map = d_map;
