@@ -175,6 +175,27 @@ def run(ctx, r, torch, ext, flush, reps=3):
         k = _kernel_ms(ctx, 3)[0] / reps
         kavg += k
         by_size["mc_avg"][key] = round(k * 1e3, 1)
+    # the 19 tilings as ONE job list / one launch (157 Mpx, mixed block sizes: prefix-sum job lookup): the rate of
+    # the kernel once the launch is long enough to hide its start-up chain (job -> rows) and its tail
+    allj = np.concatenate(per_size)
+    off = 0
+    for j in per_size:
+        a = int(j["w"][0]) * int(j["h"][0])
+        allj["tmp_off"][off:off + j.size] = 0  # put only
+        off += j.size
+    d_all = torch.from_numpy(allj.view(np.uint8).copy()).cuda()
+
+    def f_put_all():
+        ctx.check(lib.r1c_put_8tap_batch_dev(ctx.h, dst.h, src.h, d_all.data_ptr(), allj.size, BD))
+    f_put_all()
+    ctx.sync()
+    _kernel_ms(ctx, 3)
+    one_ms = _timed(torch, ext, flush, f_put_all, reps)
+    one_k = _kernel_ms(ctx, 3)[0] / reps
+    try:
+        ipeak = float(json.load(open(os.path.join(ROOT, "profiles", "int_peaks_r01.json")))["iadd"])
+    except Exception:
+        ipeak = 36000.0
     for name, call_ms, ms, bpp in (("put_8tap", put_ms, kput, 4), ("prep_8tap", prep_ms, kprep, 4),
                                    ("mc_avg", avg_ms, kavg, 6)):
         gbs = px_total * bpp / (ms / 1e3) / 1e9
@@ -185,6 +206,14 @@ def run(ctx, r, torch, ext, flush, reps=3):
                                      "roofline = the main kernel alone (19 launches, CUDA events inside the library)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_px": bpp, "peak_source": hbm_how}}
+        if name != "mc_avg":  # 16 MACs = 32 integer ops per output pixel (2-D case, halo not counted)
+            out["mc_4k10_" + name]["roofline"]["int_frac"] = px_total * 32 / (ms / 1e3) / 1e9 / ipeak
+    gbs = px_total * 4 / (one_k / 1e3) / 1e9
+    out["mc_4k10_put_8tap_one_launch"] = {
+        "workload": "the same 19 tilings as one mixed-size job list: one launch of 157 Mpx",
+        "value": px_total / 1e6 / (one_ms / 1e3), "unit": "Mpix/s", "ms": one_ms, "pixels": px_total, "kernel_ms": one_k,
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "alg_bytes_per_px": 4,
+                     "peak_source": hbm_how, "int_frac": px_total * 32 / (one_k / 1e3) / 1e9 / ipeak}}
     del tmp1, tmp2
     # ------------------------------------------ SAD / SATD, 4K 10-bit luma, one job per block
     org = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)

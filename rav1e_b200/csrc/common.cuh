@@ -32,6 +32,7 @@ struct r1c_ctx {
   // per-kernel-class device timing (r1c_profile*): event pairs around the launches
   int prof_on;
   int prof_mc_slot;  // != 0: the MC launches belong to this slot (sub-pel path)
+  int mc_taps_ready; // mc.cu: the packed filter table of this device has been written on this stream
   struct {
     cudaEvent_t ev[2][R1C_PROF_RING];
     int n;            // pairs recorded since the last read

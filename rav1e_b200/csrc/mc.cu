@@ -54,8 +54,11 @@ __constant__ short c_filters[6][16][8] = {
      {0, 0, 12, 52, 52, 12, 0, 0}, {0, 0, 12, 48, 54, 14, 0, 0}, {0, 0, 10, 46, 56, 16, 0, 0}, {0, 0, 8, 44, 58, 18, 0, 0},
      {0, 0, 6, 42, 60, 20, 0, 0}, {0, 0, 4, 40, 62, 22, 0, 0}, {0, 0, 4, 36, 62, 26, 0, 0}, {0, 0, 2, 34, 62, 30, 0, 0}}};
 
-constexpr int SEG_ROWS = 32;  // rows per item
+constexpr int SEG_ROWS = 16;  // rows per item
 constexpr int MC_THREADS = 128;
+#ifndef MC_PF
+#define MC_PF 8  // source rows in flight per thread in the fast strip walker
+#endif
 
 __host__ __device__ inline int items_of(int w, int h) { return ((w + 3) >> 2) * ((h + SEG_ROWS - 1) / SEG_ROWS); }
 
@@ -79,7 +82,10 @@ __global__ void count_items_kernel(const JOB *jobs, long long n, long long *coun
       atomicMin(minmax + 1, -wmax);  // kept negated so one memset initialises both
     }
   }
-  if (i == n) counts[i] = 0;
+  if (i == n) {
+    counts[i] = 0;
+    minmax[2] = 0;  // work counter of the main kernel (chunks of items handed to CTAs)
+  }
 }
 
 // largest j in [0, n) with offs[j] <= item (offs is the exclusive prefix sum, offs[n] = total)
@@ -93,42 +99,13 @@ __device__ __forceinline__ long long find_job(const long long *offs, long long n
   return lo;
 }
 
-// Source pixels of one row of a strip: px[k] = pixel at column x0 - 3 + k.
-// HAS_H: k = 0 .. ncols+6 are needed (horizontal filter footprint); otherwise
-// only k = 3 .. 3+ncols-1 (the strip itself).  Only aligned 32-bit words that
-// contain a needed pixel are touched, so the load never leaves the allocation.
-template <int PB, bool HAS_H>
-__device__ __forceinline__ void load_strip_row(const uint8_t *row, int x0, int ncols, int (&px)[11]) {
-  constexpr int KLO = HAS_H ? 0 : 3;
-  const int nneed = HAS_H ? ncols + 7 : ncols;
-  const uint8_t *first = row + (long long)(x0 - 3 + KLO) * PB;
-  const uintptr_t a0 = (uintptr_t)first & ~(uintptr_t)3;
-  const uint32_t *wp = (const uint32_t *)a0;
-  const int nwords = (int)(((uintptr_t)first + (uintptr_t)(nneed * PB) - a0 + 3) >> 2);
-  constexpr int NA = HAS_H ? (PB == 1 ? 3 : 6) : (PB == 1 ? 1 : 2);  // realigned words
-  uint32_t w[NA + 1];
-#pragma unroll
-  for (int i = 0; i < NA + 1; i++) w[i] = i < nwords ? __ldg(wp + i) : 0u;
-  const uint32_t sh = (uint32_t)((uintptr_t)first & 3) * 8;
-  uint32_t a[NA];
-#pragma unroll
-  for (int i = 0; i < NA; i++) a[i] = __funnelshift_r(w[i], w[i + 1], sh);
-#pragma unroll
-  for (int k = 0; k < 11; k++) {
-    constexpr int PPW = 4 / PB;  // pixels per word
-    const int q = k - KLO;
-    if (q >= 0 && q < NA * PPW) px[k] = (int)((a[q / PPW] >> ((q % PPW) * 8 * PB)) & (PB == 1 ? 0xffu : 0xffffu));
-    else px[k] = 0;
-  }
-}
-
 struct McArgs {
   PlaneView src;
   uint8_t *dst0;  // put: address of dst plane coordinate (0,0)
   int dst_stride;
   int16_t *tmp;   // prep
   const r1c_mc_job *jobs;
-  const long long *offs;
+  long long *offs;
   long long n;
   int bit_depth;
 };
@@ -167,28 +144,11 @@ __device__ __forceinline__ uint32_t pack_taps4(const short *f) {
          ((uint32_t)(uint8_t)(int8_t)f[2] << 16) | ((uint32_t)(uint8_t)(int8_t)f[3] << 24);
 }
 
-// raw aligned words of one source row of a strip (pixels x0-3 .. x0+ncols+3), `first` =
-// address of pixel x0-3.  Only words holding a needed pixel are loaded.
+// raw aligned words of one source row of a strip: the 4 (u8) / 6 (u16) words from the one holding pixel x0-3 on
 template <int PB>
 struct RowWords {
   uint32_t w[PB == 1 ? 4 : 6];
 };
-template <int PB>
-__device__ __forceinline__ void load_row_words(const uint8_t *first, uint32_t need, RowWords<PB> &rw) {
-  constexpr int NW = PB == 1 ? 4 : 6;
-  const uint32_t *wp = (const uint32_t *)((uintptr_t)first & ~(uintptr_t)3);
-#pragma unroll
-  for (int i = 0; i < NW; i++) rw.w[i] = ((need >> i) & 1u) ? __ldg(wp + i) : 0u;
-}
-// bit i set = aligned word i of a row holds a pixel the job really reads: pixels
-// [x0-3, x0+ncols+4) with a horizontal filter, [x0, x0+ncols) without
-template <int PB>
-__device__ __forceinline__ uint32_t need_mask(const uint8_t *first, int ncols, bool has_h) {
-  const int misb = (int)((uintptr_t)first & 3);
-  const int lo = has_h ? 0 : 3, hi = has_h ? ncols + 7 : 3 + ncols;
-  const int wlo = (misb + lo * PB) >> 2, whi = (misb + hi * PB + 3) >> 2;
-  return ((1u << whi) - 1u) & ~((1u << wlo) - 1u);
-}
 // horizontal 8-tap sums (+ rnd) of the 4 columns of the strip.  `mis` = misalignment of the
 // row start inside its first word: bytes (PB 1) or 0 / 1 pixel (PB 2); the same for every
 // row of an item (strides are multiples of 4 bytes).
@@ -220,125 +180,158 @@ __device__ __forceinline__ void hsum_words(const RowWords<PB> &rw, uint32_t mis,
   }
 }
 
-template <int PB, int KIND>
-__device__ __forceinline__ void store_strip_row(const McArgs &a, const r1c_mc_job &j, int orow, int x0, int ncols,
-                                                const int (&outv)[4]) {
-  if (KIND == 0 || KIND == 2) {
-    uint8_t *d = KIND == 0 ? a.dst0 + ((long long)(j.dst_y + orow) * a.dst_stride + j.dst_x + x0) * PB
-                           : (uint8_t *)a.tmp + ((long long)j.tmp_off + (long long)orow * j.w + x0) * PB;
-    if (PB == 1) {
-      if (ncols == 4 && (((uintptr_t)d) & 3) == 0) {
-        *(uint32_t *)d = (uint32_t)outv[0] | ((uint32_t)outv[1] << 8) | ((uint32_t)outv[2] << 16) | ((uint32_t)outv[3] << 24);
-      } else {
-#pragma unroll
-        for (int c = 0; c < 4; c++)
-          if (c < ncols) d[c] = (uint8_t)outv[c];
-      }
-    } else {
-      uint16_t *d16 = (uint16_t *)d;
-      if (ncols == 4 && (((uintptr_t)d) & 7) == 0) {
-        uint2 v;
-        v.x = (uint32_t)outv[0] | ((uint32_t)outv[1] << 16);
-        v.y = (uint32_t)outv[2] | ((uint32_t)outv[3] << 16);
-        *(uint2 *)d = v;
-      } else {
-#pragma unroll
-        for (int c = 0; c < 4; c++)
-          if (c < ncols) d16[c] = (uint16_t)outv[c];
-      }
-    }
-  } else {
-    int16_t *t = a.tmp + j.tmp_off + (long long)orow * j.w + x0;
-    if (ncols == 4 && (((uintptr_t)t) & 7) == 0) {
-      uint2 v;
-      v.x = ((uint32_t)outv[0] & 0xffff) | ((uint32_t)outv[1] << 16);
-      v.y = ((uint32_t)outv[2] & 0xffff) | ((uint32_t)outv[3] << 16);
-      *(uint2 *)t = v;
-    } else {
-#pragma unroll
-      for (int c = 0; c < 4; c++)
-        if (c < ncols) t[c] = (int16_t)outv[c];
-    }
-  }
-}
-
-// halved taps as s8 x 4 (every SUBPEL_FILTERS entry is even; frac 0 = the unit tap 128 -> 64)
-__device__ __forceinline__ void half_taps(int bank, int frac, uint32_t &t0, uint32_t &t1) {
-  const short *f = c_filters[bank][frac & 15];
+// halved taps as s8 x 4 (every SUBPEL_FILTERS entry is even; frac 0 = the unit tap 128 -> 64), packed once per
+// launch chain by pack_taps_kernel: lanes of a warp hold different (bank, frac), which serialises constant-bank reads
+__device__ uint2 g_half_taps[6 * 16];
+__global__ void pack_taps_kernel() {
+  const int i = threadIdx.x;
+  if (i >= 6 * 16) return;
+  const short *f = c_filters[i >> 4][i & 15];
   short h[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) h[k] = (short)(f[k] >> 1);
-  t0 = pack_taps4(h);
-  t1 = pack_taps4(h + 4);
+  g_half_taps[i] = make_uint2(pack_taps4(h), pack_taps4(h + 4));
+}
+__device__ __forceinline__ void half_taps(int bank, int frac, uint32_t &t0, uint32_t &t1) {
+  const uint2 t = __ldg(&g_half_taps[bank * 16 + (frac & 15)]);
+  t0 = t.x;
+  t1 = t.y;
 }
 
-// One strip (4 columns) of rows [r0, r1) of a job.  ONE code path for the four
-// (col_frac, row_frac) cases of put_8tap_ref / prep_8tap_ref (src/mc.rs:224-306,
-// 326-386): a zero frac is the unit filter (tap 128), for which the separable
-// formula  mid = round_shift(sum_x, 7-ib) as i16;  out = round_shift(sum_y, 7+ib | 7)
-// reproduces the reference's 1-D and copy cases bit for bit (128 * px >> (7-ib) =
-// px << ib exactly; round_shift(128 * mid, 7+ib) = round_shift(mid, ib)).  Taps are
-// halved to fit s8 (all are even), so every shift drops by one:
-// round_shift(2 S, s) = (S + 2^(s-2)) >> (s-1).  Lanes of a warp therefore never
-// diverge on the case; rows / words a case does not read are not loaded.
+// One strip (<= 4 columns) of rows [r0, r1) of a job, pixel by pixel: the kernel's path for strips the vector walker
+// below cannot take (fewer than 4 live columns, an unaligned output row, or a source footprint that touches the
+// edge of the plane allocation).  ONE formula for the four (col_frac, row_frac) cases of put_8tap_ref /
+// prep_8tap_ref (src/mc.rs:224-306, 326-386): a zero frac is the unit filter (tap 128), for which the separable
+// formula  mid = round_shift(sum_x, 7-ib) as i16;  out = round_shift(sum_y, 7+ib | 7)  reproduces the reference's
+// 1-D and copy cases bit for bit (128 * px >> (7-ib) = px << ib exactly; round_shift(128 * mid, 7+ib) =
+// round_shift(mid, ib)).  Taps are halved (all are even), so every shift drops by one:
+// round_shift(2 S, s) = (S + 2^(s-2)) >> (s-1).  Pixels under a zero tap are not read, so a case never touches
+// rows or columns the reference does not.
 template <int PB, int KIND>
-__device__ __forceinline__ void walk_strip(const McArgs &a, const r1c_mc_job &j, int x0, int ncols, int r0, int r1,
-                                           int ib, int maxv) {
-  const bool has_h = j.col_frac != 0, has_v = j.row_frac != 0;
+__device__ __forceinline__ void walk_strip_scalar(const McArgs &a, const r1c_mc_job &j, int x0, int ncols, int r0, int r1,
+                                               int ib, int maxv) {
+  const short *fx = c_filters[filter_bank(j.mode_x, j.w)][j.col_frac & 15];
+  const short *fy = c_filters[filter_bank(j.mode_y, j.h)][j.row_frac & 15];
+  const int hsh = 6 - ib, hrnd = 1 << (5 - ib);
+  const int vshift = (KIND == 1 ? 7 : 7 + ib) - 1, vrnd = 1 << (vshift - 1);
+  const uint8_t *src = (const uint8_t *)a.src.p0 + ((long long)j.src_y * a.src.stride + j.src_x + x0) * PB;
+  const long long sstride = (long long)a.src.stride * PB;
+  for (int r = r0; r < r1; r++)
+    for (int c = 0; c < ncols; c++) {
+      int sv = vrnd;
+      for (int ky = 0; ky < 8; ky++) {
+        const int ty = fy[ky] >> 1;
+        if (ty == 0) continue;
+        const uint8_t *row = src + (long long)(r + ky - 3) * sstride;
+        int sh = hrnd;
+        for (int kx = 0; kx < 8; kx++) {
+          const int tx = fx[kx] >> 1;
+          if (tx == 0) continue;
+          sh += tx * (PB == 1 ? (int)row[c + kx - 3] : (int)((const uint16_t *)row)[c + kx - 3]);
+        }
+        sv += ty * (int)(int16_t)(sh >> hsh);
+      }
+      const int v = sv >> vshift;
+      if (KIND == 1) {
+        a.tmp[(long long)j.tmp_off + (long long)r * j.w + x0 + c] = (int16_t)v;
+      } else {
+        const int o = min(max(v, 0), maxv);
+        uint8_t *d = KIND == 0 ? a.dst0 + ((long long)(j.dst_y + r) * a.dst_stride + j.dst_x + x0 + c) * PB
+                               : (uint8_t *)a.tmp + ((long long)j.tmp_off + (long long)r * j.w + x0 + c) * PB;
+        if (PB == 1) *d = (uint8_t)o;
+        else *(uint16_t *)d = (uint16_t)o;
+      }
+    }
+}
+
+// The same strip for the common case -- 4 live columns, an output row that can be stored as one aligned vector, and
+// a source footprint (all 6 / 4 aligned words of rows r0-3 .. r1+3) that lies inside the plane allocation whatever
+// the (col_frac, row_frac) case: words and rows a case does not need are read anyway and meet zero taps.  No
+// per-word predicates, row pointers advance by the stride, outputs are clamped and stored as packed pairs.
+template <int PB, int KIND, int PF>
+__device__ __forceinline__ void walk_strip_fast(const McArgs &a, const r1c_mc_job &j, int x0, int r0, int r1, int ib,
+                                                int maxv) {
   uint32_t tx0, tx1, ty0, ty1;
   half_taps(filter_bank(j.mode_x, j.w), j.col_frac, tx0, tx1);
   half_taps(filter_bank(j.mode_y, j.h), j.row_frac, ty0, ty1);
-  const uint8_t *src = (const uint8_t *)a.src.p0 + ((long long)j.src_y * a.src.stride + j.src_x + x0) * PB;
-  const long long sstride = (long long)a.src.stride * PB;
   const int hsh = 6 - ib, hrnd = 1 << (5 - ib);
   const int vshift = (KIND == 1 ? 7 : 7 + ib) - 1, vrnd = 1 << (vshift - 1);
-  const uint8_t *hfirst = src - 3 * PB;  // pixel x0-3 of row 0
+  const long long sstride = (long long)a.src.stride * PB;
+  const uint8_t *hfirst = (const uint8_t *)a.src.p0 + ((long long)(j.src_y + r0 - 3) * a.src.stride + j.src_x + x0 - 3) * PB;
   const uint32_t mis = PB == 1 ? (uint32_t)((uintptr_t)hfirst & 3) : (uint32_t)(((uintptr_t)hfirst >> 1) & 1);
-  const uint32_t need = need_mask<PB>(hfirst, ncols, has_h);
-  const int nrows = r1 - r0 + 7;            // source rows r0-3 .. r1+3
-  const int ilo = has_v ? 0 : 3, ihi = has_v ? nrows : nrows - 4;  // rows really read
-  // source rows are fetched PF rows ahead of their use: a thread walks its rows one after the other, and with a
-  // single row in flight every row paid a full DRAM latency (ncu: long-scoreboard stalls, 16 warps per SM)
-  constexpr int PF = 8;
-  RowWords<PB> ring[PF];
-  const uint8_t *rowp = hfirst + (long long)(r0 - 3) * sstride;
+  const uint8_t *wp = (const uint8_t *)((uintptr_t)hfirst & ~(uintptr_t)3);  // next row to fetch
+  constexpr int NW = PB == 1 ? 4 : 6;
+  const int nrows = r1 - r0 + 7;
+  uint8_t *dp;  // output row
+  long long dstride;
+  if (KIND == 0) {
+    dp = a.dst0 + ((long long)(j.dst_y + r0) * a.dst_stride + j.dst_x + x0) * PB;
+    dstride = (long long)a.dst_stride * PB;
+  } else {
+    const int ob = KIND == 1 ? 2 : PB;
+    dp = (uint8_t *)a.tmp + ((long long)j.tmp_off + (long long)r0 * j.w + x0) * ob;
+    dstride = (long long)j.w * ob;
+  }
+  // Source rows travel through a per-thread ring in shared memory filled by cp.async, PF rows ahead, one commit group
+  // per row.  (A ring of registers filled by plain loads does not work: a warp has six scoreboards, the loads of
+  // several rows share one, and the wait for the oldest row then also waits for the youngest -- ncu showed every
+  // row paying a full memory latency.)  wait_group<PF - 1> is exact: PF + i groups exist when row i is needed.
+  __shared__ uint32_t s_ring[PF * NW * MC_THREADS];
+  uint32_t *mine = s_ring + threadIdx.x;
+  auto fetch = [&](int slot) {
 #pragma unroll
-  for (int k = 0; k < PF; k++) load_row_words<PB>(rowp + k * sstride, (k >= ilo && k < ihi) ? need : 0u, ring[k]);
-  // vertical stage on packed pairs of consecutive intermediate rows:
-  //   pr[c][slot] = (mid[i-1], mid[i]) as two i16; out(i-7) = taps . mids(i-7 .. i)
+    for (int k = 0; k < NW; k++) {
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(mine + (slot * NW + k) * MC_THREADS);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(wp + 4 * k) : "memory");
+    }
+    wp += sstride;
+  };
+#pragma unroll
+  for (int k = 0; k < PF; k++) {
+    if (k < nrows) fetch(k);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
   uint32_t pr[4][8];
   int prev[4] = {0, 0, 0, 0};
-#pragma unroll
-  for (int c = 0; c < 4; c++)
-#pragma unroll
-    for (int k = 0; k < 8; k++) pr[c][k] = 0;
+  const uint32_t mx = (uint32_t)maxv * 0x10001u;
   for (int ib8 = 0; ib8 < nrows; ib8 += 8) {
 #pragma unroll
     for (int u = 0; u < 8; u++) {
-      const int i = ib8 + u;
+      const int i = ib8 + u;  // source row r0 - 3 + i
       if (i < nrows) {
-        const RowWords<PB> cur = ring[u % PF];
-        load_row_words<PB>(rowp + (long long)(i + PF) * sstride, (i + PF >= ilo && i + PF < ihi) ? need : 0u, ring[u % PF]);
-        int sum[4], mid[4];
+        asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");
+        RowWords<PB> cur;
+#pragma unroll
+        for (int k = 0; k < NW; k++) cur.w[k] = mine[((u % PF) * NW + k) * MC_THREADS];
+        int sum[4];
         hsum_words<PB>(cur, mis, tx0, tx1, hrnd, sum);
+        if (i + PF < nrows) fetch(u % PF);
+        asm volatile("cp.async.commit_group;" ::: "memory");
 #pragma unroll
         for (int c = 0; c < 4; c++) {
-          mid[c] = sum[c] >> hsh;
-          pr[c][(u + 7) & 7] = __byte_perm((uint32_t)prev[c], (uint32_t)mid[c], 0x5410);
-          prev[c] = mid[c];
+          const int mid = sum[c] >> hsh;
+          pr[c][(u + 7) & 7] = __byte_perm((uint32_t)prev[c], (uint32_t)mid, 0x5410);
+          prev[c] = mid;
         }
         if (i >= 7) {
-          int outv[4];
+          int v[4];
 #pragma unroll
           for (int c = 0; c < 4; c++) {
-            int v = dp2a_lo_s(pr[c][(u + 1) & 7], ty0, vrnd);
-            v = dp2a_hi_s(pr[c][(u + 3) & 7], ty0, v);
-            v = dp2a_lo_s(pr[c][(u + 5) & 7], ty1, v);
-            v = dp2a_hi_s(pr[c][(u + 7) & 7], ty1, v);
-            v >>= vshift;
-            outv[c] = KIND == 1 ? (int)(int16_t)v : min(max(v, 0), maxv);
+            int t = dp2a_lo_s(pr[c][(u + 1) & 7], ty0, vrnd);
+            t = dp2a_hi_s(pr[c][(u + 3) & 7], ty0, t);
+            t = dp2a_lo_s(pr[c][(u + 5) & 7], ty1, t);
+            t = dp2a_hi_s(pr[c][(u + 7) & 7], ty1, t);
+            v[c] = t >> vshift;
           }
-          store_strip_row<PB, KIND>(a, j, r0 + i - 7, x0, ncols, outv);
+          // every result fits i16 (a pixel plus filter overshoot; prep keeps the low 16 bits like `as i16`)
+          uint32_t p01 = __byte_perm((uint32_t)v[0], (uint32_t)v[1], 0x5410), p23 = __byte_perm((uint32_t)v[2], (uint32_t)v[3], 0x5410);
+          if (KIND != 1) {
+            p01 = __vmins2(__vmaxs2(p01, 0u), mx);
+            p23 = __vmins2(__vmaxs2(p23, 0u), mx);
+          }
+          if (KIND != 1 && PB == 1) *(uint32_t *)dp = __byte_perm(p01, p23, 0x6420);
+          else *(uint2 *)dp = make_uint2(p01, p23);
+          dp += dstride;
         }
       }
     }
@@ -348,13 +341,22 @@ __device__ __forceinline__ void walk_strip(const McArgs &a, const r1c_mc_job &j,
 // KIND 0 = put (clamped pixels into the dst plane), 1 = prep (i16, dense w*h at tmp_off),
 // 2 = put into a dense w*h pixel block at tmp_off (pixels; used by the sub-pel search)
 template <int PB, int KIND>
-__global__ void __launch_bounds__(MC_THREADS) mc_kernel(McArgs a) {
+__global__ void __launch_bounds__(MC_THREADS, 4) mc_kernel(const __grid_constant__ McArgs a) {
   const long long total = a.offs[a.n];
   const int ipj = a.offs[a.n + 1] == -a.offs[a.n + 2] ? (int)a.offs[a.n + 1] : 0;  // min == max items per job
   const int ib = a.bit_depth == 12 ? 2 : 4;
   const int maxv = (1 << a.bit_depth) - 1;
-  for (long long item = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item < total;
-       item += (long long)gridDim.x * MC_THREADS) {
+  // resident CTAs take chunks of MC_THREADS items from a counter: strips differ a lot in cost (rows, fast / scalar
+  // path), and a static split left SMs idle for the last third of the launch
+  __shared__ long long s_base;
+  unsigned long long *counter = (unsigned long long *)(a.offs + a.n + 3);
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = (long long)atomicAdd(counter, (unsigned long long)MC_THREADS);
+    __syncthreads();
+    const long long item = s_base + threadIdx.x;
+    if (s_base >= total) break;
+    if (item >= total) continue;
     // every job with the same number of items (the usual batch): no search
     const long long ji = ipj ? (long long)((unsigned long long)item / (unsigned)ipj) : find_job(a.offs, a.n, item);
     const r1c_mc_job j = a.jobs[ji];
@@ -364,7 +366,18 @@ __global__ void __launch_bounds__(MC_THREADS) mc_kernel(McArgs a) {
     const int x0 = strip * 4;
     const int ncols = min(4, j.w - x0);
     const int r0 = seg * SEG_ROWS, r1 = min((int)j.h, r0 + SEG_ROWS);
-    walk_strip<PB, KIND>(a, j, x0, ncols, r0, r1, ib, maxv);
+    // footprint [x0 - 4, x0 + 12) x [r0 - 3, r1 + 3] of the source inside the allocation, vector store aligned
+    const int fx = j.src_x + x0, fy = j.src_y;
+    const bool src_safe = fx - 4 >= -a.src.xorigin && fx + 12 <= a.src.alloc_w - a.src.xorigin &&
+                          fy + r0 - 3 >= -a.src.yorigin && fy + r1 + 3 < a.src.alloc_h - a.src.yorigin;
+    const int ob = KIND == 1 ? 2 : PB;  // bytes per output element
+    const uintptr_t daddr = KIND == 0 ? (uintptr_t)a.dst0 + (uintptr_t)(((long long)j.dst_y * a.dst_stride + j.dst_x + x0) * PB)
+                                      : (uintptr_t)a.tmp + (uintptr_t)(((long long)j.tmp_off + x0) * ob);
+    const int drow = KIND == 0 ? a.dst_stride * PB : j.w * ob;
+    if (ncols == 4 && src_safe && ((daddr | (uintptr_t)drow) & (uintptr_t)(4 * ob - 1)) == 0)
+      walk_strip_fast<PB, KIND, MC_PF>(a, j, x0, r0, r1, ib, maxv);
+    else
+      walk_strip_scalar<PB, KIND>(a, j, x0, ncols, r0, r1, ib, maxv);
   }
 }
 
@@ -461,7 +474,7 @@ template <typename JOB, int ROWS_PER_ITEM>
 int build_offsets(r1c_ctx *ctx, const JOB *d_jobs, int64_t n, long long **d_offs_out) {
   void *d_counts, *d_offs, *d_tmp;
   int rc;
-  const size_t bytes = (size_t)(n + 3) * sizeof(long long);  // offs[n+1], offs[n+2] = min / max items per job
+  const size_t bytes = (size_t)(n + 4) * sizeof(long long);  // offs[n+1], offs[n+2] = min / max items per job, offs[n+3] = work counter
   if ((rc = r1c_scratch_dev(ctx, 2, bytes, &d_counts))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 3, bytes, &d_offs))) return rc;
   long long *minmax = (long long *)d_offs + n + 1;
@@ -498,6 +511,11 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
   // the u16 horizontal filter pairs pixels on 32-bit words: rows must keep the parity
   R1C_REQUIRE(ctx, ((src->cfg.stride * src->px_bytes) & 3) == 0, R1C_ERR_ARG, "plane rows must be a multiple of 4 bytes");
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->mc_taps_ready) {  // identical values whichever context writes them
+    pack_taps_kernel<<<1, 128, 0, ctx->stream>>>();
+    R1C_LAUNCH_CHECK(ctx);
+    ctx->mc_taps_ready = 1;
+  }
   long long *d_offs;
   int rc = build_offsets<r1c_mc_job, 0>(ctx, d_jobs, n, &d_offs);
   if (rc) return rc;
