@@ -111,7 +111,8 @@ int64_t r1c_launch_count(const r1c_ctx *ctx);
 #define R1C_PROF_MC 3         /* put / prep / avg batch kernels               */
 #define R1C_PROF_TX 4         /* forward transform kernels                    */
 #define R1C_PROF_DIST 5       /* SAD / SATD / RDO distortion batch kernels    */
-#define R1C_PROF_SLOTS 6
+#define R1C_PROF_QUANT 6      /* quantize / dequantize kernels                */
+#define R1C_PROF_SLOTS 7
 int r1c_profile(r1c_ctx *ctx, int enable);
 int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches);
 
@@ -294,6 +295,41 @@ int r1c_diff_fwd_txfm_batch(r1c_ctx *ctx, const r1c_plane *input, const r1c_plan
 int r1c_diff_fwd_txfm_batch_dev(r1c_ctx *ctx, const r1c_plane *input, const r1c_plane *pred,
                                 const r1c_tx_job *d_jobs, int64_t n, int tx_size, int tx_type,
                                 int bit_depth, int32_t *d_coeffs);
+
+/* ------------------------------------------------------------------------
+ * Quantize / dequantize, src/quantize.rs.
+ *   r1c_quant_ctx            QuantizationContext, src/quantize.rs:111-121
+ *   r1c_quant_ctx_update     QuantizationContext::update, :212-255, from the VALUES
+ *                            dc_q(qindex, dc_delta_q, bit_depth) / ac_q(..) (:41-61; the
+ *                            qindex tables stay on the Rust side)
+ *   r1c_quantize_batch       QuantizationContext::quantize, :257-316, T = i32
+ *                            (the encoder's call, src/encoder.rs:1170)
+ *   r1c_dequantize_batch     dequantize, :318-334
+ * Layout = the encoder's (src/encoder.rs:1143-1155): block i reads coeffs + i*W*H and
+ * writes qcoeffs / rcoeffs + i*coded, coded = min(W,32)*min(H,32) (av1_get_coded_tx_size);
+ * `scan` = av1_scan_orders[tx_size][tx_type].scan, `coded` entries, scan[0] == 0, a
+ * permutation of 0..coded-1 (host variants check it: R1C_ERR_ARG otherwise).
+ * The fused device entry also writes the reconstruction coefficients and the tx-domain
+ * distortion of src/encoder.rs:1210-1224 in the same pass (either may be NULL).
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  uint32_t log_tx_scale, dc_quant, ac_quant;
+  int32_t dc_offset, ac_offset_eob, ac_offset0, ac_offset1;
+  uint32_t dc_mul_add[3], ac_mul_add[3]; /* divu_gen, src/quantize.rs:123-138 */
+} r1c_quant_ctx;
+int r1c_log_tx_scale(int tx_size); /* get_log_tx_scale, src/quantize.rs:34-39 */
+int r1c_quant_ctx_update(r1c_quant_ctx *qc, int tx_size, int is_intra, uint32_t dc_quant,
+                         uint32_t ac_quant);
+int r1c_quantize_batch(r1c_ctx *ctx, const r1c_quant_ctx *qc, int tx_size, const uint16_t *scan,
+                       const int32_t *coeffs, int32_t *qcoeffs, int64_t n);
+int r1c_dequantize_batch(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint32_t ac_quant,
+                         const int32_t *qcoeffs, int32_t *rcoeffs, int64_t n);
+/* device arrays; d_rcoeffs and d_tx_dist are optional outputs */
+int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int tx_size,
+                           const uint16_t *d_scan, const int32_t *d_coeffs, int32_t *d_qcoeffs,
+                           int32_t *d_rcoeffs, uint64_t *d_tx_dist, int64_t n);
+int r1c_dequantize_batch_dev(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint32_t ac_quant,
+                             const int32_t *d_qcoeffs, int32_t *d_rcoeffs, int64_t n);
 
 /* ------------------------------------------------------------------------
  * Motion search, src/me.rs.

@@ -155,6 +155,23 @@ uint64_t r1o_cdef_dist_wxh(const void *src1, int64_t stride1, int64_t x1, int64_
                            int64_t h_in_b);
 uint64_t r1o_tx_dist(const int32_t *coeffs, const int32_t *rcoeffs, int tx_size);
 
+/* ---- quantize / dequantize (r1o_quant.c), src/quantize.rs ---------------- */
+/* QuantizationContext, src/quantize.rs:111-121 */
+typedef struct {
+  uint32_t log_tx_scale, dc_quant, ac_quant;
+  int32_t dc_offset, ac_offset_eob, ac_offset0, ac_offset1;
+  uint32_t dc_mul_add[3], ac_mul_add[3];
+} r1o_quant_ctx;
+int r1o_log_tx_scale(int tx_size);
+void r1o_divu_gen(uint32_t d, uint32_t out[3]);
+int32_t r1o_divu_pair(int32_t x, const uint32_t d[3]);
+void r1o_quant_ctx_update(r1o_quant_ctx *qc, int tx_size, int is_intra, uint32_t dc_quant, uint32_t ac_quant);
+void r1o_quantize(const r1o_quant_ctx *qc, const uint16_t *scan, int scan_len, const int32_t *coeffs, int32_t *qcoeffs);
+void r1o_dequantize(uint32_t dc_quant, uint32_t ac_quant, int log_tx_scale, const int32_t *qcoeffs, int32_t *rcoeffs,
+                    int len);
+void r1o_quantize_batch(const r1o_quant_ctx *qc, int tx_size, const uint16_t *scan, const int32_t *coeffs,
+                        int32_t *qcoeffs, int32_t *rcoeffs, int64_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,6 +28,13 @@ class PlaneCfg(C.Structure):
         "xorigin", "yorigin")]
 
 
+class QuantCtx(C.Structure):
+    """r1o_quant_ctx = QuantizationContext, src/quantize.rs:111-121"""
+    _fields_ = [("log_tx_scale", C.c_uint32), ("dc_quant", C.c_uint32), ("ac_quant", C.c_uint32),
+                ("dc_offset", C.c_int32), ("ac_offset_eob", C.c_int32), ("ac_offset0", C.c_int32),
+                ("ac_offset1", C.c_int32), ("dc_mul_add", C.c_uint32 * 3), ("ac_mul_add", C.c_uint32 * 3)]
+
+
 class Mv(C.Structure):
     _fields_ = [("row", C.c_int16), ("col", C.c_int16)]
 
@@ -107,6 +114,14 @@ def lib():
         L.r1o_cdef_dist_wxh.restype = u64
         L.r1o_tx_dist.argtypes = [vp, vp, i]
         L.r1o_tx_dist.restype = u64
+        L.r1o_log_tx_scale.argtypes = [i]
+        L.r1o_log_tx_scale.restype = i
+        L.r1o_divu_gen.argtypes = [u32, P(u32 * 3)]
+        L.r1o_divu_pair.argtypes = [C.c_int32, P(u32 * 3)]
+        L.r1o_divu_pair.restype = C.c_int32
+        L.r1o_quant_ctx_update.argtypes = [P(QuantCtx), i, i, u32, u32]
+        L.r1o_quantize_batch.argtypes = [P(QuantCtx), i, vp, vp, vp, vp, i64]
+        L.r1o_dequantize.argtypes = [u32, u32, i, vp, vp, i]
         _lib = L
     return _lib
 
@@ -288,6 +303,43 @@ def tx_dist(coeffs, rcoeffs, tx_size):
     c = np.ascontiguousarray(coeffs, dtype=np.int32)
     r = np.ascontiguousarray(rcoeffs, dtype=np.int32)
     return lib().r1o_tx_dist(_p(c), _p(r), tx_size)
+
+
+def quant_ctx(tx_size, is_intra, dc_quant, ac_quant):
+    """QuantizationContext::update, src/quantize.rs:212-255, from the dc_q / ac_q values"""
+    qc = QuantCtx()
+    lib().r1o_quant_ctx_update(C.byref(qc), tx_size, int(bool(is_intra)), dc_quant, ac_quant)
+    return qc
+
+
+def quantize_batch(qc, tx_size, scan, coeffs, want_rcoeffs=False):
+    """QuantizationContext::quantize (src/quantize.rs:257-316) of N blocks (N, H*W) -> (N, coded);
+    with want_rcoeffs also dequantize (:318-334) of the result"""
+    L = lib()
+    w, h = L.r1o_tx_width(tx_size), L.r1o_tx_height(tx_size)
+    coded = min(w, 32) * min(h, 32)
+    c = np.ascontiguousarray(coeffs, dtype=np.int32)
+    sc = np.ascontiguousarray(scan, dtype=np.uint16)
+    n = c.size // (w * h)
+    assert sc.size == coded and n * w * h == c.size
+    q = np.empty((n, coded), dtype=np.int32)
+    r = np.empty((n, coded), dtype=np.int32) if want_rcoeffs else None
+    L.r1o_quantize_batch(C.byref(qc), tx_size, _p(sc), _p(c), _p(q), _p(r) if want_rcoeffs else None, n)
+    return (q, r) if want_rcoeffs else q
+
+
+def dequantize(qcoeffs, dc_quant, ac_quant, log_tx_scale):
+    """dequantize, src/quantize.rs:318-334, of one block"""
+    q = np.ascontiguousarray(qcoeffs, dtype=np.int32)
+    r = np.empty_like(q)
+    lib().r1o_dequantize(dc_quant, ac_quant, log_tx_scale, _p(q), _p(r), q.size)
+    return r
+
+
+def divu_gen(d):
+    out = (C.c_uint32 * 3)()
+    lib().r1o_divu_gen(d, C.byref(out))
+    return out
 
 
 def lookahead_intra_costs(plane: OPlane, w_in_imp_b, h_in_imp_b, bit_depth):

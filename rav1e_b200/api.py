@@ -295,6 +295,46 @@ def tx_distortion(ctx, coeffs, rcoeffs, tx_size):
     return out
 
 
+class QuantizationContext:
+    """QuantizationContext (src/quantize.rs:111-121, 212-316).  `update` takes the quantizer VALUES
+    dc_q(qindex, dc_delta_q, bit_depth) / ac_q(..) -- the qindex tables (:41-61) stay with the caller."""
+
+    def __init__(self):
+        self.c = capi.QuantCtx()
+        self.tx_size = None
+
+    def update(self, lib, tx_size, is_intra, dc_quant, ac_quant):
+        rc = lib.r1c_quant_ctx_update(C.byref(self.c), tx_size, int(bool(is_intra)), dc_quant, ac_quant)
+        if rc:
+            raise Rav1eCudaError(rc, "bad tx_size / quantizer")
+        self.tx_size = tx_size
+        return self
+
+    def quantize(self, ctx, coeffs, scan):
+        """coeffs (N, H*W) int32, scan = av1_scan_orders[tx_size][tx_type].scan (uint16, coded area)
+        -> qcoeffs (N, min(H,32)*min(W,32)) int32"""
+        coeffs, scan = _arr(coeffs, np.int32), _arr(scan, np.uint16)
+        w, h = ctx.lib.r1c_tx_width(self.tx_size), ctx.lib.r1c_tx_height(self.tx_size)
+        coded = min(w, 32) * min(h, 32)
+        n = coeffs.size // (w * h)
+        assert n * w * h == coeffs.size and scan.size == coded
+        q = np.empty((n, coded), dtype=np.int32)
+        ctx.check(ctx.lib.r1c_quantize_batch(ctx.h, C.byref(self.c), self.tx_size, _p(scan), _p(coeffs), _p(q), n))
+        return q
+
+
+def dequantize(ctx, qcoeffs, tx_size, dc_quant, ac_quant):
+    """dequantize (src/quantize.rs:318-334) of (N, coded) int32 -> rcoeffs, same shape"""
+    qcoeffs = _arr(qcoeffs, np.int32)
+    w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)
+    coded = min(w, 32) * min(h, 32)
+    n = qcoeffs.size // coded
+    assert n * coded == qcoeffs.size
+    r = np.empty(qcoeffs.shape, dtype=np.int32)
+    ctx.check(ctx.lib.r1c_dequantize_batch(ctx.h, tx_size, dc_quant, ac_quant, _p(qcoeffs), _p(r), n))
+    return r
+
+
 def forward_transform(ctx, residual, tx_size, tx_type, bit_depth):
     """residual: int16 (H, W) or a batch (N, H, W) -> int32 coefficients, same shape."""
     residual = _arr(residual, np.int16)

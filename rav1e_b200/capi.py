@@ -75,6 +75,13 @@ class BiasParams(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("w_in_imp_b", "n_imp", "w_in_b", "h_in_b")]
 
 
+class QuantCtx(C.Structure):
+    """r1c_quant_ctx = QuantizationContext, src/quantize.rs:111-121"""
+    _fields_ = [("log_tx_scale", C.c_uint32), ("dc_quant", C.c_uint32), ("ac_quant", C.c_uint32),
+                ("dc_offset", C.c_int32), ("ac_offset_eob", C.c_int32), ("ac_offset0", C.c_int32),
+                ("ac_offset1", C.c_int32), ("dc_mul_add", C.c_uint32 * 3), ("ac_mul_add", C.c_uint32 * 3)]
+
+
 class Mv(C.Structure):
     _fields_ = [("row", C.c_int16), ("col", C.c_int16)]
 
@@ -157,6 +164,12 @@ SIGNATURES = {
     "r1c_rdo_dist_batch_dev": (_i, [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp, _vp, _vp]),
     "r1c_tx_dist_batch": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
     "r1c_tx_dist_batch_dev": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
+    "r1c_log_tx_scale": (_i, [_i]),
+    "r1c_quant_ctx_update": (_i, [_P(QuantCtx), _i, _i, _u32, _u32]),
+    "r1c_quantize_batch": (_i, [_vp, _P(QuantCtx), _i, _vp, _vp, _vp, _i64]),
+    "r1c_quantize_batch_dev": (_i, [_vp, _P(QuantCtx), _i, _vp, _vp, _vp, _vp, _vp, _i64]),
+    "r1c_dequantize_batch": (_i, [_vp, _i, _u32, _u32, _vp, _vp, _i64]),
+    "r1c_dequantize_batch_dev": (_i, [_vp, _i, _u32, _u32, _vp, _vp, _i64]),
     "r1c_diff_fwd_txfm_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_diff_fwd_txfm_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_mv_range": (None, [_i64, _i64, _i64, _i64, _i, _i, _P(_i64 * 4)]),

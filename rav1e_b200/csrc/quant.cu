@@ -1,0 +1,278 @@
+// quant.cu -- batched quantize / dequantize with the tx-domain distortion fused in
+// (reference src/quantize.rs:123-153 divu_gen / divu_pair, :212-255 QuantizationContext::update,
+// :257-316 QuantizationContext::quantize, :318-334 dequantize; src/encoder.rs:1210-1224 tx_dist).
+//
+// quantize walks the coefficients in scan order with a two-state rounding machine (`level_mode`,
+// src/quantize.rs:287-311): the offset of coefficient k depends on the mode left by coefficient
+// k-1.  Here LPB lanes (16 for 4x4 blocks, else 32) take LPB consecutive scan positions at once:
+// a lane computes its coefficient's result under BOTH modes, which also gives the lane's
+// transition map {0,1} -> {0,1} (2 bits); an inclusive shuffle scan composes the maps, the
+// exclusive prefix applied to the mode carried in from the previous chunk selects each lane's
+// result.  Blocks are independent: a warp takes 32 / LPB blocks, a CTA 8 warps.
+// The end-of-block search (rposition over |coeff| >= deadzone) is a max-reduction over the
+// same lanes; coefficients are re-read for the second pass through L1.
+// Bound: HBM, 4 B read + 4 B written per coefficient (+4 with rcoeffs); `scan` stays in L1.
+#include "common.cuh"
+
+namespace {
+
+struct QuantArgs {
+  r1c_quant_ctx qc;
+  const uint16_t *scan;
+  const int32_t *coeffs;
+  int32_t *qcoeffs, *rcoeffs;
+  uint64_t *tx_dist;
+  long long n;
+  int area, coded, dist_bits;
+  int32_t deadzone;
+};
+
+// divu_pair, src/quantize.rs:140-153: ((a * |x| + b) >> 32) >> shift with the sign of x
+__device__ __forceinline__ int32_t divu_pair(int32_t x, uint32_t a, uint32_t b, uint32_t shift) {
+  const uint32_t y = (uint32_t)(x < 0 ? -x : x);
+  const int32_t q = (int32_t)((uint32_t)(((unsigned long long)a * y + b) >> 32) >> shift);
+  return x < 0 ? -q : q;
+}
+__device__ __forceinline__ int32_t signum(int32_t v) { return (v > 0) - (v < 0); }
+// dequantize, src/quantize.rs:329-332 (wrapping i32 product, arithmetic shift)
+__device__ __forceinline__ int32_t dequant1(int32_t c, uint32_t quant, int lts) {
+  return (int32_t)((uint32_t)c * quant + (uint32_t)((c >> 31) & ((1 << lts) - 1))) >> lts;
+}
+
+template <int LPB>
+__global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ QuantArgs a) {
+  constexpr int BPW = 32 / LPB;  // blocks per warp
+  const int lane = threadIdx.x & 31, l = lane & (LPB - 1);
+  const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long b = warp * BPW + lane / LPB;
+  // lanes of a block that does not exist keep shuffling with harmless values
+  const bool live = b < a.n;
+  const long long bb = live ? b : 0;
+  const int32_t *co = a.coeffs + bb * a.area;
+  int32_t *qo = a.qcoeffs + bb * a.coded;
+  const int lts = (int)a.qc.log_tx_scale;
+
+  // ---- eob: last scan index k >= 1 with |coeff| >= deadzone, else 1 (src/quantize.rs:268-276) ----
+  int eob = 1;
+  for (int k = l; k < a.coded; k += LPB) {
+    const int32_t c = __ldg(co + __ldg(a.scan + k));
+    if (k >= 1 && (c < 0 ? -c : c) >= a.deadzone) eob = k;
+  }
+#pragma unroll
+  for (int m = LPB >> 1; m; m >>= 1) eob = max(eob, __shfl_xor_sync(0xffffffffu, eob, m, LPB));
+
+  uint32_t mode = 1;  // level_mode at the start of the chunk
+  unsigned long long dist = 0;
+  for (int k0 = 0; k0 < a.coded; k0 += LPB) {
+    const int k = k0 + l;
+    const bool in = k < a.coded;
+    const int pos = in ? (int)__ldg(a.scan + k) : 0;
+    const int32_t raw = in ? __ldg(co + pos) : 0;
+    const int32_t coeff = (int32_t)((uint32_t)raw << lts);
+    // this lane's result under level_mode 0 / 1 and its transition map (bit m = next mode from mode m);
+    // the DC and the zeroed tail leave the mode alone (identity map)
+    int32_t q0, q1;
+    uint32_t map = 2u;
+    if (k == 0) {
+      // DC, src/quantize.rs:278-280
+      q0 = q1 = divu_pair(coeff + signum(coeff) * a.qc.dc_offset, a.qc.dc_mul_add[0], a.qc.dc_mul_add[1], a.qc.dc_mul_add[2]);
+    } else if (k <= eob) {
+      // src/quantize.rs:293-311
+      const uint32_t ma = a.qc.ac_mul_add[0], mb = a.qc.ac_mul_add[1], ms = a.qc.ac_mul_add[2];
+      const int32_t level0 = divu_pair(coeff, ma, mb, ms);
+      const int32_t sg = signum(coeff);
+      const int32_t qa = divu_pair(coeff + sg * a.qc.ac_offset0, ma, mb, ms);
+      const int32_t qb = divu_pair(coeff + sg * a.qc.ac_offset1, ma, mb, ms);
+      q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
+      q1 = level0 > 0 ? qb : qa;
+      // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1
+      map = (q0 > 1 ? 1u : 0u) | (q1 != 0 ? 2u : 0u);
+    } else {
+      q0 = q1 = 0;  // src/quantize.rs:313-315
+    }
+    // inclusive composition of the maps over the lanes of the block (every lane takes part)
+    uint32_t inc = map;
+#pragma unroll
+    for (int d = 1; d < LPB; d <<= 1) {
+      const uint32_t prev = __shfl_up_sync(0xffffffffu, inc, d, LPB);
+      if (l >= d) inc = ((inc >> (prev & 1u)) & 1u) | (((inc >> ((prev >> 1) & 1u)) & 1u) << 1);
+    }
+    uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1, LPB);
+    if (l == 0) exc = 2u;
+    const int32_t q = ((exc >> mode) & 1u) ? q1 : q0;
+    mode = (__shfl_sync(0xffffffffu, inc, LPB - 1, LPB) >> mode) & 1u;
+    if (in && live) {
+      qo[pos] = q;
+      if (a.rcoeffs || a.tx_dist) {
+        const int32_t r = dequant1(q, pos == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
+        if (a.rcoeffs) a.rcoeffs[bb * a.coded + pos] = r;
+        const uint32_t d = (uint32_t)raw - (uint32_t)r;
+        dist += (unsigned long long)(long long)(int32_t)(d * d);  // (c * c) as u64, wrapping i32 product
+      }
+    }
+  }
+  if (a.tx_dist) {
+#pragma unroll
+    for (int m = LPB >> 1; m; m >>= 1) dist += __shfl_xor_sync(0xffffffffu, dist, m, LPB);
+    if (l == 0 && live) a.tx_dist[b] = (dist + (1ull << (a.dist_bits - 1))) >> a.dist_bits;
+  }
+}
+
+__global__ void dequantize_kernel(const int32_t *q, int32_t *r, long long total, int coded, uint32_t dc_quant,
+                                  uint32_t ac_quant, int lts) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const bool dc = (i % coded) == 0;
+  r[i] = dequant1(__ldg(q + i), dc ? dc_quant : ac_quant, lts);
+}
+
+inline int coded_of(int tx_size) {
+  const int w = r1c_tx_width(tx_size), h = r1c_tx_height(tx_size);
+  return (w < 32 ? w : 32) * (h < 32 ? h : 32);  // av1_get_coded_tx_size, src/encoder.rs:1143
+}
+
+// divu_gen, src/quantize.rs:123-138
+void divu_gen(uint32_t d, uint32_t out[3]) {
+  uint32_t m = 31;
+  while (!((d >> m) & 1u)) m--;
+  if ((d & (d - 1)) == 0) {
+    out[0] = out[1] = 0xFFFFFFFFu;
+  } else {
+    const unsigned long long t = (1ull << (m + 32)) / d;
+    const unsigned long long r = (t * d + d) & 0xFFFFFFFFull;
+    if (r <= (1ull << m)) {
+      out[0] = (uint32_t)t + 1;
+      out[1] = 0;
+    } else {
+      out[0] = out[1] = (uint32_t)t;
+    }
+  }
+  out[2] = m;
+}
+
+}  // namespace
+
+extern "C" int r1c_log_tx_scale(int tx_size) {
+  if (tx_size < 0 || tx_size >= R1C_TX_SIZES_ALL) return -1;
+  const int area = r1c_tx_width(tx_size) * r1c_tx_height(tx_size);
+  return (area > 256) + (area > 1024);
+}
+
+extern "C" int r1c_quant_ctx_update(r1c_quant_ctx *qc, int tx_size, int is_intra, uint32_t dc_quant, uint32_t ac_quant) {
+  if (!qc || tx_size < 0 || tx_size >= R1C_TX_SIZES_ALL || dc_quant == 0 || ac_quant == 0 || dc_quant > 32767 ||
+      ac_quant > 32767)  // dc_q / ac_q return i16 (src/quantize.rs:41,52); 0 would be lossless (unsupported there too)
+    return R1C_ERR_ARG;
+  qc->log_tx_scale = (uint32_t)r1c_log_tx_scale(tx_size);
+  qc->dc_quant = dc_quant;
+  divu_gen(dc_quant, qc->dc_mul_add);
+  qc->ac_quant = ac_quant;
+  divu_gen(ac_quant, qc->ac_mul_add);
+  qc->dc_offset = (int32_t)dc_quant * (is_intra ? 109 : 108) / 256;
+  qc->ac_offset0 = (int32_t)ac_quant * (is_intra ? 98 : 97) / 256;
+  qc->ac_offset1 = (int32_t)ac_quant * (is_intra ? 109 : 108) / 256;
+  qc->ac_offset_eob = (int32_t)ac_quant * (is_intra ? 88 : 44) / 256;
+  return R1C_OK;
+}
+
+extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int tx_size, const uint16_t *d_scan,
+                                      const int32_t *d_coeffs, int32_t *d_qcoeffs, int32_t *d_rcoeffs,
+                                      uint64_t *d_tx_dist, int64_t n) {
+  if (!ctx || !qc) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, tx_size >= 0 && tx_size < R1C_TX_SIZES_ALL, R1C_ERR_ARG, "bad tx_size %d", tx_size);
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (d_scan && d_coeffs && d_qcoeffs)), R1C_ERR_ARG, "null scan / coefficient array");
+  R1C_REQUIRE(ctx, qc->ac_quant > 0 && qc->dc_quant > 0 && (int)qc->log_tx_scale == r1c_log_tx_scale(tx_size), R1C_ERR_ARG,
+              "quantization context was not updated for tx_size %d", tx_size);
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  QuantArgs a;
+  a.qc = *qc;
+  a.scan = d_scan;
+  a.coeffs = d_coeffs;
+  a.qcoeffs = d_qcoeffs;
+  a.rcoeffs = d_rcoeffs;
+  a.tx_dist = d_tx_dist;
+  a.n = n;
+  a.area = r1c_tx_width(tx_size) * r1c_tx_height(tx_size);
+  a.coded = coded_of(tx_size);
+  a.dist_bits = 2 * (3 - (int)qc->log_tx_scale);
+  // (ac_quant as usize - ac_offset_eob as usize).align_power_of_two_and_shift(log_tx_scale), src/quantize.rs:265-267
+  a.deadzone = (int32_t)(((uint64_t)qc->ac_quant - (uint64_t)qc->ac_offset_eob + (1ull << qc->log_tx_scale) - 1) >> qc->log_tx_scale);
+  r1c_prof_begin(ctx, R1C_PROF_QUANT);
+  if (a.coded == 16) quantize_kernel<16><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a);
+  else quantize_kernel<32><<<(unsigned)((n + 7) / 8), 256, 0, ctx->stream>>>(a);
+  r1c_prof_end(ctx, R1C_PROF_QUANT);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
+
+extern "C" int r1c_dequantize_batch_dev(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint32_t ac_quant,
+                                        const int32_t *d_qcoeffs, int32_t *d_rcoeffs, int64_t n) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, tx_size >= 0 && tx_size < R1C_TX_SIZES_ALL, R1C_ERR_ARG, "bad tx_size %d", tx_size);
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (d_qcoeffs && d_rcoeffs)), R1C_ERR_ARG, "null coefficient array");
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int coded = coded_of(tx_size);
+  const long long total = (long long)n * coded;
+  r1c_prof_begin(ctx, R1C_PROF_QUANT);
+  dequantize_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(d_qcoeffs, d_rcoeffs, total, coded, dc_quant,
+                                                                              ac_quant, r1c_log_tx_scale(tx_size));
+  r1c_prof_end(ctx, R1C_PROF_QUANT);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
+
+extern "C" int r1c_quantize_batch(r1c_ctx *ctx, const r1c_quant_ctx *qc, int tx_size, const uint16_t *scan,
+                                  const int32_t *coeffs, int32_t *qcoeffs, int64_t n) {
+  if (!ctx || !qc) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, tx_size >= 0 && tx_size < R1C_TX_SIZES_ALL, R1C_ERR_ARG, "bad tx_size %d", tx_size);
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (scan && coeffs && qcoeffs)), R1C_ERR_ARG, "null scan / coefficient array");
+  if (n == 0) return R1C_OK;
+  const int coded = coded_of(tx_size), area = r1c_tx_width(tx_size) * r1c_tx_height(tx_size);
+  {  // scan[0] == 0 (the DC has its own quantizer) and every index is hit once
+    unsigned char seen[1024] = {0};
+    R1C_REQUIRE(ctx, scan[0] == 0, R1C_ERR_ARG, "scan[0] must be the DC coefficient");
+    for (int k = 0; k < coded; k++) {
+      R1C_REQUIRE(ctx, scan[k] < coded && !seen[scan[k]], R1C_ERR_ARG, "scan is not a permutation of 0..%d", coded - 1);
+      seen[scan[k]] = 1;
+    }
+  }
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t cb = (size_t)n * area * 4, qb = (size_t)n * coded * 4, sb = (size_t)coded * 2;
+  void *d_c, *d_q, *d_s, *h_q;
+  int rc;
+  if ((rc = r1c_scratch_dev(ctx, 0, cb, &d_c))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 1, qb, &d_q))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 2, sb, &d_s))) return rc;
+  if ((rc = r1c_stage_host(ctx, 1, qb, &h_q))) return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_c, coeffs, cb, cudaMemcpyHostToDevice, ctx->stream));
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_s, scan, sb, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = r1c_quantize_batch_dev(ctx, qc, tx_size, (const uint16_t *)d_s, (const int32_t *)d_c, (int32_t *)d_q, nullptr,
+                                   nullptr, n)))
+    return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(h_q, d_q, qb, cudaMemcpyDeviceToHost, ctx->stream));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(qcoeffs, h_q, qb);
+  return R1C_OK;
+}
+
+extern "C" int r1c_dequantize_batch(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint32_t ac_quant,
+                                    const int32_t *qcoeffs, int32_t *rcoeffs, int64_t n) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, tx_size >= 0 && tx_size < R1C_TX_SIZES_ALL, R1C_ERR_ARG, "bad tx_size %d", tx_size);
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (qcoeffs && rcoeffs)), R1C_ERR_ARG, "null coefficient array");
+  if (n == 0) return R1C_OK;
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t qb = (size_t)n * coded_of(tx_size) * 4;
+  void *d_q, *d_r, *h_r;
+  int rc;
+  if ((rc = r1c_scratch_dev(ctx, 0, qb, &d_q))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 1, qb, &d_r))) return rc;
+  if ((rc = r1c_stage_host(ctx, 1, qb, &h_r))) return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_q, qcoeffs, qb, cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = r1c_dequantize_batch_dev(ctx, tx_size, dc_quant, ac_quant, (const int32_t *)d_q, (int32_t *)d_r, n))) return rc;
+  R1C_CUDA(ctx, cudaMemcpyAsync(h_r, d_r, qb, cudaMemcpyDeviceToHost, ctx->stream));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(rcoeffs, h_r, qb);
+  return R1C_OK;
+}

@@ -909,3 +909,77 @@ def test_lookahead_intra_costs(r, ctx, oracle, pb, bd):
     assert np.array_equal(got, oracle.lookahead_intra_costs(o, w_imp, h_imp, bd))
     with pytest.raises(r.Rav1eCudaError):
         r.lookahead_intra_costs(ctx, d, 1000, 1000, bd)
+
+
+# ------------------------------------------------ quantize / dequantize (8f.1) -----
+@pytest.mark.parametrize("is_intra", [0, 1])
+def test_quantize_matches_oracle(r, ctx, oracle, is_intra):
+    from quant_util import scans_for, synth_coeffs
+    L = oracle.lib()
+    rng = np.random.default_rng(31 + is_intra)
+    for ts in range(19):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        for (dcq, acq), kind, scan in zip(((8, 8), (37, 41), (256, 300), (1336, 1828)),
+                                          ("dense", "decay", "sparse", "edge"), scans_for(rng, w, h)):
+            n = 45 if w * h <= 256 else 11  # not a multiple of the blocks per warp / CTA
+            co = synth_coeffs(rng, n, w * h, kind, acq)
+            oq = oracle.quant_ctx(ts, is_intra, dcq, acq)
+            want_q, want_r = oracle.quantize_batch(oq, ts, scan, co, want_rcoeffs=True)
+            qc = r.QuantizationContext().update(ctx.lib, ts, is_intra, dcq, acq)
+            assert bytes(qc.c) == bytes(oq), "QuantizationContext::update"
+            got_q = qc.quantize(ctx, co, scan)
+            assert got_q.shape == (n, coded)
+            assert np.array_equal(got_q, want_q), (ts, kind)
+            assert np.array_equal(r.dequantize(ctx, got_q, ts, dcq, acq), want_r), (ts, kind)
+
+
+def test_quantize_fused_recon_and_tx_dist(r, ctx, oracle):
+    """device entry with both optional outputs: rcoeffs = dequantize(quantize), tx_dist = src/encoder.rs:1210-1224"""
+    import torch
+    from quant_util import scans_for, synth_coeffs
+    L = oracle.lib()
+    rng = np.random.default_rng(41)
+    for ts in (0, 1, 3, 4, 7, 12, 17):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        n, dcq, acq = 77, 120, 147
+        scan = scans_for(rng, w, h)[0]
+        co = synth_coeffs(rng, n, w * h, "decay", acq)
+        co[0, :] = rng.integers(-(1 << 20), 1 << 20, size=w * h)  # squares that wrap i32
+        oq = oracle.quant_ctx(ts, 0, dcq, acq)
+        want_q, want_r = oracle.quantize_batch(oq, ts, scan, co, want_rcoeffs=True)
+        qc = r.QuantizationContext().update(ctx.lib, ts, 0, dcq, acq)
+        d_co, d_sc = torch.from_numpy(co).cuda(), torch.from_numpy(scan.view(np.int16)).cuda()
+        d_q = torch.empty((n, coded), dtype=torch.int32, device="cuda")
+        d_r = torch.empty((n, coded), dtype=torch.int32, device="cuda")
+        d_d = torch.empty(n, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        ctx.check(ctx.lib.r1c_quantize_batch_dev(ctx.h, C.byref(qc.c), ts, d_sc.data_ptr(), d_co.data_ptr(), d_q.data_ptr(),
+                                                 d_r.data_ptr(), d_d.data_ptr(), n))
+        ctx.sync()
+        assert np.array_equal(d_q.cpu().numpy(), want_q) and np.array_equal(d_r.cpu().numpy(), want_r), ts
+        dist = d_d.cpu().numpy().view(np.uint64)
+        for i in range(n):
+            assert int(dist[i]) == oracle.tx_dist(co[i], want_r[i], ts), (ts, i)
+
+
+def test_quantize_errors_and_empty(r, ctx, oracle):
+    qc = r.QuantizationContext().update(ctx.lib, 1, 0, 100, 120)
+    co = np.zeros((2, 64), dtype=np.int32)
+    bad = np.arange(64, dtype=np.uint16)
+    bad[5] = 6  # not a permutation
+    with pytest.raises(r.Rav1eCudaError):
+        qc.quantize(ctx, co, bad)
+    bad = np.arange(64, dtype=np.uint16)[::-1].copy()  # scan[0] != 0
+    with pytest.raises(r.Rav1eCudaError):
+        qc.quantize(ctx, co, bad)
+    with pytest.raises(r.Rav1eCudaError):  # context updated for another transform size class
+        qc32 = r.QuantizationContext().update(ctx.lib, 3, 0, 100, 120)
+        qc32.tx_size = 1
+        qc32.quantize(ctx, co, np.arange(64, dtype=np.uint16))
+    with pytest.raises(r.Rav1eCudaError):  # lossless / out-of-range quantizer
+        r.QuantizationContext().update(ctx.lib, 1, 0, 0, 120)
+    assert qc.quantize(ctx, np.zeros((0, 64), dtype=np.int32), np.arange(64, dtype=np.uint16)).shape == (0, 64)
+    # all-zero blocks: eob = 1, everything zero
+    assert not qc.quantize(ctx, co, np.arange(64, dtype=np.uint16)).any()
