@@ -276,8 +276,42 @@ def run(ctx, r, torch, ext, flush, reps=3):
         "value": coeffs / 1e6 / (tx_ms / 1e3), "unit": "Mcoeff/s", "ms": tx_ms, "coeffs": coeffs,
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                      "alg_bytes_per_coeff": 6, "peak_source": hbm_how, "frac_by_tx_size": per}}
+    # ------------------------------ quantize (+ reconstruction coefficients + tx-domain distortion), same coefficients
+    qsum = {"q": 0.0, "fused": 0.0}
+    qper = {"q": {}, "fused": {}}
+    qcoeffs = 0
+    qout = torch.empty(n_samples, dtype=torch.int32, device="cuda")
+    rout = torch.empty(n_samples, dtype=torch.int32, device="cuda")
+    dout = torch.empty(n_samples // 16, dtype=torch.int64, device="cuda")
+    qin = torch.from_numpy(np.rint(rng.standard_normal(n_samples) * 400).astype(np.int32)).cuda()
+    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        n = n_samples // (w * h)
+        qc = r.QuantizationContext().update(lib, ts, 0, 120, 147)
+        scan = torch.from_numpy(np.concatenate([[0], 1 + rng.permutation(coded - 1)]).astype(np.int16)).cuda()
+        for key, rp, dp in (("q", 0, 0), ("fused", rout.data_ptr(), dout.data_ptr())):
+            def f_q():
+                ctx.check(lib.r1c_quantize_batch_dev(ctx.h, C.byref(qc.c), ts, scan.data_ptr(), qin.data_ptr(),
+                                                     qout.data_ptr(), rp, dp, n))
+            f_q()
+            ctx.sync()
+            _kernel_ms(ctx, 6)
+            _timed(torch, ext, flush, f_q, reps)
+            k_ms = _kernel_ms(ctx, 6)[0] / reps
+            qsum[key] += k_ms
+            qper[key]["%dx%d" % (w, h)] = round(k_ms * 1e3, 1)
+        qcoeffs += n * coded
+    for key, bpc, what in (("q", 8, "quantize"), ("fused", 12, "quantize + dequantize + tx-domain distortion in one pass")):
+        gbs = qcoeffs * bpc / (qsum[key] / 1e3) / 1e9
+        out["quant_4k10_" + key] = {
+            "workload": "4K 4:2:0 coefficients (12.4 M, sigma 400, qstep 147) tiled by each of the 19 TxSize: " + what,
+            "value": qcoeffs / 1e6 / (qsum[key] / 1e3), "unit": "Mcoeff/s", "ms": qsum[key], "coeffs": qcoeffs,
+            "kernel_us_by_tx_size": qper[key],
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                         "alg_bytes_per_coeff": bpc, "peak_source": hbm_how}}
     ctx.check(lib.r1c_profile(ctx.h, 0))
-    del res, coef, org, src, dst, d_out
+    del res, coef, org, src, dst, d_out, qout, rout, dout, qin
     # -------------------------- whole-frame motion estimation on a 4K 10-bit frame pair (u16 planes)
     if not os.environ.get("R1C_BENCH_SIZES") and not os.environ.get("R1C_BENCH_TXSIZES"):
         out["me_4k10_fullsearch_pm64"] = me_frame_line(ctx, r, torch, ext, flush, 3840, 2160, 10, 64)

@@ -10,7 +10,7 @@
 // exclusive prefix applied to the mode carried in from the previous chunk selects each lane's
 // result.  Blocks are independent: a warp takes 32 / LPB blocks, a CTA 8 warps.
 // The end-of-block search (rposition over |coeff| >= deadzone) is a max-reduction over the
-// same lanes; coefficients are re-read for the second pass through L1.
+// same lanes; a lane keeps its coefficients in registers for the second pass.
 // Bound: HBM, 4 B read + 4 B written per coefficient (+4 with rcoeffs); `scan` stays in L1.
 #include "common.cuh"
 
@@ -39,46 +39,62 @@ __device__ __forceinline__ int32_t dequant1(int32_t c, uint32_t quant, int lts) 
   return (int32_t)((uint32_t)c * quant + (uint32_t)((c >> 31) & ((1 << lts) - 1))) >> lts;
 }
 
-template <int LPB>
+// LPB lanes per block, NCH = coded / LPB chunks of scan positions; a lane keeps its NCH coefficients in registers
+// between the end-of-block search and the quantizer pass
+template <int LPB, int NCH>
 __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ QuantArgs a) {
   constexpr int BPW = 32 / LPB;  // blocks per warp
-  const int lane = threadIdx.x & 31, l = lane & (LPB - 1);
+  const int lane = threadIdx.x & 31, l = lane & (LPB - 1), sh = lane & ~(LPB - 1);
   const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long b = warp * BPW + lane / LPB;
-  // lanes of a block that does not exist keep shuffling with harmless values
-  const bool live = b < a.n;
-  const long long bb = live ? b : 0;
-  const int32_t *co = a.coeffs + bb * a.area;
-  int32_t *qo = a.qcoeffs + bb * a.coded;
+  const bool live = b < a.n;  // lanes of a block that does not exist go through the motions on zeros
   const int lts = (int)a.qc.log_tx_scale;
+  constexpr uint32_t BMASK = LPB == 32 ? 0xffffffffu : ((1u << LPB) - 1u);
+  // The warp's blocks go through shared memory: coalesced in, gathered / scattered by scan position there (a scan
+  // sends neighbouring lanes to different rows of the block: one L1 wavefront per lane when done on global memory),
+  // coalesced out.  Quantized values overwrite the coefficients in place.
+  constexpr int CODED = LPB * NCH;
+  __shared__ int32_t s_buf[8][BPW * CODED];
+  int32_t *sw = s_buf[threadIdx.x >> 5], *sb = sw + (lane / LPB) * CODED;
+#pragma unroll
+  for (int i = 0; i < BPW * CODED / 32; i++) {
+    const int e = i * 32 + lane, blk = e / CODED, off = e - blk * CODED;  // BPW > 1 only for 16-coefficient blocks
+    const long long gb = warp * BPW + blk;
+    sw[e] = gb < a.n ? __ldg(a.coeffs + gb * a.area + off) : 0;
+  }
+  __syncwarp();
 
   // ---- eob: last scan index k >= 1 with |coeff| >= deadzone, else 1 (src/quantize.rs:268-276) ----
+  int32_t raw[NCH];
+  int pos[NCH];
   int eob = 1;
-  for (int k = l; k < a.coded; k += LPB) {
-    const int32_t c = __ldg(co + __ldg(a.scan + k));
-    if (k >= 1 && (c < 0 ? -c : c) >= a.deadzone) eob = k;
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    const int k = c * LPB + l;
+    pos[c] = (int)__ldg(a.scan + k);
+    raw[c] = sb[pos[c]];
+    if (k >= 1 && (raw[c] < 0 ? -raw[c] : raw[c]) >= a.deadzone) eob = k;
   }
 #pragma unroll
   for (int m = LPB >> 1; m; m >>= 1) eob = max(eob, __shfl_xor_sync(0xffffffffu, eob, m, LPB));
 
+  const uint32_t ma = a.qc.ac_mul_add[0], mb = a.qc.ac_mul_add[1], ms = a.qc.ac_mul_add[2];
+  __syncwarp();
   uint32_t mode = 1;  // level_mode at the start of the chunk
   unsigned long long dist = 0;
-  for (int k0 = 0; k0 < a.coded; k0 += LPB) {
-    const int k = k0 + l;
-    const bool in = k < a.coded;
-    const int pos = in ? (int)__ldg(a.scan + k) : 0;
-    const int32_t raw = in ? __ldg(co + pos) : 0;
-    const int32_t coeff = (int32_t)((uint32_t)raw << lts);
-    // this lane's result under level_mode 0 / 1 and its transition map (bit m = next mode from mode m);
-    // the DC and the zeroed tail leave the mode alone (identity map)
+#pragma unroll
+  for (int c = 0; c < NCH; c++) {
+    const int k = c * LPB + l;
+    const int32_t coeff = (int32_t)((uint32_t)raw[c] << lts);
+    // this lane's result under level_mode 0 / 1 and its transition map f0 / f1 = next mode from mode 0 / 1;
+    // the DC and the zeroed tail leave the mode alone (f0 = 0, f1 = 1)
     int32_t q0, q1;
-    uint32_t map = 2u;
+    bool f0 = false, f1 = true;
     if (k == 0) {
       // DC, src/quantize.rs:278-280
       q0 = q1 = divu_pair(coeff + signum(coeff) * a.qc.dc_offset, a.qc.dc_mul_add[0], a.qc.dc_mul_add[1], a.qc.dc_mul_add[2]);
     } else if (k <= eob) {
       // src/quantize.rs:293-311
-      const uint32_t ma = a.qc.ac_mul_add[0], mb = a.qc.ac_mul_add[1], ms = a.qc.ac_mul_add[2];
       const int32_t level0 = divu_pair(coeff, ma, mb, ms);
       const int32_t sg = signum(coeff);
       const int32_t qa = divu_pair(coeff + sg * a.qc.ac_offset0, ma, mb, ms);
@@ -86,29 +102,51 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
       q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
       q1 = level0 > 0 ? qb : qa;
       // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1
-      map = (q0 > 1 ? 1u : 0u) | (q1 != 0 ? 2u : 0u);
+      f0 = q0 > 1;
+      f1 = q1 != 0;
     } else {
       q0 = q1 = 0;  // src/quantize.rs:313-315
     }
-    // inclusive composition of the maps over the lanes of the block (every lane takes part)
-    uint32_t inc = map;
+    // maps of the block's lanes as two bit masks; a lane's incoming mode = the mode left by the closest earlier
+    // lane whose map is constant (f0 == f1), else the mode carried into the chunk
+    const uint32_t A = (__ballot_sync(0xffffffffu, f0) >> sh) & BMASK, B = (__ballot_sync(0xffffffffu, f1) >> sh) & BMASK;
+    uint32_t m_in;
+    if (__any_sync(0xffffffffu, f0 && !f1)) {
+      // a map that flips the mode (q0 > 1 but q1 == 0: not seen with offset1 >= offset0, handled all the same):
+      // compose the 2-bit maps with an inclusive shuffle scan
+      uint32_t inc = (f0 ? 1u : 0u) | (f1 ? 2u : 0u);
 #pragma unroll
-    for (int d = 1; d < LPB; d <<= 1) {
-      const uint32_t prev = __shfl_up_sync(0xffffffffu, inc, d, LPB);
-      if (l >= d) inc = ((inc >> (prev & 1u)) & 1u) | (((inc >> ((prev >> 1) & 1u)) & 1u) << 1);
-    }
-    uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1, LPB);
-    if (l == 0) exc = 2u;
-    const int32_t q = ((exc >> mode) & 1u) ? q1 : q0;
-    mode = (__shfl_sync(0xffffffffu, inc, LPB - 1, LPB) >> mode) & 1u;
-    if (in && live) {
-      qo[pos] = q;
-      if (a.rcoeffs || a.tx_dist) {
-        const int32_t r = dequant1(q, pos == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
-        if (a.rcoeffs) a.rcoeffs[bb * a.coded + pos] = r;
-        const uint32_t d = (uint32_t)raw - (uint32_t)r;
-        dist += (unsigned long long)(long long)(int32_t)(d * d);  // (c * c) as u64, wrapping i32 product
+      for (int d = 1; d < LPB; d <<= 1) {
+        const uint32_t prev = __shfl_up_sync(0xffffffffu, inc, d, LPB);
+        if (l >= d) inc = ((inc >> (prev & 1u)) & 1u) | (((inc >> ((prev >> 1) & 1u)) & 1u) << 1);
       }
+      uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1, LPB);
+      if (l == 0) exc = 2u;
+      m_in = (exc >> mode) & 1u;
+      mode = (__shfl_sync(0xffffffffu, inc, LPB - 1, LPB) >> mode) & 1u;
+    } else {
+      const uint32_t fixed = ~(A ^ B) & BMASK;  // lanes that set (A = B = 1) or reset (A = B = 0) the mode
+      const uint32_t below = fixed & ((1u << l) - 1u);
+      m_in = below ? (A >> (31 - __clz(below))) & 1u : mode;
+      mode = fixed ? (A >> (31 - __clz(fixed))) & 1u : mode;
+    }
+    const int32_t q = m_in ? q1 : q0;
+    sb[pos[c]] = q;
+    if (a.tx_dist) {
+      const int32_t r = dequant1(q, pos[c] == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
+      const uint32_t d = (uint32_t)raw[c] - (uint32_t)r;
+      dist += (unsigned long long)(long long)(int32_t)(d * d);  // (c * c) as u64, wrapping i32 product
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < BPW * CODED / 32; i++) {
+    const int e = i * 32 + lane, blk = e / CODED, off = e - blk * CODED;
+    const long long gb = warp * BPW + blk;
+    if (gb < a.n) {
+      const int32_t q = sw[e];
+      a.qcoeffs[gb * CODED + off] = q;
+      if (a.rcoeffs) a.rcoeffs[gb * CODED + off] = dequant1(q, off == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
     }
   }
   if (a.tx_dist) {
@@ -198,8 +236,16 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   // (ac_quant as usize - ac_offset_eob as usize).align_power_of_two_and_shift(log_tx_scale), src/quantize.rs:265-267
   a.deadzone = (int32_t)(((uint64_t)qc->ac_quant - (uint64_t)qc->ac_offset_eob + (1ull << qc->log_tx_scale) - 1) >> qc->log_tx_scale);
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
-  if (a.coded == 16) quantize_kernel<16><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a);
-  else quantize_kernel<32><<<(unsigned)((n + 7) / 8), 256, 0, ctx->stream>>>(a);
+  const unsigned g8 = (unsigned)((n + 7) / 8);
+  switch (a.coded) {  // 4x4 .. 32x32 coded areas
+    case 16: quantize_kernel<16, 1><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
+    case 32: quantize_kernel<32, 1><<<g8, 256, 0, ctx->stream>>>(a); break;
+    case 64: quantize_kernel<32, 2><<<g8, 256, 0, ctx->stream>>>(a); break;
+    case 128: quantize_kernel<32, 4><<<g8, 256, 0, ctx->stream>>>(a); break;
+    case 256: quantize_kernel<32, 8><<<g8, 256, 0, ctx->stream>>>(a); break;
+    case 512: quantize_kernel<32, 16><<<g8, 256, 0, ctx->stream>>>(a); break;
+    default: quantize_kernel<32, 32><<<g8, 256, 0, ctx->stream>>>(a); break;
+  }
   r1c_prof_end(ctx, R1C_PROF_QUANT);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;

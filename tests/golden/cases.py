@@ -5,6 +5,8 @@ stored); `cuda_vectors(r, ctx, r1o)` computes the same vectors through the C ABI
 rebuilt from fixed seeds, only outputs are stored (full arrays when small, else the first 8 bytes
 of a SHA-256 as a u64)."""
 import hashlib
+import os
+import sys
 
 import numpy as np
 
@@ -140,8 +142,27 @@ def oracle_vectors(r1o):
     out["tx_dist"] = np.array([r1o.tx_dist(rng.integers(-(1 << 17), 1 << 17, L.r1o_tx_width(ts) * L.r1o_tx_height(ts)),
                                            rng.integers(-(1 << 17), 1 << 17, min(L.r1o_tx_width(ts), 32) * min(L.r1o_tx_height(ts), 32)), ts)
                                for ts in range(19)], dtype=np.uint64)
+    for name, (q, rc) in quant_cases(r1o, lambda qc, ts, scan, co, isi, dcq, acq: r1o.quantize_batch(
+            r1o.quant_ctx(ts, isi, dcq, acq), ts, scan, co, want_rcoeffs=True)).items():
+        out["quant_q_" + name], out["quant_r_" + name] = digest(q), digest(rc)
     del C
     return out
+
+
+def quant_cases(r1o, run):
+    """quantize + dequantize of seeded blocks of every TxSize (zig-zag scan, inter and intra)"""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from quant_util import synth_coeffs, zigzag_scan
+    L = r1o.lib()
+    rng = np.random.default_rng(61)
+    res = {}
+    for ts in range(19):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        scan = zigzag_scan(min(w, 32), min(h, 32))
+        for isi, (dcq, acq) in ((0, (37, 41)), (1, (1336, 1828))):
+            co = synth_coeffs(rng, 9, w * h, "decay", acq)
+            res["%d_%d" % (ts, isi)] = run(None, ts, scan, co, isi, dcq, acq)
+    return res
 
 
 ALL_SIZES_TO_64 = sum(1 << b for b in range(22) if b not in (13, 14, 15))
@@ -216,4 +237,10 @@ def cuda_vectors(r, ctx, r1o):
         rc = rng.integers(-(1 << 17), 1 << 17, min(L.r1o_tx_width(ts), 32) * min(L.r1o_tx_height(ts), 32))
         td.append(r.tx_distortion(ctx, c, rc, ts)[0])
     out["tx_dist"] = np.array(td, dtype=np.uint64)
+
+    def run(_, ts, scan, co, isi, dcq, acq):
+        q = r.QuantizationContext().update(ctx.lib, ts, isi, dcq, acq).quantize(ctx, co, scan)
+        return q, r.dequantize(ctx, q, ts, dcq, acq)
+    for name, (q, rc) in quant_cases(r1o, run).items():
+        out["quant_q_" + name], out["quant_r_" + name] = digest(q), digest(rc)
     return out

@@ -983,3 +983,23 @@ def test_quantize_errors_and_empty(r, ctx, oracle):
     assert qc.quantize(ctx, np.zeros((0, 64), dtype=np.int32), np.arange(64, dtype=np.uint16)).shape == (0, 64)
     # all-zero blocks: eob = 1, everything zero
     assert not qc.quantize(ctx, co, np.arange(64, dtype=np.uint16)).any()
+
+
+def test_quantize_mode_flipping_maps(r, ctx, oracle):
+    """hand-made offsets (offset0 = +quant, offset1 = -quant) make coefficients whose map FLIPS the level mode
+    (q0 > 1 and q1 == 0) -- never the case with update()'s offsets -- so the kernel's general composition of
+    transition maps is exercised too"""
+    from quant_util import scans_for, synth_coeffs
+    L = oracle.lib()
+    rng = np.random.default_rng(77)
+    for ts in (0, 1, 2, 3, 9):
+        w, h = L.r1o_tx_width(ts), L.r1o_tx_height(ts)
+        acq = 64
+        oq = oracle.quant_ctx(ts, 0, 50, acq)
+        oq.ac_offset0, oq.ac_offset1 = acq, -acq
+        qc = r.QuantizationContext().update(ctx.lib, ts, 0, 50, acq)
+        qc.c.ac_offset0, qc.c.ac_offset1 = acq, -acq
+        scan = scans_for(rng, w, h)[3]
+        co = synth_coeffs(rng, 40, w * h, "edge", acq)
+        want = oracle.quantize_batch(oq, ts, scan, co)
+        assert np.array_equal(qc.quantize(ctx, co, scan), want), ts
