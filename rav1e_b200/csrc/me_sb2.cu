@@ -102,6 +102,11 @@ __device__ __forceinline__ bool mv_ok(const Geo2 &g, int bx, int by, int bw, int
   return (bx + ox + bw >= -16) && (bx + ox <= g.W4 + 16) && (by + oy + bh >= -16) && (by + oy <= g.H4 + 16);
 }
 
+// every block of the 64x64 region may take MV offset (ox, oy): the 4x4 blocks on the region's edges decide
+__device__ __forceinline__ bool cand_free(const Geo2 &g, int ox, int oy) {
+  return (g.RX + 4 + ox >= -16) && (g.RX + 60 + ox <= g.W4 + 16) && (g.RY + 4 + oy >= -16) && (g.RY + 60 + oy <= g.H4 + 16);
+}
+
 // in-quadrant aggregation + running minima of one candidate
 template <bool MASKED, int KSHIFT>
 __device__ __forceinline__ void quad_update(const uint32_t (&cell)[4][4], uint32_t rck, uint32_t rl, uint32_t seq,
@@ -168,6 +173,11 @@ __device__ __forceinline__ void quad_update(const uint32_t (&cell)[4][4], uint32
 #undef K_UPD
 #undef P_UPD
 }
+
+template <bool V>
+struct BoolTag {
+  static constexpr bool value = V;
+};
 
 struct Chunk {
   int NX, NYc, NP, NS, iters;
@@ -247,7 +257,7 @@ __device__ __forceinline__ uint32_t fold_cell(uint32_t c, int nb) {
 template <bool MASKED, int RSW, int PB>
 __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
                                            const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
-                                           const int16_t *s_nbox,
+                                           const int16_t *s_nbox, const uint32_t *s_rcol, const uint32_t *s_rrow,
                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                            uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
@@ -255,7 +265,6 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
   constexpr int SEQ_BITS = Px<PB>::SEQ_BITS, KSHIFT = Px<PB>::KSHIFT, PXW = Px<PB>::PXW, NWQ = Px<PB>::NWQ;
   const int rsw = RSW ? RSW : a.rsw;
   const int sdx = 32 % ck.NX, sj = 32 / ck.NX;
-  const int hp = a.p.allow_high_precision_mv;
   const int M2 = 2 * a.M;
   // slot of this lane: f = it * 32 + lane = j * NX + dx
   int f = lane, j = lane / ck.NX, dx = lane - j * ck.NX;
@@ -335,18 +344,21 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
     }
     // ---- rate terms ---------------------------------------------------------------------
     const int ox = ck.cxlo + dx, oyA = ck.cylo + ck.row0 + dyA;
-    const int mvc = 8 * ox, mvrA = 8 * oyA, mvrB = mvrA + 8;
-    const uint32_t rc0 = rate1(mvc - job.pmv[0].col, hp), rc1 = rate1(mvc - job.pmv[1].col, hp) + 1;
-    const uint32_t rA = min(rate1(mvrA - job.pmv[0].row, hp) + rc0, rate1(mvrA - job.pmv[1].row, hp) + rc1);
-    const uint32_t rB = min(rate1(mvrB - job.pmv[0].row, hp) + rc0, rate1(mvrB - job.pmv[1].row, hp) + rc1);
+    // rate = min(rate(mv, pmv0), rate(mv, pmv1) + 1) from the per-column / per-row tables (two u16 halves each)
+    const uint32_t rcp = s_rcol[dx], rsA = rcp + s_rrow[dyA], rsB = rcp + s_rrow[dyA + 1];
+    const uint32_t rA = min(rsA & 0xffffu, rsA >> 16), rB = min(rsB & 0xffffu, rsB >> 16);
     const uint32_t rlA = rA * a.p.lambda, rlB = rB * a.p.lambda;
     const uint32_t seqA = (uint32_t)(j * M2 + (dx >> 5)), seqB = seqA + (uint32_t)a.M;
     const uint32_t rckA = ((rlA >> 8) << KSHIFT) | ((rlA & 255u) << SEQ_BITS) | seqA;
     const uint32_t rckB = ((rlB >> 8) << KSHIFT) | ((rlB & 255u) << SEQ_BITS) | seqB;
 
     uint32_t xsA[5], xsB[5];
-    quad_update<MASKED, KSHIFT>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
-    quad_update<MASKED, KSHIFT>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
+    // border superblocks: most candidates are still legal for every block of the region and take the unmasked code
+    const bool freeA = !MASKED || cand_free(g, ox, oyA), freeB = !MASKED || cand_free(g, ox, oyA + 1);
+    if (freeA) quad_update<false, KSHIFT>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
+    else quad_update<MASKED, KSHIFT>(cA, rckA, rlA, seqA, best, pc, ps, xsA, g, ox, oyA);
+    if (freeB) quad_update<false, KSHIFT>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
+    else quad_update<MASKED, KSHIFT>(cB, rckB, rlB, seqB, best, pc, ps, xsB, g, ox, oyA + 1);
 
     // ---- exchange of the quadrant partial sums: xb[part][quadrant][A lanes | B lanes] ---
     uint32_t *xb = s_x + (it & 1) * (5 * 16 * 64);
@@ -357,12 +369,13 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
     }
     __syncthreads();
     // ---- blocks spanning quadrants, by warp role ----------------------------------------
-    {
+    auto big_phase = [&](auto masked_tag) {
+      constexpr bool BM = decltype(masked_tag)::value;
       const uint32_t *xl = xb + lane;
 #define XA(PART, QUAD) xl[((PART) * 16 + (QUAD)) * 64]
 #define XB(PART, QUAD) xl[((PART) * 16 + (QUAD)) * 64 + 32]
 #define BIG(S, SA, SB, LX, LY, BW, BH) \
-  big_upd<MASKED>(bc[S], bs[S], SA, SB, rlA, rlB, seqA, seqB, g, LX, LY, BW, BH, ox, oyA)
+  big_upd<BM>(bc[S], bs[S], SA, SB, rlA, rlB, seqA, seqB, g, LX, LY, BW, BH, ox, oyA)
       if (rg == 0) {  // column ri: 16x16 sums of its four quadrants
         const int c = ri;
         const uint32_t a0 = XA(0, c), a1 = XA(0, c + 4), a2 = XA(0, c + 8), a3 = XA(0, c + 12);
@@ -423,7 +436,9 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
 #undef XA
 #undef XB
 #undef BIG
-    }
+    };
+    if (freeA && freeB) big_phase(BoolTag<false>{});
+    else big_phase(BoolTag<MASKED>{});
     // ---- next slot; a lane that runs out of slots repeats its last one (same keys) ----
     if (f + 32 < ck.NS) {
       f += 32;
@@ -484,7 +499,9 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
   uint32_t *s_x = s_ref + a.csz;       // 2 x [5][16][64]
   const int nrows = ck.NYc + 63;
   // u16 only: negated 4x4 box sums of the window [nrows - 3][rsw * PXW], summed-area table of org's 4x4 cells
-  uint32_t *s_sat = s_x + 2 * 5 * 16 * 64;  // [17][17]
+  uint32_t *s_rcol = s_x + 2 * 5 * 16 * 64;  // [256] rate of the column part of a candidate: pmv0 | (pmv1 + 1) << 16
+  uint32_t *s_rrow = s_rcol + 256;          // [rpc] row part
+  uint32_t *s_sat = s_rrow + a.rpc;         // [17][17]
   int16_t *s_nbox = (int16_t *)(s_sat + 17 * 17 + 3);
 
   // ---- stage the org region and phase 0 of the window (clamped into the allocation:
@@ -525,6 +542,17 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
 #pragma unroll
       for (int ph = 1; ph < PXW; ph++) s_ref[i * PXW + ph] = __funnelshift_r(lo, hi, 8 * PB * ph);
     }
+  {  // get_mv_rate (src/me.rs:1005-1021) per column and per row of the chunk's candidates
+    const int hp = a.p.allow_high_precision_mv;
+    for (int i = tid; i < ck.NX; i += T2) {
+      const int mvc = 8 * (ck.cxlo + i);
+      s_rcol[i] = rate1(mvc - job.pmv[0].col, hp) | ((rate1(mvc - job.pmv[1].col, hp) + 1u) << 16);
+    }
+    for (int i = tid; i < ck.NYc; i += T2) {
+      const int mvr = 8 * (ck.cylo + ck.row0 + i);
+      s_rrow[i] = rate1(mvr - job.pmv[0].row, hp) | (rate1(mvr - job.pmv[1].row, hp) << 16);
+    }
+  }
   if (PB == 2 && chunk == 0) {  // sums of org's 4x4 cells (-> s_x, free until the search starts)
     if (tid < 256) {
       const uint16_t *o = (const uint16_t *)s_org + (tid >> 4) * 4 * 64 + (tid & 15) * 4;
@@ -610,8 +638,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     pc[i] = bc[i] = NONE32;
     ps[i] = bs[i] = 0;
   }
-  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, best, pc, ps, bc, bs, g);
-  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, best, pc, ps, bc, bs, g);
+  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
+  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
 
   // ---- reduce over the 32 lanes and write the partial keys ------------------------------
   unsigned long long *out = a.partial + wi * NSLOT;
@@ -739,7 +767,7 @@ static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, i
     if ((long long)(last + 1) / 2 * NX < 32) continue;  // every lane needs a slot of its own
     const int nrows = rpc + 63;
     const int csz = nrows * rsw * pxw;
-    size_t smem = (size_t)64 * 64 * px_bytes + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4;
+    size_t smem = (size_t)64 * 64 * px_bytes + (size_t)csz * 4 + (size_t)2 * 5 * 16 * 64 * 4 + (size_t)(256 + rpc) * 4;
     if (px_bytes == 2) smem += (size_t)(17 * 17 + 3) * 4 + (size_t)(nrows - 3) * rsw * pxw * 2;  // s_sat, s_nbox
     if (smem > 220 * 1024) continue;
     // enough work items to balance the SMs: stop once the tail is small
