@@ -318,6 +318,19 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
       // one j have the same col_frac and source column, and their source rows start 0..2 rows apart, so
       // the S + 7 horizontally filtered rows are computed ONCE per j and every candidate is 4 DP2A per
       // output on the shared (row n, row n+1) pairs.  Candidates leave in pairs through the packed Hadamard.
+      // get_mv_range test of the 3 candidate columns (bits 0..2) and rows (bits 3..5), once per tile
+      uint32_t ok = 0;
+      {
+        const int xmin = -bx * 8 - 128 - 8 * bw, xmax = (a.W - bx - bw) * 8 + 128 + 8 * bw;
+        const int ymin = -by * 8 - 128 - 8 * bh, ymax = (a.H - by - bh) * 8 + 128 + 8 * bh;
+#pragma unroll
+        for (int u = 0; u < 3; u++) {
+          const int mc = (int)(int16_t)((int)center.col + step * (u - 1)), mr = (int)(int16_t)((int)center.row + step * (u - 1));
+          ok |= (mc >= xmin && mc <= xmax ? 1u : 0u) << u;
+          ok |= (mr >= ymin && mr <= ymax ? 8u : 0u) << u;
+        }
+        ok = tile_live ? ok : 0u;
+      }
       int dp[S];  // the candidate waiting for its pair partner
       bool dp_live = false;
       int dp_k = 0, arrived = 0;  // (compile-time after unrolling)
@@ -360,15 +373,15 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
           // taps 1..8 of the filter moved down by `off` rows (byte shifts of the 64-bit tap word)
           const uint32_t e0 = tyw.x << sh8, e1 = __funnelshift_l(tyw.x, tyw.y, sh8), e2 = __funnelshift_l(tyw.y, 0u, sh8);
           const uint32_t f0 = __funnelshift_r(e0, e1, 8), f1 = __funnelshift_r(e1, e2, 8);
-          const bool live = tile_live && mv_in_range(a, bx, by, bw, bh, mv);
-          int d[S];
+          const bool live = ((ok >> jg) & (ok >> (3 + i)) & 1u) != 0;
+          int d[S];  // of a candidate that is not live: computed all the same, never accumulated
 #pragma unroll
           for (int t = 0; t < S; t++) {
             int v = dp2a_lo_ss(P[t], f0, 512);
             v = dp2a_hi_ss(P[t + 2], f0, v);
             v = dp2a_lo_ss(P[t + 4], f1, v);
             v = dp2a_hi_ss(P[t + 6], f1, v);
-            d[t] = live ? oc[t] - min(max(v >> 10, 0), maxv) : 0;
+            d[t] = oc[t] - min(max(v >> 10, 0), maxv);
           }
           if (!PAIR) {
             const uint32_t acc = tile_dist<S>(d, lane, satd);
