@@ -52,6 +52,16 @@ def synth_frame_pair(seed):
 padded = bench_kernels.padded
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one me_sb2_kernel launch from the committed `ncu --set full`
+    capture (profiles/ncu_me_sb2_u8_r01h.json), bytes per launch; None when the summary is missing"""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_me_sb2_u8_r01h.json")))
+        return int(d["dram__bytes_read.sum"]) + int(d["dram__bytes_write.sum"])
+    except Exception:
+        return None
+
+
 # ----------------------------------------------------------------------- clocks --
 class ClockSampler(threading.Thread):
     """samples SM clock and throttle reasons of one GPU (NVML) while the timed region runs"""
@@ -312,7 +322,7 @@ def main():
         alg_bytes = n_sb * (win * PB + 849 * 16)  # window + org region per superblock, results out
         achieved = ALG_INT_OPS / (sb_ms / 1e3) / 1e9  # G int-ops/s
         roof = {"bound": "int32_alu", "kernel": "me_sb2_kernel<48> (superblock full search, every size from one 4x4 SAD layer)", "achieved": achieved, "peak": ipeak,
-                "unit": "Gop/s", "frac": achieved / ipeak, "traffic": None,
+                "unit": "Gop/s", "frac": achieved / ipeak, "traffic": ncu_traffic(),
                 "peak_source": ipeak_how,
                 "alg_ops_per_launch": ALG_INT_OPS, "ms_per_launch": sb_ms,
                 "share_of_step": prof["me_sb2_kernel"][0] / ms_total,
