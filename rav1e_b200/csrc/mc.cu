@@ -3,15 +3,17 @@
 // prep_8tap_ref :310-387, mc_avg_ref :389-408, get_filter :201-210).
 //
 // Work decomposition.  A job (one block, 2..128 px on a side) is cut into
-// ITEMS of 4 columns x up to 32 rows; one thread owns one item and walks down
+// ITEMS of 4 columns x up to 16 rows; one thread owns one item and walks down
 // its rows with the 8-row window of horizontally filtered values held in
-// registers, so the separable filter needs no shared memory: per row a thread
-// loads the 11 source pixels of its strip as aligned 32-bit words (neighbouring
-// strips overlap in L1), does 4 x 8 horizontal MACs, then 4 x 8 vertical MACs.
+// registers: per row 4 x 8 horizontal MACs, then 4 x 8 vertical MACs (DP4A /
+// DP2A on packed pixels and packed i16 pairs).  Source rows of the vector
+// walker arrive through a per-thread ring in shared memory filled by cp.async,
+// 8 rows ahead; strips it cannot take (fewer than 4 columns, unaligned output,
+// footprint on the edge of the allocation) go through a scalar per-pixel path.
 // Item counts per job go through a prefix sum (cub) so that job lists mixing
-// every block size still fill all lanes; the main kernel is persistent (grid =
-// a multiple of the SM count) and reads the item total from device memory, so
-// the `_dev` entry points never synchronise with the host.
+// every block size still fill all lanes; the main kernel's resident CTAs take
+// chunks of items from a device counter and read the item total from device
+// memory, so the `_dev` entry points never synchronise with the host.
 //
 // Arithmetic follows the `_ref` functions literally: i32 accumulation, the
 // horizontal intermediate truncated to i16 (`as i16`, src/mc.rs:281,366),

@@ -26,11 +26,15 @@
 //    [job][849] layout of r1c_me_sb_batch or straight to a caller-supplied map
 //    (whole-frame layout of r1c_frame_me).
 //  * u16 planes (template PB = 2, bit depth <= 10): two pixels per window word, two pixel
-//    phases; |a - b| of a packed pair = VIMNMX.U16x2 max - min; a cell accumulates 8 pixels
-//    per 16-bit half and is folded once per candidate.  An 8x8 SAD needs 16 bits there, so
-//    the key keeps 6 bits of seq (12 candidate rows per chunk, 11 chunks for +-64) and 18
-//    bits of sad + rl >> 8; SAD * 256 + rl of a 64x64 block still fits 32 bits (not at 12 bits).
-// INT-bound: per (pixel, candidate) 1/4 VABSDIFF4 (u8) or 7/4 full-rate instructions (u16);
+//    phases; sum |a - b| = 2 sum max(a, b) - sum a - sum b: the inner loop accumulates packed
+//    maxima only (VIMNMX.U16x2, 8 values per 16-bit half), sum b of a cell is a box filter of
+//    the window (negated s16 table in shared memory), sum a of a block leaves the cost in
+//    sb2_finalize_kernel (see max2 / fold_cell).  An 8x8 SAD + sum a needs 17 bits, so the key
+//    keeps 6 bits of seq (12 candidate rows per chunk, 11 chunks for +-64) and 18 bits of
+//    sad + rl >> 8; (SAD + sum a) * 256 + rl of a 64x64 block still fits 32 bits (not at 12 bits).
+//  * MV rates come from per-column / per-row tables in shared memory; in border superblocks
+//    only the candidates that are illegal for some block pay for the get_mv_range masks.
+// INT-bound: per (pixel, candidate) 1/4 VABSDIFF4 (u8) or 3/4 full-rate instructions (u16);
 // planes are read once per work item from L2.  Falls back to me_sb.cu for 12-bit planes,
 // step 2, huge lambda or windows too small / too large for this layout.
 #include <stdlib.h>
