@@ -543,6 +543,40 @@ int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
  * memory; ordered on the context stream) */
 int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);
 
+/* ------------------------------------------------------------------------
+ * Block importances of the lookahead:
+ * ContextInner::compute_block_importances, src/api/internal.rs:823-1075.
+ *   r1c_importance_propagate  one (frame, unique reference) pair of the loop :897-1047.
+ *       frame / ref            luma planes of the input frame and of the reference frame
+ *       mvs                    fi.lookahead_mvs[mv_index]: MI-granular field, mv_cols x mv_rows,
+ *                              row-major (FrameMotionVectors, src/me.rs:32-62); block (x, y) reads
+ *                              mvs[(2 y) * mv_cols + 2 x]
+ *       intra_costs            fi.lookahead_intra_costs (r1c_lookahead_intra_costs), w*h u32
+ *       importances            fi.block_importances of THIS frame (what the future propagated)
+ *       n_refs                 unique_indices.len()
+ *       ref_importances        block_importances of the reference frame, in/out; the shares are
+ *                              added in the reference's order (raster over source blocks; TL, TR,
+ *                              BL, BR), so the f32 sums are the reference's bit for bit
+ *     An MV that moves its 8x8 block out of the allocated reference plane is R1C_ERR_BOUNDS
+ *     (the reference's get_satd asserts); the _dev form clamps such blocks for memory safety.
+ *   r1c_importance_finalize   :1054-1071, importance = log2(1 + importance / intra_cost) or 0;
+ *     log2 is computed in f64 and rounded once; the reference takes log2f from the libm it is
+ *     linked with (not correctly rounded, platform-dependent): the two agree to 1 ulp of f32
+ *     (tested against glibc; 90+ % of the cells are equal).
+ * ---------------------------------------------------------------------- */
+int r1c_importance_propagate(r1c_ctx *ctx, const r1c_plane *frame, const r1c_plane *ref,
+                             const r1c_mv *mvs, int mv_cols, int mv_rows,
+                             const uint32_t *intra_costs, const float *importances, int n_refs,
+                             int w_in_imp_b, int h_in_imp_b, int bit_depth, float *ref_importances);
+int r1c_importance_propagate_dev(r1c_ctx *ctx, const r1c_plane *frame, const r1c_plane *ref,
+                                 const r1c_mv *d_mvs, int mv_cols, int mv_rows,
+                                 const uint32_t *d_intra_costs, const float *d_importances,
+                                 int n_refs, int w_in_imp_b, int h_in_imp_b, int bit_depth,
+                                 float *d_ref_importances);
+int r1c_importance_finalize(r1c_ctx *ctx, const uint32_t *intra_costs, float *importances, int64_t n);
+int r1c_importance_finalize_dev(r1c_ctx *ctx, const uint32_t *d_intra_costs, float *d_importances,
+                                int64_t n);
+
 #ifdef __cplusplus
 }
 #endif

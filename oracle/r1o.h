@@ -172,6 +172,12 @@ void r1o_dequantize(uint32_t dc_quant, uint32_t ac_quant, int log_tx_scale, cons
 void r1o_quantize_batch(const r1o_quant_ctx *qc, int tx_size, const uint16_t *scan, const int32_t *coeffs,
                         int32_t *qcoeffs, int32_t *rcoeffs, int64_t n);
 
+/* ---- block importances (r1o_imp.c), src/api/internal.rs:823-1075 ---------- */
+void r1o_importance_propagate(const void *frame0, const r1o_plane_cfg *fcfg, const void *ref0, const r1o_plane_cfg *rcfg,
+                              const int16_t *mvs, int mv_cols, const uint32_t *intra_costs, const float *importances,
+                              int n_refs, int w, int h, int bit_depth, int px_bytes, float *ref_importances);
+void r1o_importance_finalize(const uint32_t *intra_costs, float *importances, int64_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,6 +122,8 @@ def lib():
         L.r1o_quant_ctx_update.argtypes = [P(QuantCtx), i, i, u32, u32]
         L.r1o_quantize_batch.argtypes = [P(QuantCtx), i, vp, vp, vp, vp, i64]
         L.r1o_dequantize.argtypes = [u32, u32, i, vp, vp, i]
+        L.r1o_importance_propagate.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), vp, i, vp, vp, i, i, i, i, i, vp]
+        L.r1o_importance_finalize.argtypes = [vp, vp, i64]
         _lib = L
     return _lib
 
@@ -340,6 +342,27 @@ def divu_gen(d):
     out = (C.c_uint32 * 3)()
     lib().r1o_divu_gen(d, C.byref(out))
     return out
+
+
+def importance_propagate(frame, ref, mvs, intra_costs, importances, n_refs, bit_depth, ref_importances):
+    """one (frame, reference) pair of compute_block_importances, src/api/internal.rs:897-1047; mvs int16 (rows, cols, 2)
+    = {row, col}; ref_importances float32 (h, w) is updated in place"""
+    mv = np.ascontiguousarray(mvs, dtype=np.int16)
+    ic = np.ascontiguousarray(intra_costs, dtype=np.uint32)
+    im = np.ascontiguousarray(importances, dtype=np.float32)
+    assert ref_importances.dtype == np.float32 and ref_importances.flags.c_contiguous
+    h, w = ic.shape
+    lib().r1o_importance_propagate(frame.origin_ptr(), C.byref(frame.cfg), ref.origin_ptr(), C.byref(ref.cfg), _p(mv),
+                                   mv.shape[1], _p(ic), _p(im), n_refs, w, h, bit_depth, frame.px_bytes, _p(ref_importances))
+    return ref_importances
+
+
+def importance_finalize(intra_costs, importances):
+    """src/api/internal.rs:1054-1071, in place"""
+    ic = np.ascontiguousarray(intra_costs, dtype=np.uint32)
+    assert importances.dtype == np.float32 and importances.flags.c_contiguous
+    lib().r1o_importance_finalize(_p(ic), _p(importances), ic.size)
+    return importances
 
 
 def lookahead_intra_costs(plane: OPlane, w_in_imp_b, h_in_imp_b, bit_depth):

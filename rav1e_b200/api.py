@@ -295,6 +295,28 @@ def tx_distortion(ctx, coeffs, rcoeffs, tx_size):
     return out
 
 
+def importance_propagate(ctx, frame, ref, mvs, intra_costs, importances, n_refs, bit_depth, ref_importances):
+    """one (frame, reference) pair of compute_block_importances (src/api/internal.rs:897-1047).
+    mvs: MV array (mv_rows, mv_cols) in MI units; intra_costs uint32 (h, w); importances float32 (h, w);
+    ref_importances float32 (h, w), updated in place and returned"""
+    mvs = _arr(mvs, MV)
+    intra_costs, importances = _arr(intra_costs, np.uint32), _arr(importances, np.float32)
+    assert ref_importances.dtype == np.float32 and ref_importances.flags.c_contiguous
+    h, w = intra_costs.shape
+    assert importances.shape == (h, w) and ref_importances.shape == (h, w) and mvs.ndim == 2
+    ctx.check(ctx.lib.r1c_importance_propagate(ctx.h, frame.h, ref.h, _p(mvs), mvs.shape[1], mvs.shape[0], _p(intra_costs),
+                                               _p(importances), n_refs, w, h, bit_depth, _p(ref_importances)))
+    return ref_importances
+
+
+def importance_finalize(ctx, intra_costs, importances):
+    """the last loop of compute_block_importances (src/api/internal.rs:1054-1071), in place"""
+    intra_costs = _arr(intra_costs, np.uint32)
+    assert importances.dtype == np.float32 and importances.flags.c_contiguous and importances.size == intra_costs.size
+    ctx.check(ctx.lib.r1c_importance_finalize(ctx.h, _p(intra_costs), _p(importances), intra_costs.size))
+    return importances
+
+
 class QuantizationContext:
     """QuantizationContext (src/quantize.rs:111-121, 212-316).  `update` takes the quantizer VALUES
     dc_q(qindex, dc_delta_q, bit_depth) / ac_q(..) -- the qindex tables (:41-61) stay with the caller."""

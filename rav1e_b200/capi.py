@@ -164,6 +164,10 @@ SIGNATURES = {
     "r1c_rdo_dist_batch_dev": (_i, [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp, _vp, _vp]),
     "r1c_tx_dist_batch": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
     "r1c_tx_dist_batch_dev": (_i, [_vp, _vp, _vp, _i, _i64, _vp]),
+    "r1c_importance_propagate": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "r1c_importance_propagate_dev": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "r1c_importance_finalize": (_i, [_vp, _vp, _vp, _i64]),
+    "r1c_importance_finalize_dev": (_i, [_vp, _vp, _vp, _i64]),
     "r1c_log_tx_scale": (_i, [_i]),
     "r1c_quant_ctx_update": (_i, [_P(QuantCtx), _i, _i, _u32, _u32]),
     "r1c_quantize_batch": (_i, [_vp, _P(QuantCtx), _i, _vp, _vp, _vp, _i64]),

@@ -1003,3 +1003,42 @@ def test_quantize_mode_flipping_maps(r, ctx, oracle):
         co = synth_coeffs(rng, 40, w * h, "edge", acq)
         want = oracle.quantize_batch(oq, ts, scan, co)
         assert np.array_equal(qc.quantize(ctx, co, scan), want), ts
+
+
+# ------------------------------------------------ block importances (8f.4) -----
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+def test_block_importances_match_oracle(r, ctx, oracle, pb, bd):
+    """compute_block_importances (src/api/internal.rs:823-1075): three chained propagations into one reference array
+    (the f32 `+=` order matters), MVs of every phase incl. negative ones and blocks moved off the grid, then the
+    final log2 pass"""
+    rng = np.random.default_rng(900 + bd)
+    W, H = 328, 200
+    w, h = W // 8, H // 8
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+    ref_imp_o = (rng.random((h, w)) * 50).astype(np.float32)
+    ref_imp_g = ref_imp_o.copy()
+    for it, n_refs in enumerate((1, 2, 3)):
+        o_frm, d_frm = twin_plane(r, oracle, ctx, W, H, pb, bd, rng, smooth=True)
+        mvs = rng.integers(-60 * 8, 60 * 8 + 1, size=(2 * h, 2 * w, 2)).astype(np.int16)
+        mvs[::2, ::2][rng.random((h, w)) < 0.3] = 0
+        intra = rng.integers(0, 4000, size=(h, w)).astype(np.uint32)  # zeros too: 0 / 0 and x / 0
+        fut = (rng.random((h, w)) * (1000 if it else 0)).astype(np.float32)
+        oracle.importance_propagate(o_frm, o_ref, mvs, intra, fut, n_refs, bd, ref_imp_o)
+        mv_rec = np.zeros((2 * h, 2 * w), dtype=r.MV)
+        mv_rec["row"], mv_rec["col"] = mvs[..., 0], mvs[..., 1]
+        out = r.importance_propagate(ctx, d_frm, d_ref, mv_rec, intra, fut, n_refs, bd, ref_imp_g)
+        assert out is ref_imp_g
+        assert np.array_equal(ref_imp_g.view(np.uint32), ref_imp_o.view(np.uint32)), (it, "propagate")
+    oracle.importance_finalize(intra, ref_imp_o)
+    r.importance_finalize(ctx, intra, ref_imp_g)
+    # log2 is the one transcendental of the path: the reference takes it from the libm it is linked with (not
+    # correctly rounded, differs between platforms), the kernel rounds an f64 log2 once.  Tolerance: 1 ulp of f32.
+    ulp = np.abs(ref_imp_g.view(np.int32).astype(np.int64) - ref_imp_o.view(np.int32).astype(np.int64))
+    assert ulp.max() <= 1, int(ulp.max())
+    assert np.array_equal(ref_imp_g == 0, ref_imp_o == 0)
+    # an MV that leaves the allocated reference plane is refused like the reference's get_satd assert
+    mv_rec[0, 0] = (-(88 + 1) * 8, 0)
+    with pytest.raises(r.Rav1eCudaError):
+        r.importance_propagate(ctx, d_frm, d_ref, mv_rec, intra, fut, 1, bd, ref_imp_g)
+    with pytest.raises(r.Rav1eCudaError):
+        r.importance_propagate(ctx, d_frm, d_ref, mv_rec[:3], intra, fut, 1, bd, ref_imp_g)

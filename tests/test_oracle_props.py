@@ -360,3 +360,37 @@ def test_subset_predictors_and_save_block_motion(oracle):
     # left (16,-8), top zero (dropped but in the median), top-right (-24,40); median = (-8/3, 32/3) -> (-2, 10) -> (0, 8);
     # then the co-located previous MV
     assert p == [(0, 0), (16, -8), (-24, 40), (0, 8), (5, 5)]
+
+
+def test_importance_propagation_properties(oracle):
+    """compute_block_importances (src/api/internal.rs:823-1075): with zero MVs and ref == frame the inter cost is 0,
+    so every block hands intra_cost + future importance to the same cell; a MV of (+4, +4) px splits it 1/4 each
+    over four cells; shares that fall outside the grid are dropped; finalize is log2(1 + imp / intra)"""
+    w, h = 12, 9
+    rng = np.random.default_rng(3)
+    pl = oracle.OPlane(w * 8, h * 8, 0, 0, 88, 88, 1)
+    pl.visible[...] = rng.integers(0, 256, size=(h * 8, w * 8))
+    pl.pad()
+    intra = rng.integers(1, 5000, size=(h, w)).astype(np.uint32)
+    fut = rng.random((h, w)).astype(np.float32) * 100
+    mvs = np.zeros((2 * h, 2 * w, 2), dtype=np.int16)
+    out = oracle.importance_propagate(pl, pl, mvs, intra, fut, 1, 8, np.zeros((h, w), np.float32))
+    assert np.array_equal(out, intra.astype(np.float32) + fut)
+    out2 = oracle.importance_propagate(pl, pl, mvs, intra, fut, 2, 8, out.copy())
+    assert np.array_equal(out2, out + (intra.astype(np.float32) + fut) / np.float32(2))
+    # constant plane: any MV keeps the inter cost at 0; (+32, +32) in 1/8 px = half a block each way
+    flat = oracle.OPlane(w * 8, h * 8, 0, 0, 88, 88, 1)
+    flat.data[...] = 77
+    mvs[...] = 32
+    got = oracle.importance_propagate(flat, flat, mvs, intra, np.zeros((h, w), np.float32), 1, 8, np.zeros((h, w), np.float32))
+    want = np.zeros((h + 1, w + 1), np.float64)
+    a = intra.astype(np.float64) / 4
+    for dy in (0, 1):
+        for dx in (0, 1):
+            want[dy:dy + h, dx:dx + w] += a
+    assert np.allclose(got, want[:h, :w], rtol=1e-6)
+    imp = got.copy()
+    oracle.importance_finalize(intra, imp)
+    assert np.allclose(imp, np.log2(1 + got / intra.astype(np.float32)), rtol=1e-6)
+    z = np.array([[5.0]], np.float32)
+    assert oracle.importance_finalize(np.zeros((1, 1), np.uint32), z)[0, 0] == 0.0
