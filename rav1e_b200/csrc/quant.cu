@@ -6,9 +6,9 @@
 // src/quantize.rs:287-311): the offset of coefficient k depends on the mode left by coefficient
 // k-1.  Here LPB lanes (16 for 4x4 blocks, else 32) take LPB consecutive scan positions at once:
 // a lane computes its coefficient's result under BOTH modes, which also gives the lane's
-// transition map {0,1} -> {0,1} (2 bits); an inclusive shuffle scan composes the maps, the
-// exclusive prefix applied to the mode carried in from the previous chunk selects each lane's
-// result.  Blocks are independent: a warp takes 32 / LPB blocks, a CTA 8 warps.
+// transition map {0,1} -> {0,1} (2 bits); two ballots collect the maps and a lane's incoming mode
+// is the mode left by the closest earlier lane whose map is constant (a shuffle scan composes the
+// maps in the general, mode-flipping case).  Blocks are independent: a warp takes 32 / LPB blocks, a CTA 8 warps.
 // The end-of-block search (rposition over |coeff| >= deadzone) is a max-reduction over the
 // same lanes; a lane keeps its coefficients in registers for the second pass.
 // Bound: HBM, 4 B read + 4 B written per coefficient (+4 with rcoeffs); `scan` stays in L1.
@@ -25,6 +25,7 @@ struct QuantArgs {
   long long n;
   int area, coded, dist_bits;
   int32_t deadzone;
+  int nonneg;  // 0 <= ac_offset0 <= ac_offset1 < ac_offset0 + ac_quant: the magnitude fast path applies
 };
 
 // divu_pair, src/quantize.rs:140-153: ((a * |x| + b) >> 32) >> shift with the sign of x
@@ -32,6 +33,10 @@ __device__ __forceinline__ int32_t divu_pair(int32_t x, uint32_t a, uint32_t b, 
   const uint32_t y = (uint32_t)(x < 0 ? -x : x);
   const int32_t q = (int32_t)((uint32_t)(((unsigned long long)a * y + b) >> 32) >> shift);
   return x < 0 ? -q : q;
+}
+// the magnitude part of divu_pair
+__device__ __forceinline__ uint32_t udivu(uint32_t y, uint32_t a, uint32_t b, uint32_t shift) {
+  return (uint32_t)(((unsigned long long)a * y + b) >> 32) >> shift;
 }
 __device__ __forceinline__ int32_t signum(int32_t v) { return (v > 0) - (v < 0); }
 // dequantize, src/quantize.rs:329-332 (wrapping i32 product, arithmetic shift)
@@ -95,12 +100,30 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
       q0 = q1 = divu_pair(coeff + signum(coeff) * a.qc.dc_offset, a.qc.dc_mul_add[0], a.qc.dc_mul_add[1], a.qc.dc_mul_add[2]);
     } else if (k <= eob) {
       // src/quantize.rs:293-311
-      const int32_t level0 = divu_pair(coeff, ma, mb, ms);
-      const int32_t sg = signum(coeff);
-      const int32_t qa = divu_pair(coeff + sg * a.qc.ac_offset0, ma, mb, ms);
-      const int32_t qb = divu_pair(coeff + sg * a.qc.ac_offset1, ma, mb, ms);
-      q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
-      q1 = level0 > 0 ? qb : qa;
+      if (a.nonneg) {
+        // offsets >= 0 (always, after update()): divide magnitudes, apply the sign once.  A negative coefficient has
+        // level0 <= 0, so it takes ac_offset0 under both modes and can only reset the mode (the tests are signed)
+        // divu_pair is an exact division (Robison's multiply-add form; the reference's test_divu_pair), so
+        // level0 > 0 / > 1 are comparisons with d / 2 d, and the quotient with the larger offset is the one with the
+        // smaller offset plus a carry out of its remainder (0 <= offset1 - offset0 < d): one wide multiply per coefficient
+        const uint32_t d = a.qc.ac_quant;
+        const uint32_t y0 = (uint32_t)(coeff < 0 ? -coeff : coeff);
+        const uint32_t t0 = y0 + (uint32_t)a.qc.ac_offset0;
+        uint32_t ua = udivu(t0, ma, mb, ms);
+        uint32_t ub = ua + (t0 - ua * d + (uint32_t)(a.qc.ac_offset1 - a.qc.ac_offset0) >= d ? 1u : 0u);
+        ua = y0 ? ua : 0u;
+        ub = y0 ? ub : 0u;
+        const bool neg = coeff < 0;
+        q0 = neg ? -(int32_t)ua : (int32_t)(y0 >= 2 * d ? ub : ua);
+        q1 = neg ? -(int32_t)ua : (int32_t)(y0 >= d ? ub : ua);
+      } else {
+        const int32_t level0 = divu_pair(coeff, ma, mb, ms);
+        const int32_t sg = signum(coeff);
+        const int32_t qa = divu_pair(coeff + sg * a.qc.ac_offset0, ma, mb, ms);
+        const int32_t qb = divu_pair(coeff + sg * a.qc.ac_offset1, ma, mb, ms);
+        q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
+        q1 = level0 > 0 ? qb : qa;
+      }
       // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1
       f0 = q0 > 1;
       f1 = q1 != 0;
@@ -235,6 +258,8 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   a.dist_bits = 2 * (3 - (int)qc->log_tx_scale);
   // (ac_quant as usize - ac_offset_eob as usize).align_power_of_two_and_shift(log_tx_scale), src/quantize.rs:265-267
   a.deadzone = (int32_t)(((uint64_t)qc->ac_quant - (uint64_t)qc->ac_offset_eob + (1ull << qc->log_tx_scale) - 1) >> qc->log_tx_scale);
+  a.nonneg = qc->ac_offset0 >= 0 && qc->ac_offset1 >= qc->ac_offset0 && (uint32_t)(qc->ac_offset1 - qc->ac_offset0) < qc->ac_quant &&
+             qc->ac_quant < (1u << 30);
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
   const unsigned g8 = (unsigned)((n + 7) / 8);
   switch (a.coded) {  // 4x4 .. 32x32 coded areas
