@@ -100,6 +100,19 @@ void r1o_mv_params(const r1o_plane_cfg *rec_cfg, int64_t po_x, int64_t po_y,
                    int mv_row, int mv_col, int *row_frac, int *col_frac,
                    int64_t *src_x, int64_t *src_y);
 
+/* ---- inverse transform: src/transform/inverse.rs (r1o_itx.c) ------------- */
+/* type1d: 0 DCT, 1 ADST, 2 FLIPADST, 3 identity; -1 where the reference has no function */
+int r1o_inv_txfm1d(int type1d, int n, const int32_t *in, int32_t *out, int range);
+int r1o_inv_txfm_valid(int tx_size, int tx_type);
+/* coeffs: min(W,32)*min(H,32), row-major, stride min(W,32); residual: W*H COLUMN-major */
+int r1o_inv_txfm2d(const int32_t *coeffs, int32_t *residual, int tx_size, int tx_type, int bd);
+/* dst[r*stride + c] = clamp(dst + residual, 0, 2^bd - 1); stride in pixels */
+int r1o_inv_txfm_add(const int32_t *coeffs, void *dst, ptrdiff_t stride, int px_bytes, int tx_size,
+                     int tx_type, int bd);
+/* n non-overlapping blocks: block i reads coeffs + i*coded, lands at (xy[2i], xy[2i+1]) of dst0 */
+int r1o_inv_txfm_add_batch(const int32_t *coeffs, void *dst0, ptrdiff_t stride, int px_bytes,
+                           const int32_t *xy, int64_t n, int tx_size, int tx_type, int bd);
+
 /* ---- forward transform: src/transform/forward.rs ------------------------ */
 /* 1-D kernels on n i32 values (n = 4..64); type: 0 DCT, 1 ADST, 2 IDTX.
  * returns -1 when the reference has `unimplemented!` for (type,n). */

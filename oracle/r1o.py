@@ -87,6 +87,14 @@ def lib():
         L.r1o_full_search_batch.restype = i
         L.r1o_mc_batch.argtypes = [i, vp, P(PlaneCfg), vp, vp, vp, P(PlaneCfg), vp, i64, i, i]
         L.r1o_avg_batch.argtypes = [vp, P(PlaneCfg), vp, vp, vp, vp, i64, i, i]
+        L.r1o_inv_txfm1d.argtypes = [i, i, vp, vp, i]
+        L.r1o_inv_txfm1d.restype = i
+        L.r1o_inv_txfm_valid.argtypes = [i, i]
+        L.r1o_inv_txfm_valid.restype = i
+        L.r1o_inv_txfm2d.argtypes = [vp, vp, i, i, i]
+        L.r1o_inv_txfm2d.restype = i
+        L.r1o_inv_txfm_add_batch.argtypes = [vp, vp, i64, i, vp, i64, i, i, i]
+        L.r1o_inv_txfm_add_batch.restype = i
         L.r1o_fht_batch.argtypes = [vp, vp, i, i, i, i64]
         L.r1o_fht_batch.restype = i
         L.r1o_frame_me_layout.argtypes = [i, i, u32, P(i64 * 22), P(C.c_int32 * 22), P(C.c_int32 * 22)]
@@ -395,6 +403,48 @@ def fht_batch(residual, tx_size, tx_type, bit_depth):
     if rc != 0:
         raise ValueError("invalid (tx_size, tx_type)")
     return out
+
+
+def inv_txfm1d(type1d, vec, rng):
+    """src/transform/inverse.rs 1-D functions; type1d: 0 DCT, 1 ADST, 2 FLIPADST, 3 identity"""
+    vec = np.ascontiguousarray(vec, dtype=np.int32)
+    out = np.empty_like(vec)
+    if lib().r1o_inv_txfm1d(type1d, vec.size, _p(vec), _p(out), rng) != 0:
+        raise ValueError("unimplemented (type, n)")
+    return out
+
+
+def inv_txfm_valid(tx_size, tx_type):
+    return bool(lib().r1o_inv_txfm_valid(tx_size, tx_type))
+
+
+def coded_area(tx_size):
+    return min(lib().r1o_tx_width(tx_size), 32) * min(lib().r1o_tx_height(tx_size), 32)
+
+
+def inv_txfm2d(coeffs, tx_size, tx_type, bit_depth):
+    """inv_txfm2d, inverse.rs:2061-2107 -> (H, W) residual (the reference's column-major array, transposed)"""
+    w, h = lib().r1o_tx_width(tx_size), lib().r1o_tx_height(tx_size)
+    coeffs = np.ascontiguousarray(coeffs, dtype=np.int32)
+    assert coeffs.size == coded_area(tx_size)
+    out = np.empty(w * h, dtype=np.int32)
+    if lib().r1o_inv_txfm2d(_p(coeffs), _p(out), tx_size, tx_type, bit_depth) != 0:
+        raise ValueError("invalid (tx_size, tx_type, bit_depth)")
+    return out.reshape(w, h).T.copy()
+
+
+def inv_txfm_add_batch(coeffs, plane, xy, tx_size, tx_type, bit_depth):
+    """inv_txfm2d_add, inverse.rs:1939-2028, over n non-overlapping blocks; `plane` (2-D u8 / u16 array) is
+    updated in place, block i at column xy[i,0], row xy[i,1]"""
+    coeffs = np.ascontiguousarray(coeffs, dtype=np.int32)
+    xy = np.ascontiguousarray(xy, dtype=np.int32).reshape(-1, 2)
+    assert plane.flags.c_contiguous and plane.dtype in (np.uint8, np.uint16)
+    assert coeffs.size == xy.shape[0] * coded_area(tx_size)
+    rc = lib().r1o_inv_txfm_add_batch(_p(coeffs), _p(plane), plane.shape[1], plane.dtype.itemsize, _p(xy),
+                                      xy.shape[0], tx_size, tx_type, bit_depth)
+    if rc != 0:
+        raise ValueError("invalid (tx_size, tx_type, bit_depth)")
+    return plane
 
 
 def txfm1d(type1d, vec):

@@ -57,3 +57,54 @@ def test_subpel_filter_bank():
     tab = re.sub(r"/\*.*?\*/", "", tab, flags=re.S)
     mine = [int(x) for x in re.findall(r"-?\d+", tab)]
     assert mine == ref
+
+
+# ---- inverse transforms: the reference's own 1-D functions (transliterated at test time) -------------
+def _itx():
+    import sys
+    sys.path.insert(0, HERE)
+    import ref_inv_tx
+    sys.path.insert(0, os.path.join(HERE, ".."))
+    from oracle import r1o
+    return ref_inv_tx, r1o
+
+
+@pytest.mark.parametrize("kind,t1d,sizes", [("dct", 0, (4, 8, 16, 32, 64)), ("adst", 1, (4, 8, 16)),
+                                            ("flipadst", 2, (4, 8, 16)), ("identity", 3, (4, 8, 16, 32))])
+def test_inverse_1d_matches_reference_text(kind, t1d, sizes):
+    import numpy as np
+    R, r1o = _itx()
+    rng = np.random.default_rng(7 + t1d)
+    for n in sizes:
+        f = R.fn1d(kind, n)
+        for trial in range(60):
+            rbits = (16, 18, 20)[trial % 3]
+            mag = (1 << (rbits - 1)) - 1 if trial % 5 == 0 else 1 << (4 + trial % 12)
+            if (n == 4 and t1d in (1, 2)) or (t1d == 3 and n in (4, 16)):
+                mag = min(mag, 1 << 16)  # plain i32 products, no clamps: beyond this they overflow
+            x = rng.integers(-mag, mag + 1, n)
+            if trial % 7 == 3:
+                x[rng.integers(0, n):] = 0  # the usual shape: zeros after the eob
+            ref = [0] * 64
+            f([int(v) for v in x] + [0] * (64 - n), ref, rbits)
+            got = r1o.inv_txfm1d(t1d, x, rbits)
+            assert got.tolist() == ref[:n], (kind, n, trial)
+
+
+def test_inverse_2d_matches_reference_text():
+    import numpy as np
+    R, r1o = _itx()
+    rng = np.random.default_rng(11)
+    for tx_size in range(19):
+        w, h = r1o.lib().r1o_tx_width(tx_size), r1o.lib().r1o_tx_height(tx_size)
+        for tx_type in range(16):
+            if not r1o.inv_txfm_valid(tx_size, tx_type):
+                continue
+            if w * h > 1024 and tx_type not in (0, 9):
+                continue  # keep the pure-Python side in seconds
+            bd = (8, 10, 12)[(tx_size + tx_type) % 3]
+            c = rng.integers(-(1 << (bd + 3)), 1 << (bd + 3), r1o.coded_area(tx_size))
+            c[rng.integers(1, c.size + 1):] = 0
+            ref = np.array(R.inv_txfm2d([int(v) for v in c], w, h, tx_type, bd)).reshape(w, h).T
+            got = r1o.inv_txfm2d(c, tx_size, tx_type, bd)
+            assert np.array_equal(got, ref), (tx_size, tx_type, bd)
