@@ -112,7 +112,8 @@ int64_t r1c_launch_count(const r1c_ctx *ctx);
 #define R1C_PROF_TX 4         /* forward transform kernels                    */
 #define R1C_PROF_DIST 5       /* SAD / SATD / RDO distortion batch kernels    */
 #define R1C_PROF_QUANT 6      /* quantize / dequantize kernels                */
-#define R1C_PROF_SLOTS 7
+#define R1C_PROF_ITX 7        /* inverse transform + add kernels              */
+#define R1C_PROF_SLOTS 8
 int r1c_profile(r1c_ctx *ctx, int enable);
 int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches);
 
@@ -295,6 +296,29 @@ int r1c_diff_fwd_txfm_batch(r1c_ctx *ctx, const r1c_plane *input, const r1c_plan
 int r1c_diff_fwd_txfm_batch_dev(r1c_ctx *ctx, const r1c_plane *input, const r1c_plane *pred,
                                 const r1c_tx_job *d_jobs, int64_t n, int tx_size, int tx_type,
                                 int bit_depth, int32_t *d_coeffs);
+
+/* ------------------------------------------------------------------------
+ * Inverse transforms: inverse_transform_add, src/transform/mod.rs:568-580 ->
+ * InvTxfm2D::inv_txfm2d_add, src/transform/inverse.rs:1939-2028 (inv_txfm2d :2061-2107, the 1-D
+ * functions :35-1544).
+ * rcoeffs: block i reads rcoeffs + i*coded, coded = min(W,32)*min(H,32), row-major with stride
+ * min(W,32) -- what dequantize leaves (64-point transforms signal 32 coefficients per line).
+ * Each block is transformed and ADDED to the W x H pixels at (jobs[i].x, jobs[i].y) of `dst`
+ * (visible-area coordinates), clamped to [0, 2^bit_depth - 1].  Blocks of one call must not
+ * overlap.  (size, type) pairs: every 1-D function INV_TXFM_FNS holds (:1610-1634; DCT 4..64, ADST /
+ * FLIPADST 4..16, identity 4..32) -- the same 193 pairs as the forward side; FLIPADST is
+ * av1_iflipadst* (the reversed ADST output, :57-60), which the fork's portable Rust path leaves
+ * `unimplemented!` (:1596-1606) and only reaches through its generated kernels.
+ * ---------------------------------------------------------------------- */
+typedef struct {
+  int32_t x, y; /* block origin in the destination plane */
+} r1c_itx_job;
+int r1c_inv_txfm_valid(int tx_size, int tx_type);
+int r1c_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n,
+                           int tx_size, int tx_type, int bit_depth, const int32_t *rcoeffs);
+/* d_jobs and d_rcoeffs are device arrays; the caller guarantees the jobs stay inside the plane */
+int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n,
+                               int tx_size, int tx_type, int bit_depth, const int32_t *d_rcoeffs);
 
 /* ------------------------------------------------------------------------
  * Quantize / dequantize, src/quantize.rs.

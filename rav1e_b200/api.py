@@ -30,6 +30,7 @@ MC_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("src_x", "<i4"), ("src_y
 AVG_JOB = np.dtype([("dst_x", "<i4"), ("dst_y", "<i4"), ("w", "<i2"), ("h", "<i2"),
                     ("tmp_off", "<i4")])
 TX_JOB = np.dtype([("in_x", "<i4"), ("in_y", "<i4"), ("pred_x", "<i4"), ("pred_y", "<i4")])
+ITX_JOB = np.dtype([("x", "<i4"), ("y", "<i4")])
 BLOCK_JOB = np.dtype([("bo_x", "<i4"), ("bo_y", "<i4"), ("bsize", "<i4")])
 RDO_JOB = np.dtype([("src_x", "<i4"), ("src_y", "<i4"), ("rec_x", "<i4"), ("rec_y", "<i4"),
                     ("w", "<i4"), ("h", "<i4")])
@@ -45,7 +46,7 @@ SUBPEL_JOB = np.dtype([("po_x", "<i4"), ("po_y", "<i4"), ("bsize", "<i4"), ("lam
                        ("mvy_min", "<i4"), ("mvy_max", "<i4"), ("use_satd", "<i4"),
                        ("allow_high_precision_mv", "<i4")])
 STRUCT_PAIRS = [(DIST_JOB, capi.DistJob), (MC_JOB, capi.McJob), (AVG_JOB, capi.AvgJob),
-                (TX_JOB, capi.TxJob), (RDO_JOB, capi.RdoJob), (BLOCK_JOB, capi.BlockJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
+                (TX_JOB, capi.TxJob), (ITX_JOB, capi.ItxJob), (RDO_JOB, capi.RdoJob), (BLOCK_JOB, capi.BlockJob), (ME_RESULT, capi.MeResult), (FS_JOB, capi.FsJob),
                 (SB_JOB, capi.SbJob), (SUBPEL_JOB, capi.SubpelJob), (MV, capi.Mv)]
 
 BLOCK = {n: i for i, n in enumerate(capi.BLOCK_SIZES)}
@@ -380,6 +381,20 @@ def diff_forward_transform(ctx, plane_in, plane_pred, jobs, tx_size, tx_type, bi
     ctx.check(ctx.lib.r1c_diff_fwd_txfm_batch(ctx.h, plane_in.h, plane_pred.h, _p(jobs),
                                               jobs.size, tx_size, tx_type, bit_depth, _p(out)))
     return out
+
+
+def inverse_transform_add(ctx, rcoeffs, plane_dst, jobs, tx_size, tx_type, bit_depth):
+    """inverse_transform_add (src/transform/mod.rs:568-580) over a batch: block i of `rcoeffs`
+    ((N, coded) int32, coded = min(W,32)*min(H,32)) is inverse-transformed and added, clamped, to the
+    W x H pixels at jobs[i] = (x, y) of the device plane `plane_dst`.  Blocks must not overlap."""
+    jobs = _arr(jobs, ITX_JOB)
+    rcoeffs = _arr(rcoeffs, np.int32)
+    w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)
+    if w < 0:
+        raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad tx_size")
+    assert rcoeffs.size == jobs.size * min(w, 32) * min(h, 32)
+    ctx.check(ctx.lib.r1c_inv_txfm_add_batch(ctx.h, plane_dst.h, _p(jobs), jobs.size, tx_size, tx_type,
+                                             bit_depth, _p(rcoeffs)))
 
 
 # ----------------------------------------------------------------- motion search --

@@ -63,6 +63,10 @@ class TxJob(C.Structure):
                 ("pred_y", C.c_int32)]
 
 
+class ItxJob(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32)]
+
+
 class BlockJob(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("bo_x", "bo_y", "bsize")]
 
@@ -176,6 +180,9 @@ SIGNATURES = {
     "r1c_dequantize_batch_dev": (_i, [_vp, _i, _u32, _u32, _vp, _vp, _i64]),
     "r1c_diff_fwd_txfm_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_diff_fwd_txfm_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
+    "r1c_inv_txfm_valid": (_i, [_i, _i]),
+    "r1c_inv_txfm_add_batch": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
+    "r1c_inv_txfm_add_batch_dev": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_mv_range": (None, [_i64, _i64, _i64, _i64, _i, _i, _P(_i64 * 4)]),
     "r1c_mv_rate": (_u32, [Mv, Mv, _i]),
     "r1c_full_search_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
