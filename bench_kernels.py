@@ -310,6 +310,41 @@ def run(ctx, r, torch, ext, flush, reps=3):
             "kernel_us_by_tx_size": qper[key],
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_coeff": bpc, "peak_source": hbm_how}}
+    # ------------------------------ inverse transform + add onto the 4K 10-bit luma plane (dequantized-like coefficients)
+    isum = 0.0
+    iper = {}
+    ibytes = 0
+    icoeffs = 0
+    rin = (qin // 147) * 147  # what dequantize leaves: multiples of the step, mostly zero
+    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        coded = min(w, 32) * min(h, 32)
+        xs, ys = np.meshgrid(np.arange(0, W - w + 1, w), np.arange(0, H - h + 1, h))
+        n = min(xs.size, n_samples // coded)
+        ij = np.zeros(n, dtype=r.ITX_JOB)
+        ij["x"], ij["y"] = xs.ravel()[:n], ys.ravel()[:n]
+        d_ij = torch.from_numpy(ij.view(np.int32).reshape(-1)).cuda()
+
+        def f_i():
+            ctx.check(lib.r1c_inv_txfm_add_batch_dev(ctx.h, dst.h, d_ij.data_ptr(), n, ts, 0, BD, rin.data_ptr()))
+        f_i()
+        ctx.sync()
+        _kernel_ms(ctx, 7)
+        _timed(torch, ext, flush, f_i, reps)
+        k_ms = _kernel_ms(ctx, 7)[0] / reps
+        isum += k_ms
+        b = n * (coded * 4 + w * h * 4)  # coded coefficients + u16 destination read and written
+        ibytes += b
+        icoeffs += n * w * h
+        iper["%dx%d" % (w, h)] = round(b / (k_ms / 1e3) / 1e9 / hbm, 3)
+    gbs = ibytes / (isum / 1e3) / 1e9
+    out["itx_4k10_inv_dct_dct_add"] = {
+        "workload": "4K 10-bit luma tiled by each of the 19 TxSize, DCT_DCT inverse transform added onto the plane",
+        "value": icoeffs / 1e6 / (isum / 1e3), "unit": "Mpix/s", "ms": isum, "pixels": icoeffs,
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                     "alg_bytes": "4 per coded coefficient + 2 x 2 per pixel", "peak_source": hbm_how,
+                     "frac_by_tx_size": iper}}
+    del rin
     ctx.check(lib.r1c_profile(ctx.h, 0))
     del res, coef, org, src, dst, d_out, qout, rout, dout, qin
     # -------------------------- whole-frame motion estimation on a 4K 10-bit frame pair (u16 planes)
