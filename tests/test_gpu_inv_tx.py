@@ -16,6 +16,21 @@ BD = [(1, 8), (2, 10), (2, 12)]
 
 
 @pytest.fixture(scope="module")
+def r():
+    import rav1e_b200 as mod
+    return mod
+
+
+@pytest.fixture(scope="module")
+def ctx(r):
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    c = r.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
 def golden():
     return dict(np.load(os.path.join(HERE, "golden", "inv_tx_r01.npz")))
 
