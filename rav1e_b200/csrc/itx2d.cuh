@@ -1,7 +1,7 @@
 // itx2d.cuh -- 2-D inverse transform + add (NativeInvTxfm2D::inv_txfm2d / inv_txfm2d_add, reference
 // src/transform/inverse.rs:1939-2107) for one (W, H, column type, row type).
 //
-// A CTA takes `BPC` consecutive blocks of the call:
+// A CTA of 128 threads takes `BPC` = 128 / W consecutive blocks of the call:
 //   row pass    : one thread per coded row (the first min(H,32) rows; the first min(W,32) coefficients of
 //                 each, the rest are zero: 64-point transforms signal 32), 16-byte loads straight from the
 //                 coefficient array (a thread owns its row's contiguous bytes), the rectangular 1/sqrt2
@@ -35,8 +35,12 @@ struct ItxCfg {
   static constexpr int WI = W < 32 ? W : 32, HI = H < 32 ? H : 32;
   static constexpr int CODED = WI * HI;
   static constexpr int MAXD = W > H ? W : H;
-  static constexpr int BPC = (MAXD >= 32 ? 128 : 256) / MAXD;  // blocks per CTA
-  static constexpr int THREADS = BPC * MAXD;
+  // the column pass is the heavy one (H-point transform + the pixel read-modify-write): the CTA takes as many
+  // blocks as give every thread exactly one column; the coded rows are then looped over (tall blocks) or leave
+  // threads idle (wide blocks)
+  static constexpr int THREADS = 128;
+  static constexpr int BPC = THREADS / W;  // blocks per CTA
+  static constexpr bool ROWS_ONCE = BPC * HI <= THREADS;
   static constexpr int STRIDE = W + 1;
   static constexpr size_t SMEM = (size_t)BPC * H * STRIDE * 4;
 };
@@ -53,8 +57,8 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     const int nb = (int)min((long long)C::BPC, a.n - blk0);
 
     // ---- rows (:2073-2092) -----------------------------------------------------------
-    if (tid < nb * C::HI) {
-      const int b = tid / C::HI, r = tid % C::HI;
+    auto row_item = [&](int it) {
+      const int b = it / C::HI, r = it % C::HI;
       const int32_t *src = a.coeffs + (blk0 + b) * C::CODED + r * C::WI;
       int v[W], o[W];
       if (a.in16) {
@@ -84,6 +88,11 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
 #pragma unroll
         for (int c = 0; c < W; c++) dst[c] = cl((o[c] + a.rnd) >> a.sh, a.rg_col);
       }
+    };
+    if constexpr (C::ROWS_ONCE) {
+      if (tid < nb * C::HI) row_item(tid);
+    } else {
+      for (int it = tid; it < nb * C::HI; it += C::THREADS) row_item(it);
     }
     __syncthreads();
 
