@@ -13,6 +13,8 @@
 // Algorithmic traffic per coefficient: 4 B of coefficients (coded ones) + px_bytes read + px_bytes written.
 #pragma once
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "itx1d.cuh"
 
@@ -100,22 +102,33 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     if (tid < nb * W) {
       const int b = tid / W, c = tid % W;
       const int *col = s_mid + b * H * C::STRIDE + c;
+      using Px = typename std::conditional<PB == 1, uint8_t, uint16_t>::type;
+      const r1c_itx_job j = a.jobs[blk0 + b];
+      Px *p = (Px *)a.dst.p0 + ((long long)j.y * a.dst.stride + j.x + c);
+      // the destination pixels are read in batches of up to 32 independent loads (a load placed after a store
+      // through another pointer could not be moved above it by the compiler: one DRAM latency per row otherwise);
+      // blocks up to 32 rows have them in flight while the transform runs
+      constexpr int CH = H < 32 ? H : 32;
+      int px[CH];
+      if (H <= 32) {
+#pragma unroll
+        for (int r = 0; r < H; r++) px[r] = p[(long long)r * a.dst.stride];
+      }
       int v[H], o[H];
 #pragma unroll
       for (int r = 0; r < H; r++) v[r] = r < C::HI ? col[r * C::STRIDE] : 0;
       inv1d<CT, H>(v, o, a.rg_col);
-      const r1c_itx_job j = a.jobs[blk0 + b];
-      const long long base = (long long)j.y * a.dst.stride + j.x + c;
 #pragma unroll
-      for (int r = 0; r < H; r++) {
-        const int rr = a.col_flip ? H - 1 - r : r;
-        const int t = (o[r] + 8) >> 4;
-        if (PB == 1) {
-          uint8_t *p = (uint8_t *)a.dst.p0 + base + (long long)rr * a.dst.stride;
-          *p = (uint8_t)min(max((int)*p + t, 0), a.maxv);
-        } else {
-          uint16_t *p = (uint16_t *)a.dst.p0 + base + (long long)rr * a.dst.stride;
-          *p = (uint16_t)min(max((int)*p + t, 0), a.maxv);
+      for (int r0 = 0; r0 < H; r0 += CH) {
+        if (H > 32) {
+#pragma unroll
+          for (int r = 0; r < CH; r++) px[r] = p[(long long)(r0 + r) * a.dst.stride];
+        }
+#pragma unroll
+        for (int r = 0; r < CH; r++) {
+          // av1_iflipadst*: output row rr of the block comes from o[H - 1 - rr]
+          const int t = ((a.col_flip ? o[H - 1 - (r0 + r)] : o[r0 + r]) + 8) >> 4;
+          p[(long long)(r0 + r) * a.dst.stride] = (Px)min(max(px[r] + t, 0), a.maxv);
         }
       }
     }
