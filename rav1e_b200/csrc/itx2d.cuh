@@ -58,6 +58,23 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     const long long blk0 = (long long)slab * C::BPC;
     const int nb = (int)min((long long)C::BPC, a.n - blk0);
 
+    using Px = typename std::conditional<PB == 1, uint8_t, uint16_t>::type;
+    // the destination pixels are read in batches of up to 32 independent loads (a load placed after a store
+    // through another pointer could not be moved above it by the compiler: one DRAM latency per row otherwise);
+    // blocks up to 32 rows issue them here, so that they are in flight during both transforms
+    constexpr int CH = H < 32 ? H : 32;
+    const bool col_live = tid < nb * W;
+    Px *p = nullptr;
+    int px[CH];
+    if (col_live) {
+      const r1c_itx_job j = a.jobs[blk0 + tid / W];
+      p = (Px *)a.dst.p0 + ((long long)j.y * a.dst.stride + j.x + tid % W);
+      if (H <= 32) {
+#pragma unroll
+        for (int r = 0; r < H; r++) px[r] = p[(long long)r * a.dst.stride];
+      }
+    }
+
     // ---- rows (:2073-2092) -----------------------------------------------------------
     auto row_item = [&](int it) {
       const int b = it / C::HI, r = it % C::HI;
@@ -99,21 +116,9 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     __syncthreads();
 
     // ---- columns (:2095-2106) and the add (:2017-2028) ------------------------------------
-    if (tid < nb * W) {
+    if (col_live) {
       const int b = tid / W, c = tid % W;
       const int *col = s_mid + b * H * C::STRIDE + c;
-      using Px = typename std::conditional<PB == 1, uint8_t, uint16_t>::type;
-      const r1c_itx_job j = a.jobs[blk0 + b];
-      Px *p = (Px *)a.dst.p0 + ((long long)j.y * a.dst.stride + j.x + c);
-      // the destination pixels are read in batches of up to 32 independent loads (a load placed after a store
-      // through another pointer could not be moved above it by the compiler: one DRAM latency per row otherwise);
-      // blocks up to 32 rows have them in flight while the transform runs
-      constexpr int CH = H < 32 ? H : 32;
-      int px[CH];
-      if (H <= 32) {
-#pragma unroll
-        for (int r = 0; r < H; r++) px[r] = p[(long long)r * a.dst.stride];
-      }
       int v[H], o[H];
 #pragma unroll
       for (int r = 0; r < H; r++) v[r] = r < C::HI ? col[r * C::STRIDE] : 0;
