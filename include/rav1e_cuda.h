@@ -319,6 +319,15 @@ int r1c_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs
 /* d_jobs and d_rcoeffs are device arrays; the caller guarantees the jobs stay inside the plane */
 int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n,
                                int tx_size, int tx_type, int bit_depth, const int32_t *d_rcoeffs);
+/* dequantize (src/quantize.rs:318-334) fused into the load of the row pass: the array holds
+ * QUANTIZED coefficients, same layout; the pair of calls at src/encoder.rs:1192-1209 in one pass,
+ * without the rcoeffs array in between */
+int r1c_dequant_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n,
+                                   int tx_size, int tx_type, int bit_depth, const int32_t *qcoeffs,
+                                   uint32_t dc_quant, uint32_t ac_quant);
+int r1c_dequant_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs,
+                                       int64_t n, int tx_size, int tx_type, int bit_depth,
+                                       const int32_t *d_qcoeffs, uint32_t dc_quant, uint32_t ac_quant);
 
 /* ------------------------------------------------------------------------
  * Quantize / dequantize, src/quantize.rs.

@@ -383,16 +383,21 @@ def diff_forward_transform(ctx, plane_in, plane_pred, jobs, tx_size, tx_type, bi
     return out
 
 
-def inverse_transform_add(ctx, rcoeffs, plane_dst, jobs, tx_size, tx_type, bit_depth):
+def inverse_transform_add(ctx, rcoeffs, plane_dst, jobs, tx_size, tx_type, bit_depth, dequant=None):
     """inverse_transform_add (src/transform/mod.rs:568-580) over a batch: block i of `rcoeffs`
     ((N, coded) int32, coded = min(W,32)*min(H,32)) is inverse-transformed and added, clamped, to the
-    W x H pixels at jobs[i] = (x, y) of the device plane `plane_dst`.  Blocks must not overlap."""
+    W x H pixels at jobs[i] = (x, y) of the device plane `plane_dst`.  Blocks must not overlap.
+    dequant = (dc_quant, ac_quant): `rcoeffs` holds QUANTIZED coefficients and dequantize is fused in."""
     jobs = _arr(jobs, ITX_JOB)
     rcoeffs = _arr(rcoeffs, np.int32)
     w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)
     if w < 0:
         raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad tx_size")
     assert rcoeffs.size == jobs.size * min(w, 32) * min(h, 32)
+    if dequant is not None:
+        ctx.check(ctx.lib.r1c_dequant_inv_txfm_add_batch(ctx.h, plane_dst.h, _p(jobs), jobs.size, tx_size, tx_type,
+                                                         bit_depth, _p(rcoeffs), int(dequant[0]), int(dequant[1])))
+        return
     ctx.check(ctx.lib.r1c_inv_txfm_add_batch(ctx.h, plane_dst.h, _p(jobs), jobs.size, tx_size, tx_type,
                                              bit_depth, _p(rcoeffs)))
 

@@ -53,18 +53,20 @@ extern "C" int r1c_inv_txfm_valid(int tx_size, int tx_type) {
   return itx::lookup(tx_size, tx_type, &cf, &rf) != nullptr;
 }
 
-extern "C" int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n,
-                                          int tx_size, int tx_type, int bit_depth, const int32_t *d_rcoeffs) {
+// dq: nullptr, or {dc_quant, ac_quant} for the fused dequantize
+static int launch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n, int tx_size, int tx_type,
+                      int bit_depth, const int32_t *d_coeffs, const uint32_t *dq) {
   if (!ctx || !dst) return R1C_ERR_ARG;
   R1C_REQUIRE(ctx, bit_depth_ok(bit_depth, dst->px_bytes), R1C_ERR_ARG, "bit_depth %d vs %d-byte pixels", bit_depth, dst->px_bytes);
   R1C_REQUIRE(ctx, tx_size >= 0 && tx_size < R1C_TX_SIZES_ALL && tx_type >= 0 && tx_type < R1C_TX_TYPES, R1C_ERR_ARG,
               "bad (tx_size, tx_type) = (%d, %d)", tx_size, tx_type);
-  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (d_jobs && d_rcoeffs)), R1C_ERR_ARG, "null job/coeff array");
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (d_jobs && d_coeffs)), R1C_ERR_ARG, "null job/coeff array");
+  R1C_REQUIRE(ctx, !dq || (dq[0] && dq[1]), R1C_ERR_ARG, "zero quantizer");
   itx::ItxArgs a = {};
   itx::itx_launch_fn fn = itx::lookup(tx_size, tx_type, &a.col_flip, &a.row_flip);
   R1C_REQUIRE(ctx, fn != nullptr, R1C_ERR_UNIMPLEMENTED, "inverse transform (size %d, type %d) is unimplemented in the reference",
               tx_size, tx_type);
-  a.coeffs = d_rcoeffs;
+  a.coeffs = d_coeffs;
   a.dst = make_view(dst);
   a.jobs = d_jobs;
   a.n = n;
@@ -73,6 +75,12 @@ extern "C" int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1
   a.sh = itx::intermediate_shift(tx_size);
   a.rnd = (1 << a.sh) >> 1;
   a.maxv = (1 << bit_depth) - 1;
+  if (dq) {
+    a.dq_on = 1;
+    a.dq_dc = dq[0];
+    a.dq_ac = dq[1];
+    a.dq_lts = r1c_log_tx_scale(tx_size);
+  }
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   r1c_prof_begin(ctx, R1C_PROF_ITX);
   const int rc = fn(ctx, a, dst->px_bytes);
@@ -80,8 +88,20 @@ extern "C" int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1
   return rc;
 }
 
-extern "C" int r1c_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n, int tx_size,
-                                      int tx_type, int bit_depth, const int32_t *rcoeffs) {
+extern "C" int r1c_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n,
+                                          int tx_size, int tx_type, int bit_depth, const int32_t *d_rcoeffs) {
+  return launch_dev(ctx, dst, d_jobs, n, tx_size, tx_type, bit_depth, d_rcoeffs, nullptr);
+}
+
+extern "C" int r1c_dequant_inv_txfm_add_batch_dev(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *d_jobs, int64_t n,
+                                                  int tx_size, int tx_type, int bit_depth, const int32_t *d_qcoeffs,
+                                                  uint32_t dc_quant, uint32_t ac_quant) {
+  const uint32_t dq[2] = {dc_quant, ac_quant};
+  return launch_dev(ctx, dst, d_jobs, n, tx_size, tx_type, bit_depth, d_qcoeffs, dq);
+}
+
+static int launch_host(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n, int tx_size, int tx_type,
+                       int bit_depth, const int32_t *rcoeffs, const uint32_t *dq) {
   if (!ctx || !dst) return R1C_ERR_ARG;
   R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (jobs && rcoeffs)), R1C_ERR_ARG, "null job/coeff array");
   R1C_REQUIRE(ctx, r1c_tx_width(tx_size) > 0, R1C_ERR_ARG, "bad tx_size %d", tx_size);
@@ -106,8 +126,19 @@ extern "C" int r1c_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_it
   memcpy(h_c, rcoeffs, cb);
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
   R1C_CUDA(ctx, cudaMemcpyAsync(d_c, h_c, cb, cudaMemcpyHostToDevice, ctx->stream));
-  if ((rc = r1c_inv_txfm_add_batch_dev(ctx, dst, (const r1c_itx_job *)d_jobs, n, tx_size, tx_type, bit_depth, (const int32_t *)d_c)))
-    return rc;
+  if ((rc = launch_dev(ctx, dst, (const r1c_itx_job *)d_jobs, n, tx_size, tx_type, bit_depth, (const int32_t *)d_c, dq))) return rc;
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return R1C_OK;
+}
+
+extern "C" int r1c_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n, int tx_size,
+                                      int tx_type, int bit_depth, const int32_t *rcoeffs) {
+  return launch_host(ctx, dst, jobs, n, tx_size, tx_type, bit_depth, rcoeffs, nullptr);
+}
+
+extern "C" int r1c_dequant_inv_txfm_add_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_itx_job *jobs, int64_t n, int tx_size,
+                                              int tx_type, int bit_depth, const int32_t *qcoeffs, uint32_t dc_quant,
+                                              uint32_t ac_quant) {
+  const uint32_t dq[2] = {dc_quant, ac_quant};
+  return launch_host(ctx, dst, jobs, n, tx_size, tx_type, bit_depth, qcoeffs, dq);
 }

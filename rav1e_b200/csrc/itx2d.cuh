@@ -30,6 +30,9 @@ struct ItxArgs {
   int maxv;              // (1 << bd) - 1
   int col_flip, row_flip;
   int in16;              // coefficient array is 16-byte aligned
+  // fused dequantize (src/quantize.rs:318-334): the array holds qcoeffs, each one is scaled on load
+  int dq_on, dq_lts;
+  unsigned dq_dc, dq_ac;
 };
 
 template <int W, int H>
@@ -89,6 +92,12 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
       } else {
 #pragma unroll
         for (int c = 0; c < C::WI; c++) v[c] = __ldg(src + c);
+      }
+      if (a.dq_on) {  // *r = (c * quant + ((c >> 31) & offset)) >> log_tx_scale, wrapping i32 product
+        const unsigned off = (1u << a.dq_lts) - 1u;
+#pragma unroll
+        for (int c = 0; c < C::WI; c++)
+          v[c] = (int)((unsigned)v[c] * ((c == 0 && r == 0) ? a.dq_dc : a.dq_ac) + ((unsigned)(v[c] >> 31) & off)) >> a.dq_lts;
       }
 #pragma unroll
       for (int c = 0; c < W; c++) {

@@ -118,6 +118,31 @@ def test_inverse_all_pairs_match_oracle(r, ctx, oracle, pb, bd):
     assert pairs == 193
 
 
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+def test_dequantize_fused_into_inverse(r, ctx, oracle, pb, bd):
+    """r1c_dequant_inv_txfm_add_batch == dequantize (src/quantize.rs:318-334) then inverse_transform_add, for
+    every log_tx_scale (0: up to 16x16 ..., 1: 32x32 / 16x64 ..., 2: 64x64 ...) and negative levels"""
+    rng = np.random.default_rng(90 + bd)
+    L = oracle.lib()
+    for s, t, dcq, acq in ((0, 3, 8, 9), (1, 0, 40, 52), (2, 1, 300, 367), (3, 0, 96, 120), (4, 0, 1336, 1828),
+                           (9, 0, 24, 30), (17, 0, 60, 71), (16, 11, 16, 20), (13, 9, 500, 600)):
+        w, h = L.r1o_tx_width(s), L.r1o_tx_height(s)
+        coded = min(w, 32) * min(h, 32)
+        o, d = twin_plane(r, oracle, ctx, 256, 192, pb, bd, rng, xpad=0, ypad=0)
+        jobs = _grid_jobs(r, rng, 23, w, h, 256, 192)
+        n = jobs.size
+        q = (rng.integers(-40, 41, (n, coded)) * (rng.random((n, coded)) < 0.2)).astype(np.int32)
+        q[:, 0] = rng.integers(-60, 61, n)
+        lts = r.capi.load().r1c_log_tx_scale(s)
+        rc = np.stack([oracle.dequantize(q[i], dcq, acq, lts) for i in range(n)])
+        xy = np.stack([jobs["x"] + o.cfg.xorigin, jobs["y"] + o.cfg.yorigin], 1)
+        oracle.inv_txfm_add_batch(rc, o.data, xy, s, t, bd)
+        r.inverse_transform_add(ctx, q, d, jobs, s, t, bd, dequant=(dcq, acq))
+        assert np.array_equal(d.download(), o.data), (s, t)
+    with pytest.raises(r.Rav1eCudaError):
+        r.inverse_transform_add(ctx, q, d, jobs, s, t, bd, dequant=(0, 5))
+
+
 def test_inverse_errors_and_empty(r, ctx, oracle):
     rng = np.random.default_rng(9)
     o, d = twin_plane(r, oracle, ctx, 64, 64, 1, 8, rng, xpad=8, ypad=8)
