@@ -310,41 +310,52 @@ def run(ctx, r, torch, ext, flush, reps=3):
             "kernel_us_by_tx_size": qper[key],
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_coeff": bpc, "peak_source": hbm_how}}
-    # ------------------------------ inverse transform + add onto the 4K 10-bit luma plane (dequantized-like coefficients)
-    isum = 0.0
-    iper = {}
-    ibytes = 0
-    icoeffs = 0
+    # ------------------------------ inverse transform + add onto a 4K luma plane (dequantized-like coefficients):
+    # 10-bit (u16 plane `dst`) and 8-bit (u8 plane), and the 10-bit case with dequantize fused into the load
     rin = (qin // 147) * 147  # what dequantize leaves: multiples of the step, mostly zero
-    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
-        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
-        coded = min(w, 32) * min(h, 32)
-        xs, ys = np.meshgrid(np.arange(0, W - w + 1, w), np.arange(0, H - h + 1, h))
-        n = min(xs.size, n_samples // coded)
-        ij = np.zeros(n, dtype=r.ITX_JOB)
-        ij["x"], ij["y"] = xs.ravel()[:n], ys.ravel()[:n]
-        d_ij = torch.from_numpy(ij.view(np.int32).reshape(-1)).cuda()
+    qlv = qin // 147          # the quantized levels themselves, for the fused variant
+    dst8 = r.Plane(ctx, W, H, 0, 0, 88, 88, 1)
+    dst8.upload(rng.integers(0, 256, size=dst8.shape, dtype=np.uint8))
+    for key, plane, bd_i, pxb, fused in (("itx_4k10_inv_dct_dct_add", dst, BD, 2, 0), ("itx_4k8_inv_dct_dct_add", dst8, 8, 1, 0),
+                                         ("itx_4k10_dequant_inv_dct_dct_add", dst, BD, 2, 1)):
+        isum = 0.0
+        iper = {}
+        ibytes = 0
+        ipix = 0
+        for ts in ([int(v) for v in only.split(",")] if only else range(19)):
+            w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+            coded = min(w, 32) * min(h, 32)
+            xs, ys = np.meshgrid(np.arange(0, W - w + 1, w), np.arange(0, H - h + 1, h))
+            n = min(xs.size, n_samples // coded)
+            ij = np.zeros(n, dtype=r.ITX_JOB)
+            ij["x"], ij["y"] = xs.ravel()[:n], ys.ravel()[:n]
+            d_ij = torch.from_numpy(ij.view(np.int32).reshape(-1)).cuda()
 
-        def f_i():
-            ctx.check(lib.r1c_inv_txfm_add_batch_dev(ctx.h, dst.h, d_ij.data_ptr(), n, ts, 0, BD, rin.data_ptr()))
-        f_i()
-        ctx.sync()
-        _kernel_ms(ctx, 7)
-        _timed(torch, ext, flush, f_i, reps)
-        k_ms = _kernel_ms(ctx, 7)[0] / reps
-        isum += k_ms
-        b = n * (coded * 4 + w * h * 4)  # coded coefficients + u16 destination read and written
-        ibytes += b
-        icoeffs += n * w * h
-        iper["%dx%d" % (w, h)] = round(b / (k_ms / 1e3) / 1e9 / hbm, 3)
-    gbs = ibytes / (isum / 1e3) / 1e9
-    out["itx_4k10_inv_dct_dct_add"] = {
-        "workload": "4K 10-bit luma tiled by each of the 19 TxSize, DCT_DCT inverse transform added onto the plane",
-        "value": icoeffs / 1e6 / (isum / 1e3), "unit": "Mpix/s", "ms": isum, "pixels": icoeffs,
-        "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
-                     "alg_bytes": "4 per coded coefficient + 2 x 2 per pixel", "peak_source": hbm_how,
-                     "frac_by_tx_size": iper}}
-    del rin
+            def f_i():
+                if fused:
+                    ctx.check(lib.r1c_dequant_inv_txfm_add_batch_dev(ctx.h, plane.h, d_ij.data_ptr(), n, ts, 0, bd_i,
+                                                                     qlv.data_ptr(), 120, 147))
+                else:
+                    ctx.check(lib.r1c_inv_txfm_add_batch_dev(ctx.h, plane.h, d_ij.data_ptr(), n, ts, 0, bd_i, rin.data_ptr()))
+            f_i()
+            ctx.sync()
+            _kernel_ms(ctx, 7)
+            _timed(torch, ext, flush, f_i, reps)
+            k_ms = _kernel_ms(ctx, 7)[0] / reps
+            isum += k_ms
+            b = n * (coded * 4 + w * h * 2 * pxb)  # coded coefficients + destination read and written
+            ibytes += b
+            ipix += n * w * h
+            iper["%dx%d" % (w, h)] = round(b / (k_ms / 1e3) / 1e9 / hbm, 3)
+        gbs = ibytes / (isum / 1e3) / 1e9
+        out[key] = {
+            "workload": "4K %d-bit luma tiled by each of the 19 TxSize, DCT_DCT inverse transform added onto the plane%s"
+                        % (bd_i, " (quantized levels in, dequantize fused)" if fused else ""),
+            "value": ipix / 1e6 / (isum / 1e3), "unit": "Mpix/s", "ms": isum, "pixels": ipix,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                         "alg_bytes": "4 per coded coefficient + 2 x %d per pixel" % pxb, "peak_source": hbm_how,
+                         "frac_by_tx_size": iper}}
+    del rin, qlv, dst8
     ctx.check(lib.r1c_profile(ctx.h, 0))
     del res, coef, org, src, dst, d_out, qout, rout, dout, qin
     # -------------------------- whole-frame motion estimation on a 4K 10-bit frame pair (u16 planes)
