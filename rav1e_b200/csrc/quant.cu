@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
     // the DC and the zeroed tail leave the mode alone (f0 = 0, f1 = 1)
     int32_t q0, q1;
     bool f0 = false, f1 = true;
-    if (k == 0) {
+    if (k == 0 && !a.nonneg) {
       // DC, src/quantize.rs:278-280
       q0 = q1 = divu_pair(coeff + signum(coeff) * a.qc.dc_offset, a.qc.dc_mul_add[0], a.qc.dc_mul_add[1], a.qc.dc_mul_add[2]);
     } else if (k <= eob) {
@@ -105,12 +105,18 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
         // level0 <= 0, so it takes ac_offset0 under both modes and can only reset the mode (the tests are signed)
         // divu_pair is an exact division (Robison's multiply-add form; the reference's test_divu_pair), so
         // level0 > 0 / > 1 are comparisons with d / 2 d, and the quotient with the larger offset is the one with the
-        // smaller offset plus a carry out of its remainder (0 <= offset1 - offset0 < d): one wide multiply per coefficient
-        const uint32_t d = a.qc.ac_quant;
+        // smaller offset plus a carry out of its remainder (0 <= offset1 - offset0 < d): one wide multiply per coefficient.
+        // The DC (:278-280) is the same formula with its own divisor and one offset for both roles, so lane 0 of
+        // chunk 0 only swaps its constants instead of sending the warp through a second division
+        const bool dc = c == 0 && k == 0;
+        const uint32_t d = dc ? a.qc.dc_quant : a.qc.ac_quant;
+        const uint32_t off0 = (uint32_t)(dc ? a.qc.dc_offset : a.qc.ac_offset0);
+        const uint32_t doff = dc ? 0u : (uint32_t)(a.qc.ac_offset1 - a.qc.ac_offset0);
         const uint32_t y0 = (uint32_t)(coeff < 0 ? -coeff : coeff);
-        const uint32_t t0 = y0 + (uint32_t)a.qc.ac_offset0;
-        uint32_t ua = udivu(t0, ma, mb, ms);
-        uint32_t ub = ua + (t0 - ua * d + (uint32_t)(a.qc.ac_offset1 - a.qc.ac_offset0) >= d ? 1u : 0u);
+        const uint32_t t0 = y0 + off0;
+        uint32_t ua = c == 0 ? udivu(t0, dc ? a.qc.dc_mul_add[0] : ma, dc ? a.qc.dc_mul_add[1] : mb, dc ? a.qc.dc_mul_add[2] : ms)
+                             : udivu(t0, ma, mb, ms);
+        uint32_t ub = ua + (t0 - ua * d + doff >= d ? 1u : 0u);
         ua = y0 ? ua : 0u;
         ub = y0 ? ub : 0u;
         const bool neg = coeff < 0;
@@ -124,9 +130,10 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
         q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
         q1 = level0 > 0 ? qb : qa;
       }
-      // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1
-      f0 = q0 > 1;
-      f1 = q1 != 0;
+      // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1;
+      // the DC is outside the state machine
+      f0 = k != 0 && q0 > 1;
+      f1 = k == 0 || q1 != 0;
     } else {
       q0 = q1 = 0;  // src/quantize.rs:313-315
     }
@@ -259,7 +266,7 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   // (ac_quant as usize - ac_offset_eob as usize).align_power_of_two_and_shift(log_tx_scale), src/quantize.rs:265-267
   a.deadzone = (int32_t)(((uint64_t)qc->ac_quant - (uint64_t)qc->ac_offset_eob + (1ull << qc->log_tx_scale) - 1) >> qc->log_tx_scale);
   a.nonneg = qc->ac_offset0 >= 0 && qc->ac_offset1 >= qc->ac_offset0 && (uint32_t)(qc->ac_offset1 - qc->ac_offset0) < qc->ac_quant &&
-             qc->ac_quant < (1u << 30);
+             qc->ac_quant < (1u << 30) && qc->dc_offset >= 0 && (uint32_t)qc->dc_offset < qc->dc_quant && qc->dc_quant < (1u << 30);
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
   const unsigned g8 = (unsigned)((n + 7) / 8);
   switch (a.coded) {  // 4x4 .. 32x32 coded areas
