@@ -70,15 +70,21 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
   __syncwarp();
 
   // ---- eob: last scan index k >= 1 with |coeff| >= deadzone, else 1 (src/quantize.rs:268-276) ----
-  int32_t raw[NCH];
-  int pos[NCH];
+  // up to 8 chunks per lane: both loops fully unrolled, the lane's coefficients and scan positions stay in registers
+  // between them.  16 and 32 chunks (512 / 1024 coded coefficients): rolled loops that read them again from shared
+  // memory / the scan table -- the unrolled form needs 64 - 124 registers and does not fit the instruction cache
+  constexpr bool ROLLED = NCH >= 16;
+  constexpr int UNR = ROLLED ? 4 : NCH;
+  int32_t raw_keep[ROLLED ? 1 : NCH];
+  int pos_keep[ROLLED ? 1 : NCH];
   int eob = 1;
-#pragma unroll
+#pragma unroll UNR
   for (int c = 0; c < NCH; c++) {
     const int k = c * LPB + l;
-    pos[c] = (int)__ldg(a.scan + k);
-    raw[c] = sb[pos[c]];
-    if (k >= 1 && (raw[c] < 0 ? -raw[c] : raw[c]) >= a.deadzone) eob = k;
+    const int p = (int)__ldg(a.scan + k);
+    const int32_t r = sb[p];
+    if (!ROLLED) pos_keep[c] = p, raw_keep[c] = r;
+    if (k >= 1 && (r < 0 ? -r : r) >= a.deadzone) eob = k;
   }
 #pragma unroll
   for (int m = LPB >> 1; m; m >>= 1) eob = max(eob, __shfl_xor_sync(0xffffffffu, eob, m, LPB));
@@ -87,10 +93,12 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
   __syncwarp();
   uint32_t mode = 1;  // level_mode at the start of the chunk
   unsigned long long dist = 0;
-#pragma unroll
+#pragma unroll UNR
   for (int c = 0; c < NCH; c++) {
     const int k = c * LPB + l;
-    const int32_t coeff = (int32_t)((uint32_t)raw[c] << lts);
+    const int pos_c = ROLLED ? (int)__ldg(a.scan + k) : pos_keep[c];
+    const int32_t raw_c = ROLLED ? sb[pos_c] : raw_keep[c];  // each position is read and rewritten by its one lane
+    const int32_t coeff = (int32_t)((uint32_t)raw_c << lts);
     // this lane's result under level_mode 0 / 1 and its transition map f0 / f1 = next mode from mode 0 / 1;
     // the DC and the zeroed tail leave the mode alone (f0 = 0, f1 = 1)
     int32_t q0, q1;
@@ -161,10 +169,10 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
       mode = fixed ? (A >> (31 - __clz(fixed))) & 1u : mode;
     }
     const int32_t q = m_in ? q1 : q0;
-    sb[pos[c]] = q;
+    sb[pos_c] = q;
     if (a.tx_dist) {
-      const int32_t r = dequant1(q, pos[c] == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
-      const uint32_t d = (uint32_t)raw[c] - (uint32_t)r;
+      const int32_t r = dequant1(q, pos_c == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
+      const uint32_t d = (uint32_t)raw_c - (uint32_t)r;
       dist += (unsigned long long)(long long)(int32_t)(d * d);  // (c * c) as u64, wrapping i32 product
     }
   }
