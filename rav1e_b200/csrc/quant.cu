@@ -278,9 +278,11 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
   const unsigned g8 = (unsigned)((n + 7) / 8);
   switch (a.coded) {  // 4x4 .. 32x32 coded areas
-    case 16: quantize_kernel<16, 1><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
-    case 32: quantize_kernel<32, 1><<<g8, 256, 0, ctx->stream>>>(a); break;
-    case 64: quantize_kernel<32, 2><<<g8, 256, 0, ctx->stream>>>(a); break;
+    // small blocks share a warp (8 or 16 lanes each): the per-block steps (end-of-block reduction, ballots,
+    // staging index arithmetic) are then spread over two to four coefficients per lane instead of one
+    case 16: quantize_kernel<8, 2><<<(unsigned)((n + 31) / 32), 256, 0, ctx->stream>>>(a); break;
+    case 32: quantize_kernel<16, 2><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
+    case 64: quantize_kernel<16, 4><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
     case 128: quantize_kernel<32, 4><<<g8, 256, 0, ctx->stream>>>(a); break;
     case 256: quantize_kernel<32, 8><<<g8, 256, 0, ctx->stream>>>(a); break;
     case 512: quantize_kernel<32, 16><<<g8, 256, 0, ctx->stream>>>(a); break;
