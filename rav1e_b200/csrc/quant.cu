@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
   int32_t *sw = s_buf[threadIdx.x >> 5], *sb = sw + (lane / LPB) * CODED;
 #pragma unroll
   for (int i = 0; i < BPW * CODED / 32; i++) {
-    const int e = i * 32 + lane, blk = e / CODED, off = e - blk * CODED;  // BPW > 1 only for 16-coefficient blocks
+    const int e = i * 32 + lane, blk = e / CODED, off = e - blk * CODED;
     const long long gb = warp * BPW + blk;
     sw[e] = gb < a.n ? __ldg(a.coeffs + gb * a.area + off) : 0;
   }
@@ -278,11 +278,11 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
   const unsigned g8 = (unsigned)((n + 7) / 8);
   switch (a.coded) {  // 4x4 .. 32x32 coded areas
-    // small blocks share a warp (8 or 16 lanes each): the per-block steps (end-of-block reduction, ballots,
-    // staging index arithmetic) are then spread over two to four coefficients per lane instead of one
-    case 16: quantize_kernel<8, 2><<<(unsigned)((n + 31) / 32), 256, 0, ctx->stream>>>(a); break;
-    case 32: quantize_kernel<16, 2><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
-    case 64: quantize_kernel<16, 4><<<(unsigned)((n + 15) / 16), 256, 0, ctx->stream>>>(a); break;
+    // small blocks share a warp (4 or 8 lanes each): the per-block steps (end-of-block reduction, ballots,
+    // staging index arithmetic) are then spread over four to eight coefficients per lane instead of one or two
+    case 16: quantize_kernel<4, 4><<<(unsigned)((n + 63) / 64), 256, 0, ctx->stream>>>(a); break;
+    case 32: quantize_kernel<8, 4><<<(unsigned)((n + 31) / 32), 256, 0, ctx->stream>>>(a); break;
+    case 64: quantize_kernel<8, 8><<<(unsigned)((n + 31) / 32), 256, 0, ctx->stream>>>(a); break;
     case 128: quantize_kernel<32, 4><<<g8, 256, 0, ctx->stream>>>(a); break;
     case 256: quantize_kernel<32, 8><<<g8, 256, 0, ctx->stream>>>(a); break;
     case 512: quantize_kernel<32, 16><<<g8, 256, 0, ctx->stream>>>(a); break;
