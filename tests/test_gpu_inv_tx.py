@@ -66,6 +66,20 @@ def test_inverse_reference_vectors(r, ctx, oracle, golden):
     assert n == 193
 
 
+def test_forward_reference_vectors(r, ctx):
+    """tests/golden/fwd_tx_r01.npz: the CUDA forward transforms against coefficients made by the reference's own
+    1-D functions (tests/golden/make_fwd_tx_golden.py), all 193 pairs"""
+    g = dict(np.load(os.path.join(HERE, "golden", "fwd_tx_r01.npz")))
+    n = 0
+    for k in sorted(g):
+        if not k.startswith("x_"):
+            continue
+        s, t, bd = (int(v) for v in k.split("_")[1:])
+        assert np.array_equal(r.forward_transform(ctx, g[k], s, t, bd), g["y" + k[1:]]), k
+        n += 1
+    assert n == 193
+
+
 def test_inverse_add_reference_vectors(r, ctx, oracle, golden):
     """inv_txfm2d_add cases of the reference with both clamps biting"""
     for k in sorted(golden):

@@ -43,6 +43,20 @@ def test_inverse_add_reproduces_reference_vectors(oracle, golden):
     assert n == 8
 
 
+def test_forward_2d_reproduces_reference_vectors(oracle):
+    """tests/golden/fwd_tx_r01.npz: residual -> coefficients made by the reference's own forward 1-D functions
+    (tests/golden/make_fwd_tx_golden.py), all 193 pairs"""
+    g = dict(np.load(os.path.join(HERE, "golden", "fwd_tx_r01.npz")))
+    n = 0
+    for k in sorted(g):
+        if not k.startswith("x_"):
+            continue
+        s, t, bd = (int(v) for v in k.split("_")[1:])
+        assert np.array_equal(oracle.fht(g[k], s, t, bd), g["y" + k[1:]]), k
+        n += 1
+    assert n == 193
+
+
 # (tx_size, tx_type, tolerance): src/transform/mod.rs:665-708; sizes / types by their enum values
 ROUNDTRIPS = ([(0, t, 0) for t in (0, 1, 2, 3, 9, 10, 11, 12, 13)]
               + [(1, 0, 1), (1, 1, 1), (1, 2, 1), (1, 3, 1), (1, 9, 0), (1, 10, 0), (1, 11, 0), (1, 12, 0), (1, 13, 1)]

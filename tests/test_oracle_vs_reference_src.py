@@ -108,3 +108,53 @@ def test_inverse_2d_matches_reference_text():
             ref = np.array(R.inv_txfm2d([int(v) for v in c], w, h, tx_type, bd)).reshape(w, h).T
             got = r1o.inv_txfm2d(c, tx_size, tx_type, bd)
             assert np.array_equal(got, ref), (tx_size, tx_type, bd)
+
+
+# ---- forward transforms: the reference's own 1-D functions (transliterated at test time) -------------
+def _ftx():
+    import sys
+    sys.path.insert(0, HERE)
+    import ref_fwd_tx
+    sys.path.insert(0, os.path.join(HERE, ".."))
+    from oracle import r1o
+    return ref_fwd_tx, r1o
+
+
+@pytest.mark.parametrize("kind,t1d,sizes", [("dct", 0, (4, 8, 16, 32, 64)), ("adst", 1, (4, 8, 16)),
+                                            ("identity", 2, (4, 8, 16, 32))])
+def test_forward_1d_matches_reference_text(kind, t1d, sizes):
+    """daala_fdct* / daala_fdst* / fidentity* (src/transform/forward.rs:338-1700) run from their own text, against
+    the oracle: small, typical and 32-bit-wrapping magnitudes"""
+    import numpy as np
+    F, r1o = _ftx()
+    rng = np.random.default_rng(17 + t1d)
+    for n in sizes:
+        f = F.fn1d(kind, n)
+        for trial in range(40):
+            mag = (1 << 30) if trial % 10 == 9 else 1 << (3 + trial % 16)
+            x = rng.integers(-mag, mag + 1, n)
+            if trial % 7 == 3:
+                x[:] = mag if trial % 2 else -mag
+            assert r1o.txfm1d(t1d, x).tolist() == f([int(v) for v in x]), (kind, n, trial)
+
+
+def test_forward_2d_matches_reference_text():
+    """every valid (TxSize, TxType) pair through the reference's 1-D text under a restatement of fht
+    (forward.rs:1804-1899) with the shift tables parsed from the source (:22-40), against the oracle's fht"""
+    import numpy as np
+    F, r1o = _ftx()
+    rng = np.random.default_rng(23)
+    pairs = 0
+    for tx_size in range(19):
+        w, h = r1o.lib().r1o_tx_width(tx_size), r1o.lib().r1o_tx_height(tx_size)
+        for tx_type in range(16):
+            if not r1o.lib().r1o_fht_valid(tx_size, tx_type):
+                continue
+            pairs += 1
+            if w * h > 1024 and tx_type != 0:
+                continue  # keep the pure-Python side in seconds
+            bd = (8, 10, 12)[(tx_size + tx_type) % 3]
+            res = rng.integers(-(1 << bd) + 1, 1 << bd, (h, w)).astype(np.int16)
+            ref = F.fht(res.reshape(-1), w, h, tx_type, bd)
+            assert r1o.fht(res, tx_size, tx_type, bd).reshape(-1).tolist() == ref, (tx_size, tx_type, bd)
+    assert pairs == 193
