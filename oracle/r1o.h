@@ -10,10 +10,14 @@
  * Parity pinning status (see DESIGN.md "Oracle"):
  *   SAD / SATD   : PINNED by the 44 golden values of src/dist.rs:379-402,437-460
  *   plane pad    : PINNED by the golden of src/frame/plane.rs:709-752
- *   MC, fwd TX, ME search : parity UNPINNED (the reference holds no golden
- *                  vectors for them and cannot be compiled here: no rustc /
- *                  nasm).  They are literal restatements cross-checked by
- *                  independent properties (tests/test_oracle_*.py).
+ *   fwd / inv TX : PINNED against the reference's own functions, whose Rust
+ *                  text is transliterated and run at test time (tests/ref_fwd_tx.py,
+ *                  tests/ref_inv_tx.py), and by golden vectors made that way
+ *   MC, ME search, RDO distortion, quantize state machine, importances :
+ *                  parity UNPINNED (the reference holds no golden vectors for
+ *                  them and cannot be compiled here: no rustc / nasm).  They
+ *                  are literal restatements cross-checked by independent
+ *                  properties (tests/test_oracle_*.py).
  *
  * All strides are in PIXELS (the Rust API convention, plane_cfg.stride).
  * px_bytes is 1 (u8, bit_depth 8) or 2 (u16, bit_depth 10/12).

@@ -4,12 +4,16 @@
  * TxOperations for i32`, forward.rs:114-130) and the 2-D driver
  * FwdTxfm2D::fht (forward.rs:1804-1899).
  *
- * Parity: UNPINNED -- the reference holds no golden coefficients for the
- * forward transforms (only a fwd->inv round-trip tolerance test,
- * src/transform/mod.rs:589-725).  Constants are taken from the CODE, never
- * from the comments (several differ).  Cross-checks:
- * tests/test_oracle_props.py compares every 1-D kernel against the
- * floating-point DCT-II / DST-IV / DST-VII it approximates.
+ * Parity: PINNED against the reference's own functions.  The reference holds
+ * no golden coefficients (only a fwd->inv round-trip tolerance test,
+ * src/transform/mod.rs:589-725), but tests/ref_fwd_tx.py runs the text of
+ * forward.rs:100-1700 itself (transliterated at test time, dev container
+ * only): tests/test_oracle_vs_reference_src.py compares every 1-D kernel and
+ * all 193 2-D pairs with it, and tests/golden/fwd_tx_r01.npz holds vectors
+ * made the same way.  The round-trip test is run too (test_oracle_inv_tx.py).
+ * Constants are taken from the CODE, never from the comments (several differ,
+ * SURVEY.md A1).  tests/test_oracle_props.py also compares every 1-D kernel
+ * against the floating-point DCT-II / DST-IV / DST-VII it approximates.
  *
  * Arithmetic is 32-bit two's complement with wrap-around (release-mode Rust
  * and every SIMD lane wrap): build with -fwrapv.  `>>` on negative values is
