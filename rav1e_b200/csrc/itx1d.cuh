@@ -136,17 +136,19 @@ __device__ __forceinline__ void idct(const int (&in)[N], int (&out)[N], Range rg
   for (int p = 0; p < N; p++) out[p] = s[p];
 }
 
-__device__ __forceinline__ int rshift12(int v) { return (v + 2048) >> 12; }
+// round_shift(v, 12) of a wrapping i32 value (unsigned arithmetic: overflow is defined and wraps like the
+// reference's release build)
+__device__ __forceinline__ int rshift12(unsigned v) { return (int)(v + 2048u) >> 12; }
 
 // av1_iadst4: SINPI_INV = {0, 1321, 2482, 3344, 3803}, :31; plain i32 products, one rounding at the end
 __device__ __forceinline__ void iadst4(const int (&in)[4], int (&out)[4]) {
-  const int x0 = in[0], x1 = in[1], x2 = in[2], x3 = in[3];
-  const int p = 1321 * x0 + 3803 * x2 + 2482 * x3;
-  const int q = 2482 * x0 - 1321 * x2 - 3803 * x3;
-  const int m = 3344 * x1;
+  const unsigned x0 = (unsigned)in[0], x1 = (unsigned)in[1], x2 = (unsigned)in[2], x3 = (unsigned)in[3];
+  const unsigned p = 1321u * x0 + 3803u * x2 + 2482u * x3;
+  const unsigned q = 2482u * x0 - 1321u * x2 - 3803u * x3;
+  const unsigned m = 3344u * x1;
   out[0] = rshift12(p + m);
   out[1] = rshift12(q + m);
-  out[2] = rshift12(3344 * (x0 - x2 + x3));
+  out[2] = rshift12(3344u * (x0 - x2 + x3));
   out[3] = rshift12(p + q - m);
 }
 
@@ -192,7 +194,8 @@ template <int N>
 __device__ __forceinline__ void iident(const int (&in)[N], int (&out)[N]) {
 #pragma unroll
   for (int i = 0; i < N; i++)
-    out[i] = N == 4 ? rshift12(5793 * in[i]) : N == 8 ? 2 * in[i] : N == 16 ? rshift12(5793 * 2 * in[i]) : 4 * in[i];
+    out[i] = N == 4 ? rshift12(5793u * (unsigned)in[i]) : N == 8 ? (int)(2u * (unsigned)in[i])
+           : N == 16 ? rshift12(5793u * 2u * (unsigned)in[i]) : (int)(4u * (unsigned)in[i]);
 }
 
 template <int TYPE, int N>
