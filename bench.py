@@ -229,7 +229,13 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (rav1e_b200 has no CPU fallback)")
     torch.cuda.set_device(local)
+    stdout_fd = None
     if world > 1:
+        # stdout carries exactly one JSON line: while NCCL is in use, file descriptor 1 points at stderr (NCCL prints
+        # its version banner to stdout on some boxes); it is put back just before rank 0 prints the line
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W_ = max(args.warmup, 3)
     K = args.steps
@@ -365,7 +371,13 @@ def main():
                 line["kernels"] = bench_kernels.run(ctx, r, torch, ext, flush)
             except Exception as e:  # the headline line must still print
                 line["kernels"] = {"error": repr(e)}
+        if stdout_fd is not None:
+            sys.stdout.flush()
+            os.dup2(stdout_fd, 1)
         print(json.dumps(line))
+        sys.stdout.flush()
+        if stdout_fd is not None:
+            os.dup2(2, 1)  # NCCL's teardown messages, if any, go to stderr again
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
