@@ -435,6 +435,25 @@ int r1c_me_sb_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
 int r1c_me_sb_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                         const r1c_sb_params *params, const r1c_sb_job *d_jobs, int64_t n,
                         int bit_depth, r1c_me_result *d_results);
+/* Allocation-free variant of r1c_me_sb_batch_dev.  It has NO counterpart in the reference; it
+ * was added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs
+ * and results as r1c_me_sb_batch_dev, but the search kernel's scratch (partial keys per
+ * (superblock, chunk of candidate rows); org sums for u16 planes) lives in one file-scope
+ * `static __device__` array of R1C_SB_NOALLOC_SCRATCH_BYTES (8 MiB, held by every GPU that loads
+ * the library until exit) instead of the context's grow-on-demand scratch, and the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  Limits: only what the second-generation
+ * kernel takes (step 1, 8-bit planes or u16 planes up to 10 bits, lambda <= 60000; anything else
+ * -> R1C_ERR_UNIMPLEMENTED, there is no fallback kernel here) and
+ * n * chunks * 849 * 8 (+ n * 849 * 4 for u16 planes) <= R1C_SB_NOALLOC_SCRATCH_BYTES -- e.g. all
+ * 510 superblocks of a 1080p 8-bit frame at +-64 (2 chunks, 6.9 MB); more -> R1C_ERR_NOMEM with
+ * the sizes in r1c_last_error().  All calls on a device share the array: calls that overlap on
+ * the GPU (different streams or contexts) race; calls on one stream are ordered.  Nothing is
+ * carried from one call to the next (every slot read is written by the same call first). */
+#define R1C_SB_NOALLOC_SCRATCH_BYTES (8u << 20)
+int r1c_me_sb_batch_dev_noalloc(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                const r1c_sb_params *params, const r1c_sb_job *d_jobs, int64_t n,
+                                int bit_depth, r1c_me_result *d_results);
 
 /* The full-pel stages of FullSearch motion estimation on the frame pyramid, batched over
  * blocks (window arithmetic of the reference on the host, searches = r1c_full_search_batch):

@@ -18,6 +18,7 @@ R1C_ERR_BOUNDS = -3
 R1C_ERR_UNIMPLEMENTED = -4
 R1C_ERR_NOMEM = -5
 R1C_SB_RESULTS = 849
+R1C_SB_NOALLOC_SCRATCH_BYTES = 8 << 20
 
 BLOCK_SIZES = [
     "BLOCK_4X4", "BLOCK_4X8", "BLOCK_8X4", "BLOCK_8X8", "BLOCK_8X16", "BLOCK_16X8",
@@ -192,6 +193,7 @@ SIGNATURES = {
     "r1c_sb_result_offset": (_i, [_i]), "r1c_sb_result_count": (_i, [_i]),
     "r1c_me_sb_batch": (_i, [_vp, _vp, _vp, _P(SbParams), _vp, _i64, _i, _vp]),
     "r1c_me_sb_batch_dev": (_i, [_vp, _vp, _vp, _P(SbParams), _vp, _i64, _i, _vp]),
+    "r1c_me_sb_batch_dev_noalloc": (_i, [_vp, _vp, _vp, _P(SbParams), _vp, _i64, _i, _vp]),
     "r1c_subpel_cost_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _vp]),
     "r1c_subpel_refine_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_subpel_refine_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),

@@ -845,3 +845,91 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   }
   return R1C_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// r1c_me_sb_batch_dev_noalloc -- the search above for callers that may not allocate (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The partial keys (and the org sums of u16
+// planes) live in ONE file-scope device array of R1C_SB_NOALLOC_SCRATCH_BYTES instead of the
+// context's grow-on-demand scratch: every GPU that loads the library holds it until exit, every
+// call on a device shares it, and calls that overlap on the GPU (two streams, two contexts)
+// race on it.  Every slot the finalize kernel reads is written by the search kernel of the same
+// call first (849 keys per work item, 849 sums per job), so nothing has to start at zero and
+// the contents left by the previous call are never read.
+// In host code `g_sb2_noalloc_scratch` is only a stand-in for the symbol; the device address
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) unsigned char g_sb2_noalloc_scratch[R1C_SB_NOALLOC_SCRATCH_BYTES];
+
+#include <mutex>
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_ptr[64];  // per device ordinal; nullptr = not looked up yet
+
+extern "C" int r1c_me_sb_batch_dev_noalloc(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                           const r1c_sb_params *p, const r1c_sb_job *d_jobs, int64_t n,
+                                           int bit_depth, r1c_me_result *d_results) {
+  if (!ctx || !org || !ref || !p) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, org->px_bytes == ref->px_bytes, R1C_ERR_ARG, "org/ref pixel types differ");
+  R1C_REQUIRE(ctx, bit_depth_ok(bit_depth, org->px_bytes), R1C_ERR_ARG, "bit_depth %d vs %d-byte pixels", bit_depth,
+              org->px_bytes);
+  R1C_REQUIRE(ctx, p->range_x >= 0 && p->range_y >= 0 && p->w_in_b > 0 && p->h_in_b > 0, R1C_ERR_ARG, "bad range / frame size");
+  R1C_REQUIRE(ctx, n >= 0 && n < (1ll << 31), R1C_ERR_ARG, "bad job count");
+  R1C_REQUIRE(ctx, n == 0 || (d_jobs && d_results), R1C_ERR_ARG, "null job/result array");
+  R1C_REQUIRE(ctx, ctx->device >= 0 && ctx->device < 64, R1C_ERR_ARG, "device ordinal %d not supported by the no-alloc path", ctx->device);
+  Sb2Plan pl = {};
+  R1C_REQUIRE(ctx, sb2_plan(ctx, p, org->px_bytes, bit_depth, n, &pl), R1C_ERR_UNIMPLEMENTED,
+              "no-alloc search: step 1, 8-bit or <= 10-bit planes and a window this kernel's layout can take only "
+              "(range %dx%d, step %d, lambda %u)", p->range_x, p->range_y, p->step, p->lambda);
+  if (n == 0) return R1C_OK;
+  const size_t partial_bytes = (size_t)n * pl.split * NSLOT * sizeof(unsigned long long);
+  const size_t bias_bytes = org->px_bytes == 2 ? (size_t)n * NSLOT * sizeof(uint32_t) : 0;
+  R1C_REQUIRE(ctx, partial_bytes + bias_bytes <= (size_t)R1C_SB_NOALLOC_SCRATCH_BYTES, R1C_ERR_NOMEM,
+              "no-alloc search: %lld superblocks x %d chunks need %zu bytes of scratch, the static array holds %u "
+              "(R1C_SB_NOALLOC_SCRATCH_BYTES); split the job list or use r1c_me_sb_batch_dev",
+              (long long)n, pl.split, partial_bytes + bias_bytes, (unsigned)R1C_SB_NOALLOC_SCRATCH_BYTES);
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  void *d_scratch;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[ctx->device]) {
+      void *sym = nullptr;
+      R1C_CUDA(ctx, cudaGetSymbolAddress(&sym, g_sb2_noalloc_scratch));
+      R1C_REQUIRE(ctx, sym != nullptr, R1C_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+      g_noalloc_ptr[ctx->device] = sym;
+    }
+    d_scratch = g_noalloc_ptr[ctx->device];
+  }
+  Sb2Args a;
+  a.org = make_view(org);
+  a.ref = make_view(ref);
+  a.p = *p;
+  a.jobs = d_jobs;
+  a.partial = (unsigned long long *)d_scratch;
+  a.bias = bias_bytes ? (uint32_t *)((uint8_t *)d_scratch + partial_bytes) : nullptr;
+  a.n = n;
+  a.split = pl.split;
+  a.rpc = pl.rpc;
+  a.rsw = pl.rsw;
+  a.csz = pl.csz;
+  a.M = pl.M;
+  auto kern = org->px_bytes == 1 ? (pl.rsw == 48 ? me_sb2_kernel<48, 1> : me_sb2_kernel<0, 1>)
+                                 : (pl.rsw == 96 ? me_sb2_kernel<96, 2> : me_sb2_kernel<0, 2>);
+  R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
+  kern<<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
+  R1C_LAUNCH_CHECK(ctx);
+  FinArgs fa;
+  fa.partial = a.partial;
+  fa.bias = a.bias;
+  fa.jobs = d_jobs;
+  fa.results = d_results;
+  fa.map = nullptr;
+  fa.n_out = n * NSLOT;
+  fa.split = pl.split;
+  fa.NX = 2 * p->range_x + 1;
+  fa.Rx = p->range_x;
+  fa.Ry = p->range_y;
+  fa.W4 = p->w_in_b * 4;
+  fa.H4 = p->h_in_b * 4;
+  sb2_finalize_kernel<<<(unsigned)((fa.n_out + 255) / 256), 256, 0, ctx->stream>>>(fa);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
