@@ -119,7 +119,7 @@ def mc_jobs(r, rng, lib, W, H):
     return jobs
 
 
-def run(ctx, r, torch, ext, flush, reps=3):
+def run(ctx, r, torch, ext, flush, reps=3, only=None):
     lib = ctx.lib
     hbm, hbm_how = _hbm_peak()
     out = {}
@@ -215,6 +215,9 @@ def run(ctx, r, torch, ext, flush, reps=3):
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "alg_bytes_per_px": 4,
                      "peak_source": hbm_how, "int_frac": px_total * 32 / (one_k / 1e3) / 1e9 / ipeak}}
     del tmp1, tmp2
+    if only == "mc":
+        ctx.check(lib.r1c_profile(ctx.h, 0))
+        return out
     # ------------------------------------------ SAD / SATD, 4K 10-bit luma, one job per block
     org = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
     org.upload(rng.integers(0, 1024, size=src.shape, dtype=np.uint16))

@@ -92,6 +92,9 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
 int r1c_refine_frame(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_frame_me_params *p,
                      int bit_depth, const long long *off, const int *cols, const int *rows, const r1c_sb_job *d_sbs, int64_t n_sb,
                      r1c_me_result *d_results, int *handled);
+// mc_tma.cu: put (kind 0) / prep (1) / dense put (2) through the TMA tile kernel; *handled = 0 -> caller uses mc.cu's kernel
+int r1c_mc_tma_launch(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_plane *src, const r1c_mc_job *d_jobs,
+                      int64_t n, int bit_depth, int *handled);
 int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
                          int64_t n, int bit_depth);
 

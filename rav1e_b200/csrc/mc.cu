@@ -21,6 +21,8 @@
 // row_frac) cases with their own rounding.
 // Algorithmic bytes: put/prep 2*px_bytes per output pixel (1 read + 1 write,
 // halo served by L1/L2); mc_avg 2*2 B read + px_bytes written.
+#include <stdlib.h>
+
 #include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
@@ -517,6 +519,14 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
     pack_taps_kernel<<<1, 128, 0, ctx->stream>>>();
     R1C_LAUNCH_CHECK(ctx);
     ctx->mc_taps_ready = 1;
+  }
+  {  // second generation: source windows staged by 2-D TMA (mc_tma.cu), enabled by R1C_MC_TMA=1
+    const char *v2 = getenv("R1C_MC_TMA");  // off until the tensor-load fault on the GPU box is understood
+    if (v2 && v2[0] == '1') {
+      int handled = 0;
+      const int rc2 = r1c_mc_tma_launch(ctx, kind, dst, d_tmp, src, d_jobs, n, bit_depth, &handled);
+      if (rc2 || handled) return rc2;
+    }
   }
   long long *d_offs;
   int rc = build_offsets<r1c_mc_job, 0>(ctx, d_jobs, n, &d_offs);

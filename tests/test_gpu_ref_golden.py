@@ -161,6 +161,9 @@ def _sp_jobs(r, rows, ranges):
 
 @pytest.mark.parametrize("bd", [8, 10, 12])
 def test_subpel_cost_and_telescopic_match_reference(r, ctx, oracle, bd):
+    """get_mv_rd_cost through predict_inter (src/me.rs:787-856) per candidate, and r1c_subpel_refine_batch =
+    motion_estimation's tail (:232-271): with use_satd it re-evaluates the start MV by SATD (the stored start cost of
+    those jobs is that very value, made by the reference's get_mv_rd_cost), then telescopic_subpel_search (:858-941)"""
     g = load_golden("me")
     W, H, xpad, ypad = (int(v) for v in g["geom"])
     pb = 1 if bd == 8 else 2
@@ -170,18 +173,19 @@ def test_subpel_cost_and_telescopic_match_reference(r, ctx, oracle, bd):
     jobs = _sp_jobs(r, rows, g["sp_range_%d" % bd])
     cand = np.zeros(g["sp_cand_%d" % bd].shape[:2], dtype=r.MV)
     cand["row"], cand["col"] = g["sp_cand_%d" % bd][:, :, 0], g["sp_cand_%d" % bd][:, :, 1]
-    got = r.subpel_cost_batch(ctx, d_org, d_ref, jobs, cand, bd)
-    assert np.array_equal(got, g["sp_cost_%d" % bd])
-    # r1c_subpel_refine_batch = motion_estimation's tail (src/me.rs:232-271): with use_satd it re-evaluates the start MV
-    # by SATD (the stored start cost of those jobs is that very value, made by the reference's get_mv_rd_cost), then
-    # telescopic_subpel_search
     start = np.zeros(len(rows), dtype=r.ME_RESULT)
     start["mv"]["row"], start["mv"]["col"] = rows[:, 10], rows[:, 11]
     start["cost"] = g["tele_start_cost_%d" % bd]
-    out = r.subpel_refine_batch(ctx, d_org, d_ref, jobs, start, bd)
-    assert np.array_equal(out["mv"]["row"], g["tele_mv_%d" % bd][:, 0])
-    assert np.array_equal(out["mv"]["col"], g["tele_mv_%d" % bd][:, 1])
-    assert np.array_equal(out["cost"], g["tele_cost_%d" % bd])
+    for hp in (0, 1):  # jobs of one batch share allow_high_precision_mv
+        sel = np.nonzero(rows[:, 9] == hp)[0]
+        if sel.size == 0:
+            continue
+        got = r.subpel_cost_batch(ctx, d_org, d_ref, jobs[sel], cand[sel], bd)
+        assert np.array_equal(got, g["sp_cost_%d" % bd][sel]), hp
+        out = r.subpel_refine_batch(ctx, d_org, d_ref, jobs[sel], start[sel], bd)
+        assert np.array_equal(out["mv"]["row"], g["tele_mv_%d" % bd][sel, 0]), hp
+        assert np.array_equal(out["mv"]["col"], g["tele_mv_%d" % bd][sel, 1]), hp
+        assert np.array_equal(out["cost"], g["tele_cost_%d" % bd][sel]), hp
 
 
 @pytest.mark.parametrize("bd", [8, 10])
