@@ -99,17 +99,24 @@ def padded(cfg, vis):
     return a
 
 
-def mc_jobs(r, rng, lib, W, H):
+MC_CANDS = int(os.environ.get("R1C_BENCH_MC_CANDS", "4"))  # candidate MVs per block and launch
+
+
+def mc_jobs(r, rng, lib, W, H, K=1):
+    """per block size: the tiling of the frame by that size, K times over (K candidate MVs per block, as a motion
+    search or a compound prediction hands them over in one launch); candidate c predicts into rows [c*H, (c+1)*H) of
+    the destination"""
     jobs = []
     only = os.environ.get("R1C_BENCH_SIZES")  # profiling aid: restrict to some BlockSize values
     for b in ([int(v) for v in only.split(",")] if only else SIZES_TO_64):
         bw, bh = lib.r1c_block_width(b), lib.r1c_block_height(b)
         xs, ys = np.meshgrid(np.arange(0, W - bw + 1, bw), np.arange(0, H - bh + 1, bh))
-        n = xs.size
+        n = xs.size * K
         j = np.zeros(n, dtype=r.MC_JOB)
-        j["dst_x"], j["dst_y"] = xs.ravel(), ys.ravel()
+        j["dst_x"], j["dst_y"] = np.tile(xs.ravel(), K), np.tile(ys.ravel(), K)
         j["src_x"] = j["dst_x"] + rng.integers(-32, 33, size=n)
         j["src_y"] = j["dst_y"] + rng.integers(-32, 33, size=n)
+        j["dst_y"] += np.repeat(np.arange(K), xs.size) * H
         j["w"], j["h"] = bw, bh
         j["col_frac"] = rng.integers(0, 16, size=n)
         j["row_frac"] = rng.integers(0, 16, size=n)
@@ -126,18 +133,19 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
     rng = np.random.default_rng(3)
     # ------------------------------------------------------------------ MC, 4K 10-bit luma
     W, H, BD = 3840, 2160, 10
+    K = MC_CANDS
     src = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
-    dst = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
+    dst = r.Plane(ctx, W, K * H, 0, 0, 88, 88, 2)
     host = rng.integers(0, 1024, size=src.shape, dtype=np.uint16)
     src.upload(host)
-    per_size = mc_jobs(r, rng, lib, W, H)
+    per_size = mc_jobs(r, rng, lib, W, H, K)
     put_ms = prep_ms = avg_ms = 0.0
     kput = kprep = kavg = 0.0
     px_total = 0
     by_size = {"put_8tap": {}, "prep_8tap": {}, "mc_avg": {}}
     ctx.check(lib.r1c_profile(ctx.h, 1))
-    tmp1 = torch.empty(W * H, dtype=torch.int16, device="cuda")
-    tmp2 = torch.empty(W * H, dtype=torch.int16, device="cuda")
+    tmp1 = torch.empty(K * W * H, dtype=torch.int16, device="cuda")
+    tmp2 = torch.empty(K * W * H, dtype=torch.int16, device="cuda")
     for j in per_size:
         n = j.size
         area = int(j["w"][0]) * int(j["h"][0])
@@ -200,7 +208,7 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
                                    ("mc_avg", avg_ms, kavg, 6)):
         gbs = px_total * bpp / (ms / 1e3) / 1e9
         out["mc_4k10_" + name] = {
-            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, random fracs / filter pairs / +-32 px",
+            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, %d candidate MVs per block and launch (%.0f Mpx per launch), random fracs / filter pairs / +-32 px" % (K, K * W * H / 1e6),
             "value": px_total / 1e6 / (call_ms / 1e3), "unit": "Mpix/s", "ms": call_ms, "pixels": px_total,
             "kernel_ms": ms, "kernel_us_by_block_size": by_size[name], "note": "value / ms = whole _dev call (item count + prefix sum + kernel); "
                                      "roofline = the main kernel alone (19 launches, CUDA events inside the library)",
@@ -210,7 +218,7 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
             out["mc_4k10_" + name]["roofline"]["int_frac"] = px_total * 32 / (ms / 1e3) / 1e9 / ipeak
     gbs = px_total * 4 / (one_k / 1e3) / 1e9
     out["mc_4k10_put_8tap_one_launch"] = {
-        "workload": "the same 19 tilings as one mixed-size job list: one launch of 157 Mpx",
+        "workload": "the same 19 tilings as one mixed-size job list: one launch of %.0f Mpx" % (px_total / 1e6),
         "value": px_total / 1e6 / (one_ms / 1e3), "unit": "Mpix/s", "ms": one_ms, "pixels": px_total, "kernel_ms": one_k,
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm, "alg_bytes_per_px": 4,
                      "peak_source": hbm_how, "int_frac": px_total * 32 / (one_k / 1e3) / 1e9 / ipeak}}

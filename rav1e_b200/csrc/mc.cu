@@ -520,9 +520,9 @@ int launch_mc(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_
     R1C_LAUNCH_CHECK(ctx);
     ctx->mc_taps_ready = 1;
   }
-  {  // second generation: source windows staged by 2-D TMA (mc_tma.cu), enabled by R1C_MC_TMA=1
-    const char *v2 = getenv("R1C_MC_TMA");  // off until the tensor-load fault on the GPU box is understood
-    if (v2 && v2[0] == '1') {
+  {  // second generation: source windows staged by 2-D TMA (mc_tma.cu); R1C_MC_V1=1 keeps this file's kernel
+    const char *v1 = getenv("R1C_MC_V1");
+    if (!(v1 && v1[0] == '1')) {
       int handled = 0;
       const int rc2 = r1c_mc_tma_launch(ctx, kind, dst, d_tmp, src, d_jobs, n, bit_depth, &handled);
       if (rc2 || handled) return rc2;

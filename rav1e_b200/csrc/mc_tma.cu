@@ -7,13 +7,14 @@
 //
 //  * unit = one job, or one 32x32 tile of a larger job; units are binned by (width class, height class) into 16
 //    classes by two small kernels (count, scatter) -- no prefix sum over the job list;
-//  * per class ONE tensor map of the source plane with box = (tile_w + 7 rounded up to 16 bytes) x (tile_h + 7);
-//    a producer warp issues one cp.async.bulk.tensor.2d per unit (box origin = src - 3, any alignment, out-of-plane
+//  * per class ONE tensor map of the source plane with box = (tile_w + 7 + alignment slack, in 16-byte steps) x (tile_h + 7);
+//    a producer warp issues one cp.async.bulk.tensor.2d per unit (box origin = src - 3 floored to 16 bytes, out-of-plane
 //    parts arrive as zeros and only ever meet zero taps) into a two-stage shared-memory ring, completion on an
 //    mbarrier per stage; it also drops the unit's job record next to the pixels, so the compute warps read nothing
 //    from global memory;
-//  * compute: a thread owns a strip of 4 output columns and walks down the unit's rows.  Because the box starts at
-//    src - 3, pixel (x0 - 3) of strip x0 sits on a word boundary of the staged row: no funnel shifts.  Odd columns
+//  * compute: a thread owns a strip of 4 output columns and walks down the unit's rows.  The box starts at src - 3
+//    rounded down to 16 bytes (a hardware rule of tensor loads), so pixel (x0 - 3) of a strip sits at a known phase
+//    inside a word of the staged row: one PRMT (u16) / funnel shift (u8) per word realigns it.  Odd columns
 //    use byte-shifted copies of the packed s8 taps instead of re-packed pixels (u8: 2 / 3 / 3 / 3 DP4A for the four
 //    columns, u16: 4 / 5 / 4 / 5 DP2A), the horizontally filtered rows are kept as (even row, odd row) i16 pairs in
 //    a five-deep register ring and every pair of output rows costs 4 + 5 DP2A per column.
@@ -30,26 +31,33 @@
 
 namespace {
 
-constexpr int NCLS = 16;               // width class (w <= 4, 8, 16, 32) x height class (h <= 4, 8, 16, 32)
+constexpr int NCLS = 12;               // width class (w <= 4, 8, 16, 32) x height class (h <= 4, 8, 16)
+constexpr int NHC = 3;
 constexpr int CT = 128;                // compute threads per CTA
 constexpr int THREADS = CT + 32;       // + the producer warp
-constexpr int STAGE_BYTES = 51200;     // pixels of one stage (16 units of the largest box)
+constexpr int STAGE_BYTES = 36864;     // pixels of one stage (16 units of the largest box: 48 px x 24 rows of u16)
 constexpr int MAX_UPB = 128;           // units per batch, at most
 constexpr int REC_WORDS = 8;           // job record per unit: the 7 words of r1c_mc_job + (tile_x | tile_y << 8)
-constexpr int STAGES = 2;
+#ifndef MC_TMA_STAGES
+#define MC_TMA_STAGES 1
+#endif
+constexpr int STAGES = MC_TMA_STAGES;  // 1: the CTAs of an SM (4 resident) overlap each other's loads; 2: double buffer inside the CTA
 
 __host__ __device__ inline int wclass_of(int w) { return w <= 4 ? 0 : w <= 8 ? 1 : w <= 16 ? 2 : 3; }
-__host__ __device__ inline int hclass_of(int h) { return h <= 4 ? 0 : h <= 8 ? 1 : h <= 16 ? 2 : 3; }
+__host__ __device__ inline int hclass_of(int h) { return h <= 4 ? 0 : h <= 8 ? 1 : 2; }
 __host__ __device__ inline int strips_of(int wc) { return 1 << wc; }          // 4-column strips of a unit
 __host__ __device__ inline int tile_h_of(int hc) { return 4 << hc; }
-// staged row of a unit, in pixels: tile width + 7 rounded up to 16 bytes
+// staged row of a unit, in pixels.  The hardware wants the global address of a box row on a 16-byte boundary (a
+// tensor load whose inner coordinate * element size is not a multiple of 16 faults with "illegal instruction";
+// tools/tma_probe2.cu), so the box starts at (src_x - 3) rounded DOWN to 16 bytes and is up to 16 / pb - 1 pixels wider
+// than tile width + 7; rounded up to 16 bytes.
 __host__ __device__ inline int box_w_of(int wc, int pb) {
-  const int tw = wc == 0 ? 8 : (4 << wc);  // w <= 4 shares the 8-wide box (11 px need 16 / 32 bytes either way)
+  const int tw = wc == 0 ? 8 : (4 << wc);  // w <= 4 shares the 8-wide box
   const int px16 = 16 / pb;
-  return (tw + 7 + px16 - 1) / px16 * px16;
+  return (tw + 7 + (px16 - 1) + px16 - 1) / px16 * px16;
 }
 __host__ __device__ inline int box_h_of(int hc) { return tile_h_of(hc) + 7; }
-// + one row: the last (even, odd) pair of a strip may read one row past the box (it meets a zero tap)
+// + one row: the last (even, odd) pair of a strip reads one row past the box (it meets a zero tap)
 __host__ __device__ inline int slot_bytes_of(int wc, int hc, int pb) {
   return (box_w_of(wc, pb) * pb * (box_h_of(hc) + 1) + 127) & ~127;
 }
@@ -59,14 +67,14 @@ __host__ __device__ inline int upb_of(int wc, int hc, int pb) {
 }
 
 struct TmaArgs {
-  alignas(64) CUtensorMap map[12];  // [box width class 0..2][height class 0..3]
+  alignas(64) CUtensorMap map[9];   // [box width class 0..2][height class 0..2]
   PlaneView src;
   uint8_t *dst0;
   int dst_stride;
   int16_t *tmp;
   const r1c_mc_job *jobs;
-  const uint32_t *units;       // unit list, class-major: job index | tile << 27
-  const uint32_t *cls_count;   // [16] units per class (written by the count kernel)
+  const uint32_t *units;       // unit list, class-major: job index | tile << 26
+  const uint32_t *cls_count;   // [12] units per class (written by the count kernel)
   long long n;
   int bit_depth;
 };
@@ -74,10 +82,10 @@ struct TmaArgs {
 // ---- binning ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void unit_shape(const r1c_mc_job &j, int &cls, int &tiles_x, int &nunits) {
   tiles_x = (j.w + 31) >> 5;
-  const int tiles_y = (j.h + 31) >> 5;
-  nunits = tiles_x * tiles_y;
-  const int w = j.w > 32 ? 32 : j.w, h = j.h > 32 ? 32 : j.h;  // edge tiles of large jobs may be smaller: same class, fewer live strips / rows
-  cls = wclass_of(w) * 4 + hclass_of(h);
+  const int tiles_y = (j.h + 15) >> 4;
+  nunits = tiles_x * tiles_y;  // <= 4 x 8
+  const int w = j.w > 32 ? 32 : j.w, h = j.h > 16 ? 16 : j.h;  // edge tiles of large jobs may be smaller: same class, fewer live strips / rows
+  cls = wclass_of(w) * NHC + hclass_of(h);
 }
 
 // pass 1: units per class.  cursor[0..15] = counts, then (pass 2) running offsets
@@ -98,7 +106,7 @@ __global__ void mc_count_kernel(const r1c_mc_job *jobs, long long n, uint32_t *c
   if (threadIdx.x < NCLS && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], s_cnt[threadIdx.x]);
 }
 
-// pass 2: scatter (job, tile) into the class-major unit list.  counts[16..31] = cursors (zeroed by the host memset)
+// pass 2: scatter (job, tile) into the class-major unit list.  counts[NCLS ..] = cursors (zeroed by the host memset)
 __global__ void mc_scatter_kernel(const r1c_mc_job *jobs, long long n, uint32_t *counts, uint32_t *units) {
   __shared__ uint32_t s_cnt[NCLS], s_base[NCLS];
   if (threadIdx.x < NCLS) s_cnt[threadIdx.x] = 0;
@@ -120,7 +128,7 @@ __global__ void mc_scatter_kernel(const r1c_mc_job *jobs, long long n, uint32_t 
     s_base[threadIdx.x] = start + (s_cnt[threadIdx.x] ? atomicAdd(&counts[NCLS + threadIdx.x], s_cnt[threadIdx.x]) : 0u);
   }
   __syncthreads();
-  for (int u = 0; u < nu; u++) units[s_base[cls] + local + u] = (uint32_t)i | ((uint32_t)u << 27);
+  for (int u = 0; u < nu; u++) units[s_base[cls] + local + u] = (uint32_t)i | ((uint32_t)u << 26);
 }
 
 // ---- PTX helpers -------------------------------------------------------------------------------------------------
@@ -141,6 +149,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *b, uint32_t parity) {
       "MCT_WAIT:\n"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
       "@p bra MCT_DONE;\n"
+      "nanosleep.u32 40;\n"  // the spin loops of waiting warps cost issue slots of the working ones
       "bra MCT_WAIT;\n"
       "MCT_DONE:\n"
       "}" ::"r"(s32(b)),
@@ -197,21 +206,24 @@ struct Taps {
   }
 };
 
-// horizontal sums of the 4 columns of a strip from the staged row (word-aligned at pixel x0 - 3)
+// horizontal sums of the 4 columns of a strip from the staged row; `row` = the aligned word holding pixel x0 - 3,
+// `phase` = its position inside that word (u8: shift in bits, u16: PRMT selector)
 template <int PB>
-__device__ __forceinline__ void hsum4(const uint32_t *row, const Taps &t, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t d0,
-                                      uint32_t d1, uint32_t d2, int rnd, int (&s)[4]) {
+__device__ __forceinline__ void hsum4(const uint32_t *row, uint32_t phase, const Taps &t, uint32_t c0, uint32_t c1, uint32_t c2,
+                                      uint32_t d0, uint32_t d1, uint32_t d2, int rnd, int (&s)[4]) {
   if (PB == 1) {
-    // bytes x0-3 .. x0+7 = words 0..2; column c needs bytes c .. c+7
-    const uint32_t w0 = row[0], w1 = row[1], w2 = row[2];
+    // bytes x0-3 .. x0+7 = words 0..2 after the funnel shift; column c needs bytes c .. c+7
+    const uint32_t r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
+    const uint32_t w0 = __funnelshift_r(r0, r1, phase), w1 = __funnelshift_r(r1, r2, phase), w2 = __funnelshift_r(r2, r3, phase);
     s[0] = dp4a_us(w1, t.a1, dp4a_us(w0, t.a0, rnd));
     s[1] = dp4a_us(w2, t.b2, dp4a_us(w1, t.b1, dp4a_us(w0, t.b0, rnd)));
     s[2] = dp4a_us(w2, c2, dp4a_us(w1, c1, dp4a_us(w0, c0, rnd)));
     s[3] = dp4a_us(w2, d2, dp4a_us(w1, d1, dp4a_us(w0, d0, rnd)));
   } else {
-    // pixels x0-3 .. x0+7 = halves of words 0..5; column c needs pixels c .. c+7
-    const uint2 p01 = *(const uint2 *)row, p23 = *(const uint2 *)(row + 2), p45 = *(const uint2 *)(row + 4);
-    const uint32_t e0 = p01.x, e1 = p01.y, e2 = p23.x, e3 = p23.y, e4 = p45.x, e5 = p45.y;
+    // pixels x0-3 .. x0+7 = halves of words 0..5 after the PRMT; column c needs pixels c .. c+7
+    const uint32_t r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3], r4 = row[4], r5 = row[5], r6 = row[6];
+    const uint32_t e0 = __byte_perm(r0, r1, phase), e1 = __byte_perm(r1, r2, phase), e2 = __byte_perm(r2, r3, phase),
+                   e3 = __byte_perm(r3, r4, phase), e4 = __byte_perm(r4, r5, phase), e5 = __byte_perm(r5, r6, phase);
     s[0] = dp2a_hi_us(e3, t.a1, dp2a_lo_us(e2, t.a1, dp2a_hi_us(e1, t.a0, dp2a_lo_us(e0, t.a0, rnd))));
     s[1] = dp2a_lo_us(e4, t.b2, dp2a_hi_us(e3, t.b1, dp2a_lo_us(e2, t.b1, dp2a_hi_us(e1, t.b0, dp2a_lo_us(e0, t.b0, rnd)))));
     s[2] = dp2a_hi_us(e4, t.a1, dp2a_lo_us(e3, t.a1, dp2a_hi_us(e2, t.a0, dp2a_lo_us(e1, t.a0, rnd))));
@@ -245,7 +257,7 @@ __device__ __forceinline__ void store_row(uint8_t *dp, bool vec, int ncols, cons
 // KIND 0 = put (clamped pixels into the dst plane), 1 = prep (i16, dense w*h at tmp_off), 2 = put into a dense w*h
 // pixel block at tmp_off (sub-pel search)
 template <int PB, int KIND>
-__global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constant__ TmaArgs a) {
+__global__ void __launch_bounds__(THREADS, STAGES == 1 ? 5 : 2) mc_tma_kernel(const __grid_constant__ TmaArgs a) {
   extern __shared__ __align__(1024) unsigned char smem[];
   // [stage pixels x 2][records x 2][mbarriers full x 2, empty x 2]
   unsigned char *s_px = smem;
@@ -266,51 +278,113 @@ __global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constan
   const int maxv = (1 << a.bit_depth) - 1;
 
   // the same batch sequence in the producer and the consumers: classes in order, batches b = blockIdx.x, + gridDim.x ...
-  uint32_t it = 0;  // batches of this CTA so far: stage = it & 1, phase = (it >> 1) & 1
-  uint32_t cls_start = 0;
-  for (int cls = 0; cls < NCLS; cls++) {
-    const uint32_t cnt = __ldg(&a.cls_count[cls]);
-    if (cnt == 0) continue;
-    const int wc = cls >> 2, hc = cls & 3;
-    const int upb = upb_of(wc, hc, PB);
-    const int slot = slot_bytes_of(wc, hc, PB);
-    const int pitch = box_w_of(wc, PB) * PB;  // bytes per staged row
-    const uint32_t nbatch = (cnt + upb - 1) / upb;
-    if (warp == CT / 32) {
-      // ================= producer warp =================
-      const CUtensorMap *map = &a.map[(wc == 0 ? 0 : wc - 1) * 4 + hc];
-      for (uint32_t b = blockIdx.x; b < nbatch; b += gridDim.x, it++) {
-        const int st = it & 1;
-        if (it >= STAGES) mbar_wait(&s_empty[st], ((it >> 1) - 1) & 1);
-        const uint32_t u0 = b * upb, nu = min((uint32_t)upb, cnt - u0);
-        if (lane == 0) mbar_expect_tx(&s_full[st], nu * (uint32_t)(box_w_of(wc, PB) * PB * box_h_of(hc)));
-        for (uint32_t u = lane; u < nu; u += 32) {
-          const uint32_t e = __ldg(&a.units[cls_start + u0 + u]);
-          const uint32_t ji = e & 0x7ffffffu, tile = e >> 27;
-          const uint32_t *jw = (const uint32_t *)(a.jobs + ji);
-          uint32_t *rec = s_rec + (st * MAX_UPB + u) * REC_WORDS;
-          uint32_t w[7];
+  struct Cursor {
+    int cls;
+    uint32_t b, start, cnt, nbatch;
+    int wc, hc, upb;
+    __device__ __forceinline__ void next_class(const TmaArgs &a) {
+      for (;;) {
+        start += cnt;
+        cls++;
+        if (cls >= NCLS) {
+          cnt = 0;
+          return;
+        }
+        cnt = __ldg(&a.cls_count[cls]);
+        if (cnt == 0) continue;
+        wc = cls / NHC;
+        hc = cls - wc * NHC;
+        upb = upb_of(wc, hc, PB);
+        nbatch = (cnt + upb - 1) / upb;
+        if (blockIdx.x < nbatch) {
+          b = blockIdx.x;
+          return;
+        }
+      }
+    }
+    __device__ __forceinline__ void init(const TmaArgs &a) {
+      cls = -1;
+      start = cnt = 0;
+      next_class(a);
+    }
+    __device__ __forceinline__ void advance(const TmaArgs &a) {
+      b += gridDim.x;
+      if (b >= nbatch) next_class(a);
+    }
+    __device__ __forceinline__ bool done() const { return cls >= NCLS; }
+  };
+  Cursor cur;
+  cur.init(a);
+  uint32_t it = 0;  // batches of this CTA so far: stage = it % STAGES, phase = (it / STAGES) & 1
+  if (warp == CT / 32) {
+    // ================= producer warp =================
+    // The unit and job records of a batch are fetched one batch ahead (while the compute warps work on the previous
+    // one), so that only the tensor loads themselves lie between "stage free" and "stage full".
+    constexpr int UPL = MAX_UPB / 32;  // units per lane
+    uint32_t pw[UPL][7];  // [0] = tile index, [1..6] = words 1..6 of r1c_mc_job
+    uint32_t pdx[UPL];
+    auto fetch = [&](const Cursor &c) {
+      const uint32_t u0 = c.b * c.upb, nu = min((uint32_t)c.upb, c.cnt - u0);
 #pragma unroll
-          for (int k = 0; k < 7; k++) w[k] = __ldg(jw + k);
-          const int jwid = (int)(int16_t)(w[4] & 0xffffu);
+      for (int k = 0; k < UPL; k++) {
+        const uint32_t u = lane + 32 * k;
+        if (u < nu) {
+          const uint32_t e = __ldg(&a.units[c.start + u0 + u]);
+          const uint32_t *jw = (const uint32_t *)(a.jobs + (e & 0x3ffffffu));
+          pdx[k] = __ldg(jw);
+#pragma unroll
+          for (int i = 1; i < 7; i++) pw[k][i] = __ldg(jw + i);
+          pw[k][0] = e >> 26;
+        }
+      }
+    };
+    if (!cur.done()) fetch(cur);
+    while (!cur.done()) {
+      const int st = it % STAGES;
+      const int wc = cur.wc, hc = cur.hc;
+      const int slot = slot_bytes_of(wc, hc, PB);
+      const CUtensorMap *map = &a.map[(wc == 0 ? 0 : wc - 1) * NHC + hc];
+      if (it >= STAGES) mbar_wait(&s_empty[st], ((it / STAGES) - 1) & 1);
+      const uint32_t u0 = cur.b * cur.upb, nu = min((uint32_t)cur.upb, cur.cnt - u0);
+      if (lane == 0) mbar_expect_tx(&s_full[st], nu * (uint32_t)(box_w_of(wc, PB) * PB * box_h_of(hc)));
+#pragma unroll
+      for (int k = 0; k < UPL; k++) {
+        const uint32_t u = lane + 32 * k;
+        if (u < nu) {
+          uint32_t *rec = s_rec + (st * MAX_UPB + u) * REC_WORDS;
+          const uint32_t tile = pw[k][0];
+          const int jwid = (int)(int16_t)(pw[k][4] & 0xffffu);
           const int tiles_x = (jwid + 31) >> 5;
           const int ty = tile / tiles_x, tx = tile - ty * tiles_x;
+          rec[0] = pdx[k];
 #pragma unroll
-          for (int k = 0; k < 7; k++) rec[k] = w[k];
-          rec[7] = (uint32_t)tx | ((uint32_t)ty << 8);
-          const int x = a.src.xorigin + (int)w[2] + 32 * tx - 3, y = a.src.yorigin + (int)w[3] + 32 * ty - 3;
-          tma_load_2d(s_px + st * STAGE_BYTES + u * slot, map, x, y, &s_full[st]);
+          for (int i = 1; i < 7; i++) rec[i] = pw[k][i];
+          const int x = a.src.xorigin + (int)pw[k][2] + 32 * tx - 3, y = a.src.yorigin + (int)pw[k][3] + 16 * ty - 3;
+          const int x_al = x & ~(16 / PB - 1);  // floor to 16 bytes (two's complement: also for negative x)
+          rec[7] = (uint32_t)tx | ((uint32_t)ty << 8) | ((uint32_t)(x - x_al) << 16);
+          tma_load_2d(s_px + st * STAGE_BYTES + u * slot, map, x_al, y, &s_full[st]);
         }
-        mbar_arrive(&s_full[st]);  // release: after this lane's record stores
       }
-    } else {
+      mbar_arrive(&s_full[st]);  // release: after this lane's record stores
+      cur.advance(a);
+      if (!cur.done()) fetch(cur);
+      it++;
+    }
+  } else {
+    while (!cur.done()) {
+      const int wc = cur.wc, hc = cur.hc;
+      const int upb = cur.upb;
+      const int slot = slot_bytes_of(wc, hc, PB);
+      const int pitch = box_w_of(wc, PB) * PB;  // bytes per staged row
+      const uint32_t cnt = cur.cnt;
+      {
       // ================= compute warps =================
       const int strips = strips_of(wc);
       const int un = tid >> wc, strip = tid & (strips - 1);
-      for (uint32_t b = blockIdx.x; b < nbatch; b += gridDim.x, it++) {
-        const int st = it & 1;
-        const uint32_t u0 = b * upb, nu = min((uint32_t)upb, cnt - u0);
-        mbar_wait(&s_full[st], (it >> 1) & 1);
+      {
+        const int st = it % STAGES;
+        const uint32_t u0 = cur.b * upb, nu = min((uint32_t)upb, cnt - u0);
+        mbar_wait(&s_full[st], (it / STAGES) & 1);
         if ((uint32_t)un < nu) {
           const uint32_t *rec = s_rec + (st * MAX_UPB + un) * REC_WORDS;
           const int dst_x = (int)rec[0], dst_y = (int)rec[1];
@@ -318,10 +392,10 @@ __global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constan
           const int col_frac = (int)(int8_t)(rec[5] & 0xff), row_frac = (int)(int8_t)((rec[5] >> 8) & 0xff);
           const int mode_x = (int)(int8_t)((rec[5] >> 16) & 0xff), mode_y = (int)(int8_t)(rec[5] >> 24);
           const long long tmp_off = (long long)(int)rec[6];
-          const int tx = (int)(rec[7] & 0xff), ty = (int)(rec[7] >> 8);
+          const int tx = (int)(rec[7] & 0xff), ty = (int)((rec[7] >> 8) & 0xff), dx = (int)(rec[7] >> 16);
           const int x0 = 32 * tx + 4 * strip;          // first column of the strip inside the job
           const int ncols = min(4, jw - x0);
-          const int r0 = 32 * ty, nout = min(jh - r0, tile_h_of(hc));
+          const int r0 = 16 * ty, nout = min(jh - r0, tile_h_of(hc));
           if (ncols > 0 && nout > 0) {
             Taps hx, vy;
             {
@@ -335,7 +409,11 @@ __global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constan
             const int hsh = 6 - ib, hrnd = 1 << (5 - ib);
             const int vshift = (KIND == 1 ? 7 : 7 + ib) - 1, vrnd = 1 << (vshift - 1);
             const uint32_t mx = (uint32_t)maxv * 0x10001u;
-            const unsigned char *rowp = s_px + st * STAGE_BYTES + un * slot + strip * 4 * PB;
+            // pixel (x0 - 3) of the strip sits dx + 4 * strip pixels into the staged row: word-aligned base + a phase of
+            // 0 / 1 pixel (u16) or 0..3 bytes (u8), undone per row by one PRMT / funnel shift per word
+            const int boff = (dx + 4 * strip) * PB;
+            const uint32_t phase = PB == 1 ? (uint32_t)(boff & 3) * 8u : ((boff & 2) ? 0x5432u : 0x3210u);
+            const unsigned char *rowp = s_px + st * STAGE_BYTES + un * slot + (boff & ~3);
             uint8_t *dp;
             long long dstride;
             constexpr int OB = KIND == 1 ? 2 : PB;  // bytes per output element
@@ -347,50 +425,62 @@ __global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constan
               dstride = (long long)jw * OB;
             }
             const bool vec = ncols == 4 && (((uintptr_t)dp | (uintptr_t)dstride) & (uintptr_t)(4 * OB - 1)) == 0;
-            // rows in (even, odd) pairs: pair p = filtered rows 2p, 2p + 1 (row i of the box = source row r0 - 3 + i).
-            // Output row y needs rows y .. y + 7: y = 2p - 6 from pairs p-3 .. p, y = 2p - 7 from pairs p-4 .. p with the
-            // taps shifted by one.
+            // Filtered rows in (even, odd) pairs: pair p = rows 2p, 2p + 1 of the box (row i = source row r0 - 3 + i).
+            // Output rows 2q and 2q + 1 need filtered rows 2q .. 2q + 8 = pairs q .. q + 4: the even one with the taps as
+            // they are on pairs q .. q + 3, the odd one with the taps shifted by one row on pairs q .. q + 4.
             uint32_t ring[4][5];
-            const int npairs = (nout + 8) >> 1;
-            for (int p0 = 0; p0 < npairs; p0 += 5) {
+            auto hpair = [&](int slot_) {
+              int se[4], so[4];
+              hsum4<PB>((const uint32_t *)rowp, phase, hx, c0, c1, c2, d0, d1, d2, hrnd, se);
+              hsum4<PB>((const uint32_t *)(rowp + pitch), phase, hx, c0, c1, c2, d0, d1, d2, hrnd, so);
+              rowp += 2 * pitch;
 #pragma unroll
-              for (int u = 0; u < 5; u++) {
-                const int p = p0 + u;
-                if (p < npairs) {
-                  int se[4], so[4];
-                  hsum4<PB>((const uint32_t *)rowp, hx, c0, c1, c2, d0, d1, d2, hrnd, se);
-                  hsum4<PB>((const uint32_t *)(rowp + pitch), hx, c0, c1, c2, d0, d1, d2, hrnd, so);
-                  rowp += 2 * pitch;
+              for (int c = 0; c < 4; c++) ring[c][slot_] = __byte_perm((uint32_t)(se[c] >> hsh), (uint32_t)(so[c] >> hsh), 0x5410);
+            };
+            hpair(0);
+            hpair(1);
+            hpair(2);
+            hpair(3);
+            auto vpair = [&](int u, bool both) {  // output rows 2q, 2q + 1 from ring slots u .. u + 4 (mod 5)
+              int v[4];
 #pragma unroll
-                  for (int c = 0; c < 4; c++) ring[c][u] = __byte_perm((uint32_t)(se[c] >> hsh), (uint32_t)(so[c] >> hsh), 0x5410);
-                  const int y1 = 2 * p - 7;
-                  if (y1 >= 0) {  // pairs p-4 .. p, taps (0 t0)(t1 t2)(t3 t4)(t5 t6)(t7 0)
-                    int v[4];
+              for (int c = 0; c < 4; c++) {
+                int t = dp2a_lo_ss(ring[c][u], vy.a0, vrnd);
+                t = dp2a_hi_ss(ring[c][(u + 1) % 5], vy.a0, t);
+                t = dp2a_lo_ss(ring[c][(u + 2) % 5], vy.a1, t);
+                t = dp2a_hi_ss(ring[c][(u + 3) % 5], vy.a1, t);
+                v[c] = t >> vshift;
+              }
+              store_row<PB, KIND>(dp, vec, ncols, v, mx);
+              if (both) {
 #pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                      int t = dp2a_lo_ss(ring[c][(u + 1) % 5], vy.b0, vrnd);
-                      t = dp2a_hi_ss(ring[c][(u + 2) % 5], vy.b0, t);
-                      t = dp2a_lo_ss(ring[c][(u + 3) % 5], vy.b1, t);
-                      t = dp2a_hi_ss(ring[c][(u + 4) % 5], vy.b1, t);
-                      t = dp2a_lo_ss(ring[c][u], vy.b2, t);
-                      v[c] = t >> vshift;
-                    }
-                    store_row<PB, KIND>(dp, vec, ncols, v, mx);
-                    dp += dstride;
-                  }
-                  const int y0 = 2 * p - 6;
-                  if (y0 >= 0 && y0 < nout) {  // pairs p-3 .. p
-                    int v[4];
+                for (int c = 0; c < 4; c++) {
+                  int t = dp2a_lo_ss(ring[c][u], vy.b0, vrnd);
+                  t = dp2a_hi_ss(ring[c][(u + 1) % 5], vy.b0, t);
+                  t = dp2a_lo_ss(ring[c][(u + 2) % 5], vy.b1, t);
+                  t = dp2a_hi_ss(ring[c][(u + 3) % 5], vy.b1, t);
+                  t = dp2a_lo_ss(ring[c][(u + 4) % 5], vy.b2, t);
+                  v[c] = t >> vshift;
+                }
+                store_row<PB, KIND>(dp + dstride, vec, ncols, v, mx);
+              }
+              dp += 2 * dstride;
+            };
+            if (nout == 16) {  // the common unit: a full-height tile, no per-row predicates
 #pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                      int t = dp2a_lo_ss(ring[c][(u + 2) % 5], vy.a0, vrnd);
-                      t = dp2a_hi_ss(ring[c][(u + 3) % 5], vy.a0, t);
-                      t = dp2a_lo_ss(ring[c][(u + 4) % 5], vy.a1, t);
-                      t = dp2a_hi_ss(ring[c][u], vy.a1, t);
-                      v[c] = t >> vshift;
-                    }
-                    store_row<PB, KIND>(dp, vec, ncols, v, mx);
-                    dp += dstride;
+              for (int q = 0; q < 8; q++) {
+                hpair((q + 4) % 5);
+                vpair(q % 5, true);
+              }
+            } else {
+              const int nq = (nout + 1) >> 1;
+              for (int q0 = 0; q0 < nq; q0 += 5) {
+#pragma unroll
+                for (int u = 0; u < 5; u++) {
+                  const int q = q0 + u;
+                  if (q < nq) {
+                    hpair((u + 4) % 5);
+                    vpair(u, 2 * q + 1 < nout);
                   }
                 }
               }
@@ -400,8 +490,10 @@ __global__ void __launch_bounds__(THREADS, 2) mc_tma_kernel(const __grid_constan
         __syncwarp();
         if (lane == 0) mbar_arrive(&s_empty[st]);
       }
+      }
+      cur.advance(a);
+      it++;
     }
-    cls_start += cnt;
   }
 }
 
@@ -417,7 +509,7 @@ struct MapCacheEntry {
   const void *data;
   int64_t stride, alloc_h;
   int pb, device;
-  CUtensorMap map[12];
+  CUtensorMap map[9];
 };
 constexpr int MAP_CACHE = 16;
 MapCacheEntry g_cache[MAP_CACHE];
@@ -455,9 +547,9 @@ bool get_maps(const r1c_plane *src, int device, CUtensorMap *out) {
   const cuuint64_t strides[1] = {(cuuint64_t)e.stride * (cuuint64_t)e.pb};
   const cuuint32_t estr[2] = {1, 1};
   for (int wc = 1; wc < 4; wc++)
-    for (int hc = 0; hc < 4; hc++) {
+    for (int hc = 0; hc < NHC; hc++) {
       const cuuint32_t box[2] = {(cuuint32_t)box_w_of(wc, e.pb), (cuuint32_t)box_h_of(hc)};
-      const CUresult r = g_encode(&e.map[(wc - 1) * 4 + hc], e.pb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+      const CUresult r = g_encode(&e.map[(wc - 1) * NHC + hc], e.pb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
                                   const_cast<void *>(e.data), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       if (r != CUDA_SUCCESS) return false;
@@ -487,16 +579,16 @@ int launch_kernel(r1c_ctx *ctx, const TmaArgs &a) {
 int r1c_mc_tma_launch(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, const r1c_plane *src, const r1c_mc_job *d_jobs,
                       int64_t n, int bit_depth, int *handled) {
   *handled = 0;
-  if (((src->cfg.stride * src->px_bytes) & 15) != 0 || ((uintptr_t)src->d_data & 15) != 0 || n >= (1ll << 27)) return R1C_OK;
+  if (((src->cfg.stride * src->px_bytes) & 15) != 0 || ((uintptr_t)src->d_data & 15) != 0 || n >= (1ll << 26)) return R1C_OK;
   TmaArgs a;
   if (!get_maps(src, ctx->device, a.map)) return R1C_OK;
   *handled = 1;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  // unit list: one entry per job, plus one per extra 32x32 tile of the jobs larger than that (at most 16 per job)
+  // unit list: one entry per job, plus one per extra 32x16 tile of the jobs larger than that (at most 32 per job)
   void *d_counts, *d_units;
   int rc;
   if ((rc = r1c_scratch_dev(ctx, 2, 2 * NCLS * sizeof(uint32_t), &d_counts))) return rc;
-  if ((rc = r1c_scratch_dev(ctx, 3, (size_t)n * 16 * sizeof(uint32_t), &d_units))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 3, (size_t)n * 32 * sizeof(uint32_t), &d_units))) return rc;
   R1C_CUDA(ctx, cudaMemsetAsync(d_counts, 0, 2 * NCLS * sizeof(uint32_t), ctx->stream));
   const unsigned nb = (unsigned)((n + 255) / 256);
   mc_count_kernel<<<nb, 256, 0, ctx->stream>>>(d_jobs, n, (uint32_t *)d_counts);

@@ -94,6 +94,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 int main(int argc, char **argv) {
   const int flags = argc > 1 ? atoi(argv[1]) : 0;
+  const int X = argc > 2 ? atoi(argv[2]) : 32;
   const int W = 4096, H = 256;
   uint16_t *h = (uint16_t *)malloc(W * H * 2), *d, *out;
   for (int i = 0; i < W * H; i++) h[i] = (uint16_t)((i / W) * 100 + (i % W) % 100);
@@ -112,11 +113,11 @@ int main(int argc, char **argv) {
   if (flags & 2) { ArgsB b; b.map[0] = map; b.map[1] = map; b.out = out; b.x = 32; b.y = 5; b.bytes = 512; b.flags = flags; probeB<<<1, 128>>>(b); }
   else if (flags & 4) { cudaFuncSetAttribute(probeC, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384); probeC<<<1, 128, 16384>>>(map, out, 32, 5, 512, flags); }
   else if (flags & 16) probeD<<<1, (flags & 8) ? 160 : 128>>>(map, out, 32, 5, 512, flags);
-  else probe<<<1, (flags & 8) ? 160 : 128>>>(map, out, 32, 5, 512, flags);
+  else probe<<<1, (flags & 8) ? 160 : 128>>>(map, out, X, 5, 512, flags);
   cudaError_t e = cudaDeviceSynchronize();
   printf("sync: %s\n", cudaGetErrorString(e));
   uint16_t res[256];
   cudaMemcpy(res, out, 512, cudaMemcpyDeviceToHost);
-  printf("row0: %d %d %d ; row1: %d %d (want 532 533 534 ; 632 633)\n", res[0], res[1], res[2], res[16], res[17]);
+  printf("x=%d row0: %d %d %d ; row1: %d %d (want %d.. ; %d..)\n", X, res[0], res[1], res[2], res[16], res[17], 500 + X % 100, 600 + X % 100);
   return 0;
 }
