@@ -114,6 +114,16 @@ int64_t r1c_launch_count(const r1c_ctx *ctx);
 #define R1C_PROF_QUANT 6      /* quantize / dequantize kernels                */
 #define R1C_PROF_ITX 7        /* inverse transform + add kernels              */
 #define R1C_PROF_SLOTS 8
+/* Diagnostics: measured rate of one integer instruction class on this context's device, in giga lane-operations per
+ * second (dependency-free streams on every SM; a few milliseconds).  The INT roofline denominator bench.py reports
+ * against (a measured peak, not the nominal one).  No counterpart in the reference. */
+#define R1C_PEAK_IADD 0       /* IADD3: the scalar 32-bit lane rate */
+#define R1C_PEAK_VABSDIFF4 1  /* VABSDIFF4 with accumulate: 8 byte-ops per lane-op */
+#define R1C_PEAK_DP4A 2
+#define R1C_PEAK_DP2A 3
+#define R1C_PEAK_IMAD 4
+#define R1C_PEAK_PRMT 5
+int r1c_int_peak(r1c_ctx *ctx, int which, double *giga_lane_ops_per_s);
 int r1c_profile(r1c_ctx *ctx, int enable);
 int r1c_profile_read(r1c_ctx *ctx, int slot, double *ms, int64_t *launches);
 

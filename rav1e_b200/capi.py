@@ -211,6 +211,7 @@ SIGNATURES = {
     "r1c_frame_me": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
     "r1c_frame_me_dev": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
     "r1c_plane_upload_async": (_i, [_vp, _vp, _vp]),
+    "r1c_int_peak": (_i, [_vp, _i, _P(C.c_double)]),
     "r1c_profile": (_i, [_vp, _i]),
     "r1c_profile_read": (_i, [_vp, _i, _P(C.c_double), _P(_i64)]),
 }
