@@ -4,8 +4,9 @@
 Headline workload (BASELINE.json configs[1]): 1080p 8-bit full-search motion
 estimation, +-64 px, every block of all 19 sizes 4x4..64x64, SAD search then the
 SATD re-evaluation + telescopic sub-pel tail of MotionEstimation::motion_estimation
-(src/me.rs:193-271).  A "step" is one frame pair (cur, ref) -> every block's
-(best_mv, lowest_cost).  Metric: Mpix/s = frame pixels / time.
+(src/me.rs:193-271).  A "step" is one lookahead window of 32 distinct frame pairs
+(cur, ref) -> every block's (best_mv, lowest_cost), 3 kernel launches per pair.
+Metric: Mpix/s = frame pixels / time.
 
     python bench.py [--gpus N] [--steps K] [--warmup W]      # the CUDA path
     python bench.py --impl reference ...                     # CPU arm: the oracle
@@ -14,7 +15,9 @@ SATD re-evaluation + telescopic sub-pel tail of MotionEstimation::motion_estimat
 
 N > 1 (torchrun): frames are sharded over ranks (lookahead motion search is
 independent per frame) -- no collective on the data path; the time
-is the max over ranks, value = N frames' pixels / time ("weak").
+is the max over ranks, value = N windows' pixels / time ("weak").  Every N also
+reports the within-frame split (bench_scaling.py): one 4K 10-bit frame pair by
+superblock rows ("strong_4k10_me"), MC by tile column and forward TX split evenly.
 
 Only the `cpu_baseline` leg and `--impl reference` touch oracle/; the timed CUDA
 path is librav1e_cuda.so through its C ABI (rav1e_b200.capi).
@@ -30,6 +33,7 @@ import time
 import numpy as np
 
 import bench_kernels
+import bench_scaling
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -40,8 +44,27 @@ RANGE = 64
 LAMBDA = 160  # (me_lambda * 256 * 0.5) as u32 at a mid-range quantizer
 LUMA_PAD = 88  # src/frame/mod.rs:23,60
 WORKLOAD = "me_1080p_8bit_fullsearch_pm64_19sizes_sad_then_satd_subpel"
-ALG_INT_OPS = 2.0 * W * H * (2 * RANGE + 1) ** 2  # SURVEY 8(d) cfg 1: abs-diff + add per (pixel, candidate)
-ALG_HBM_BYTES_SB = None  # filled once the plane geometry is known
+# A step = the frame pairs of one lookahead window: 32 distinct 1080p pairs (170 MB of planes, more than the 126 MB L2),
+# so that the driver's 20 steps time seconds, not milliseconds, of back-to-back work.
+FRAMES_PER_STEP = 32
+# the same dict in both arms (the driver compares them)
+CONFIG = {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE, "lambda": LAMBDA,
+          "frames_per_step": FRAMES_PER_STEP,
+          "l2": "inputs larger than L2 (32 distinct frame pairs = 170 MB per step) and L2 flushed between steps",
+          "sharding": "one lookahead window of frame pairs per GPU, no collective"}
+
+
+def clipped_int_ops():
+    """SURVEY 8(d) cfg 1 counts one abs-diff + one add per (pixel, candidate) of the 4x4 base layer; candidates that
+    get_mv_range (src/me.rs:64-80) forbids for a 4x4 block at that position are not searched and not counted:
+    dx in [max(-R, -(x + 20)), min(R, W - x - 4 + 20)], likewise dy."""
+    xs, ys = np.arange(0, W, 4), np.arange(0, H, 4)
+    nx = np.minimum(RANGE, W - xs - 4 + 20) - np.maximum(-RANGE, -(xs + 20)) + 1
+    ny = np.minimum(RANGE, H - ys - 4 + 20) - np.maximum(-RANGE, -(ys + 20)) + 1
+    return 2.0 * 16.0 * float(nx.sum()) * float(ny.sum())
+
+
+ALG_INT_OPS = clipped_int_ops()
 
 
 # ----------------------------------------------------------------- synthetic frames --
@@ -168,6 +191,11 @@ def run_cpu(seconds_target, steps=1, warmup=0):
     return mpix / dt, cores, sample, dt * 1e3
 
 
+CPU_NOTE = ("C restatement of the reference's _ref functions, OpenMP over blocks; the u8 SAD inner loop is psadbw "
+            "(_mm256_sad_epu8 / _mm_sad_epu8), the instruction the reference's AVX2 asm is built on, SATD / MC / search "
+            "control are scalar; the reference's own Rust/NASM build is unavailable on this box (no rustc/cargo/nasm)")
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -177,24 +205,24 @@ def reference_arm(args):
         "impl": "reference", "metric": "Mpix/s", "value": v, "unit": "Mpix/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE,
-                   "lambda": LAMBDA},
-        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample,
-                         "note": "C restatement of the reference's scalar _ref functions; the reference's "
-                                 "own Rust/NASM build is unavailable on this box (no rustc/cargo/nasm)"},
+        "config": dict(CONFIG),
+        "cpu_baseline": {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample, "note": CPU_NOTE},
         "e2e": {"value": v, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
 
 
 # -------------------------------------------------------------------- CUDA arm --
-def int_peak():
-    p = os.path.join(ROOT, "profiles", "int_peaks_r01.json")
-    try:
-        d = json.load(open(p))
-        return float(d["iadd"]), "measured (tools/int_peak.cu on B200: independent IADD3 stream, G lane-ops/s)", d
-    except Exception:
-        return 148 * 128 * 1.965, "fallback (148 SM x 128 lanes x 1.965 GHz)", {}
+def int_peak(ctx):
+    """INT roofline denominators measured in this run on this device (r1c_int_peak: dependency-free streams of one
+    instruction on every SM), G lane-ops/s"""
+    names = (("iadd", 0), ("vabsdiff4_acc", 1), ("dp4a", 2), ("dp2a", 3), ("imad", 4), ("prmt", 5))
+    out = {}
+    for name, which in names:
+        v = C.c_double()
+        ctx.check(ctx.lib.r1c_int_peak(ctx.h, which, C.byref(v)))
+        out[name] = v.value
+    return out["iadd"], "measured in this run (r1c_int_peak: independent IADD3 streams on every SM, G lane-ops/s)", out
 
 
 def hbm_peak():
@@ -213,6 +241,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the MC / forward-TX kernel lines")
+    ap.add_argument("--no-scaling", action="store_true", help="skip the within-frame sharding lines (4K ME by SB row, MC / TX by tile)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
@@ -244,14 +273,19 @@ def main():
     lib = ctx.lib
     ext = torch.cuda.ExternalStream(ctx.stream, device=local)
 
-    # this rank's frame pair (frame-sharded lookahead: rank i takes frame i)
+    # this rank's lookahead window (frame-sharded lookahead: rank i takes window i): 32 distinct frame pairs derived
+    # from one synthetic pair by moving both frames together (the block motion between cur and ref is kept)
     cur, ref = synth_frame_pair(1 + 2 * rank)
-    p_org = r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
-    p_ref = r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB)
-    h_org = torch.from_numpy(padded(p_org.cfg, cur)).pin_memory()
-    h_ref = torch.from_numpy(padded(p_ref.cfg, ref)).pin_memory()
-    p_org.upload(h_org.numpy())
-    p_ref.upload(h_ref.numpy())
+    F = FRAMES_PER_STEP
+    p_org = [r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB) for _ in range(F)]
+    p_ref = [r.Plane(ctx, W, H, 0, 0, LUMA_PAD, LUMA_PAD, PB) for _ in range(F)]
+    h_org, h_ref = [], []
+    for i in range(F):
+        sh = (37 * i % H, 91 * i % W)
+        h_org.append(torch.from_numpy(padded(p_org[i].cfg, np.roll(cur, sh, axis=(0, 1)))).pin_memory())
+        h_ref.append(torch.from_numpy(padded(p_ref[i].cfg, np.roll(ref, sh, axis=(0, 1)))).pin_memory())
+        p_org[i].upload(h_org[i].numpy())
+        p_ref[i].upload(h_ref[i].numpy())
     params = r.make_frame_me_params(W, H, RANGE, RANGE, LAMBDA, refine=1, use_satd=1)
     n_res = r.frame_me_count(params)
     d_res = torch.empty(n_res * 16, dtype=torch.uint8, device="cuda")
@@ -259,12 +293,14 @@ def main():
     flush = torch.zeros(512 << 20, dtype=torch.uint8, device="cuda")  # each half > 126 MB L2
 
     def step_dev():
-        ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, d_res.data_ptr()))
+        for i in range(F):
+            ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, d_res.data_ptr()))
 
     def step_e2e():
-        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org.h, h_org.data_ptr()))
-        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref.h, h_ref.data_ptr()))
-        ctx.check(lib.r1c_frame_me(ctx.h, p_org.h, p_ref.h, C.byref(params), BD, h_res.ctypes.data))
+        for i in range(F):
+            ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org[i].h, h_org[i].data_ptr()))
+            ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref[i].h, h_ref[i].data_ptr()))
+            ctx.check(lib.r1c_frame_me(ctx.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, h_res.ctypes.data))
 
     def barrier():
         torch.cuda.synchronize()
@@ -294,6 +330,7 @@ def main():
     for _ in range(W_):
         step_dev()
     ctx.sync()
+    ipeak, ipeak_how, ipk = int_peak(ctx)  # a few ms of integer streams: also warms the clocks
     # ---- device-resident throughput + the dominant kernel's duration --------------
     ctx.check(lib.r1c_profile(ctx.h, 1))
     sampler = ClockSampler(local)
@@ -308,19 +345,27 @@ def main():
         prof[name] = (ms.value, n.value)
     ctx.check(lib.r1c_profile(ctx.h, 0))
     # ---- end to end: host planes in, host results out, every step ------------------
-    for _ in range(2):
-        step_e2e()
+    step_e2e()
     ms_e2e = timed(step_e2e, K)
     clocks = sampler.summary()
 
-    mpix = W * H / 1e6
+    mpix = F * W * H / 1e6
     value = world * mpix / (ms_total / K / 1e3)
     e2e = world * mpix / (ms_e2e / K / 1e3)
-    h2d = int(h_org.numel() + h_ref.numel())
-    d2h = int(n_res * 16)
+    h2d = int(sum(t.numel() for t in h_org) + sum(t.numel() for t in h_ref))
+    d2h = int(F * n_res * 16)
+    # ---- within-frame sharding (every N, N = 1 is the base point): 4K 10-bit ME by superblock rows, MC / TX by tile ---
+    extra = {}
+    if not args.no_scaling:
+        p_org.clear()  # the planes of the headline workload are no longer needed
+        p_ref.clear()
+        try:
+            extra["strong_4k10_me"] = bench_scaling.me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps=max(5, min(K, 20)))
+            extra.update(bench_scaling.mc_tx_sharded(ctx, r, torch, dist, ext, flush, rank, world))
+        except Exception as e:  # the headline line must still print
+            extra["scaling_error"] = repr(e)
 
     if rank == 0:
-        ipeak, ipeak_how, ipk = int_peak()
         hpeak, hpeak_how = hbm_peak()
         sb_ms = prof["me_sb2_kernel"][0] / max(1, prof["me_sb2_kernel"][1])
         n_sb = ((W + 63) // 64) * ((H + 63) // 64)
@@ -337,7 +382,7 @@ def main():
                         "peak_source": hpeak_how},
                 "packed_simd": {"vabsdiff4_peak_Ginstr_s": ipk.get("vabsdiff4_acc"),
                                 "note": "1 VABSDIFF4.ACC = 8 byte-ops; packed peak = 8 x this"},
-                "other_kernels_ms_per_step": {k: v[0] / K for k, v in prof.items()}}
+                "kernels_ms_per_frame": {k: v[0] / (K * F) for k, v in prof.items()}}
         # second kernel of the step: fused sub-pel tail.  Integer work per pixel of every block: SATD re-evaluation
         # (1 diff + 6 Hadamard + 2 abs/add = 9) + 24 candidates x (8 + 8 filter MACs + 9) = 609 lane-ops
         rf_ms = prof["me_refine_kernel"][0] / max(1, prof["me_refine_kernel"][1])
@@ -352,25 +397,25 @@ def main():
             "metric": "Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K, "warmup": W_,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "frame": "%dx%d" % (W, H), "bit_depth": BD, "range": RANGE,
-                       "lambda": LAMBDA, "blocks_per_frame": int(n_res),
-                       "l2": "flushed between steps (256 MiB written, then 256 MiB read back, untimed)",
-                       "sharding": "one frame pair per GPU, no collective"},
+            "config": dict(CONFIG),
+            "setup": {"blocks_per_frame": int(n_res), "frames_per_step": F, "launches_per_frame": 3,
+                      "flush": "256 MiB written, then 256 MiB read back, untimed, before every step"},
             "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / K,
-                    "path": "r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (pinned host result array)"},
+                    "path": "per frame pair: r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (pinned host result array)"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
         }
         if world == 1 and not args.no_cpu_baseline:
             v, cores, sample, _ = run_cpu(12.0)
-            line["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample}
+            line["cpu_baseline"] = {"value": v, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample, "note": CPU_NOTE}
         if world == 1 and not args.no_extras:
             try:
                 line["kernels"] = bench_kernels.run(ctx, r, torch, ext, flush)
             except Exception as e:  # the headline line must still print
                 line["kernels"] = {"error": repr(e)}
+        line.update(extra)
         if stdout_fd is not None:
             sys.stdout.flush()
             os.dup2(stdout_fd, 1)

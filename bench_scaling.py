@@ -1,0 +1,157 @@
+"""Within-frame sharding of the hot path over the GPUs of one box (north_star: "by AV1 tile"), measured by
+bench.py at every N next to the frame-sharded headline:
+
+  * me_strong():  ONE 3840x2160 10-bit frame pair, full-search ME +-64 + SATD sub-pel tail, superblock rows split over the
+                  ranks (rav1e_b200.shard.split_sb_rows; the reference splits the same work by tile,
+                  src/encoder.rs:2772-2781), both planes resident on every rank, every rank copies the (mv, cost) segments
+                  of its rows to page-locked host memory.  Strong scaling: the frame is fixed, time = max over ranks.
+  * mc_tx_sharded(): the 4K 10-bit MC put list (19 block sizes, one mixed list) split by tile column (8 columns of 480 px,
+                  src/tiling/tiler.rs:87-109) and the forward-transform blocks split evenly: same rule, no collective.
+
+No collective touches the data path; torch.distributed is used for the barrier and the max-over-ranks of the times."""
+import ctypes as C
+
+import numpy as np
+
+import bench_kernels
+from rav1e_b200 import shard
+
+W4K, H4K, BD4K, RANGE, LAMBDA = 3840, 2160, 10, 64, 160
+
+
+def _max_over_ranks(torch, dist, world, v):
+    if world == 1:
+        return v
+    t = torch.tensor([v], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _barrier(torch, dist, world):
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _segments(slots):
+    """sorted slot indices -> list of contiguous [start, end) ranges"""
+    if slots.size == 0:
+        return []
+    cut = np.nonzero(np.diff(slots) != 1)[0] + 1
+    return [(int(s[0]), int(s[-1]) + 1) for s in np.split(slots, cut)]
+
+
+def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
+    lib = ctx.lib
+    cur, ref = bench_kernels.synth_frame_pair(11, W4K, H4K, BD4K)
+    p_org = r.Plane(ctx, W4K, H4K, 0, 0, 88, 88, 2)
+    p_ref = r.Plane(ctx, W4K, H4K, 0, 0, 88, 88, 2)
+    h_org = torch.from_numpy(bench_kernels.padded(p_org.cfg, cur)).pin_memory()
+    h_ref = torch.from_numpy(bench_kernels.padded(p_ref.cfg, ref)).pin_memory()
+    p_org.upload(h_org.numpy())
+    p_ref.upload(h_ref.numpy())
+    rows = shard.split_sb_rows(H4K, world)
+    lo, hi = rows[rank]
+    params = r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA, refine=1, use_satd=1, sb_rows=(lo, hi))
+    n_res = r.frame_me_count(params)
+    slots = shard.shard_slots(W4K, H4K, r.ALL_SIZES_TO_64, lo, hi)
+    segs = _segments(slots)
+    d_res = torch.zeros(n_res * 16, dtype=torch.uint8, device="cuda")
+    h_res = torch.zeros(n_res * 16, dtype=torch.uint8).pin_memory()
+
+    def gather():
+        with torch.cuda.stream(ext):
+            for s, e in segs:
+                h_res[s * 16:e * 16].copy_(d_res[s * 16:e * 16], non_blocking=True)
+
+    def step_dev():
+        if hi > lo:
+            ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD4K, d_res.data_ptr()))
+            gather()
+
+    def step_e2e():
+        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org.h, h_org.data_ptr()))
+        ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref.h, h_ref.data_ptr()))
+        step_dev()
+
+    def timed(fn):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        _barrier(torch, dist, world)
+        for a, b in evs:
+            with torch.cuda.stream(ext):
+                bench_kernels.flush_l2(torch, flush)
+                a.record(ext)
+            fn()
+            b.record(ext)
+        _barrier(torch, dist, world)
+        return _max_over_ranks(torch, dist, world, sum(a.elapsed_time(b) for a, b in evs)) / steps
+
+    for _ in range(warmup):
+        step_dev()
+    ms = timed(step_dev)
+    ms_e2e = timed(step_e2e)
+    mpix = W4K * H4K / 1e6
+    return {
+        "workload": "ONE 3840x2160 10-bit frame pair, full search +-64, 19 sizes, SATD sub-pel tail; superblock rows split "
+                    "over the ranks, planes replicated, (mv, cost) segments copied to page-locked host memory",
+        "scaling": "strong", "n_gpus": world, "value": mpix / (ms / 1e3), "unit": "Mpix/s", "ms_per_frame": ms,
+        "sb_rows_per_rank": [b - a for a, b in rows], "sb_rows": (H4K + 63) // 64,
+        "d2h_bytes_this_rank": int(sum(e - s for s, e in segs) * 16), "d2h_copies_this_rank": len(segs),
+        "e2e": {"value": mpix / (ms_e2e / 1e3), "unit": "Mpix/s", "ms_per_frame": ms_e2e,
+                "h2d_bytes_per_rank": int(h_org.numel() * 2 + h_ref.numel() * 2),
+                "note": "every rank uploads both whole planes (MVs may point anywhere in the reference): the upload does "
+                        "not shrink with N"},
+        "note": "34 superblock rows do not divide by 8: the largest share is ceil(34 / N) rows, so the best possible "
+                "speed-up is 34 / ceil(34 / N) = %.2f at N = %d" % (34 / -(-34 // world), world)}
+
+
+def mc_tx_sharded(ctx, r, torch, dist, ext, flush, rank, world, reps=3):
+    lib = ctx.lib
+    rng = np.random.default_rng(3)
+    src = r.Plane(ctx, W4K, H4K, 0, 0, 88, 88, 2)
+    dst = r.Plane(ctx, W4K, H4K, 0, 0, 88, 88, 2)
+    src.upload(rng.integers(0, 1024, size=src.shape, dtype=np.uint16))
+    allj = np.concatenate(bench_kernels.mc_jobs(r, rng, lib, W4K, H4K, 1))
+    tile_w = W4K // 8  # 8 tile columns (60 superblock columns -> 8, 8, ... : src/tiling/tiler.rs:87-109; 480 px here)
+    col = np.minimum(allj["dst_x"] // tile_w, 7)
+    mine = allj[(col * world) // 8 == rank]
+    px_all = int((allj["w"].astype(np.int64) * allj["h"]).sum())
+    px_mine = int((mine["w"].astype(np.int64) * mine["h"]).sum())
+    d_jobs = torch.from_numpy(mine.view(np.uint8).copy()).cuda()
+
+    def f_put():
+        ctx.check(lib.r1c_put_8tap_batch_dev(ctx.h, dst.h, src.h, d_jobs.data_ptr(), mine.size, BD4K))
+
+    def timed(fn):
+        fn()
+        _barrier(torch, dist, world)
+        ms = bench_kernels._timed(torch, ext, flush, fn, reps)
+        _barrier(torch, dist, world)
+        return _max_over_ranks(torch, dist, world, ms)
+
+    mc_ms = timed(f_put)
+    n_samples = W4K * H4K * 3 // 2
+    res = torch.from_numpy(rng.integers(-1023, 1024, size=n_samples, dtype=np.int16)).cuda()
+    coef = torch.empty(n_samples, dtype=torch.int32, device="cuda")
+    tx_ms, coeffs = 0.0, 0
+    for ts in range(19):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        n = n_samples // (w * h)
+        lo, hi = n * rank // world, n * (rank + 1) // world
+
+        def f_tx():
+            ctx.check(lib.r1c_fwd_txfm_batch_dev(ctx.h, ts, 0, BD4K, res.data_ptr() + lo * w * h * 2,
+                                                 coef.data_ptr() + lo * w * h * 4, hi - lo))
+        tx_ms += timed(f_tx)
+        coeffs += n * w * h
+    return {
+        "mc_put_4k10_tile_columns": {
+            "workload": "4K 10-bit luma, the 19 tilings as one mixed job list (%.0f Mpx), jobs split by tile column "
+                        "(8 columns of 480 px), source plane on every rank; whole r1c_put_8tap_batch_dev call" % (px_all / 1e6),
+            "scaling": "strong", "n_gpus": world, "value": px_all / 1e6 / (mc_ms / 1e3), "unit": "Mpix/s", "ms": mc_ms,
+            "pixels_this_rank": px_mine},
+        "fwd_tx_4k10_split": {
+            "workload": "4K 10-bit 4:2:0 residual (12.4 M samples) tiled by each of the 19 TxSize, DCT_DCT, blocks split "
+                        "evenly over the ranks; 19 r1c_fwd_txfm_batch_dev calls",
+            "scaling": "strong", "n_gpus": world, "value": coeffs / 1e6 / (tx_ms / 1e3), "unit": "Mcoeff/s", "ms": tx_ms}}
