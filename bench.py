@@ -33,6 +33,7 @@ import time
 import numpy as np
 
 import bench_kernels
+import bench_baselines
 import bench_scaling
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -415,6 +416,11 @@ def main():
                 line["kernels"] = bench_kernels.run(ctx, r, torch, ext, flush)
             except Exception as e:  # the headline line must still print
                 line["kernels"] = {"error": repr(e)}
+            if "error" not in line["kernels"] and not args.no_cpu_baseline:
+                try:  # CPU baselines + host-buffer e2e of the MC / TX / SAD-SATD classes, configs[0]
+                    bench_baselines.run(ctx, r, torch, ext, flush, line["kernels"])
+                except Exception as e:
+                    line["kernels"]["baselines_error"] = repr(e)
         line.update(extra)
         if stdout_fd is not None:
             sys.stdout.flush()

@@ -255,7 +255,7 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
     for name, ms in (("sad", sad_ms), ("satd", satd_ms)):
         gbs = dist_px * 4 / (ms / 1e3) / 1e9
         out["dist_4k10_" + name] = {
-            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, one job per block, reference offset +-32 px",
+            "workload": "4K 10-bit luma tiled by each of the 19 block sizes, %d candidate reference positions per block and launch (+-32 px; the org block is shared by its candidates, so DRAM reads less than the 4 B per pixel counted)" % MC_CANDS,
             "value": dist_px / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "pixels": dist_px,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_px": 4, "peak_source": hbm_how}}

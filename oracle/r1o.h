@@ -198,4 +198,7 @@ void r1o_importance_finalize(const uint32_t *intra_costs, float *importances, in
 #ifdef __cplusplus
 }
 #endif
+/* benches/dist.rs recipe: ns per get_sad / get_satd call, one thread (bench.py configs[0] line) */
+double r1o_bench_dist(int use_satd, const void *org, ptrdiff_t os, const void *ref, ptrdiff_t rs, int w, int h, int pb,
+                      int64_t iters);
 #endif /* R1O_H */

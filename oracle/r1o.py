@@ -82,6 +82,8 @@ def lib():
                                       P(Mv * 2), u32, i, i, P(i64 * 4), i, i]
         L.r1o_subpel_cost.restype = u64
         L.r1o_num_threads.restype = i
+        L.r1o_bench_dist.argtypes = [i, vp, pd, vp, pd, i, i, i, i64]
+        L.r1o_bench_dist.restype = C.c_double
         L.r1o_dist_batch.argtypes = [i, vp, P(PlaneCfg), vp, P(PlaneCfg), vp, i64, i, vp]
         L.r1o_full_search_batch.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), vp, i64, i, vp, vp]
         L.r1o_full_search_batch.restype = i

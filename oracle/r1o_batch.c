@@ -90,3 +90,21 @@ int r1o_fht_batch(const int16_t *residual, int32_t *coeffs, int tx_size, int tx_
     r1o_fht(residual + i * area, coeffs + i * area, tx_size, tx_type, bd);
   return 0;
 }
+
+/* benches/dist.rs:101-118 (criterion's b.iter over one get_sad / get_satd call at region (0, 0)): `iters` back-to-back
+ * calls on one thread, nanoseconds per call.  The result of every call is kept live through a volatile sink. */
+#include <time.h>
+double r1o_bench_dist(int use_satd, const void *org, ptrdiff_t os, const void *ref, ptrdiff_t rs, int w, int h, int pb,
+                      int64_t iters) {
+  volatile uint32_t sink = 0;
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (int64_t i = 0; i < iters; i++) {
+    const void *o = org;
+    __asm__ volatile("" : "+r"(o));  /* the compiler may not hoist the call out of the loop */
+    sink = use_satd ? r1o_satd(o, os, ref, rs, w, h, pb) : r1o_sad(o, os, ref, rs, w, h, pb);
+  }
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  (void)sink;
+  return ((double)(t1.tv_sec - t0.tv_sec) * 1e9 + (double)(t1.tv_nsec - t0.tv_nsec)) / (double)iters;
+}
