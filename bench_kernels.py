@@ -321,6 +321,72 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
             "kernel_us_by_tx_size": qper[key],
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_coeff": bpc, "peak_source": hbm_how}}
+    # ------------------------------ the fused residual chain of encode_tx_block on a 4K 10-bit luma plane: source = `org`,
+    # prediction = source + noise of +-24 held in `rec` (restored from page-locked memory before every launch, outside
+    # the timed kernel), DCT_DCT, the 14 TxSize without a 64-point side; the same work through the four separate kernels
+    # is timed next to it (diff + fht, quantize with tx_dist, dequantize + inverse add: three launches)
+    rec = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
+    org_host = org.download()
+    h_pred = torch.from_numpy(np.clip(org_host.astype(np.int32) + rng.integers(-24, 25, size=org_host.shape), 0, 1023)
+                              .astype(np.uint16)).pin_memory()
+    del org_host
+    esum = {"fused": 0.0, "chain": 0.0}
+    eper = {}
+    ebytes = epix = 0
+    co_tmp = torch.empty(W * H, dtype=torch.int32, device="cuda")
+    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        if not lib.r1c_encode_tx_block_valid(ts, 0):
+            continue
+        xs, ys = np.meshgrid(np.arange(0, W - w + 1, w), np.arange(0, H - h + 1, h))
+        n = xs.size
+        tj = np.zeros(n, dtype=r.TX_JOB)
+        tj["in_x"] = tj["pred_x"] = xs.ravel()
+        tj["in_y"] = tj["pred_y"] = ys.ravel()
+        ij = np.zeros(n, dtype=r.ITX_JOB)
+        ij["x"], ij["y"] = xs.ravel(), ys.ravel()
+        d_tj = torch.from_numpy(tj.view(np.int32).reshape(-1)).cuda()
+        d_ij = torch.from_numpy(ij.view(np.int32).reshape(-1)).cuda()
+        qc = r.QuantizationContext().update(lib, ts, 0, 40, 52)
+        scan = torch.from_numpy(np.concatenate([[0], 1 + rng.permutation(w * h - 1)]).astype(np.int16)).cuda()
+
+        def f_e():
+            ctx.check(lib.r1c_plane_upload_async(ctx.h, rec.h, h_pred.data_ptr()))
+            ctx.check(lib.r1c_encode_tx_block_batch_dev(ctx.h, org.h, rec.h, d_tj.data_ptr(), n, ts, 0, BD, C.byref(qc.c),
+                                                        scan.data_ptr(), 1, qout.data_ptr(), dout.data_ptr()))
+
+        def f_c():
+            ctx.check(lib.r1c_plane_upload_async(ctx.h, rec.h, h_pred.data_ptr()))
+            ctx.check(lib.r1c_diff_fwd_txfm_batch_dev(ctx.h, org.h, rec.h, d_tj.data_ptr(), n, ts, 0, BD, co_tmp.data_ptr()))
+            ctx.check(lib.r1c_quantize_batch_dev(ctx.h, C.byref(qc.c), ts, scan.data_ptr(), co_tmp.data_ptr(), qout.data_ptr(),
+                                                 0, dout.data_ptr(), n))
+            ctx.check(lib.r1c_dequant_inv_txfm_add_batch_dev(ctx.h, rec.h, d_ij.data_ptr(), n, ts, 0, BD, qout.data_ptr(), 40, 52))
+        k_ms = {}
+        for key, fn in (("fused", f_e), ("chain", f_c)):
+            fn()
+            ctx.sync()
+            for slot in (4, 6, 7):
+                _kernel_ms(ctx, slot)
+            _timed(torch, ext, flush, fn, reps)
+            k_ms[key] = sum(_kernel_ms(ctx, slot)[0] for slot in (4, 6, 7)) / reps
+            esum[key] += k_ms[key]
+        b = n * (w * h * 10 + 8)  # 2 + 2 B read, 4 B qcoeff + 2 B pixel written per pixel, 8 B tx_dist per block
+        ebytes += b
+        epix += n * w * h
+        eper["%dx%d" % (w, h)] = {"frac": round(b / (k_ms["fused"] / 1e3) / 1e9 / hbm, 3), "us": round(k_ms["fused"] * 1e3, 1),
+                                  "separate_kernels_us": round(k_ms["chain"] * 1e3, 1)}
+    if epix:
+        gbs = ebytes / (esum["fused"] / 1e3) / 1e9
+        out["enc_tx_4k10_fused_dct_dct"] = {
+            "workload": "4K 10-bit luma tiled by each of the 14 TxSize up to 32x32: diff + forward DCT_DCT + quantize (qstep 52) + "
+                        "dequantize + inverse transform added back + tx-domain distortion as ONE kernel per size "
+                        "(r1c_encode_tx_block_batch_dev); prediction = source +- 24",
+            "value": epix / 1e6 / (esum["fused"] / 1e3), "unit": "Mpix/s", "ms": esum["fused"], "pixels": epix,
+            "separate_kernels_ms": esum["chain"], "speedup_vs_separate_kernels": esum["chain"] / esum["fused"],
+            "by_tx_size": eper,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                         "alg_bytes": "10 per pixel (2 + 2 read, 4 + 2 written) + 8 per block", "peak_source": hbm_how}}
+    del rec, h_pred, co_tmp
     # ------------------------------ inverse transform + add onto a 4K luma plane (dequantized-like coefficients):
     # 10-bit (u16 plane `dst`) and 8-bit (u8 plane), and the 10-bit case with dequantize fused into the load
     rin = (qin // 147) * 147  # what dequantize leaves: multiples of the step, mostly zero

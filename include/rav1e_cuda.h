@@ -375,6 +375,40 @@ int r1c_dequantize_batch_dev(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint3
                              const int32_t *d_qcoeffs, int32_t *d_rcoeffs, int64_t n);
 
 /* ------------------------------------------------------------------------
+ * encode_tx_block, src/encoder.rs:1143-1224 -- the residual chain of one transform block as ONE
+ * kernel: diff (:1045-1059, :1157-1163) -> forward_transform (:1165-1168) -> quantize (:1170) ->
+ * dequantize (:1192-1200) -> inverse_transform_add (:1203-1208) -> tx-domain distortion
+ * (:1210-1224).  The entropy coder (write_coeffs_lv_map, :1173-1190) stays on the Rust side: it
+ * reads `qcoeffs`.  Intra prediction (:1096-1119) is not part of the call: `rec` must already
+ * hold the block's prediction (what motion_compensate / predict_intra leave there), it is the
+ * subtrahend of the diff and, when `reconstruct` is set, receives the reconstruction
+ * (`!fi.use_tx_domain_distortion || need_recon_pixel`).  Blocks of one call are independent in
+ * the reference only if no block's prediction reads another's reconstruction (inter blocks, or
+ * intra blocks of one wave front): the jobs of one call must not overlap in `rec`.
+ *   jobs[i]   (in_x, in_y) in `input`, (pred_x, pred_y) in `rec`
+ *   qcoeffs   block i at qcoeffs + i*W*H (coded area == area: sizes with a 64-point side are
+ *             not fused; r1c_encode_tx_block_valid() == 0 for them and for the (size, type)
+ *             pairs the reference leaves `unimplemented!`; the batch calls then return
+ *             R1C_ERR_UNIMPLEMENTED and the caller chains the separate entry points)
+ *   tx_dist   optional (`rdo_type.needs_tx_dist()`): sum((coeff - rcoeff)^2) rounded and
+ *             shifted by 2*(3 - log_tx_scale), before the bias / dist_scale factors of :1238-1240
+ *   qc, scan  as for r1c_quantize_batch
+ * Bit-exact with the chain r1c_diff_fwd_txfm_batch -> r1c_quantize_batch_dev ->
+ * r1c_dequant_inv_txfm_add_batch.
+ * ---------------------------------------------------------------------- */
+int r1c_encode_tx_block_valid(int tx_size, int tx_type);
+int r1c_encode_tx_block_batch(r1c_ctx *ctx, const r1c_plane *input, r1c_plane *rec,
+                              const r1c_tx_job *jobs, int64_t n, int tx_size, int tx_type,
+                              int bit_depth, const r1c_quant_ctx *qc, const uint16_t *scan,
+                              int reconstruct, int32_t *qcoeffs, uint64_t *tx_dist);
+/* d_jobs, d_scan, d_qcoeffs, d_tx_dist are device arrays; the caller guarantees the jobs stay
+ * inside the planes and that d_scan is a permutation with d_scan[0] == 0 */
+int r1c_encode_tx_block_batch_dev(r1c_ctx *ctx, const r1c_plane *input, r1c_plane *rec,
+                                  const r1c_tx_job *d_jobs, int64_t n, int tx_size, int tx_type,
+                                  int bit_depth, const r1c_quant_ctx *qc, const uint16_t *d_scan,
+                                  int reconstruct, int32_t *d_qcoeffs, uint64_t *d_tx_dist);
+
+/* ------------------------------------------------------------------------
  * Motion search, src/me.rs.
  * ---------------------------------------------------------------------- */
 typedef struct { int16_t row, col; } r1c_mv; /* MotionVector, src/mc.rs:27-31; 1/8 px */

@@ -402,6 +402,27 @@ def inverse_transform_add(ctx, rcoeffs, plane_dst, jobs, tx_size, tx_type, bit_d
                                              bit_depth, _p(rcoeffs)))
 
 
+def encode_tx_block_batch(ctx, plane_in, plane_rec, jobs, tx_size, tx_type, bit_depth, qc, scan, reconstruct=True,
+                          want_tx_dist=True):
+    """The residual chain of encode_tx_block (src/encoder.rs:1143-1224) for a batch of transform blocks as one kernel:
+    diff of `plane_in` and the prediction held in `plane_rec` at jobs[i] -> forward transform -> quantize (qc: a
+    QuantizationContext updated for tx_size; scan: the scan order) -> dequantize -> inverse transform added back onto
+    `plane_rec` (when `reconstruct`) -> tx-domain distortion.  Returns (qcoeffs (N, W*H) int32, tx_dist (N,) uint64 or
+    None).  Sizes with a 64-point side raise R1C_ERR_UNIMPLEMENTED: chain the separate calls for them."""
+    jobs = _arr(jobs, TX_JOB)
+    scan = _arr(scan, np.uint16)
+    w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)
+    if w < 0:
+        raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad tx_size")
+    assert scan.size == min(w, 32) * min(h, 32)
+    q = np.empty((jobs.size, min(w, 32) * min(h, 32)), dtype=np.int32)
+    d = np.empty(jobs.size, dtype=np.uint64) if want_tx_dist else None
+    ctx.check(ctx.lib.r1c_encode_tx_block_batch(ctx.h, plane_in.h, plane_rec.h, _p(jobs), jobs.size, tx_size, tx_type,
+                                                bit_depth, C.byref(qc.c), _p(scan), int(bool(reconstruct)), _p(q),
+                                                _p(d) if d is not None else None))
+    return q, d
+
+
 # ----------------------------------------------------------------- motion search --
 def get_mv_range(w_in_b, h_in_b, bo, blk_w, blk_h):
     out = (C.c_int64 * 4)()

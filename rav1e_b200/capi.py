@@ -186,6 +186,9 @@ SIGNATURES = {
     "r1c_inv_txfm_add_batch_dev": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "r1c_dequant_inv_txfm_add_batch": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _u32, _u32]),
     "r1c_dequant_inv_txfm_add_batch_dev": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _vp, _u32, _u32]),
+    "r1c_encode_tx_block_valid": (_i, [_i, _i]),
+    "r1c_encode_tx_block_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _P(QuantCtx), _vp, _i, _vp, _vp]),
+    "r1c_encode_tx_block_batch_dev": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _P(QuantCtx), _vp, _i, _vp, _vp]),
     "r1c_mv_range": (None, [_i64, _i64, _i64, _i64, _i, _i, _P(_i64 * 4)]),
     "r1c_mv_rate": (_u32, [Mv, Mv, _i]),
     "r1c_full_search_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),

@@ -98,6 +98,11 @@ int r1c_mc_tma_launch(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, co
 int r1c_mc_put_dense_dev(r1c_ctx *ctx, void *d_dense, const r1c_plane *src, const r1c_mc_job *d_jobs,
                          int64_t n, int bit_depth);
 
+// tx.cu / itx.cu: per-size constants shared with enc_tx.cu (FWD_SHIFT_* row of forward.rs:22-40 for this bit depth;
+// InvBlock::INTERMEDIATE_SHIFT, inverse.rs:1656-1665)
+void r1c_fwd_shift_row(int tx_size, int bit_depth, int out[3]);
+int r1c_inv_intermediate_shift(int tx_size);
+
 // scoped event pair around a kernel launch (no-op unless r1c_profile(ctx, 1))
 void r1c_prof_begin(r1c_ctx *ctx, int slot);
 void r1c_prof_end(r1c_ctx *ctx, int slot);

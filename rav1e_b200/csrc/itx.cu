@@ -48,6 +48,8 @@ static Range range_of(int bits) {  // clamp_value, src/transform/mod.rs:492-496
 }
 }  // namespace itx
 
+int r1c_inv_intermediate_shift(int tx_size) { return itx::intermediate_shift(tx_size); }
+
 extern "C" int r1c_inv_txfm_valid(int tx_size, int tx_type) {
   int cf, rf;
   return itx::lookup(tx_size, tx_type, &cf, &rf) != nullptr;

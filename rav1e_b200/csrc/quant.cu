@@ -12,37 +12,19 @@
 // The end-of-block search (rposition over |coeff| >= deadzone) is a max-reduction over the
 // same lanes; a lane keeps its coefficients in registers for the second pass.
 // Bound: HBM, 4 B read + 4 B written per coefficient (+4 with rcoeffs); `scan` stays in L1.
-#include "common.cuh"
+#include "quant_dev.cuh"
 
 namespace {
+using quant::dequant1;
 
 struct QuantArgs {
-  r1c_quant_ctx qc;
-  const uint16_t *scan;
+  quant::QuantConsts q;
   const int32_t *coeffs;
   int32_t *qcoeffs, *rcoeffs;
   uint64_t *tx_dist;
   long long n;
   int area, coded, dist_bits;
-  int32_t deadzone;
-  int nonneg;  // 0 <= ac_offset0 <= ac_offset1 < ac_offset0 + ac_quant: the magnitude fast path applies
 };
-
-// divu_pair, src/quantize.rs:140-153: ((a * |x| + b) >> 32) >> shift with the sign of x
-__device__ __forceinline__ int32_t divu_pair(int32_t x, uint32_t a, uint32_t b, uint32_t shift) {
-  const uint32_t y = (uint32_t)(x < 0 ? -x : x);
-  const int32_t q = (int32_t)((uint32_t)(((unsigned long long)a * y + b) >> 32) >> shift);
-  return x < 0 ? -q : q;
-}
-// the magnitude part of divu_pair
-__device__ __forceinline__ uint32_t udivu(uint32_t y, uint32_t a, uint32_t b, uint32_t shift) {
-  return (uint32_t)(((unsigned long long)a * y + b) >> 32) >> shift;
-}
-__device__ __forceinline__ int32_t signum(int32_t v) { return (v > 0) - (v < 0); }
-// dequantize, src/quantize.rs:329-332 (wrapping i32 product, arithmetic shift)
-__device__ __forceinline__ int32_t dequant1(int32_t c, uint32_t quant, int lts) {
-  return (int32_t)((uint32_t)c * quant + (uint32_t)((c >> 31) & ((1 << lts) - 1))) >> lts;
-}
 
 // LPB lanes per block, NCH = coded / LPB chunks of scan positions; a lane keeps its NCH coefficients in registers
 // between the end-of-block search and the quantizer pass
@@ -53,8 +35,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
   const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const long long b = warp * BPW + lane / LPB;
   const bool live = b < a.n;  // lanes of a block that does not exist go through the motions on zeros
-  const int lts = (int)a.qc.log_tx_scale;
-  constexpr uint32_t BMASK = LPB == 32 ? 0xffffffffu : ((1u << LPB) - 1u);
+  const int lts = (int)a.q.qc.log_tx_scale;
   // The warp's blocks go through shared memory: coalesced in, gathered / scattered by scan position there (a scan
   // sends neighbouring lanes to different rows of the block: one L1 wavefront per lane when done on global memory),
   // coalesced out.  Quantized values overwrite the coefficients in place.
@@ -69,113 +50,8 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
   }
   __syncwarp();
 
-  // ---- eob: last scan index k >= 1 with |coeff| >= deadzone, else 1 (src/quantize.rs:268-276) ----
-  // up to 8 chunks per lane: both loops fully unrolled, the lane's coefficients and scan positions stay in registers
-  // between them.  16 and 32 chunks (512 / 1024 coded coefficients): rolled loops that read them again from shared
-  // memory / the scan table -- the unrolled form needs 64 - 124 registers and does not fit the instruction cache
-  constexpr bool ROLLED = NCH >= 16;
-  constexpr int UNR = ROLLED ? 4 : NCH;
-  int32_t raw_keep[ROLLED ? 1 : NCH];
-  int pos_keep[ROLLED ? 1 : NCH];
-  int eob = 1;
-#pragma unroll UNR
-  for (int c = 0; c < NCH; c++) {
-    const int k = c * LPB + l;
-    const int p = (int)__ldg(a.scan + k);
-    const int32_t r = sb[p];
-    if (!ROLLED) pos_keep[c] = p, raw_keep[c] = r;
-    if (k >= 1 && (r < 0 ? -r : r) >= a.deadzone) eob = k;
-  }
-#pragma unroll
-  for (int m = LPB >> 1; m; m >>= 1) eob = max(eob, __shfl_xor_sync(0xffffffffu, eob, m, LPB));
-
-  const uint32_t ma = a.qc.ac_mul_add[0], mb = a.qc.ac_mul_add[1], ms = a.qc.ac_mul_add[2];
-  __syncwarp();
-  uint32_t mode = 1;  // level_mode at the start of the chunk
-  unsigned long long dist = 0;
-#pragma unroll UNR
-  for (int c = 0; c < NCH; c++) {
-    const int k = c * LPB + l;
-    const int pos_c = ROLLED ? (int)__ldg(a.scan + k) : pos_keep[c];
-    const int32_t raw_c = ROLLED ? sb[pos_c] : raw_keep[c];  // each position is read and rewritten by its one lane
-    const int32_t coeff = (int32_t)((uint32_t)raw_c << lts);
-    // this lane's result under level_mode 0 / 1 and its transition map f0 / f1 = next mode from mode 0 / 1;
-    // the DC and the zeroed tail leave the mode alone (f0 = 0, f1 = 1)
-    int32_t q0, q1;
-    bool f0 = false, f1 = true;
-    if (k == 0 && !a.nonneg) {
-      // DC, src/quantize.rs:278-280
-      q0 = q1 = divu_pair(coeff + signum(coeff) * a.qc.dc_offset, a.qc.dc_mul_add[0], a.qc.dc_mul_add[1], a.qc.dc_mul_add[2]);
-    } else if (k <= eob) {
-      // src/quantize.rs:293-311
-      if (a.nonneg) {
-        // offsets >= 0 (always, after update()): divide magnitudes, apply the sign once.  A negative coefficient has
-        // level0 <= 0, so it takes ac_offset0 under both modes and can only reset the mode (the tests are signed)
-        // divu_pair is an exact division (Robison's multiply-add form; the reference's test_divu_pair), so
-        // level0 > 0 / > 1 are comparisons with d / 2 d, and the quotient with the larger offset is the one with the
-        // smaller offset plus a carry out of its remainder (0 <= offset1 - offset0 < d): one wide multiply per coefficient.
-        // The DC (:278-280) is the same formula with its own divisor and one offset for both roles, so lane 0 of
-        // chunk 0 only swaps its constants instead of sending the warp through a second division
-        const bool dc = c == 0 && k == 0;
-        const uint32_t d = dc ? a.qc.dc_quant : a.qc.ac_quant;
-        const uint32_t off0 = (uint32_t)(dc ? a.qc.dc_offset : a.qc.ac_offset0);
-        const uint32_t doff = dc ? 0u : (uint32_t)(a.qc.ac_offset1 - a.qc.ac_offset0);
-        const uint32_t y0 = (uint32_t)(coeff < 0 ? -coeff : coeff);
-        const uint32_t t0 = y0 + off0;
-        uint32_t ua = c == 0 ? udivu(t0, dc ? a.qc.dc_mul_add[0] : ma, dc ? a.qc.dc_mul_add[1] : mb, dc ? a.qc.dc_mul_add[2] : ms)
-                             : udivu(t0, ma, mb, ms);
-        uint32_t ub = ua + (t0 - ua * d + doff >= d ? 1u : 0u);
-        ua = y0 ? ua : 0u;
-        ub = y0 ? ub : 0u;
-        const bool neg = coeff < 0;
-        q0 = neg ? -(int32_t)ua : (int32_t)(y0 >= 2 * d ? ub : ua);
-        q1 = neg ? -(int32_t)ua : (int32_t)(y0 >= d ? ub : ua);
-      } else {
-        const int32_t level0 = divu_pair(coeff, ma, mb, ms);
-        const int32_t sg = signum(coeff);
-        const int32_t qa = divu_pair(coeff + sg * a.qc.ac_offset0, ma, mb, ms);
-        const int32_t qb = divu_pair(coeff + sg * a.qc.ac_offset1, ma, mb, ms);
-        q0 = level0 > 1 ? qb : qa;  // `level0 > 1 - level_mode`
-        q1 = level0 > 0 ? qb : qa;
-      }
-      // mode 0: `else if qcoeff > 1 { level_mode = 1 }`; mode 1: `qcoeff == 0` -> 0, otherwise it stays 1;
-      // the DC is outside the state machine
-      f0 = k != 0 && q0 > 1;
-      f1 = k == 0 || q1 != 0;
-    } else {
-      q0 = q1 = 0;  // src/quantize.rs:313-315
-    }
-    // maps of the block's lanes as two bit masks; a lane's incoming mode = the mode left by the closest earlier
-    // lane whose map is constant (f0 == f1), else the mode carried into the chunk
-    const uint32_t A = (__ballot_sync(0xffffffffu, f0) >> sh) & BMASK, B = (__ballot_sync(0xffffffffu, f1) >> sh) & BMASK;
-    uint32_t m_in;
-    if (__any_sync(0xffffffffu, f0 && !f1)) {
-      // a map that flips the mode (q0 > 1 but q1 == 0: not seen with offset1 >= offset0, handled all the same):
-      // compose the 2-bit maps with an inclusive shuffle scan
-      uint32_t inc = (f0 ? 1u : 0u) | (f1 ? 2u : 0u);
-#pragma unroll
-      for (int d = 1; d < LPB; d <<= 1) {
-        const uint32_t prev = __shfl_up_sync(0xffffffffu, inc, d, LPB);
-        if (l >= d) inc = ((inc >> (prev & 1u)) & 1u) | (((inc >> ((prev >> 1) & 1u)) & 1u) << 1);
-      }
-      uint32_t exc = __shfl_up_sync(0xffffffffu, inc, 1, LPB);
-      if (l == 0) exc = 2u;
-      m_in = (exc >> mode) & 1u;
-      mode = (__shfl_sync(0xffffffffu, inc, LPB - 1, LPB) >> mode) & 1u;
-    } else {
-      const uint32_t fixed = ~(A ^ B) & BMASK;  // lanes that set (A = B = 1) or reset (A = B = 0) the mode
-      const uint32_t below = fixed & ((1u << l) - 1u);
-      m_in = below ? (A >> (31 - __clz(below))) & 1u : mode;
-      mode = fixed ? (A >> (31 - __clz(fixed))) & 1u : mode;
-    }
-    const int32_t q = m_in ? q1 : q0;
-    sb[pos_c] = q;
-    if (a.tx_dist) {
-      const int32_t r = dequant1(q, pos_c == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
-      const uint32_t d = (uint32_t)raw_c - (uint32_t)r;
-      dist += (unsigned long long)(long long)(int32_t)(d * d);  // (c * c) as u64, wrapping i32 product
-    }
-  }
+  const unsigned long long part = quant::quantize_lanes<LPB, NCH, -1>(sb, l, sh, a.q, a.tx_dist != nullptr);
+  unsigned long long dist = part;
   __syncwarp();
 #pragma unroll
   for (int i = 0; i < BPW * CODED / 32; i++) {
@@ -184,7 +60,7 @@ __global__ void __launch_bounds__(256) quantize_kernel(const __grid_constant__ Q
     if (gb < a.n) {
       const int32_t q = sw[e];
       a.qcoeffs[gb * CODED + off] = q;
-      if (a.rcoeffs) a.rcoeffs[gb * CODED + off] = dequant1(q, off == 0 ? a.qc.dc_quant : a.qc.ac_quant, lts);
+      if (a.rcoeffs) a.rcoeffs[gb * CODED + off] = dequant1(q, off == 0 ? a.q.qc.dc_quant : a.q.qc.ac_quant, lts);
     }
   }
   if (a.tx_dist) {
@@ -261,8 +137,7 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   QuantArgs a;
-  a.qc = *qc;
-  a.scan = d_scan;
+  a.q = quant::make_consts(*qc, d_scan);
   a.coeffs = d_coeffs;
   a.qcoeffs = d_qcoeffs;
   a.rcoeffs = d_rcoeffs;
@@ -271,10 +146,6 @@ extern "C" int r1c_quantize_batch_dev(r1c_ctx *ctx, const r1c_quant_ctx *qc, int
   a.area = r1c_tx_width(tx_size) * r1c_tx_height(tx_size);
   a.coded = coded_of(tx_size);
   a.dist_bits = 2 * (3 - (int)qc->log_tx_scale);
-  // (ac_quant as usize - ac_offset_eob as usize).align_power_of_two_and_shift(log_tx_scale), src/quantize.rs:265-267
-  a.deadzone = (int32_t)(((uint64_t)qc->ac_quant - (uint64_t)qc->ac_offset_eob + (1ull << qc->log_tx_scale) - 1) >> qc->log_tx_scale);
-  a.nonneg = qc->ac_offset0 >= 0 && qc->ac_offset1 >= qc->ac_offset0 && (uint32_t)(qc->ac_offset1 - qc->ac_offset0) < qc->ac_quant &&
-             qc->ac_quant < (1u << 30) && qc->dc_offset >= 0 && (uint32_t)qc->dc_offset < qc->dc_quant && qc->dc_quant < (1u << 30);
   r1c_prof_begin(ctx, R1C_PROF_QUANT);
   const unsigned g8 = (unsigned)((n + 7) / 8);
   switch (a.coded) {  // 4x4 .. 32x32 coded areas

@@ -70,6 +70,11 @@ static int launch(r1c_ctx *ctx, int tx_size, int tx_type, int bit_depth, FhtArgs
 }
 }  // namespace tx
 
+void r1c_fwd_shift_row(int tx_size, int bit_depth, int out[3]) {
+  const signed char *sh = tx::shift_rows(tx_size)[(bit_depth - 8) / 2];
+  out[0] = sh[0], out[1] = sh[1], out[2] = sh[2];
+}
+
 extern "C" int r1c_fwd_txfm_valid(int tx_size, int tx_type) {
   int cf, rf;
   return tx::lookup(tx_size, tx_type, &cf, &rf) != nullptr;
