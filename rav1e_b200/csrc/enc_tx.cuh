@@ -11,6 +11,8 @@
 // against 2 px + 4 | 4 + 4 (+4) | 4 + 4 | 4 + 2 px for the four separate kernels.
 //   phase 1  forward columns : one thread per column; pixels of both planes straight from global memory
 //   phase 2  forward rows    : one thread per row, in place
+//            (BPC = THREADS / min(W, H): the pass with the long 1-D transforms has exactly one item per thread, the
+//            pass with the short ones max / min times as many and loops)
 //   phase 3  quantize        : LPB lanes per block walk the scan (quant_dev.cuh), in place; tx_dist
 //   phase 4  qcoeffs out (coalesced), then inverse rows with the dequantizer on the load, in place
 //   phase 5  inverse columns + add onto the prediction + clamp, pixels stored
@@ -43,9 +45,11 @@ struct EncArgs {
 template <int W, int H>
 struct EncCfg {
   static_assert(W <= 32 && H <= 32, "64-point transforms go through the separate kernels");
-  static constexpr int MAXD = W > H ? W : H;
+  static constexpr int MAXD = W > H ? W : H, MIND = W < H ? W : H;
   static constexpr int THREADS = MAXD >= 32 ? 128 : 256;
-  static constexpr int BPC = THREADS / MAXD;  // blocks per CTA
+  // blocks per CTA: the pass with the LONG transforms (columns of a tall block, rows of a wide one) has THREADS items,
+  // one per thread; the other pass has MAXD / MIND times as many short ones and loops
+  static constexpr int BPC = THREADS / MIND;
   static constexpr int STRIDE = W + 1;
   static constexpr int BLK = H * STRIDE;  // words per block in shared memory
   static constexpr int CODED = W * H;
@@ -77,13 +81,12 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     const int nb = (int)min((long long)C::BPC, a.n - blk0);
 
     // ---- 1: diff + forward columns (forward.rs:1826-1869) ---------------------------------------
-    const bool col_live = tid < nb * W;
-    long long rec_off = 0;
-    if (col_live) {
-      const int b = tid / W, c = tid % W;
+#pragma unroll 1
+    for (int it = tid; it < nb * W; it += C::THREADS) {
+      const int b = it / W, c = it % W;
       const r1c_tx_job j = a.jobs[blk0 + b];
       const long long in_off = (long long)j.in_y * a.input.stride + j.in_x + c;
-      rec_off = (long long)j.pred_y * a.rec.stride + j.pred_x + c;
+      const long long rec_off = (long long)j.pred_y * a.rec.stride + j.pred_x + c;
       int v[H], o[H];
       if (a.px_bytes == 1) {
 #pragma unroll
@@ -117,9 +120,9 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     __syncthreads();
 
     // ---- 2: forward rows (forward.rs:1872-1898), in place ----------------------------------------
-    const bool row_live = tid < nb * H;
-    int *row = s_c + (tid / H) * C::BLK + (tid % H) * C::STRIDE;
-    if (row_live) {
+#pragma unroll 1
+    for (int it = tid; it < nb * H; it += C::THREADS) {  // it = b * H + r: rows of the slab are STRIDE words apart
+      int *row = s_c + it * C::STRIDE;
       int v[W], o[W];
 #pragma unroll
       for (int c = 0; c < W; c++) v[c] = row[c];
@@ -135,8 +138,8 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     __syncthreads();
 
     // ---- 3: quantize in place (quantize.rs:257-316) + tx-domain distortion (encoder.rs:1210-1224) --
-    for (int g = wrp; g < C::GROUPS; g += C::THREADS / 32) {
-      const int b = g * C::BPW + lane / C::LPB;  // blocks past nb go through the motions on stale words
+    for (int g = wrp; g < C::GROUPS && g * C::BPW < nb; g += C::THREADS / 32) {
+      const int b = g * C::BPW + lane / C::LPB;  // blocks past nb (same warp) go through the motions on stale words
       unsigned long long dist = quant::quantize_lanes<C::LPB, C::NCH, C::LOGW>(s_c + b * C::BLK, lane & (C::LPB - 1),
                                                                                lane & ~(C::LPB - 1), a.q, a.tx_dist != nullptr);
       if (a.tx_dist) {
@@ -169,8 +172,10 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     __syncthreads();
 
     // ---- 4b: dequantize (quantize.rs:318-334) + inverse rows (inverse.rs:2073-2092), in place -----
-    if (row_live) {
-      const int r = tid % H;
+#pragma unroll 1
+    for (int it = tid; it < nb * H; it += C::THREADS) {
+      int *row = s_c + it * C::STRIDE;
+      const int r = it % H;
       int v[W], o[W];
       const unsigned off = (1u << lts) - 1u;
 #pragma unroll
@@ -192,8 +197,11 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     __syncthreads();
 
     // ---- 5: inverse columns (inverse.rs:2095-2106) and the add (:2017-2028) -------------------------
-    if (col_live) {
-      const int b = tid / W, c = tid % W;
+#pragma unroll 1
+    for (int it = tid; it < nb * W; it += C::THREADS) {
+      const int b = it / W, c = it % W;
+      const r1c_tx_job j = a.jobs[blk0 + b];
+      const long long rec_off = (long long)j.pred_y * a.rec.stride + j.pred_x + c;
       const int *col = s_c + b * C::BLK + c;
       int v[H], o[H];
 #pragma unroll
