@@ -179,8 +179,22 @@ int r1c_sad_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                   const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out);
 int r1c_satd_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                    const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out);
+/* `use_satd` of the device entry: R1C_DIST_SAD, R1C_DIST_SATD, or R1C_DIST_SATD_I16 */
+#define R1C_DIST_SAD 0
+#define R1C_DIST_SATD 1
+#define R1C_DIST_SATD_I16 2
 int r1c_dist_batch_dev(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
                        const r1c_dist_job *d_jobs, int64_t n, int bit_depth, uint32_t *d_out);
+/* The `compat_i16_wrap` switch.  r1c_satd* follow get_satd_ref (i32 arithmetic,
+ * src/dist.rs:197-328), which is what the reference's check_asm asserts against.  The kernels
+ * this fork GENERATES and ships (build/kernel/gen/dist.rs:171-350) compute in i16 lanes for every
+ * pixel type (`let calc_prim = PrimType::I16`, :189-194, :252-257): identical for 8-bit input,
+ * but 10- and 12-bit blocks of high amplitude wrap (a term of 2^15 or more after the doubling).  This entry reproduces THAT arithmetic
+ * (wrapping i16 butterflies, abs().max() * 2 on the merged last stage, sign-extending cast to
+ * u32, wrapping sum) so that results can be compared with a reference binary built from the
+ * fork.  Not a fast path. */
+int r1c_satd_i16_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                       const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out);
 
 /* compute_lookahead_intra_costs, src/api/internal.rs:680-765: out[y*w_in_imp_b + x] = get_satd of the
  * 8x8 importance block (x, y) of the input luma plane against its DC_PRED prediction.  The
@@ -456,7 +470,15 @@ int r1c_full_search_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plan
  * starting from (best_mv = 0, lowest_cost = MAX).
  * Results: out[job*R1C_SB_RESULTS + r1c_sb_result_offset(bsize) + k], k =
  * raster index of the block inside the region; sizes not in bsize_mask are
- * left untouched. */
+ * left untouched.
+ * Precondition on cmv: the search centre must be a legal MV for every block of the region, i.e.
+ * inside get_mv_range of each of them (true for the centres the encoder uses: 0, or a coarse MV
+ * that full_search itself produced for the enclosing block).  r1c_me_sb_batch checks it
+ * (R1C_ERR_ARG); the _dev forms cannot look at device job lists and do NOT: for a centre whose
+ * whole window cmv +- range lies outside a block's range the reference clamps x_lo == x_hi to
+ * the boundary and still evaluates that column, whereas these kernels mask every candidate and
+ * return (mv 0, cost UINT64_MAX) for that block.  Callers with such centres clamp them first
+ * (r1c_mv_range) or use r1c_full_search_batch, which reproduces the clamped window. */
 #define R1C_SB_RESULTS 849
 typedef struct {
   int32_t po_x, po_y;   /* region origin, multiple of 4, region inside the frame */
@@ -536,7 +558,9 @@ int r1c_estimate_motion_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plan
  *                          k < n_cmvs[i]) quantised to full-pel, EPZS subsets A/B from `field` and
  *                          C from `prev_field` (NULL = no reference frame); predictors[i*17 ..]
  *                          holds counts[i] entries in the reference's order, the rest repeats the
- *                          last one (the layout r1c_diamond_search_batch takes with n_pred = 17). */
+ *                          last one (the layout r1c_diamond_search_batch takes with n_pred = 17).
+ * Jobs with bo outside [0, cols) x [0, rows) (or a bad bsize): R1C_ERR_ARG from the host forms;
+ * the _dev forms skip them on the device (nothing written / counts[i] = 0, zero predictors). */
 int r1c_save_block_motion_batch(r1c_ctx *ctx, r1c_mv *field, int cols, int rows,
                                 const r1c_block_job *jobs, const r1c_mv *mvs, int64_t n);
 int r1c_save_block_motion_batch_dev(r1c_ctx *ctx, r1c_mv *d_field, int cols, int rows,
@@ -607,7 +631,11 @@ int r1c_diamond_search_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_p
  *   refine 1 : + the tail of motion_estimation (src/me.rs:232-271): SATD
  *              re-evaluation of the full-pel winner when use_satd, then
  *              telescopic_subpel_search (steps 8, 4, 2 (,1)).
- * pmv = {0, 0} for both predictors (what the lookahead passes).
+ * pmv = {0, 0} for both predictors (what the lookahead passes).  This is full_search over
+ * +-range at step 1 around cmv = 0 for every block, NOT a replay of the encoder's per-block
+ * calls (FullSearch::full_pixel_me is +-16 at step 2 around a per-block cmv with the caller's
+ * pmv, src/me.rs:533-565): those go through r1c_me_sb_batch (step, cmv, pmv per region) or
+ * r1c_estimate_motion_batch (per block).
  * Result layout: for each BlockSize b of bsize_mask in enum order, the
  * (width / bw) x (height / bh) whole blocks in raster order:
  *   results[r1c_frame_me_offset(...b) + by * cols + bx].

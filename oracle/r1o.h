@@ -84,6 +84,9 @@ uint32_t r1o_sad(const void *org, ptrdiff_t org_stride, const void *ref,
                  ptrdiff_t ref_stride, int w, int h, int px_bytes);
 uint32_t r1o_satd(const void *org, ptrdiff_t org_stride, const void *ref,
                   ptrdiff_t ref_stride, int w, int h, int px_bytes);
+/* the fork's generated kernels: i16 lanes for every pixel type (build/kernel/gen/dist.rs:171-350, :553-556) */
+uint32_t r1o_satd_i16(const void *org, ptrdiff_t org_stride, const void *ref,
+                      ptrdiff_t ref_stride, int w, int h, int px_bytes);
 
 /* ---- motion compensation: src/mc.rs:201-408 ----------------------------- */
 /* src points at the block origin (already integer-offset); filters read

@@ -58,7 +58,7 @@ def lib():
         L.r1o_plane_pad.argtypes = [vp, P(PlaneCfg), i64, i64, i]
         L.r1o_plane_downsample.argtypes = [vp, P(PlaneCfg), vp, P(PlaneCfg), i]
         L.r1o_plane_downsample.restype = i
-        for f in (L.r1o_sad, L.r1o_satd):
+        for f in (L.r1o_sad, L.r1o_satd, L.r1o_satd_i16):
             f.argtypes = [vp, pd, vp, pd, i, i, i]
             f.restype = u32
         L.r1o_put_8tap.argtypes = [vp, pd, vp, pd, i, i, i, i, i, i, i, i]
@@ -180,6 +180,12 @@ def sad(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
 def satd(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
     return lib().r1o_satd(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
                           org.px_bytes)
+
+
+def satd_i16(org: OPlane, ox, oy, ref: OPlane, rx, ry, w, h):
+    """SATD as the fork's generated kernels compute it: i16 lanes (build/kernel/gen/dist.rs:171-350)"""
+    return lib().r1o_satd_i16(org.ptr(ox, oy), org.cfg.stride, ref.ptr(rx, ry), ref.cfg.stride, w, h,
+                              org.px_bytes)
 
 
 def diamond_search(org: OPlane, ref: OPlane, po, blk_w, blk_h, predictors, pmv, lambda_, use_satd, allow_hp, mv_range,

@@ -135,6 +135,57 @@ uint32_t r1o_satd(const void *org, ptrdiff_t os, const void *ref, ptrdiff_t rs,
   return (uint32_t)((sum + ((1ull << ln) >> 1)) >> ln);
 }
 
+/* The fork's GENERATED SATD kernels compute in i16 lanes for every pixel type (build/kernel/gen/dist.rs:189-194 and
+ * :252-257: `let calc_prim = PrimType::I16`, the per-type choice is left unused), so 10- and 12-bit input of high
+ * amplitude wraps where get_satd_ref (above) does not.  This restates that arithmetic (satd_4nx4n_kernel :171-241,
+ * satd_8nx8n_kernel :242-350, normalisation :553-556) for the `compat_i16_wrap` switch of SURVEY 7 / A16:
+ *   - every add / sub of the butterflies wraps in 16 bits; +,- mod 2^16 form a ring, so a lane holds the exact
+ *     Hadamard term reduced mod 2^16 whatever the order of the stages;
+ *   - the last butterfly of the second dimension is merged with the abs: (|a+b| + |a-b|) = 2 max(|a|, |b|), computed as
+ *     `a.abs().max(b.abs()) * 2` in i16 (abs and the doubling wrap), on the pairs the generated code forms: lanes k and
+ *     k + 4 of the two half-transforms (8x8: 4-point transforms of columns 0-3 and 4-7; 4x4: c0 +- c1 against c2 +- c3);
+ *   - each i16 lane is cast to u32 (`from_cast`: sign extension) and summed with wrapping u32 adds.
+ * Unpinned: the generator emits code for a SIMD crate that is not part of /root/reference, so this text cannot be
+ * executed here; it is test infrastructure for a later comparison with a real reference binary. */
+static int16_t w16(int32_t v) { return (int16_t)(uint16_t)(uint32_t)v; }
+static int16_t abs16(int16_t v) { return w16(v < 0 ? -(int32_t)v : (int32_t)v); }
+static uint32_t merged16(int32_t a, int32_t b) {
+  int16_t x = abs16(w16(a)), y = abs16(w16(b));
+  int16_t m = x > y ? x : y;
+  return (uint32_t)(int32_t)w16(2 * (int32_t)m);
+}
+
+uint32_t r1o_satd_i16(const void *org, ptrdiff_t os, const void *ref, ptrdiff_t rs, int w, int h, int px_bytes) {
+  int size = w < h ? w : h;
+  if (size > 8) size = 8;
+  uint32_t sum = 0;
+  for (int cy = 0; cy < h; cy += size)
+    for (int cx = 0; cx < w; cx += size) {
+      int32_t buf[64];
+      for (int r = 0; r < size; r++)
+        for (int c = 0; c < size; c++)
+          buf[r * size + c] = px_at(org, (cy + r) * os + cx + c, px_bytes) - px_at(ref, (cy + r) * rs + cx + c, px_bytes);
+      if (size == 4) {
+        hadamard4_1d(buf, 4, 1, 4); /* vertical, exact */
+        for (int k = 0; k < 4; k++) {
+          const int32_t *c = buf + 4 * k;
+          sum += merged16(c[0] + c[1], c[2] + c[3]);
+          sum += merged16(c[0] - c[1], c[2] - c[3]);
+        }
+      } else {
+        hadamard8_1d(buf, 8, 1, 8);
+        for (int j = 0; j < 8; j++) {
+          int32_t *c = buf + 8 * j;
+          hadamard4_1d(c, 1, 4, 1);     /* columns 0-3 of this vertical frequency */
+          hadamard4_1d(c + 4, 1, 4, 1); /* columns 4-7 */
+          for (int k = 0; k < 4; k++) sum += merged16(c[k], c[4 + k]);
+        }
+      }
+    }
+  int ln = size == 4 ? 2 : 3;
+  return (sum + ((1u << ln) >> 1)) >> ln;
+}
+
 /* ---- plane geometry ----------------------------------------------------- */
 static int64_t align_pow2(int64_t v, int n) { return (v + (1ll << n) - 1) & ~((1ll << n) - 1); }
 

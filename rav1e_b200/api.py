@@ -188,7 +188,15 @@ def sad_batch(ctx, plane_org, plane_ref, jobs, bit_depth, satd=False):
     return out
 
 
-def satd_batch(ctx, plane_org, plane_ref, jobs, bit_depth):
+def satd_batch(ctx, plane_org, plane_ref, jobs, bit_depth, compat_i16_wrap=False):
+    """get_satd over a batch.  compat_i16_wrap: the arithmetic of the kernels the fork generates (i16 lanes for every
+    pixel type, build/kernel/gen/dist.rs:171-350) instead of get_satd_ref's i32 -- differs on high-amplitude 10- / 12-bit
+    blocks only; for comparisons with a reference binary."""
+    if compat_i16_wrap:
+        jobs = _arr(jobs, DIST_JOB)
+        out = np.empty(jobs.size, dtype=np.uint32)
+        ctx.check(ctx.lib.r1c_satd_i16_batch(ctx.h, plane_org.h, plane_ref.h, _p(jobs), jobs.size, bit_depth, _p(out)))
+        return out
     return sad_batch(ctx, plane_org, plane_ref, jobs, bit_depth, satd=True)
 
 

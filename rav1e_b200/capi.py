@@ -151,6 +151,7 @@ SIGNATURES = {
     "r1c_satd": (_i, [_vp, _vp, _i, _i, _vp, _i, _i, _i, _i, _P(_u32)]),
     "r1c_sad_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_satd_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
+    "r1c_satd_i16_batch": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _vp]),
     "r1c_lookahead_intra_costs": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "r1c_lookahead_intra_costs_dev": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "r1c_dist_batch_dev": (_i, [_vp, _i, _vp, _vp, _vp, _i64, _i, _vp]),

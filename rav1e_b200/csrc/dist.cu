@@ -199,6 +199,80 @@ __global__ void __launch_bounds__(128) intra_cost_kernel(PlaneView v, int w_imp,
   out[i] = (acc + 4) >> 3;
 }
 
+// ---- SATD as the fork's GENERATED kernels compute it: i16 lanes for every pixel type ------------------------
+// (build/kernel/gen/dist.rs:171-350, normalisation :553-556; `let calc_prim = PrimType::I16` at :189-194 and :252-257).
+// Adds and subtractions mod 2^16 form a ring, so a lane of the generated code holds the exact Hadamard term reduced
+// mod 2^16; only the merged last stage -- a.abs().max(b.abs()) * 2 on i16, pairs (k, k + 4) of the two half transforms
+// of the second dimension -- the sign-extending cast to u32 and the wrapping u32 sum differ from get_satd_ref.  A
+// compatibility switch for comparisons with a reference binary, not a fast path: one warp per job, a lane per tile.
+__device__ __forceinline__ int w16(int v) { return (int)(short)v; }
+__device__ __forceinline__ uint32_t merged16(int a, int b) {
+  const int x = w16(abs(w16(a))), y = w16(abs(w16(b)));
+  return (uint32_t)w16(2 * max(x, y));
+}
+
+template <typename Px>
+__global__ void __launch_bounds__(128) satd_i16_kernel(const __grid_constant__ DistArgs a) {
+  const long long job = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (job >= a.n) return;
+  const int lane = threadIdx.x & 31;
+  const r1c_dist_job j = a.jobs[job];
+  const int w = blk_w_of(j.bsize), h = blk_h_of(j.bsize);
+  const int S = min(min(w, h), 8), tw = w / S, tiles = tw * (h / S);
+  const Px *po = (const Px *)a.org.p0 + (long long)j.org_y * a.org.stride + j.org_x;
+  const Px *pr = (const Px *)a.ref.p0 + (long long)j.ref_y * a.ref.stride + j.ref_x;
+  uint32_t sum = 0;
+  for (int t = lane; t < tiles; t += 32) {
+    const int ty = (t / tw) * S, tx = (t % tw) * S;
+    const Px *o = po + (long long)ty * a.org.stride + tx, *r = pr + (long long)ty * a.ref.stride + tx;
+    if (S == 4) {
+      int d[4][4];
+#pragma unroll
+      for (int y = 0; y < 4; y++)
+#pragma unroll
+        for (int x = 0; x < 4; x++) d[y][x] = (int)o[(long long)y * a.org.stride + x] - (int)r[(long long)y * a.ref.stride + x];
+#pragma unroll
+      for (int x = 0; x < 4; x++) {  // vertical 4-point Hadamard, exact
+        const int a0 = d[0][x] + d[1][x], a1 = d[0][x] - d[1][x], a2 = d[2][x] + d[3][x], a3 = d[2][x] - d[3][x];
+        d[0][x] = a0 + a2, d[1][x] = a1 + a3, d[2][x] = a0 - a2, d[3][x] = a1 - a3;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; k++) sum += merged16(d[k][0] + d[k][1], d[k][2] + d[k][3]) + merged16(d[k][0] - d[k][1], d[k][2] - d[k][3]);
+    } else {
+      int d[8][8];
+#pragma unroll
+      for (int y = 0; y < 8; y++)
+#pragma unroll
+        for (int x = 0; x < 8; x++) d[y][x] = (int)o[(long long)y * a.org.stride + x] - (int)r[(long long)y * a.ref.stride + x];
+#pragma unroll
+      for (int x = 0; x < 8; x++) {  // vertical 8-point Hadamard, exact (any order: only the sum over a row's terms matters)
+#pragma unroll
+        for (int st = 1; st < 8; st <<= 1)
+#pragma unroll
+          for (int y = 0; y < 8; y++)
+            if (!(y & st)) {
+              const int u = d[y][x], v = d[y | st][x];
+              d[y][x] = u + v, d[y | st][x] = u - v;
+            }
+      }
+#pragma unroll
+      for (int y = 0; y < 8; y++) {
+#pragma unroll
+        for (int hh = 0; hh < 8; hh += 4) {  // 4-point transforms of columns 0-3 and 4-7
+          const int a0 = d[y][hh] + d[y][hh + 1], a1 = d[y][hh] - d[y][hh + 1], a2 = d[y][hh + 2] + d[y][hh + 3], a3 = d[y][hh + 2] - d[y][hh + 3];
+          d[y][hh] = a0 + a2, d[y][hh + 1] = a1 + a3, d[y][hh + 2] = a0 - a2, d[y][hh + 3] = a1 - a3;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) sum += merged16(d[y][k], d[y][4 + k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 16; m; m >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, m);
+  const int ln = S == 4 ? 2 : 3;
+  if (lane == 0) a.out[job] = (sum + ((1u << ln) >> 1)) >> ln;
+}
+
 int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plane *ref,
                 const r1c_dist_job *d_jobs, int64_t n, uint32_t *d_out) {
   if (n == 0) return R1C_OK;
@@ -210,7 +284,11 @@ int launch_dist(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_plan
   a.n = n;
   r1c_prof_begin(ctx, R1C_PROF_DIST);
   const bool vec = planes_vec_ok(org) && planes_vec_ok(ref);
-  if (org->px_bytes == 1) launch_dist_pb<1>(ctx, use_satd, vec, a);
+  if (use_satd == R1C_DIST_SATD_I16) {
+    const unsigned grid = (unsigned)((n + 3) / 4);
+    if (org->px_bytes == 1) satd_i16_kernel<uint8_t><<<grid, 128, 0, ctx->stream>>>(a);
+    else satd_i16_kernel<uint16_t><<<grid, 128, 0, ctx->stream>>>(a);
+  } else if (org->px_bytes == 1) launch_dist_pb<1>(ctx, use_satd, vec, a);
   else launch_dist_pb<2>(ctx, use_satd, vec, a);
   r1c_prof_end(ctx, R1C_PROF_DIST);
   R1C_LAUNCH_CHECK(ctx);
@@ -264,12 +342,17 @@ extern "C" int r1c_satd_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plan
                               const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out) {
   return dist_batch_host(ctx, 1, org, ref, jobs, n, bit_depth, out);
 }
+extern "C" int r1c_satd_i16_batch(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                                  const r1c_dist_job *jobs, int64_t n, int bit_depth, uint32_t *out) {
+  return dist_batch_host(ctx, R1C_DIST_SATD_I16, org, ref, jobs, n, bit_depth, out);
+}
 extern "C" int r1c_dist_batch_dev(r1c_ctx *ctx, int use_satd, const r1c_plane *org,
                                   const r1c_plane *ref, const r1c_dist_job *d_jobs, int64_t n,
                                   int bit_depth, uint32_t *d_out) {
   int rc = check_common(ctx, org, ref, bit_depth);
   if (rc) return rc;
   R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (d_jobs && d_out)), R1C_ERR_ARG, "null job/result array");
+  R1C_REQUIRE(ctx, use_satd >= R1C_DIST_SAD && use_satd <= R1C_DIST_SATD_I16, R1C_ERR_ARG, "bad distortion kind %d", use_satd);
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   return launch_dist(ctx, use_satd, org, ref, d_jobs, n, d_out);
 }

@@ -35,6 +35,8 @@ __global__ void save_motion_kernel(FieldArgs a) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.n) return;
   const r1c_block_job j = a.jobs[i];
+  // a job outside the field (device lists are not validated by the host) writes nothing
+  if (j.bsize < 0 || j.bsize >= R1C_BLOCK_SIZES_ALL || j.bo_x < 0 || j.bo_y < 0 || j.bo_x >= a.cols || j.bo_y >= a.rows) return;
   const int x1 = min(j.bo_x + blk_w_of(j.bsize) / 4, a.cols), y1 = min(j.bo_y + blk_h_of(j.bsize) / 4, a.rows);
   const r1c_mv mv = a.mvs[i];
   for (int y = j.bo_y; y < y1; y++)
@@ -47,6 +49,11 @@ __global__ void subset_predictors_kernel(FieldArgs a) {
   const r1c_block_job j = a.jobs[i];
   r1c_mv *p = a.out + i * 17;
   int n = 0;
+  if (j.bo_x < 0 || j.bo_y < 0 || j.bo_x >= a.cols || j.bo_y >= a.rows) {  // outside the field: no predictors, count 0
+    for (int k = 0; k < 17; k++) p[k] = r1c_mv{0, 0};
+    a.out_n[i] = 0;
+    return;
+  }
   p[n++] = r1c_mv{0, 0};
   const int nc = min((int)a.n_cmvs[i], 7);
   for (int k = 0; k < nc; k++) p[n++] = fullpel(a.mvs[i * 7 + k]);

@@ -123,6 +123,39 @@ def test_satd_extreme_amplitude(r, ctx, oracle):
         assert r.get_sad(ctx, d_a, (0, 0), d_b, (0, 0), b, 12) == w * h * 4095
 
 
+def test_satd_compat_i16_wrap(r, ctx, oracle):
+    """the `compat_i16_wrap` switch (the arithmetic of the fork's generated kernels, build/kernel/gen/dist.rs:171-350):
+    equal to get_satd_ref for 8-bit planes and for 10- / 12-bit input of ordinary amplitude, different from it -- and
+    equal to the oracle's restatement -- on high-amplitude 10- / 12-bit blocks"""
+    rng = np.random.default_rng(16)
+    L = oracle.lib()
+    for pb, bd in BD:
+        a = rng.integers(0, 1 << bd, size=(128, 128))
+        cases = [("noise", a, np.clip(a + rng.integers(-60, 61, size=a.shape), 0, (1 << bd) - 1)),
+                 ("random", a, rng.integers(0, 1 << bd, size=a.shape))]
+        yy, xx = np.indices((128, 128))
+        board = ((xx + yy) & 1) * ((1 << bd) - 1)
+        cases.append(("checkerboard", board, (1 << bd) - 1 - board))
+        for name, x, y in cases:
+            o_a, d_a = twin_plane(r, oracle, ctx, 128, 128, pb, bd, data=x.astype(np.uint16 if pb == 2 else np.uint8))
+            o_b, d_b = twin_plane(r, oracle, ctx, 128, 128, pb, bd, data=y.astype(np.uint16 if pb == 2 else np.uint8))
+            jobs = np.zeros(22 * 3, dtype=r.DIST_JOB)
+            for i in range(jobs.size):
+                jobs[i] = (int(rng.integers(0, 64)), int(rng.integers(0, 64)), int(rng.integers(-8, 64)), int(rng.integers(-8, 64)), i % 22)
+                if L.r1o_block_width(i % 22) > 64 or L.r1o_block_height(i % 22) > 64:
+                    jobs[i] = (0, 0, 0, 0, i % 22)
+            got = r.satd_batch(ctx, d_a, d_b, jobs, bd, compat_i16_wrap=True)
+            ref = r.satd_batch(ctx, d_a, d_b, jobs, bd)
+            want = np.array([oracle.satd_i16(o_a, int(j["org_x"]), int(j["org_y"]), o_b, int(j["ref_x"]), int(j["ref_y"]),
+                                             L.r1o_block_width(int(j["bsize"])), L.r1o_block_height(int(j["bsize"]))) for j in jobs],
+                            dtype=np.uint32)
+            assert np.array_equal(got, want), (bd, name)
+            if bd == 8 or name == "noise":
+                assert np.array_equal(got, ref), (bd, name)
+            elif name == "checkerboard":  # one term of 64 * max: its halves double to 2^16 - 64 and wrap
+                assert (got != ref).sum() > jobs.size // 2, (bd, name)
+
+
 def test_dist_errors(r, ctx, oracle):
     rng = np.random.default_rng(5)
     _, d = twin_plane(r, oracle, ctx, 64, 64, 1, 8, rng, xpad=8, ypad=8)

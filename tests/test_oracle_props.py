@@ -394,3 +394,35 @@ def test_importance_propagation_properties(oracle):
     assert np.allclose(imp, np.log2(1 + got / intra.astype(np.float32)), rtol=1e-6)
     z = np.array([[5.0]], np.float32)
     assert oracle.importance_finalize(np.zeros((1, 1), np.uint32), z)[0, 0] == 0.0
+
+
+def test_satd_i16_lanes_equal_reference_semantics_until_they_wrap(oracle):
+    """r1o_satd_i16 (the fork's generated kernels, i16 lanes for every pixel type, build/kernel/gen/dist.rs:171-350):
+    the merged last butterfly (|a + b| + |a - b| = 2 max(|a|, |b|)) makes it EQUAL to get_satd_ref whenever no lane
+    leaves 16 bits -- always for 8-bit input (|term| <= 64 * 255) -- and different for 10- / 12-bit blocks of high
+    amplitude (a flat 10-bit difference of 1023: the DC halves are 32 * 1023 each and their doubling wraps)"""
+    rng = np.random.default_rng(23)
+    L = oracle.lib()
+    for pb, bd in ((1, 8), (2, 10), (2, 12)):
+        a = oracle.OPlane(64, 64, 0, 0, 8, 8, pb)
+        b = oracle.OPlane(64, 64, 0, 0, 8, 8, pb)
+        top = (1 << bd) - 1
+        yy, xx = np.indices((64, 64))
+        board = ((xx + yy) & 1) * top
+        for name, x, y in (("noise", None, None), ("random", rng.integers(0, top + 1, size=(64, 64)), rng.integers(0, top + 1, size=(64, 64))),
+                           ("flat", np.full((64, 64), top), np.zeros((64, 64), int)), ("checkerboard", board, top - board)):
+            if x is None:
+                x = rng.integers(0, top + 1, size=(64, 64))
+                y = np.clip(x + rng.integers(-60, 61, size=(64, 64)), 0, top)
+            a.visible[...] = x
+            b.visible[...] = y
+            differ = 0
+            for bs in range(22):
+                w, h = L.r1o_block_width(bs), L.r1o_block_height(bs)
+                if w > 64 or h > 64:
+                    continue
+                differ += oracle.satd(a, 0, 0, b, 0, 0, w, h) != oracle.satd_i16(a, 0, 0, b, 0, 0, w, h)
+            if bd == 8 or name == "noise":
+                assert differ == 0, (bd, name)
+            if bd >= 10 and name in ("flat", "checkerboard"):
+                assert differ > 0, (bd, name)
