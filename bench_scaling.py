@@ -1,10 +1,11 @@
 """Within-frame sharding of the hot path over the GPUs of one box (north_star: "by AV1 tile"), measured by
 bench.py at every N next to the frame-sharded headline:
 
-  * me_strong():  ONE 3840x2160 10-bit frame pair, full-search ME +-64 + SATD sub-pel tail, superblock rows split over the
-                  ranks (rav1e_b200.shard.split_sb_rows; the reference splits the same work by tile,
-                  src/encoder.rs:2772-2781), both planes resident on every rank, every rank copies the (mv, cost) segments
-                  of its rows to page-locked host memory.  Strong scaling: the frame is fixed, time = max over ranks.
+  * me_strong():  ONE 3840x2160 10-bit frame pair, full-search ME +-64 + SATD sub-pel tail, the frame cut into one tile of
+                  whole superblocks per rank (rav1e_b200.shard.split_tiles; the reference splits the same work by tile,
+                  src/encoder.rs:2772-2781), both planes resident on every rank, every rank packs the (mv, cost) results of
+                  its tile (r1c_frame_me_compact_dev) and copies them to page-locked host memory.  Strong scaling: the
+                  frame is fixed, time = max over ranks.
   * mc_tx_sharded(): the 4K 10-bit MC put list (19 block sizes, one mixed list) split by tile column (8 columns of 480 px,
                   src/tiling/tiler.rs:87-109) and the forward-transform blocks split evenly: same rule, no collective.
 
@@ -34,14 +35,6 @@ def _barrier(torch, dist, world):
     torch.cuda.synchronize()
 
 
-def _segments(slots):
-    """sorted slot indices -> list of contiguous [start, end) ranges"""
-    if slots.size == 0:
-        return []
-    cut = np.nonzero(np.diff(slots) != 1)[0] + 1
-    return [(int(s[0]), int(s[-1]) + 1) for s in np.split(slots, cut)]
-
-
 def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
     lib = ctx.lib
     steps0 = steps
@@ -52,24 +45,22 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
     h_ref = torch.from_numpy(bench_kernels.padded(p_ref.cfg, ref)).pin_memory()
     p_org.upload(h_org.numpy())
     p_ref.upload(h_ref.numpy())
-    rows = shard.split_sb_rows(H4K, world)
-    lo, hi = rows[rank]
-    params = r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA, refine=1, use_satd=1, sb_rows=(lo, hi))
+    tiles = shard.split_tiles(W4K, H4K, world)
+    (lo, hi), (clo, chi) = tiles[rank]
+    params = r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA, refine=1, use_satd=1, sb_rows=(lo, hi), sb_cols=(clo, chi))
     n_res = r.frame_me_count(params)
-    slots = shard.shard_slots(W4K, H4K, r.ALL_SIZES_TO_64, lo, hi)
-    segs = _segments(slots)
+    n_mine = lib.r1c_frame_me_shard_count(ctx.h, C.byref(params))
+    assert n_mine == shard.shard_slots(W4K, H4K, r.ALL_SIZES_TO_64, lo, hi, clo, chi).size
     d_res = torch.zeros(n_res * 16, dtype=torch.uint8, device="cuda")
-    h_res = torch.zeros(n_res * 16, dtype=torch.uint8).pin_memory()
-
-    def gather():
-        with torch.cuda.stream(ext):
-            for s, e in segs:
-                h_res[s * 16:e * 16].copy_(d_res[s * 16:e * 16], non_blocking=True)
+    d_cmp = torch.zeros(max(n_mine, 1) * 16, dtype=torch.uint8, device="cuda")
+    h_res = torch.zeros(max(n_mine, 1) * 16, dtype=torch.uint8).pin_memory()
 
     def step_dev():
-        if hi > lo:
+        if n_mine:
             ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD4K, d_res.data_ptr()))
-            gather()
+            ctx.check(lib.r1c_frame_me_compact_dev(ctx.h, C.byref(params), d_res.data_ptr(), d_cmp.data_ptr()))
+            with torch.cuda.stream(ext):
+                h_res.copy_(d_cmp, non_blocking=True)
 
     def step_e2e():
         ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org.h, h_org.data_ptr()))
@@ -93,23 +84,25 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
     # the timed region is at least 2 s of device time on every N: a 3-step estimate (max over ranks) sets the count
     steps = 3
     est = timed(step_e2e)
-    steps = max(steps0, int(np.ceil(2000.0 / max(est, 1e-3))))
+    steps = max(steps0, int(np.ceil(2300.0 / max(est, 1e-3))))
     ms = timed(step_dev)
     ms_e2e = timed(step_e2e)
     mpix = W4K * H4K / 1e6
     return {
-        "workload": "ONE 3840x2160 10-bit frame pair, full search +-64, 19 sizes, SATD sub-pel tail; superblock rows split "
-                    "over the ranks, planes replicated, (mv, cost) segments copied to page-locked host memory",
+        "workload": "ONE 3840x2160 10-bit frame pair, full search +-64, 19 sizes, SATD sub-pel tail; the frame cut into N tiles "
+                    "of whole superblocks (rav1e_b200.shard.split_tiles), one per rank, planes replicated, every rank packs "
+                    "its (mv, cost) results and copies them to page-locked host memory in one piece",
         "scaling": "strong", "n_gpus": world, "value": mpix / (ms / 1e3), "unit": "Mpix/s", "ms_per_frame": ms,
         "steps": steps, "timed_region_s": steps * ms / 1e3,
-        "sb_rows_per_rank": [b - a for a, b in rows], "sb_rows": (H4K + 63) // 64,
-        "d2h_bytes_this_rank": int(sum(e - s for s, e in segs) * 16), "d2h_copies_this_rank": len(segs),
+        "tiles_sb_rows_x_cols": ["%dx%d" % (b - a, d - c) for (a, b), (c, d) in tiles], "superblocks": [(H4K + 63) // 64, (W4K + 63) // 64],
+        "d2h_bytes_this_rank": int(n_mine * 16), "d2h_copies_this_rank": 1,
         "e2e": {"value": mpix / (ms_e2e / 1e3), "unit": "Mpix/s", "ms_per_frame": ms_e2e,
                 "h2d_bytes_per_rank": int(h_org.numel() * 2 + h_ref.numel() * 2),
                 "note": "every rank uploads both whole planes (MVs may point anywhere in the reference): the upload does "
                         "not shrink with N"},
-        "note": "34 superblock rows do not divide by 8: the largest share is ceil(34 / N) rows, so the best possible "
-                "speed-up is 34 / ceil(34 / N) = %.2f at N = %d" % (34 / -(-34 // world), world)}
+        "note": "largest tile = %d of %d superblocks: the best possible speed-up is %.2f at N = %d"
+                % (max((b - a) * (d - c) for (a, b), (c, d) in tiles), 34 * 60,
+                   34 * 60 / max((b - a) * (d - c) for (a, b), (c, d) in tiles), world)}
 
 
 def mc_tx_sharded(ctx, r, torch, dist, ext, flush, rank, world, reps=3):

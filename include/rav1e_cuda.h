@@ -652,6 +652,9 @@ typedef struct {
    * origin lies in superblock rows [sb_row_lo, sb_row_hi) are computed; the
    * other entries of `results` are left untouched.  0, 0 = the whole frame. */
   int32_t sb_row_lo, sb_row_hi;
+  /* ... and in superblock columns [sb_col_lo, sb_col_hi): with the rows, an AV1 tile (a rectangle of
+   * superblocks, src/tiling/tiler.rs:87-109).  0, 0 = all columns. */
+  int32_t sb_col_lo, sb_col_hi;
 } r1c_frame_me_params;
 /* number of result entries of the whole frame; offset / grid of one size
  * (returns -1 for sizes outside the mask) */
@@ -663,6 +666,13 @@ int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                  const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results);
 int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                      const r1c_frame_me_params *p, int bit_depth, r1c_me_result *d_results);
+/* The results of the tile `p` describes, packed: d_compact[i] = d_results[slot_i], slots in the
+ * order BlockSize, block row, block column (the order of the frame layout restricted to the
+ * tile); r1c_frame_me_shard_count() entries.  One contiguous device-to-host copy then returns a
+ * rank's share of a frame (the tile's slots are not contiguous in the frame layout). */
+int64_t r1c_frame_me_shard_count(r1c_ctx *ctx, const r1c_frame_me_params *p);
+int r1c_frame_me_compact_dev(r1c_ctx *ctx, const r1c_frame_me_params *p,
+                             const r1c_me_result *d_results, r1c_me_result *d_compact);
 /* plane upload without the trailing synchronisation (pinned or pageable host
  * memory; ordered on the context stream) */
 int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);

@@ -574,9 +574,10 @@ ALL_SIZES_TO_64 = sum(1 << b for b in range(22) if b not in (13, 14, 15))
 
 
 def make_frame_me_params(width, height, range_x, range_y, lambda_, bsize_mask=ALL_SIZES_TO_64,
-                         refine=1, use_satd=1, allow_hp=False, sb_rows=(0, 0)):
+                         refine=1, use_satd=1, allow_hp=False, sb_rows=(0, 0), sb_cols=(0, 0)):
+    """sb_rows / sb_cols: the tile (superblock rows [lo, hi) x columns [lo, hi)) a sharded call computes; (0, 0) = all"""
     return capi.FrameMeParams(width, height, range_x, range_y, lambda_, bsize_mask, int(refine),
-                              int(use_satd), int(allow_hp), sb_rows[0], sb_rows[1])
+                              int(use_satd), int(allow_hp), sb_rows[0], sb_rows[1], sb_cols[0], sb_cols[1])
 
 
 def frame_me_count(params):

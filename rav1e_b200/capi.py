@@ -126,7 +126,7 @@ class FrameMeParams(C.Structure):
                 ("range_y", C.c_int32), ("lambda_", C.c_uint32), ("bsize_mask", C.c_uint32),
                 ("refine", C.c_int32), ("use_satd", C.c_int32),
                 ("allow_high_precision_mv", C.c_int32), ("sb_row_lo", C.c_int32),
-                ("sb_row_hi", C.c_int32)]
+                ("sb_row_hi", C.c_int32), ("sb_col_lo", C.c_int32), ("sb_col_hi", C.c_int32)]
 
 
 # every symbol include/rav1e_cuda.h declares: name -> (restype, argtypes)
@@ -214,6 +214,8 @@ SIGNATURES = {
     "r1c_frame_me_offset": (_i64, [_P(FrameMeParams), _i, _P(C.c_int32), _P(C.c_int32)]),
     "r1c_frame_me": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
     "r1c_frame_me_dev": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
+    "r1c_frame_me_shard_count": (_i64, [_vp, _P(FrameMeParams)]),
+    "r1c_frame_me_compact_dev": (_i, [_vp, _P(FrameMeParams), _vp, _vp]),
     "r1c_plane_upload_async": (_i, [_vp, _vp, _vp]),
     "r1c_int_peak": (_i, [_vp, _i, _P(C.c_double)]),
     "r1c_profile": (_i, [_vp, _i]),

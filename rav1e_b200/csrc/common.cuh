@@ -44,7 +44,7 @@ struct r1c_ctx {
   // (frame size, parameters) seen, resident on the device
   struct {
     int valid;
-    int32_t key[10];
+    int32_t key[12];
     void *d_sbjobs, *d_map, *d_subjobs;
     int64_t n_sb, n_blocks;
   } frame_me;

@@ -27,7 +27,8 @@ bool params_ok(const r1c_frame_me_params *p) {
   return p && p->width >= 4 && p->height >= 4 && (p->width & 3) == 0 && (p->height & 3) == 0 &&
          p->width <= 16384 && p->height <= 16384 && p->range_x >= 0 && p->range_y >= 0 && p->bsize_mask != 0 &&
          (p->bsize_mask >> R1C_BLOCK_SIZES_ALL) == 0 && p->sb_row_lo >= 0 && p->sb_row_hi >= 0 &&
-         (p->sb_row_hi == 0 || p->sb_row_hi > p->sb_row_lo);
+         (p->sb_row_hi == 0 || p->sb_row_hi > p->sb_row_lo) && p->sb_col_lo >= 0 && p->sb_col_hi >= 0 &&
+         (p->sb_col_hi == 0 || p->sb_col_hi > p->sb_col_lo);
 }
 
 void make_layout(const r1c_frame_me_params *p, Layout *l) {
@@ -69,16 +70,19 @@ __global__ void scatter_kernel(const r1c_me_result *__restrict__ src, const int2
   *(uint4 *)(dst + map[i].y) = *(const uint4 *)(src + i);
 }
 
-void key_of(const r1c_frame_me_params *p, int32_t key[10]) {
+bool is_whole(const r1c_frame_me_params *p) { return p->sb_row_hi == 0 && p->sb_col_hi == 0; }
+
+void key_of(const r1c_frame_me_params *p, int32_t key[12]) {
   key[0] = p->width; key[1] = p->height; key[2] = p->range_x; key[3] = p->range_y;
   key[4] = (int32_t)p->lambda; key[5] = (int32_t)p->bsize_mask; key[6] = p->use_satd;
   key[7] = p->allow_high_precision_mv; key[8] = p->sb_row_lo; key[9] = p->sb_row_hi;
+  key[10] = p->sb_col_lo; key[11] = p->sb_col_hi;
 }
 
 // job lists of one (frame geometry, parameters): superblock jobs, the
 // (superblock slot -> frame slot) map and the sub-pel jobs of every block
 int build_lists(r1c_ctx *ctx, const r1c_frame_me_params *p) {
-  int32_t key[10];
+  int32_t key[12];
   key_of(p, key);
   if (ctx->frame_me.valid && memcmp(key, ctx->frame_me.key, sizeof key) == 0) return R1C_OK;
   ctx->frame_me.valid = 0;
@@ -92,12 +96,14 @@ int build_lists(r1c_ctx *ctx, const r1c_frame_me_params *p) {
   make_layout(p, &l);
   const int sbc = (p->width + 63) / 64, sbr = (p->height + 63) / 64;
   const int r_lo = p->sb_row_hi ? p->sb_row_lo : 0, r_hi = p->sb_row_hi ? (p->sb_row_hi < sbr ? p->sb_row_hi : sbr) : sbr;
-  const int64_t n_sb = r_hi > r_lo ? (int64_t)(r_hi - r_lo) * sbc : 0;
+  const int c_lo = p->sb_col_hi ? p->sb_col_lo : 0, c_hi = p->sb_col_hi ? (p->sb_col_hi < sbc ? p->sb_col_hi : sbc) : sbc;
+  const int tc = c_hi > c_lo ? c_hi - c_lo : 0;  // superblock columns of the tile
+  const int64_t n_sb = r_hi > r_lo ? (int64_t)(r_hi - r_lo) * tc : 0;
   r1c_sb_job *sb = (r1c_sb_job *)calloc((size_t)(n_sb ? n_sb : 1), sizeof(r1c_sb_job));
   // upper bound on the blocks of the shard
   int64_t cap = 0;
   for (int b = 0; b < R1C_BLOCK_SIZES_ALL; b++)
-    if (l.off[b] >= 0) cap += (int64_t)l.cols[b] * (((int64_t)(r_hi - r_lo) * 64) / blk_h_of(b) + 1);
+    if (l.off[b] >= 0 && n_sb) cap += (((int64_t)tc * 64) / blk_w_of(b) + 1) * (((int64_t)(r_hi - r_lo) * 64) / blk_h_of(b) + 1);
   int2 *map = (int2 *)malloc((size_t)(cap ? cap : 1) * sizeof(int2));
   r1c_subpel_job *sj = (r1c_subpel_job *)calloc((size_t)(cap ? cap : 1), sizeof(r1c_subpel_job));
   if (!sb || !map || !sj) {
@@ -105,8 +111,8 @@ int build_lists(r1c_ctx *ctx, const r1c_frame_me_params *p) {
     return r1c_set_err(ctx, R1C_ERR_NOMEM, "frame_me: host job lists");
   }
   for (int64_t i = 0; i < n_sb; i++) {
-    sb[i].po_x = (int32_t)(i % sbc) * 64;
-    sb[i].po_y = (int32_t)(r_lo + i / sbc) * 64;
+    sb[i].po_x = (int32_t)(c_lo + i % tc) * 64;
+    sb[i].po_y = (int32_t)(r_lo + i / tc) * 64;
     sb[i].bsize_mask = p->bsize_mask;
   }
   const int w_in_b = p->width / 4, h_in_b = p->height / 4;
@@ -120,7 +126,8 @@ int build_lists(r1c_ctx *ctx, const r1c_frame_me_params *p) {
       if (sy < r_lo || sy >= r_hi) continue;
       for (int bx = 0; bx < l.cols[b]; bx++) {
         const int x = bx * bw, sx = x / 64;
-        const int64_t sbi = (int64_t)(sy - r_lo) * sbc + sx;
+        if (sx < c_lo || sx >= c_hi) continue;
+        const int64_t sbi = (int64_t)(sy - r_lo) * tc + (sx - c_lo);
         map[n].x = (int)(sbi * R1C_SB_RESULTS + sb_off + ((y & 63) / bh) * per_row + (x & 63) / bw);
         map[n].y = (int)(l.off[b] + (int64_t)by * l.cols[b] + bx);
         r1c_subpel_job &j = sj[n];
@@ -202,7 +209,7 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
   sp.allow_high_precision_mv = p->allow_high_precision_mv;
   R1C_REQUIRE(ctx, org->px_bytes == ref->px_bytes && bit_depth_ok(bit_depth, org->px_bytes), R1C_ERR_ARG,
               "frame_me: bit_depth %d vs %d-byte pixels", bit_depth, org->px_bytes);
-  const bool whole = p->sb_row_hi == 0;
+  const bool whole = is_whole(p);
   const unsigned grid = (unsigned)((n + 255) / 256);
   const r1c_sb_job *d_sbs = (const r1c_sb_job *)ctx->frame_me.d_sbjobs;
   const int2 *d_map = (const int2 *)ctx->frame_me.d_map;
@@ -240,6 +247,27 @@ extern "C" int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_pl
   return R1C_OK;
 }
 
+extern "C" int64_t r1c_frame_me_shard_count(r1c_ctx *ctx, const r1c_frame_me_params *p) {
+  if (!ctx || !params_ok(p)) return -1;
+  if (cudaSetDevice(ctx->device) != cudaSuccess || build_lists(ctx, p)) return -1;
+  return ctx->frame_me.n_blocks;
+}
+
+extern "C" int r1c_frame_me_compact_dev(r1c_ctx *ctx, const r1c_frame_me_params *p, const r1c_me_result *d_results,
+                                        r1c_me_result *d_compact) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, params_ok(p), R1C_ERR_ARG, "frame_me: bad parameters");
+  R1C_REQUIRE(ctx, d_results && d_compact, R1C_ERR_ARG, "frame_me: null result array");
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = build_lists(ctx, p);
+  if (rc) return rc;
+  const int64_t n = ctx->frame_me.n_blocks;
+  if (n == 0) return R1C_OK;
+  gather_frame_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_results, (const int2 *)ctx->frame_me.d_map, n, d_compact);
+  R1C_LAUNCH_CHECK(ctx);
+  return R1C_OK;
+}
+
 extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
                             const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results) {
   if (!ctx || !org || !ref) return R1C_ERR_ARG;
@@ -259,7 +287,7 @@ extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane 
     if ((rc = r1c_stage_host(ctx, 3, rb, &h_res))) return rc;
   }
   if ((rc = r1c_scratch_dev(ctx, 14, rb, &d_res))) return rc;
-  const bool whole = p->sb_row_hi == 0;
+  const bool whole = is_whole(p);
   if (!whole) {  // entries outside the shard keep the caller's values
     if (!direct) memcpy(h_res, results, rb);
     R1C_CUDA(ctx, cudaMemcpyAsync(d_res, h_res, rb, cudaMemcpyHostToDevice, ctx->stream));

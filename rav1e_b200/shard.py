@@ -30,9 +30,42 @@ def split_sb_rows(height, world):
     return out
 
 
-def shard_slots(width, height, bsize_mask, sb_row_lo, sb_row_hi):
-    """frame_me result slots (include/rav1e_cuda.h layout) whose block origin lies in
-    superblock rows [sb_row_lo, sb_row_hi)"""
+def _split(n, parts):
+    base, extra = divmod(n, parts)
+    out, lo = [], 0
+    for r in range(parts):
+        hi = lo + base + (1 if r < extra else 0)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
+def split_tiles(width, height, world):
+    """-> list (per rank) of ((sb_row_lo, sb_row_hi), (sb_col_lo, sb_col_hi)): the frame cut into a grid of `world`
+    tiles of whole superblocks (AV1 tiles, src/tiling/tiler.rs:87-109), the grid shape that minimises the largest
+    tile; rank = tile_row * tile_cols + tile_col.  3840x2160 over 8 ranks: 34 x 60 superblocks as 2 x 4 tiles of
+    17 x 15 (superblock rows alone would give 5, 5, 4, 4, ... of 34: 6.8x at best)."""
+    rows, cols = (height + 63) // 64, (width + 63) // 64
+    best = None
+    for tr in range(1, world + 1):
+        if world % tr:
+            continue
+        tc = world // tr
+        if tr > rows or tc > cols:
+            continue
+        area = -(-rows // tr) * -(-cols // tc)
+        if best is None or area < best[0]:
+            best = (area, tr, tc)
+    if best is None:  # more ranks than superblocks along both axes: rows only, some ranks idle
+        return [(rc, (0, cols)) for rc in split_sb_rows(height, world)]
+    _, tr, tc = best
+    return [(rr, cc) for rr in _split(rows, tr) for cc in _split(cols, tc)]
+
+
+def shard_slots(width, height, bsize_mask, sb_row_lo, sb_row_hi, sb_col_lo=0, sb_col_hi=0):
+    """frame_me result slots (include/rav1e_cuda.h layout) whose block origin lies in superblock rows
+    [sb_row_lo, sb_row_hi) and columns [sb_col_lo, sb_col_hi) (0, 0 = all columns), in the order BlockSize, block row,
+    block column -- the order r1c_frame_me_compact_dev packs them in"""
     lib = capi.load()
     idx, off = [], 0
     for b in range(len(capi.BLOCK_SIZES)):
@@ -42,7 +75,10 @@ def shard_slots(width, height, bsize_mask, sb_row_lo, sb_row_hi):
         cols, rows = width // bw, height // bh
         by = np.arange(rows)
         sel = by[((by * bh) // 64 >= sb_row_lo) & ((by * bh) // 64 < sb_row_hi)]
-        idx.append((off + sel[:, None] * cols + np.arange(cols)[None, :]).ravel())
+        bx = np.arange(cols)
+        if sb_col_hi:
+            bx = bx[((bx * bw) // 64 >= sb_col_lo) & ((bx * bw) // 64 < sb_col_hi)]
+        idx.append((off + sel[:, None] * cols + bx[None, :]).ravel())
         off += cols * rows
     return np.concatenate(idx).astype(np.int64) if idx else np.zeros(0, dtype=np.int64)
 

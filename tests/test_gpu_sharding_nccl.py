@@ -1,6 +1,6 @@
 """N > 1 path on the GPUs: the CUDA-side twin of tests/test_sharding_gloo.py.  Two ranks, one GPU each, NCCL process
-group: every rank runs r1c_frame_me on its own device for its share of the superblock rows of ONE frame pair
-(rav1e_b200.shard.split_sb_rows, the split the reference makes by tile, src/encoder.rs:2772-2781), the (mv, cost)
+group: every rank runs r1c_frame_me on its own device for its tile (superblock rows x columns) of ONE frame pair
+(rav1e_b200.shard.split_tiles, the split the reference makes by tile, src/encoder.rs:2772-2781), the (mv, cost)
 shards are gathered to rank 0 through the process group and must equal both the whole-frame search of one GPU and the
 oracle.  Skipped on boxes with fewer than two GPUs (the driver's 1-GPU tier); `gpurun --gpus 2` runs it."""
 import os
@@ -39,10 +39,10 @@ def _worker(rank, world, port, pb, bd, q):
     o_org, o_ref = _planes(r1o, pb, bd)
     org = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(o_org.data)
     ref = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(o_ref.data)
-    lo, hi = shard.split_sb_rows(H, world)[rank]
-    p = r.make_frame_me_params(W, H, RNG, RNG, LAM, refine=1, use_satd=1, sb_rows=(lo, hi))
+    (lo, hi), (clo, chi) = shard.split_tiles(W, H, world)[rank]
+    p = r.make_frame_me_params(W, H, RNG, RNG, LAM, refine=1, use_satd=1, sb_rows=(lo, hi), sb_cols=(clo, chi))
     local = r.frame_me(ctx, org, ref, p, bd)
-    slots = shard.shard_slots(W, H, r.ALL_SIZES_TO_64, lo, hi)
+    slots = shard.shard_slots(W, H, r.ALL_SIZES_TO_64, lo, hi, clo, chi)
     merged = shard.gather_frame_results(local, slots, local.size, dist)
     if rank == 0:
         whole = r.frame_me(ctx, org, ref, r.make_frame_me_params(W, H, RNG, RNG, LAM, refine=1, use_satd=1), bd)
@@ -54,7 +54,7 @@ def _worker(rank, world, port, pb, bd, q):
 
 @pytest.mark.timeout(600)
 @pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
-def test_two_rank_nccl_sb_row_shards_equal_whole_frame(pb, bd):
+def test_two_rank_nccl_tile_shards_equal_whole_frame(pb, bd):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")

@@ -1,4 +1,4 @@
-"""N > 1 path on CPU: world_size-2 gloo run of the superblock-row sharding + gather
+"""N > 1 path on CPU: world_size-2 gloo run of the tile (superblock rows x columns) sharding + gather
 (rav1e_b200.shard).  The compute inside each rank is the oracle (no GPU here); what
 is under test is the partition and the merge: shards are disjoint, cover every
 block, and the gathered array equals the whole-frame result."""
@@ -32,8 +32,8 @@ def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     mask = (1 << api.BLOCK["BLOCK_8X8"]) | (1 << api.BLOCK["BLOCK_16X16"]) | (1 << api.BLOCK["BLOCK_64X64"])
-    lo, hi = shard.split_sb_rows(H, world)[rank]
-    slots = shard.shard_slots(W, H, mask, lo, hi)
+    (lo, hi), (clo, chi) = shard.split_tiles(W, H, world)[rank]  # 128 x 200: two tile columns of 4 superblock rows
+    slots = shard.shard_slots(W, H, mask, lo, hi, clo, chi)
     o_org, o_ref = _planes(r1o)
     mv, cost = r1o.frame_me(o_org, o_ref, RNG, RNG, LAM, mask, 0, 0, 0, 8, idx=slots)
     local = np.zeros(cost.size, dtype=api.ME_RESULT)
@@ -57,6 +57,23 @@ def test_sb_row_split_is_a_partition():
         p = api.make_frame_me_params(1920, 1080, 8, 8, 1)
         assert np.array_equal(allidx, np.arange(api.frame_me_count(p)))
     assert shard.split_frames(5, 2) == [[0, 2, 4], [1, 3]]
+
+
+def test_tile_split_is_a_partition_and_balanced():
+    sys.path.insert(0, ROOT)
+    from rav1e_b200 import api, shard
+    for (w, h) in ((3840, 2160), (1920, 1080), (256, 200), (64, 64)):
+        p = api.make_frame_me_params(w, h, 8, 8, 1)
+        rows, cols = (h + 63) // 64, (w + 63) // 64
+        for world in (1, 2, 3, 4, 6, 8):
+            tiles = shard.split_tiles(w, h, world)
+            assert len(tiles) == world
+            sl = [shard.shard_slots(w, h, api.ALL_SIZES_TO_64, lo, hi, clo, chi) for (lo, hi), (clo, chi) in tiles]
+            assert np.array_equal(np.sort(np.concatenate(sl)), np.arange(api.frame_me_count(p))), (w, h, world)
+            assert sum((hi - lo) * (chi - clo) for (lo, hi), (clo, chi) in tiles) == rows * cols
+    # 4K over 8 ranks: 2 x 4 tiles of 17 x 15 superblocks -- every rank the same share (rows alone: 5 of 34 at most)
+    t8 = shard.split_tiles(3840, 2160, 8)
+    assert {(hi - lo, chi - clo) for (lo, hi), (clo, chi) in t8} == {(17, 15)}
 
 
 @pytest.mark.timeout(300)
