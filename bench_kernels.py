@@ -313,6 +313,39 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
             qsum[key] += k_ms
             qper[key]["%dx%d" % (w, h)] = round(k_ms * 1e3, 1)
         qcoeffs += n * coded
+    # the same pass on coefficients shaped like a real residual: energy decaying with frequency (sigma = 900 exp(-0.45 (r + c)))
+    # under the zig-zag scan, so most of a large block lies past its end of block -- the chunks the quantizer skips
+    ssum, sper = 0.0, {}
+    for ts in ([int(v) for v in only.split(",")] if only else range(19)):
+        w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
+        cw, ch = min(w, 32), min(h, 32)
+        n = n_samples // (w * h)
+        rr, cc = np.indices((h, w))
+        sig = 900.0 * np.exp(-0.45 * (rr + cc))
+        blk = np.rint(rng.standard_normal((min(n, 4096), h, w)) * sig).astype(np.int32)
+        qs = torch.from_numpy(np.tile(blk.reshape(-1), -(-n // blk.shape[0]))[: n * w * h].copy()).cuda()
+        order = sorted(range(cw * ch), key=lambda p_: (p_ // cw + p_ % cw, p_ // cw if (p_ // cw + p_ % cw) & 1 else p_ % cw))
+        zz = torch.from_numpy(np.array(order, dtype=np.int16)).cuda()
+        qc = r.QuantizationContext().update(lib, ts, 0, 120, 147)
+
+        def f_qs():
+            ctx.check(lib.r1c_quantize_batch_dev(ctx.h, C.byref(qc.c), ts, zz.data_ptr(), qs.data_ptr(), qout.data_ptr(),
+                                                 rout.data_ptr(), dout.data_ptr(), n))
+        f_qs()
+        ctx.sync()
+        _kernel_ms(ctx, 6)
+        _timed(torch, ext, flush, f_qs, reps)
+        k_ms = _kernel_ms(ctx, 6)[0] / reps
+        ssum += k_ms
+        sper["%dx%d" % (w, h)] = round(k_ms * 1e3, 1)
+        del qs
+    gbs = qcoeffs * 12 / (ssum / 1e3) / 1e9
+    out["quant_4k10_fused_sparse"] = {
+        "workload": "the fused pass on coefficients shaped like a real residual (sigma = 900 exp(-0.45 (row + col)), zig-zag scan, "
+                    "qstep 147: most of a large block lies past its end of block)",
+        "value": qcoeffs / 1e6 / (ssum / 1e3), "unit": "Mcoeff/s", "ms": ssum, "coeffs": qcoeffs, "kernel_us_by_tx_size": sper,
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
+                     "alg_bytes_per_coeff": 12, "peak_source": hbm_how}}
     for key, bpc, what in (("q", 8, "quantize"), ("fused", 12, "quantize + dequantize + tx-domain distortion in one pass")):
         gbs = qcoeffs * bpc / (qsum[key] / 1e3) / 1e9
         out["quant_4k10_" + key] = {
@@ -438,6 +471,8 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
     # -------------------------- whole-frame motion estimation on a 4K 10-bit frame pair (u16 planes)
     if not os.environ.get("R1C_BENCH_SIZES") and not os.environ.get("R1C_BENCH_TXSIZES"):
         out["me_4k10_fullsearch_pm64"] = me_frame_line(ctx, r, torch, ext, flush, 3840, 2160, 10, 64)
+        # 12-bit planes: the first-generation superblock search (me_sb.cu) and the generic sub-pel composition
+        out["me_1080p12_fullsearch_pm64"] = me_frame_line(ctx, r, torch, ext, flush, 1920, 1080, 12, 64, reps=1)
     return out
 
 
@@ -464,7 +499,7 @@ def me_frame_line(ctx, r, torch, ext, flush, W, H, BD, RANGE, reps=2):
     ms = _timed(torch, ext, flush, step, reps)
     launches = (ctx.launches - l0) // reps
     sb_ms = _kernel_ms(ctx, 0)[0] / reps
-    _kernel_ms(ctx, 1)
+    mc_ms = _kernel_ms(ctx, 1)[0] / reps
     rf_ms = _kernel_ms(ctx, 2)[0] / reps
     ctx.check(lib.r1c_profile(ctx.h, 0))
     try:
@@ -475,7 +510,9 @@ def me_frame_line(ctx, r, torch, ext, flush, W, H, BD, RANGE, reps=2):
     ops = 2.0 * W * H * (2 * RANGE + 1) ** 2
     return {"workload": "%dx%d %d-bit full-search ME +-%d, 19 sizes, SAD then SATD sub-pel (planes resident)" % (W, H, BD, RANGE),
             "value": W * H / 1e3 / ms, "unit": "Mpix/s", "ms": ms, "launches_per_frame": launches,
-            "blocks_per_frame": int(n_res), "kernel_ms": {"me_sb2_kernel": sb_ms, "me_refine_kernel": rf_ms},
-            "roofline": {"bound": "int32_alu", "kernel": "me_sb2_kernel (u16 variant)", "achieved": ops / (sb_ms / 1e3) / 1e9 if sb_ms else None,
+            "blocks_per_frame": int(n_res),
+            "kernel_ms": {"me_sb2_kernel": sb_ms, "me_refine_kernel": rf_ms} if BD <= 10 else
+                         {"me_sb_kernel (first generation)": sb_ms, "sub-pel put_8tap launches": mc_ms, "sub-pel cost launches": rf_ms},
+            "roofline": {"bound": "int32_alu", "kernel": "me_sb2_kernel (u16 variant)" if BD <= 10 else "me_sb_kernel (12-bit fallback)", "achieved": ops / (sb_ms / 1e3) / 1e9 if sb_ms else None,
                          "peak": ipeak, "unit": "Gop/s", "frac": ops / (sb_ms / 1e3) / 1e9 / ipeak if sb_ms else None,
                          "alg_ops_per_launch": ops, "peak_source": ihow}}

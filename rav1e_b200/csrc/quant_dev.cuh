@@ -75,14 +75,26 @@ __device__ __forceinline__ unsigned long long quantize_lanes_fast(int32_t *sb, i
   const uint32_t blk_all = BMASK << sh;               // this block's lanes in a ballot
   const uint32_t blk_below = ((1u << l) - 1u) << sh;  // the earlier ones
   const uint32_t dq_mask = (1u << lts) - 1u;
+  // chunks that lie past the end of block of EVERY block of the warp are zeroed without going through the
+  // quantizer (residuals of a real encode leave most of a large block's scan behind the end of block)
+  int weob = eob;
+#pragma unroll
+  for (int m = 16; m >= LPB; m >>= 1) weob = max(weob, __shfl_xor_sync(0xffffffffu, weob, m));
   __syncwarp();
   uint32_t mode = 1;  // level_mode at the start of the chunk (the same in all lanes of a block)
   unsigned long long dist = 0;
+  // rolled loops stop at the warp's last live chunk (the tail is zeroed below); unrolled ones test every chunk
+  const int nlive = ROLLED ? min(NCH, weob / LPB + 1) : NCH;
 #pragma unroll UNR
-  for (int c = 0; c < NCH; c++) {
+  for (int c = 0; c < nlive; c++) {
     const int k = c * LPB + l;
     const int pos_c = ROLLED ? sidx((int)__ldg(a.scan + k)) : pos_keep[c];
     const int32_t raw_c = ROLLED ? sb[pos_c] : raw_keep[c];  // each position is read and rewritten by its one lane
+    if (!ROLLED && c * LPB > weob) {  // warp-uniform
+      sb[pos_c] = 0;
+      if (want_dist) dist += (unsigned long long)(long long)(int32_t)((uint32_t)raw_c * (uint32_t)raw_c);
+      continue;
+    }
     const int32_t coeff = (int32_t)((uint32_t)raw_c << lts);
     const bool neg = coeff < 0;
     const uint32_t y0 = (uint32_t)(neg ? -coeff : coeff);
@@ -115,6 +127,14 @@ __device__ __forceinline__ unsigned long long quantize_lanes_fast(int32_t *sb, i
       const int32_t r = (int32_t)((uint32_t)q * (pos_c == 0 ? a.qc.dc_quant : d_ac) + ((uint32_t)(q >> 31) & dq_mask)) >> lts;
       const uint32_t e = (uint32_t)raw_c - (uint32_t)r;
       dist += (unsigned long long)(long long)(int32_t)(e * e);  // (c * c) as u64, wrapping i32 product
+    }
+  }
+  if (ROLLED) {
+    for (int c = nlive; c < NCH; c++) {
+      const int pos_c = sidx((int)__ldg(a.scan + c * LPB + l));
+      const uint32_t raw_c = (uint32_t)sb[pos_c];
+      sb[pos_c] = 0;
+      if (want_dist) dist += (unsigned long long)(long long)(int32_t)(raw_c * raw_c);
     }
   }
   return dist;
