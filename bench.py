@@ -6,7 +6,13 @@ estimation, +-64 px, every block of all 19 sizes 4x4..64x64, SAD search then the
 SATD re-evaluation + telescopic sub-pel tail of MotionEstimation::motion_estimation
 (src/me.rs:193-271).  A "step" is one lookahead window of 32 distinct frame pairs
 (cur, ref) -> every block's (best_mv, lowest_cost), 3 kernel launches per pair.
-Metric: Mpix/s = frame pixels / time.
+Metric: Mpix/s = frame pixels / time.  The window's frames go to two r1c_ctx
+(two CUDA streams) in turn, as a caller with a lookahead window would drive the
+library ("one r1c_ctx per thread"): the tail of one frame's kernels is filled by
+the next frame's, and on the host-buffer path (`e2e`) the copies of one frame
+overlap the kernels of another.  The same steps on ONE stream are timed first:
+that pass gives the per-kernel durations of `roofline` and is reported as
+`one_stream`.
 
     python bench.py [--gpus N] [--steps K] [--warmup W]      # the CUDA path
     python bench.py --impl reference ...                     # CPU arm: the oracle
@@ -23,6 +29,7 @@ Only the `cpu_baseline` leg and `--impl reference` touch oracle/; the timed CUDA
 path is librav1e_cuda.so through its C ABI (rav1e_b200.capi).
 """
 import argparse
+import concurrent.futures
 import ctypes as C
 import json
 import os
@@ -303,6 +310,55 @@ def main():
             ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref[i].h, h_ref[i].data_ptr()))
             ctx.check(lib.r1c_frame_me(ctx.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, h_res.ctypes.data))
 
+    # the same step with NCTX contexts (= streams; "one r1c_ctx per thread") taking frames in turn: the tail
+    # of one frame's kernels is filled by the next frame's, and on the host-buffer path (one host thread per context) the
+    # copies of one frame overlap the kernels of another
+    NCTX = max(1, int(os.environ.get("R1C_BENCH_CTX", "2")))
+    ctxs = [ctx] + [r.Context(local) for _ in range(NCTX - 1)]
+    exts = [ext] + [torch.cuda.ExternalStream(c.stream, device=local) for c in ctxs[1:]]
+    h_ress = [h_res] + [torch.zeros(n_res * 16, dtype=torch.uint8).pin_memory().numpy().view(r.ME_RESULT) for _ in ctxs[1:]]
+    d_ress = [d_res] + [torch.empty(n_res * 16, dtype=torch.uint8, device="cuda") for _ in ctxs[1:]]
+    pool = concurrent.futures.ThreadPoolExecutor(NCTX)
+
+    def _frames(c, res, idx):
+        for i in idx:
+            c.check(lib.r1c_plane_upload_async(c.h, p_org[i].h, h_org[i].data_ptr()))
+            c.check(lib.r1c_plane_upload_async(c.h, p_ref[i].h, h_ref[i].data_ptr()))
+            c.check(lib.r1c_frame_me(c.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, res.ctypes.data))
+
+    def step_dev_nctx():
+        for i in range(F):
+            c, d = ctxs[i % NCTX], d_ress[i % NCTX]
+            c.check(lib.r1c_frame_me_dev(c.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, d.data_ptr()))
+
+    def step_e2e_nctx():
+        for f in [pool.submit(_frames, ctxs[k], h_ress[k], range(k, F, NCTX)) for k in range(NCTX)]:
+            f.result()
+
+    def timed_nctx(fn, k):
+        """as timed(), for a step that runs on all contexts' streams: the other streams wait for the start event, the
+        step ends when the last stream is done, and the next step's flush waits for that"""
+        evs = [(torch.cuda.Event(enable_timing=True), [torch.cuda.Event(enable_timing=True) for _ in exts]) for _ in range(k)]
+        barrier()
+        for a, ends in evs:
+            with torch.cuda.stream(ext):
+                bench_kernels.flush_l2(torch, flush)
+                a.record(ext)
+            for e in exts[1:]:
+                e.wait_event(a)
+            fn()
+            for e, b in zip(exts, ends):
+                b.record(e)
+            for b in ends[1:]:
+                ext.wait_event(b)
+        barrier()
+        ms = sum(max(a.elapsed_time(b) for b in ends) for a, ends in evs)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
@@ -337,18 +393,32 @@ def main():
     sampler = ClockSampler(local)
     sampler.start()
     l0 = ctx.launches
-    ms_total = timed(step_dev, K)
-    launches = ctx.launches - l0
+    ms_serial = timed(step_dev, K)  # one stream, kernels one after the other: the per-kernel durations of the roofline
+    launches_serial = ctx.launches - l0
     prof = {}
     for name, slot in (("me_sb2_kernel", 0), ("subpel_mc_generic", 1), ("me_refine_kernel", 2)):
         ms, n = C.c_double(), C.c_int64()
         ctx.check(lib.r1c_profile_read(ctx.h, slot, C.byref(ms), C.byref(n)))
         prof[name] = (ms.value, n.value)
     ctx.check(lib.r1c_profile(ctx.h, 0))
+    # ---- the same K steps with alternate frames on two contexts (two streams): the tail of one frame's kernels is
+    # filled by the other frame's -- the throughput a caller with a lookahead window gets, and the headline `value`
+    step_dev_nctx()
+    l0 = sum(c.launches for c in ctxs)
+    ms_total = timed_nctx(step_dev_nctx, K)
+    launches = sum(c.launches for c in ctxs) - l0
     # ---- end to end: host planes in, host results out, every step ------------------
     step_e2e()
-    ms_e2e = timed(step_e2e, K)
+    ms_e2e_serial = timed(step_e2e, K)
+    step_e2e_nctx()
+    l1 = sum(c.launches for c in ctxs)
+    ms_e2e = timed_nctx(step_e2e_nctx, K)
+    launches_e2e = sum(c.launches for c in ctxs) - l1
     clocks = sampler.summary()
+    pool.shutdown()
+    for c in ctxs[1:]:
+        c.close()
+    del d_ress[1:], h_ress[1:]
 
     mpix = F * W * H / 1e6
     value = world * mpix / (ms_total / K / 1e3)
@@ -377,7 +447,7 @@ def main():
                 "unit": "Gop/s", "frac": achieved / ipeak, "traffic": ncu_traffic(),
                 "peak_source": ipeak_how,
                 "alg_ops_per_launch": ALG_INT_OPS, "ms_per_launch": sb_ms,
-                "share_of_step": prof["me_sb2_kernel"][0] / ms_total,
+                "share_of_step": prof["me_sb2_kernel"][0] / ms_serial,
                 "hbm": {"achieved": alg_bytes / (sb_ms / 1e3) / 1e9, "peak": hpeak, "unit": "GB/s",
                         "frac": alg_bytes / (sb_ms / 1e3) / 1e9 / hpeak, "alg_bytes_per_launch": alg_bytes,
                         "peak_source": hpeak_how},
@@ -392,18 +462,26 @@ def main():
             roof["me_refine_kernel"] = {"bound": "int32_alu", "achieved": rf_ops / (rf_ms / 1e3) / 1e9, "peak": ipeak,
                                         "unit": "Gop/s", "frac": rf_ops / (rf_ms / 1e3) / 1e9 / ipeak,
                                         "alg_ops_per_launch": rf_ops, "ms_per_launch": rf_ms,
-                                        "share_of_step": prof["me_refine_kernel"][0] / ms_total,
+                                        "share_of_step": prof["me_refine_kernel"][0] / ms_serial,
                                         "note": "MACs counted as one op each; the kernel issues them as DP4A (4 MACs)"}
         line = {
             "metric": "Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world, "steps": K, "warmup": W_,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u8", "data": "synthetic",
             "config": dict(CONFIG),
-            "setup": {"blocks_per_frame": int(n_res), "frames_per_step": F, "launches_per_frame": 3,
+            "one_stream": {"value": world * mpix / (ms_serial / K / 1e3), "ms_per_step": ms_serial / K, "gpu_launches": int(launches_serial),
+                           "note": "the same K steps on ONE context / stream, kernels strictly one after the other: the pass the "
+                                   "roofline's per-kernel durations and share_of_step are measured in; `value` hands the "
+                                   "frames to %d contexts (streams) in turn, which fills the tail of each kernel" % NCTX},
+            "setup": {"blocks_per_frame": int(n_res), "frames_per_step": F, "launches_per_frame": 3, "contexts": NCTX,
                       "flush": "256 MiB written, then 256 MiB read back, untimed, before every step"},
             "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / K,
-                    "path": "per frame pair: r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (pinned host result array)"},
+                    "ms_per_step": ms_e2e / K, "gpu_launches": int(launches_e2e),
+                    "path": "per frame pair: r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (pinned host result "
+                            "array); %d r1c_ctx (streams), one host thread each, take the frames in turn, so the copies of one "
+                            "frame overlap the kernels of another" % NCTX,
+                    "one_context": {"value": world * mpix / (ms_e2e_serial / K / 1e3), "ms_per_step": ms_e2e_serial / K,
+                                    "note": "the same calls from one thread on one context: copies and kernels serialised"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,
