@@ -47,37 +47,63 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
     p_ref.upload(h_ref.numpy())
     tiles = shard.split_tiles(W4K, H4K, world)
     (lo, hi), (clo, chi) = tiles[rank]
-    params = r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA, refine=1, use_satd=1, sb_rows=(lo, hi), sb_cols=(clo, chi))
-    n_res = r.frame_me_count(params)
-    n_mine = lib.r1c_frame_me_shard_count(ctx.h, C.byref(params))
+    # the rank's tile goes to two contexts (two streams) as two sub-tiles, so that the tail of one sub-tile's kernels is
+    # filled by the other's (a rank has 5 waves of work items or fewer per kernel at N = 8)
+    if chi - clo >= 2:
+        cm = (clo + chi + 1) // 2
+        subs = [((lo, hi), (clo, cm)), ((lo, hi), (cm, chi))]
+    elif hi - lo >= 2:
+        rm = (lo + hi + 1) // 2
+        subs = [((lo, rm), (clo, chi)), ((rm, hi), (clo, chi))]
+    else:
+        subs = [((lo, hi), (clo, chi))]
+    ctxs = [ctx] + [r.Context(torch.cuda.current_device()) for _ in subs[1:]]
+    exts = [ext] + [torch.cuda.ExternalStream(c.stream, device=torch.cuda.current_device()) for c in ctxs[1:]]
+    n_res = r.frame_me_count(r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA))
+    d_res = torch.zeros(n_res * 16, dtype=torch.uint8, device="cuda")  # frame layout, the sub-tiles write disjoint slots
+    work = []
+    for c, e, ((a0, a1), (b0, b1)) in zip(ctxs, exts, subs):
+        p = r.make_frame_me_params(W4K, H4K, RANGE, RANGE, LAMBDA, refine=1, use_satd=1, sb_rows=(a0, a1), sb_cols=(b0, b1))
+        n = lib.r1c_frame_me_shard_count(c.h, C.byref(p))
+        assert n == shard.shard_slots(W4K, H4K, r.ALL_SIZES_TO_64, a0, a1, b0, b1).size
+        work.append((c, e, p, n, torch.zeros(max(n, 1) * 16, dtype=torch.uint8, device="cuda"),
+                     torch.zeros(max(n, 1) * 16, dtype=torch.uint8).pin_memory()))
+    n_mine = sum(w[3] for w in work)
     assert n_mine == shard.shard_slots(W4K, H4K, r.ALL_SIZES_TO_64, lo, hi, clo, chi).size
-    d_res = torch.zeros(n_res * 16, dtype=torch.uint8, device="cuda")
-    d_cmp = torch.zeros(max(n_mine, 1) * 16, dtype=torch.uint8, device="cuda")
-    h_res = torch.zeros(max(n_mine, 1) * 16, dtype=torch.uint8).pin_memory()
+    up_done = torch.cuda.Event()
 
     def step_dev():
-        if n_mine:
-            ctx.check(lib.r1c_frame_me_dev(ctx.h, p_org.h, p_ref.h, C.byref(params), BD4K, d_res.data_ptr()))
-            ctx.check(lib.r1c_frame_me_compact_dev(ctx.h, C.byref(params), d_res.data_ptr(), d_cmp.data_ptr()))
-            with torch.cuda.stream(ext):
-                h_res.copy_(d_cmp, non_blocking=True)
+        for c, e, p, n, d_cmp, h_cmp in work:
+            if n:
+                c.check(lib.r1c_frame_me_dev(c.h, p_org.h, p_ref.h, C.byref(p), BD4K, d_res.data_ptr()))
+                c.check(lib.r1c_frame_me_compact_dev(c.h, C.byref(p), d_res.data_ptr(), d_cmp.data_ptr()))
+                with torch.cuda.stream(e):
+                    h_cmp.copy_(d_cmp, non_blocking=True)
 
     def step_e2e():
         ctx.check(lib.r1c_plane_upload_async(ctx.h, p_org.h, h_org.data_ptr()))
         ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref.h, h_ref.data_ptr()))
+        up_done.record(ext)
+        for e in exts[1:]:
+            e.wait_event(up_done)
         step_dev()
 
     def timed(fn):
-        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        evs = [(torch.cuda.Event(enable_timing=True), [torch.cuda.Event(enable_timing=True) for _ in exts]) for _ in range(steps)]
         _barrier(torch, dist, world)
-        for a, b in evs:
+        for a, ends in evs:
             with torch.cuda.stream(ext):
                 bench_kernels.flush_l2(torch, flush)
                 a.record(ext)
+            for e in exts[1:]:
+                e.wait_event(a)
             fn()
-            b.record(ext)
+            for e, b in zip(exts, ends):
+                b.record(e)
+            for b in ends[1:]:
+                ext.wait_event(b)  # the next step's flush (and upload) starts when every stream is done
         _barrier(torch, dist, world)
-        return _max_over_ranks(torch, dist, world, sum(a.elapsed_time(b) for a, b in evs)) / steps
+        return _max_over_ranks(torch, dist, world, sum(max(a.elapsed_time(b) for b in ends) for a, ends in evs)) / steps
 
     for _ in range(warmup):
         step_dev()
@@ -88,14 +114,20 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
     ms = timed(step_dev)
     ms_e2e = timed(step_e2e)
     mpix = W4K * H4K / 1e6
+    n_work = len(work)
+    work.clear()  # the page-locked blocks were used on the extra streams: they go before those streams do
+    torch.cuda.synchronize()
+    for c in ctxs[1:]:
+        c.close()
     return {
         "workload": "ONE 3840x2160 10-bit frame pair, full search +-64, 19 sizes, SATD sub-pel tail; the frame cut into N tiles "
-                    "of whole superblocks (rav1e_b200.shard.split_tiles), one per rank, planes replicated, every rank packs "
-                    "its (mv, cost) results and copies them to page-locked host memory in one piece",
+                    "of whole superblocks (rav1e_b200.shard.split_tiles), one per rank, planes replicated; a rank runs its tile "
+                    "as two sub-tiles on two contexts (streams), packs the (mv, cost) results of each and copies them to "
+                    "page-locked host memory",
         "scaling": "strong", "n_gpus": world, "value": mpix / (ms / 1e3), "unit": "Mpix/s", "ms_per_frame": ms,
         "steps": steps, "timed_region_s": steps * ms / 1e3,
         "tiles_sb_rows_x_cols": ["%dx%d" % (b - a, d - c) for (a, b), (c, d) in tiles], "superblocks": [(H4K + 63) // 64, (W4K + 63) // 64],
-        "d2h_bytes_this_rank": int(n_mine * 16), "d2h_copies_this_rank": 1,
+        "d2h_bytes_this_rank": int(n_mine * 16), "d2h_copies_this_rank": n_work, "contexts_per_rank": n_work,
         "e2e": {"value": mpix / (ms_e2e / 1e3), "unit": "Mpix/s", "ms_per_frame": ms_e2e,
                 "h2d_bytes_per_rank": int(h_org.numel() * 2 + h_ref.numel() * 2),
                 "note": "every rank uploads both whole planes (MVs may point anywhere in the reference): the upload does "
