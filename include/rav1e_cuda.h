@@ -676,6 +676,12 @@ int r1c_frame_me_compact_dev(r1c_ctx *ctx, const r1c_frame_me_params *p,
 /* plane upload without the trailing synchronisation (pinned or pageable host
  * memory; ordered on the context stream) */
 int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);
+/* rows [row_lo, row_hi) of the ALLOCATION only (row 0 = the first padding row; host_data still
+ * points at row 0 of the whole padded plane).  A rank that searches one tile of a frame needs
+ * the tile's rows of `org` and those rows +- (range_y + 16) of `ref`
+ * (rav1e_b200.shard.tile_plane_rows), not the whole planes. */
+int r1c_plane_upload_rows_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data,
+                                int64_t row_lo, int64_t row_hi);
 
 /* ------------------------------------------------------------------------
  * Block importances of the lookahead:

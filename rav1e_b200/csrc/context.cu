@@ -258,6 +258,18 @@ extern "C" int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *p, const void *ho
   return R1C_OK;
 }
 
+extern "C" int r1c_plane_upload_rows_async(r1c_ctx *ctx, r1c_plane *p, const void *host, int64_t row_lo, int64_t row_hi) {
+  if (!ctx || !p || !host) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, row_lo >= 0 && row_lo <= row_hi && row_hi <= p->cfg.alloc_height, R1C_ERR_ARG,
+              "upload rows [%lld, %lld) outside the allocation of %lld rows", (long long)row_lo, (long long)row_hi,
+              (long long)p->cfg.alloc_height);
+  if (row_lo == row_hi) return R1C_OK;
+  const size_t pitch = (size_t)p->cfg.stride * p->px_bytes;
+  R1C_CUDA(ctx, cudaMemcpyAsync((uint8_t *)p->d_data + (size_t)row_lo * pitch, (const uint8_t *)host + (size_t)row_lo * pitch,
+                                (size_t)(row_hi - row_lo) * pitch, cudaMemcpyHostToDevice, ctx->stream));
+  return R1C_OK;
+}
+
 extern "C" int r1c_plane_download(r1c_ctx *ctx, const r1c_plane *p, void *host) {
   if (!ctx || !p || !host) return R1C_ERR_ARG;
   size_t bytes = (size_t)p->cfg.stride * p->cfg.alloc_height * p->px_bytes;

@@ -62,6 +62,15 @@ def split_tiles(width, height, world):
     return [(rr, cc) for rr in _split(rows, tr) for cc in _split(cols, tc)]
 
 
+def tile_plane_rows(cfg, sb_row_lo, sb_row_hi, range_y):
+    """rows [lo, hi) of a plane's ALLOCATION (r1c_plane_upload_rows_async) that the search of superblock rows
+    [sb_row_lo, sb_row_hi) can touch: the tile's rows +- (range_y + 16): the full-pel window, the +-2 px the sub-pel
+    steps add, and the 3 + 4 rows of the 8-tap filter"""
+    lo = int(cfg.yorigin) + sb_row_lo * 64 - range_y - 16
+    hi = int(cfg.yorigin) + min(sb_row_hi * 64, int(cfg.height)) + range_y + 16
+    return max(lo, 0), min(hi, int(cfg.alloc_height))
+
+
 def shard_slots(width, height, bsize_mask, sb_row_lo, sb_row_hi, sb_col_lo=0, sb_col_hi=0):
     """frame_me result slots (include/rav1e_cuda.h layout) whose block origin lies in superblock rows
     [sb_row_lo, sb_row_hi) and columns [sb_col_lo, sb_col_hi) (0, 0 = all columns), in the order BlockSize, block row,

@@ -706,6 +706,34 @@ def test_frame_me_tiles_equal_whole_frame_and_pack(r, ctx, oracle):
             assert np.array_equal(part, whole), (bd, world)
 
 
+def test_tile_search_needs_only_its_rows_of_the_planes(r, ctx, oracle):
+    """r1c_plane_upload_rows_async + shard.tile_plane_rows: planes pre-filled with garbage, only the rows a tile can touch
+    uploaded -- the tile's results equal the whole-frame search on the full planes (8- and 10-bit, sub-pel tail on)"""
+    from rav1e_b200 import shard
+    W, H, RNGE = 192, 448, 16
+    for pb, bd in ((1, 8), (2, 10)):
+        o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, W, H, pb, bd, 91)
+        whole = r.frame_me(ctx, d_org, d_ref, r.make_frame_me_params(W, H, RNGE, RNGE, 31), bd)
+        junk = np.full(o_org.data.shape, (1 << bd) - 1, dtype=o_org.data.dtype)
+        junk[::2, 1::3] = 0
+        for (lo, hi) in ((0, 2), (2, 5), (5, 7)):
+            g_org = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(junk)
+            g_ref = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(junk)
+            r0, r1 = shard.tile_plane_rows(g_ref.cfg, lo, hi, RNGE)
+            assert r1 - r0 < g_ref.cfg.alloc_height  # a real subset
+            for g, o in ((g_org, o_org), (g_ref, o_ref)):
+                host = np.ascontiguousarray(o.data)
+                ctx.check(ctx.lib.r1c_plane_upload_rows_async(ctx.h, g.h, host.ctypes.data, r0, r1))
+            ctx.sync()
+            p = r.make_frame_me_params(W, H, RNGE, RNGE, 31, sb_rows=(lo, hi))
+            slots = shard.shard_slots(W, H, r.ALL_SIZES_TO_64, lo, hi)
+            got = r.frame_me(ctx, g_org, g_ref, p, bd)
+            assert np.array_equal(got[slots], whole[slots]), (bd, lo, hi)
+    with pytest.raises(r.Rav1eCudaError) as e:
+        ctx.check(ctx.lib.r1c_plane_upload_rows_async(ctx.h, d_org.h, o_org.data.ctypes.data, 0, d_org.cfg.alloc_height + 1))
+    assert e.value.code == r.capi.R1C_ERR_ARG
+
+
 def test_profile_hooks_count_launches(r, ctx, oracle):
     o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, 128, 128, 1, 8, 5)
     ctx.check(ctx.lib.r1c_profile(ctx.h, 1))
