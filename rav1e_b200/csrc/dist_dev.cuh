@@ -175,11 +175,11 @@ template <int S>
 __device__ __forceinline__ void hadamard_lanes(int (&d)[S], int lane, unsigned mask = 0xffffffffu) {
 #pragma unroll
   for (int m = 1; m < S; m <<= 1) {
-    const bool upper = (lane & m) != 0;
+    const int sg = (lane & m) ? -1 : 1;  // upper lane of the pair: o - d, lower: d + o -- one IMAD either way
 #pragma unroll
     for (int i = 0; i < S; i++) {
       int o = __shfl_xor_sync(mask, d[i], m);
-      d[i] = upper ? (o - d[i]) : (d[i] + o);
+      d[i] = (int)((unsigned)d[i] * (unsigned)sg + (unsigned)o);
     }
   }
 }

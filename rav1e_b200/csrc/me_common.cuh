@@ -10,9 +10,13 @@ __host__ __device__ inline uint32_t diff_to_rate(int16_t diff, int allow_hp) {
   const int16_t d = allow_hp ? diff : (int16_t)(diff >> 1);
   if (d == 0) return 0;
   const uint32_t a = (uint32_t)(uint16_t)(d < 0 ? -d : d);
-  int bits = 0;  // 16 - leading_zeros(u16)
+#ifdef __CUDA_ARCH__
+  return 2u * (uint32_t)(32 - __clz((int)a));  // 16 - leading_zeros(u16)
+#else
+  int bits = 0;
   for (uint32_t v = a; v; v >>= 1) bits++;
   return 2u * (uint32_t)bits;
+#endif
 }
 __host__ __device__ inline uint32_t mv_rate(r1c_mv a, r1c_mv b, int allow_hp) {
   return diff_to_rate((int16_t)(a.row - b.row), allow_hp) + diff_to_rate((int16_t)(a.col - b.col), allow_hp);

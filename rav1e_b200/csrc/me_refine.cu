@@ -334,6 +334,48 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
       int dp[S];  // the candidate waiting for its pair partner
       bool dp_live = false;
       int dp_k = 0, arrived = 0;  // (compile-time after unrolling)
+      if (step == 8) {
+        // First step: the centre is the full-pel winner, so all 8 neighbours are full-pel MVs and put_8tap copies
+        // (src/mc.rs:224-231; the unified formula below gives the same pixels through unit taps: (16 px * 64 + 512) >> 10):
+        // one window pixel per output, no filtering.  Same clamped origins as the general path.
+#pragma unroll
+        for (int jg = 0; jg < 3; jg++) {
+          const int mvc = (int)center.col + 8 * (jg - 1);
+          const int sx = max(min(bx + (mvc >> 3) - 3, a.ref.width), -a.ref.xorigin) + 3;
+          const int wx = min(max(sx + tx + c - wx0, 0), a.winW - 1);  // clamped for memory safety only
+#pragma unroll
+          for (int i = 0; i < 3; i++) {
+            if (i == 1 && jg == 1) continue;  // the centre itself
+            const int kk = 3 * i + jg, k = kk < 4 ? kk : kk - 1;
+            const int mvr = (int)center.row + 8 * (i - 1);
+            const int sy = max(min(by + (mvr >> 3) - 3, a.ref.height), -a.ref.yorigin) + 3;
+            const int wy = min(max(sy + ty - wy0, 0), a.winH - S);
+            const uint8_t *p = sh.win + wy * a.wstride + wx * PB;
+            const bool live = ((ok >> jg) & (ok >> (3 + i)) & 1u) != 0;
+            int d[S];
+#pragma unroll
+            for (int t = 0; t < S; t++)
+              d[t] = oc[t] - (PB == 1 ? (int)p[t * a.wstride] : (int)*(const uint16_t *)(p + t * a.wstride));
+            if (!PAIR) {
+              const uint32_t acc = tile_dist<S>(d, lane, satd);
+              if (live && c == 0) atomicAdd(&sh.dist[slot * 8 + k], acc);
+            } else if ((arrived++ & 1) == 0) {
+#pragma unroll
+              for (int t = 0; t < S; t++) dp[t] = d[t];
+              dp_live = live;
+              dp_k = k;
+            } else {
+              uint32_t a0, a1;
+              tile_dist2<S>(dp, d, lane, satd, a0, a1);
+              if (c == 0) {
+                if (dp_live) atomicAdd(&sh.dist[slot * 8 + dp_k], a0);
+                if (live) atomicAdd(&sh.dist[slot * 8 + k], a1);
+              }
+            }
+          }
+        }
+        continue;
+      }
 #pragma unroll
       for (int jg = 0; jg < 3; jg++) {
         // predict_inter's get_params (src/predict.rs:267-284), luma, column part
