@@ -455,9 +455,10 @@ def main():
                                 "note": "1 VABSDIFF4.ACC = 8 byte-ops; packed peak = 8 x this"},
                 "kernels_ms_per_frame": {k: v[0] / (K * F) for k, v in prof.items()}}
         # second kernel of the step: fused sub-pel tail.  Integer work per pixel of every block: SATD re-evaluation
-        # (1 diff + 6 Hadamard + 2 abs/add = 9) + 24 candidates x (8 + 8 filter MACs + 9) = 609 lane-ops
+        # (1 diff + 6 Hadamard + 2 abs/add = 9) + the 8 full-pel neighbours of the first step (copies: 9 each) + 16
+        # sub-pel candidates x (8 + 8 filter MACs + 9) = 481 lane-ops
         rf_ms = prof["me_refine_kernel"][0] / max(1, prof["me_refine_kernel"][1])
-        rf_ops = 19 * W * H * (9 + 24 * 25)
+        rf_ops = 19 * W * H * (9 + 8 * 9 + 16 * 25)
         if rf_ms > 0:
             roof["me_refine_kernel"] = {"bound": "int32_alu", "achieved": rf_ops / (rf_ms / 1e3) / 1e9, "peak": ipeak,
                                         "unit": "Gop/s", "frac": rf_ops / (rf_ms / 1e3) / 1e9 / ipeak,
