@@ -6,13 +6,13 @@ estimation, +-64 px, every block of all 19 sizes 4x4..64x64, SAD search then the
 SATD re-evaluation + telescopic sub-pel tail of MotionEstimation::motion_estimation
 (src/me.rs:193-271).  A "step" is one lookahead window of 32 distinct frame pairs
 (cur, ref) -> every block's (best_mv, lowest_cost), 3 kernel launches per pair.
-Metric: Mpix/s = frame pixels / time.  The window's frames go to two r1c_ctx
-(two CUDA streams) in turn, as a caller with a lookahead window would drive the
-library ("one r1c_ctx per thread"): the tail of one frame's kernels is filled by
-the next frame's, and on the host-buffer path (`e2e`) the copies of one frame
-overlap the kernels of another.  The same steps on ONE stream are timed first:
-that pass gives the per-kernel durations of `roofline` and is reported as
-`one_stream`.
+Metric: Mpix/s = frame pixels / time.  A step is ONE call of the library's window
+entry point (r1c_frame_me_window_dev; r1c_frame_me_window with host buffers for
+`e2e`), which sends the pairs to two CUDA streams in turn: the tail of one
+frame's kernels is filled by the next frame's, and on the host-buffer path the
+copies of one frame overlap the kernels of another.  The same steps as a loop
+of per-frame calls on ONE stream are timed first: that pass gives the per-kernel
+durations of `roofline` and is reported as `one_stream`.
 
     python bench.py [--gpus N] [--steps K] [--warmup W]      # the CUDA path
     python bench.py --impl reference ...                     # CPU arm: the oracle
@@ -29,7 +29,6 @@ Only the `cpu_baseline` leg and `--impl reference` touch oracle/; the timed CUDA
 path is librav1e_cuda.so through its C ABI (rav1e_b200.capi).
 """
 import argparse
-import concurrent.futures
 import ctypes as C
 import json
 import os
@@ -310,54 +309,23 @@ def main():
             ctx.check(lib.r1c_plane_upload_async(ctx.h, p_ref[i].h, h_ref[i].data_ptr()))
             ctx.check(lib.r1c_frame_me(ctx.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, h_res.ctypes.data))
 
-    # the same step with NCTX contexts (= streams; "one r1c_ctx per thread") taking frames in turn: the tail
-    # of one frame's kernels is filled by the next frame's, and on the host-buffer path (one host thread per context) the
-    # copies of one frame overlap the kernels of another
-    NCTX = max(1, int(os.environ.get("R1C_BENCH_CTX", "2")))
-    ctxs = [ctx] + [r.Context(local) for _ in range(NCTX - 1)]
-    exts = [ext] + [torch.cuda.ExternalStream(c.stream, device=local) for c in ctxs[1:]]
-    h_ress = [h_res] + [torch.zeros(n_res * 16, dtype=torch.uint8).pin_memory().numpy().view(r.ME_RESULT) for _ in ctxs[1:]]
-    d_ress = [d_res] + [torch.empty(n_res * 16, dtype=torch.uint8, device="cuda") for _ in ctxs[1:]]
-    pool = concurrent.futures.ThreadPoolExecutor(NCTX)
+    # the same step through the library's window entry points: ONE call per step hands the 32 pairs over, the library
+    # sends them to two streams in turn (its own second context inside): the tail of one frame's kernels is filled by
+    # the next frame's, and with host buffers the copies of one frame overlap the kernels of another
+    d_ress = [d_res, torch.empty(n_res * 16, dtype=torch.uint8, device="cuda")]
+    h_ress = [h_res, torch.zeros(n_res * 16, dtype=torch.uint8).pin_memory().numpy().view(r.ME_RESULT)]
+    win_dev = (r.capi.FramePair * F)()
+    win_e2e = (r.capi.FramePair * F)()
+    for i in range(F):
+        win_dev[i].org, win_dev[i].ref, win_dev[i].results = p_org[i].h, p_ref[i].h, d_ress[i % 2].data_ptr()
+        win_e2e[i].org, win_e2e[i].ref, win_e2e[i].results = p_org[i].h, p_ref[i].h, h_ress[i % 2].ctypes.data
+        win_e2e[i].org_host, win_e2e[i].ref_host = h_org[i].data_ptr(), h_ref[i].data_ptr()
 
-    def _frames(c, res, idx):
-        for i in idx:
-            c.check(lib.r1c_plane_upload_async(c.h, p_org[i].h, h_org[i].data_ptr()))
-            c.check(lib.r1c_plane_upload_async(c.h, p_ref[i].h, h_ref[i].data_ptr()))
-            c.check(lib.r1c_frame_me(c.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, res.ctypes.data))
+    def step_dev_win():
+        ctx.check(lib.r1c_frame_me_window_dev(ctx.h, win_dev, F, C.byref(params), BD))
 
-    def step_dev_nctx():
-        for i in range(F):
-            c, d = ctxs[i % NCTX], d_ress[i % NCTX]
-            c.check(lib.r1c_frame_me_dev(c.h, p_org[i].h, p_ref[i].h, C.byref(params), BD, d.data_ptr()))
-
-    def step_e2e_nctx():
-        for f in [pool.submit(_frames, ctxs[k], h_ress[k], range(k, F, NCTX)) for k in range(NCTX)]:
-            f.result()
-
-    def timed_nctx(fn, k):
-        """as timed(), for a step that runs on all contexts' streams: the other streams wait for the start event, the
-        step ends when the last stream is done, and the next step's flush waits for that"""
-        evs = [(torch.cuda.Event(enable_timing=True), [torch.cuda.Event(enable_timing=True) for _ in exts]) for _ in range(k)]
-        barrier()
-        for a, ends in evs:
-            with torch.cuda.stream(ext):
-                bench_kernels.flush_l2(torch, flush)
-                a.record(ext)
-            for e in exts[1:]:
-                e.wait_event(a)
-            fn()
-            for e, b in zip(exts, ends):
-                b.record(e)
-            for b in ends[1:]:
-                ext.wait_event(b)
-        barrier()
-        ms = sum(max(a.elapsed_time(b) for b in ends) for a, ends in evs)
-        if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms
+    def step_e2e_win():
+        ctx.check(lib.r1c_frame_me_window(ctx.h, win_e2e, F, C.byref(params), BD))
 
     def barrier():
         torch.cuda.synchronize()
@@ -403,21 +371,19 @@ def main():
     ctx.check(lib.r1c_profile(ctx.h, 0))
     # ---- the same K steps with alternate frames on two contexts (two streams): the tail of one frame's kernels is
     # filled by the other frame's -- the throughput a caller with a lookahead window gets, and the headline `value`
-    step_dev_nctx()
-    l0 = sum(c.launches for c in ctxs)
-    ms_total = timed_nctx(step_dev_nctx, K)
-    launches = sum(c.launches for c in ctxs) - l0
+    step_dev_win()
+    ctx.sync()
+    l0 = ctx.launches  # r1c_launch_count: both streams of the context
+    ms_total = timed(step_dev_win, K)
+    launches = ctx.launches - l0
     # ---- end to end: host planes in, host results out, every step ------------------
     step_e2e()
     ms_e2e_serial = timed(step_e2e, K)
-    step_e2e_nctx()
-    l1 = sum(c.launches for c in ctxs)
-    ms_e2e = timed_nctx(step_e2e_nctx, K)
-    launches_e2e = sum(c.launches for c in ctxs) - l1
+    step_e2e_win()
+    l1 = ctx.launches
+    ms_e2e = timed(step_e2e_win, K)
+    launches_e2e = ctx.launches - l1
     clocks = sampler.summary()
-    pool.shutdown()
-    for c in ctxs[1:]:
-        c.close()
     del d_ress[1:], h_ress[1:]
 
     mpix = F * W * H / 1e6
@@ -472,17 +438,18 @@ def main():
             "config": dict(CONFIG),
             "one_stream": {"value": world * mpix / (ms_serial / K / 1e3), "ms_per_step": ms_serial / K, "gpu_launches": int(launches_serial),
                            "note": "the same K steps on ONE context / stream, kernels strictly one after the other: the pass the "
-                                   "roofline's per-kernel durations and share_of_step are measured in; `value` hands the "
-                                   "frames to %d contexts (streams) in turn, which fills the tail of each kernel" % NCTX},
-            "setup": {"blocks_per_frame": int(n_res), "frames_per_step": F, "launches_per_frame": 3, "contexts": NCTX,
+                                   "roofline's per-kernel durations and share_of_step are measured in; `value` is one "
+                                   "r1c_frame_me_window_dev call per step (two streams inside the library), which fills the tail of "
+                                   "each kernel"},
+            "setup": {"blocks_per_frame": int(n_res), "frames_per_step": F, "launches_per_frame": 3, "streams": 2,
                       "flush": "256 MiB written, then 256 MiB read back, untimed, before every step"},
             "e2e": {"value": e2e, "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / K, "gpu_launches": int(launches_e2e),
-                    "path": "per frame pair: r1c_plane_upload_async x2 (pinned host planes) + r1c_frame_me (pinned host result "
-                            "array); %d r1c_ctx (streams), one host thread each, take the frames in turn, so the copies of one "
-                            "frame overlap the kernels of another" % NCTX,
+                    "path": "one r1c_frame_me_window call per step: per frame pair 2 plane uploads from page-locked host memory, "
+                            "the three kernels, the results copied into a page-locked host array; the library sends the pairs "
+                            "to two streams in turn, so the copies of one frame overlap the kernels of another",
                     "one_context": {"value": world * mpix / (ms_e2e_serial / K / 1e3), "ms_per_step": ms_e2e_serial / K,
-                                    "note": "the same calls from one thread on one context: copies and kernels serialised"}},
+                                    "note": "r1c_plane_upload_async x2 + r1c_frame_me per pair in a loop: copies and kernels serialised on one stream"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roof,

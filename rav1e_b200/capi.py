@@ -121,6 +121,11 @@ class SubpelJob(C.Structure):
                 ("use_satd", C.c_int32), ("allow_high_precision_mv", C.c_int32)]
 
 
+class FramePair(C.Structure):
+    _fields_ = [("org", C.c_void_p), ("ref", C.c_void_p), ("org_host", C.c_void_p), ("ref_host", C.c_void_p),
+                ("results", C.c_void_p)]
+
+
 class FrameMeParams(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("range_x", C.c_int32),
                 ("range_y", C.c_int32), ("lambda_", C.c_uint32), ("bsize_mask", C.c_uint32),
@@ -214,6 +219,8 @@ SIGNATURES = {
     "r1c_frame_me_offset": (_i64, [_P(FrameMeParams), _i, _P(C.c_int32), _P(C.c_int32)]),
     "r1c_frame_me": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
     "r1c_frame_me_dev": (_i, [_vp, _vp, _vp, _P(FrameMeParams), _i, _vp]),
+    "r1c_frame_me_window": (_i, [_vp, _vp, _i64, _P(FrameMeParams), _i]),
+    "r1c_frame_me_window_dev": (_i, [_vp, _vp, _i64, _P(FrameMeParams), _i]),
     "r1c_frame_me_shard_count": (_i64, [_vp, _P(FrameMeParams)]),
     "r1c_frame_me_compact_dev": (_i, [_vp, _P(FrameMeParams), _vp, _vp]),
     "r1c_plane_upload_async": (_i, [_vp, _vp, _vp]),

@@ -48,6 +48,11 @@ struct r1c_ctx {
     void *d_sbjobs, *d_map, *d_subjobs;
     int64_t n_sb, n_blocks;
   } frame_me;
+  // r1c_frame_me_window*: a second context (stream + scratch of its own) that takes every other frame pair of a
+  // window, created on first use, destroyed with this one; and the events that fork / join the two streams
+  r1c_ctx *peer;
+  cudaEvent_t win_ev[2];
+  int win_ev_created;
 };
 
 // Device-side view of a plane: pointer to plane coordinate (0,0) + geometry.

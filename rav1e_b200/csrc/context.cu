@@ -42,6 +42,11 @@ extern "C" void r1c_destroy(r1c_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->peer) r1c_destroy(ctx->peer);
+  if (ctx->win_ev_created) {
+    cudaEventDestroy(ctx->win_ev[0]);
+    cudaEventDestroy(ctx->win_ev[1]);
+  }
   for (int i = 0; i < 4; i++)
     if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
   for (int i = 0; i < 16; i++)
@@ -67,7 +72,9 @@ extern "C" int r1c_sync(r1c_ctx *ctx) {
 extern "C" const char *r1c_last_error(const r1c_ctx *ctx) { return ctx ? ctx->err : "no context"; }
 extern "C" void *r1c_stream(r1c_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
 extern "C" int r1c_device(const r1c_ctx *ctx) { return ctx ? ctx->device : -1; }
-extern "C" int64_t r1c_launch_count(const r1c_ctx *ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int64_t r1c_launch_count(const r1c_ctx *ctx) {
+  return ctx ? ctx->launches + (ctx->peer ? ctx->peer->launches : 0) : 0;
+}
 
 // ---- per-kernel-class timing ---------------------------------------------------
 static void prof_fold(r1c_ctx *ctx, int slot) {

@@ -268,8 +268,12 @@ extern "C" int r1c_frame_me_compact_dev(r1c_ctx *ctx, const r1c_frame_me_params 
   return R1C_OK;
 }
 
-extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
-                            const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results) {
+// host result array: the shard's entries are computed on the device and copied back on the context stream.  Returns
+// without synchronising when `results` is page-locked (*pending = 1: the copy is still in flight); pageable memory
+// goes through the pinned stage and is complete on return.
+static int frame_me_host(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_frame_me_params *p, int bit_depth,
+                         r1c_me_result *results, int *pending) {
+  *pending = 0;
   if (!ctx || !org || !ref) return R1C_ERR_ARG;
   R1C_REQUIRE(ctx, params_ok(p), R1C_ERR_ARG, "frame_me: bad parameters");
   R1C_REQUIRE(ctx, results != nullptr, R1C_ERR_ARG, "frame_me: null result array");
@@ -294,7 +298,90 @@ extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane 
   }
   if ((rc = r1c_frame_me_dev(ctx, org, ref, p, bit_depth, (r1c_me_result *)d_res))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_res, d_res, rb, cudaMemcpyDeviceToHost, ctx->stream));
+  if (direct) {
+    *pending = 1;
+    return R1C_OK;
+  }
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  if (!direct) memcpy(results, h_res, rb);
+  memcpy(results, h_res, rb);
+  return R1C_OK;
+}
+
+extern "C" int r1c_frame_me(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref,
+                            const r1c_frame_me_params *p, int bit_depth, r1c_me_result *results) {
+  int pending = 0;
+  const int rc = frame_me_host(ctx, org, ref, p, bit_depth, results, &pending);
+  if (rc) return rc;
+  if (pending) R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return R1C_OK;
+}
+
+// ---- a lookahead window of frame pairs in one call ----------------------------------------------------------
+// The pairs go to two streams in turn (this context's and its peer's): the tail of one frame's kernels is filled
+// by the next frame's, and with host buffers the copies of one frame overlap the kernels of another.
+static int window_fork(r1c_ctx *ctx) {
+  R1C_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->peer) {
+    ctx->peer = r1c_create(ctx->device);
+    if (!ctx->peer) return r1c_set_err(ctx, R1C_ERR_NOMEM, "frame_me_window: cannot create the second stream");
+  }
+  if (!ctx->win_ev_created) {
+    R1C_CUDA(ctx, cudaEventCreateWithFlags(&ctx->win_ev[0], cudaEventDisableTiming));
+    R1C_CUDA(ctx, cudaEventCreateWithFlags(&ctx->win_ev[1], cudaEventDisableTiming));
+    ctx->win_ev_created = 1;
+  }
+  // the peer starts after everything already queued on the context stream (the planes' uploads, ...)
+  R1C_CUDA(ctx, cudaEventRecord(ctx->win_ev[0], ctx->stream));
+  R1C_CUDA(ctx, cudaStreamWaitEvent(ctx->peer->stream, ctx->win_ev[0], 0));
+  return R1C_OK;
+}
+static int window_join(r1c_ctx *ctx) {  // later work on the context stream sees the peer's results
+  R1C_CUDA(ctx, cudaEventRecord(ctx->win_ev[1], ctx->peer->stream));
+  R1C_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->win_ev[1], 0));
+  return R1C_OK;
+}
+static int peer_error(r1c_ctx *ctx, int rc) {
+  snprintf(ctx->err, sizeof ctx->err, "%s", ctx->peer->err);
+  return rc;
+}
+
+extern "C" int r1c_frame_me_window_dev(r1c_ctx *ctx, const r1c_frame_pair *pairs, int64_t n, const r1c_frame_me_params *p,
+                                       int bit_depth) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || pairs), R1C_ERR_ARG, "frame_me_window: null pair array");
+  if (n == 0) return R1C_OK;
+  int rc = window_fork(ctx);
+  if (rc) return rc;
+  for (int64_t i = 0; i < n; i++) {
+    r1c_ctx *c = (i & 1) ? ctx->peer : ctx;
+    if ((rc = r1c_frame_me_dev(c, pairs[i].org, pairs[i].ref, p, bit_depth, (r1c_me_result *)pairs[i].results)))
+      return c == ctx ? rc : peer_error(ctx, rc);
+  }
+  return window_join(ctx);
+}
+
+extern "C" int r1c_frame_me_window(r1c_ctx *ctx, const r1c_frame_pair *pairs, int64_t n, const r1c_frame_me_params *p,
+                                   int bit_depth) {
+  if (!ctx) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, n >= 0 && (n == 0 || pairs), R1C_ERR_ARG, "frame_me_window: null pair array");
+  if (n == 0) return R1C_OK;
+  int rc = window_fork(ctx);
+  if (rc) return rc;
+  r1c_ctx *bad = nullptr;
+  for (int64_t i = 0; i < n && !rc; i++) {
+    r1c_ctx *c = (i & 1) ? ctx->peer : ctx;
+    int pending;
+    if (pairs[i].org_host) rc = r1c_plane_upload_async(c, (r1c_plane *)pairs[i].org, pairs[i].org_host);
+    if (!rc && pairs[i].ref_host) rc = r1c_plane_upload_async(c, (r1c_plane *)pairs[i].ref, pairs[i].ref_host);
+    if (!rc) rc = frame_me_host(c, pairs[i].org, pairs[i].ref, p, bit_depth, (r1c_me_result *)pairs[i].results, &pending);
+    if (rc) bad = c;
+  }
+  if (rc) {  // drain what was queued before reporting
+    cudaStreamSynchronize(ctx->peer->stream);
+    cudaStreamSynchronize(ctx->stream);
+    return bad == ctx->peer ? peer_error(ctx, rc) : rc;
+  }
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->peer->stream));
+  R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return R1C_OK;
 }

@@ -734,6 +734,49 @@ def test_tile_search_needs_only_its_rows_of_the_planes(r, ctx, oracle):
     assert e.value.code == r.capi.R1C_ERR_ARG
 
 
+def test_frame_me_window_equals_frame_by_frame(r, ctx, oracle):
+    """r1c_frame_me_window(_dev): a lookahead window of frame pairs over two streams == r1c_frame_me pair by pair; host
+    form with the planes uploaded by the call (garbage in the planes before), device form with resident planes; odd and
+    even window lengths, a window of one, an empty window; a bad pair is reported and nothing hangs"""
+    import torch
+    W, H = 192, 136
+    for pb, bd in ((1, 8), (2, 10)):
+        params = r.make_frame_me_params(W, H, 12, 12, 40)
+        n_res = r.frame_me_count(params)
+        pairs, want, hosts = [], [], []
+        for k in range(5):
+            o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, W, H, pb, bd, 300 + k)
+            want.append(r.frame_me(ctx, d_org, d_ref, params, bd))
+            pairs.append((d_org, d_ref))
+            hosts.append((o_org.data.copy(), o_ref.data.copy()))
+        assert not np.array_equal(want[0], want[1])
+        for n in (5, 4, 1, 0):
+            got = r.frame_me_window(ctx, pairs[:n], params, bd)
+            assert len(got) == n and all(np.array_equal(g, w) for g, w in zip(got, want)), (bd, n)
+        # host form with uploads: the planes hold garbage until the call uploads them
+        junk = np.full(hosts[0][0].shape, (1 << bd) - 1, dtype=hosts[0][0].dtype)
+        for d_org, d_ref in pairs:
+            d_org.upload(junk)
+            d_ref.upload(junk)
+        got = r.frame_me_window(ctx, [(a, b, ho, hr) for (a, b), (ho, hr) in zip(pairs, hosts)], params, bd)
+        assert all(np.array_equal(g, w) for g, w in zip(got, want)), bd
+        # device form: results stay on the device; later work on the context stream sees both streams' results
+        d_out = [torch.zeros(n_res * 16, dtype=torch.uint8, device="cuda") for _ in pairs]
+        arr = (r.capi.FramePair * len(pairs))()
+        for i, (a, b) in enumerate(pairs):
+            arr[i].org, arr[i].ref, arr[i].results = a.h, b.h, d_out[i].data_ptr()
+        ctx.check(ctx.lib.r1c_frame_me_window_dev(ctx.h, arr, len(pairs), C.byref(params), bd))
+        ctx.sync()
+        for i, w in enumerate(want):
+            assert np.array_equal(d_out[i].cpu().numpy().view(r.ME_RESULT), w), (bd, i)
+        # a pair whose plane does not match the frame size: error code, the call returns
+        _, d_small = twin_plane(r, oracle, ctx, W - 64, H, pb, bd, np.random.default_rng(1))
+        with pytest.raises(r.Rav1eCudaError) as e:
+            r.frame_me_window(ctx, [pairs[0], (d_small, pairs[1][1]), pairs[2]], params, bd)
+        assert e.value.code == r.capi.R1C_ERR_ARG
+        assert np.array_equal(r.frame_me(ctx, pairs[3][0], pairs[3][1], params, bd), want[3])  # the context is still usable
+
+
 def test_profile_hooks_count_launches(r, ctx, oracle):
     o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, 128, 128, 1, 8, 5)
     ctx.check(ctx.lib.r1c_profile(ctx.h, 1))
