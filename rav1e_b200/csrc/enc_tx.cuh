@@ -176,16 +176,25 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
     for (int it = tid; it < nb * H; it += C::THREADS) {
       int *row = s_c + it * C::STRIDE;
       const int r = it % H;
-      int v[W], o[W];
+      int v[W], o[W], l1 = 0;
       const unsigned off = (1u << lts) - 1u;
 #pragma unroll
       for (int c = 0; c < W; c++) {
         const int qv = row[c];
         int t = (int)((unsigned)qv * ((c == 0 && r == 0) ? a.q.qc.dc_quant : a.q.qc.ac_quant) + ((unsigned)(qv >> 31) & off)) >> lts;
         if (RECT) t = (int)((unsigned)t * 2896u + 2048u) >> 12;  // round_shift(raw * INV_SQRT2, SQRT2_BITS)
-        v[c] = itx::cl(t, a.rg_row);
+        v[c] = t;
+        l1 = (int)min((unsigned)l1 + (unsigned)abs(t), 0x40000000u);
       }
-      itx::inv1d<RT, W>(v, o, a.rg_row);
+      // the input clamp and the clamps inside the transform are no-ops when the row's L1 norm stays inside the range
+      // (itx1d.cuh, NOCLAMP_MARGIN): the usual case for the residual of a prediction
+      if (__all_sync(__activemask(), l1 + itx::NOCLAMP_MARGIN <= a.rg_row.hi)) {
+        itx::inv1d<RT, W, false>(v, o, a.rg_row);
+      } else {
+#pragma unroll
+        for (int c = 0; c < W; c++) v[c] = itx::cl(v[c], a.rg_row);
+        itx::inv1d<RT, W, true>(v, o, a.rg_row);
+      }
       if (a.row_flip) {
 #pragma unroll
         for (int c = 0; c < W; c++) row[W - 1 - c] = itx::cl((o[c] + a.irnd) >> a.ish, a.rg_col);
@@ -204,9 +213,14 @@ __global__ void __launch_bounds__(EncCfg<W, H>::THREADS) enc_tx_kernel(const __g
       const long long rec_off = (long long)j.pred_y * a.rec.stride + j.pred_x + c;
       const int *col = s_c + b * C::BLK + c;
       int v[H], o[H];
+      int l1 = 0;
 #pragma unroll
-      for (int r = 0; r < H; r++) v[r] = col[r * C::STRIDE];
-      itx::inv1d<CT, H>(v, o, a.rg_col);
+      for (int r = 0; r < H; r++) {
+        v[r] = col[r * C::STRIDE];
+        l1 += abs(v[r]);  // |v| < 2^17 after the row pass' clamp
+      }
+      if (__all_sync(__activemask(), l1 + itx::NOCLAMP_MARGIN <= a.rg_col.hi)) itx::inv1d<CT, H, false>(v, o, a.rg_col);
+      else itx::inv1d<CT, H, true>(v, o, a.rg_col);
       if (a.px_bytes == 1) {
         uint8_t *p = (uint8_t *)a.rec.p0 + rec_off;
         int px[H];

@@ -58,6 +58,14 @@ struct Range {
   int lo, hi;
 };
 __device__ __forceinline__ int cl(int v, Range r) { return min(max(v, r.lo), r.hi); }
+// The 1-D transforms take CL = false when their clamps are provably no-ops.  Every value the reference clamps
+// inside av1_idct* / av1_iadst* is a linear combination of the inputs with weights of magnitude <= 1 (measured on the
+// reference's own text, unit inputs through every clamp site: 0.924 .. 0.9999) plus the rounding of at most 162
+// half_btf calls, each of which reaches a later clamp site with gain <= 1 (measured the same way): so
+//   sum |input| + 128 <= range.hi   ==>   no clamp_value of that transform changes its argument.
+constexpr int NOCLAMP_MARGIN = 128;
+template <bool CL>
+__device__ __forceinline__ int clq(int v, Range r) { return CL ? cl(v, r) : v; }
 
 __host__ __device__ constexpr int bitrev(int v, int bits) {
   int r = 0;
@@ -71,7 +79,7 @@ __host__ __device__ constexpr int log2c(int n) {
 }
 
 // odd half of the 2M-point DCT, in place on s[M .. 2M)
-template <int N, int M>
+template <int N, int M, bool CL>
 __device__ __forceinline__ void idct_odd(int (&s)[N], Range rg) {
   constexpr int LM = log2c(M);
 #pragma unroll
@@ -85,11 +93,11 @@ __device__ __forceinline__ void idct_odd(int (&s)[N], Range rg) {
       if (j < i) continue;
       const int u = s[M + i], v = s[M + j];
       if ((i >> l) & 1) {
-        s[M + i] = cl(v - u, rg);
-        s[M + j] = cl(u + v, rg);
+        s[M + i] = clq<CL>(v - u, rg);
+        s[M + j] = clq<CL>(u + v, rg);
       } else {
-        s[M + i] = cl(u + v, rg);
-        s[M + j] = cl(u - v, rg);
+        s[M + i] = clq<CL>(u + v, rg);
+        s[M + j] = clq<CL>(u - v, rg);
       }
     }
 #pragma unroll
@@ -104,13 +112,13 @@ __device__ __forceinline__ void idct_odd(int (&s)[N], Range rg) {
   }
 }
 
-template <int N, int M>
+template <int N, int M, bool CL>
 __device__ __forceinline__ void idct_odd_all(int (&s)[N], Range rg) {
-  idct_odd<N, M>(s, rg);
-  if constexpr (2 * M < N) idct_odd_all<N, 2 * M>(s, rg);
+  idct_odd<N, M, CL>(s, rg);
+  if constexpr (2 * M < N) idct_odd_all<N, 2 * M, CL>(s, rg);
 }
 
-template <int N>
+template <int N, bool CL = true>
 __device__ __forceinline__ void idct(const int (&in)[N], int (&out)[N], Range rg) {
   constexpr int LN = log2c(N);
   int s[N];
@@ -121,15 +129,15 @@ __device__ __forceinline__ void idct(const int (&in)[N], int (&out)[N], Range rg
     s[0] = btf(c_cospi[32], u, c_cospi[32], v);
     s[1] = btf(c_cospi[32], u, -c_cospi[32], v);
   }
-  idct_odd_all<N, 2>(s, rg);
+  idct_odd_all<N, 2, CL>(s, rg);
 #pragma unroll
   for (int l = 1; l < LN; l++) {
     const int M = 1 << l;
 #pragma unroll
     for (int i = 0; i < M; i++) {
       const int u = s[i], v = s[2 * M - 1 - i];
-      s[i] = cl(u + v, rg);
-      s[2 * M - 1 - i] = cl(u - v, rg);
+      s[i] = clq<CL>(u + v, rg);
+      s[2 * M - 1 - i] = clq<CL>(u - v, rg);
     }
   }
 #pragma unroll
@@ -152,7 +160,7 @@ __device__ __forceinline__ void iadst4(const int (&in)[4], int (&out)[4]) {
   out[3] = rshift12(p + q - m);
 }
 
-template <int N>
+template <int N, bool CL = true>
 __device__ __forceinline__ void iadst(const int (&in)[N], int (&out)[N], Range rg) {
   constexpr int LN = log2c(N);
   int s[N];
@@ -169,8 +177,8 @@ __device__ __forceinline__ void iadst(const int (&in)[N], int (&out)[N], Range r
     for (int i = 0; i < N; i++) {
       if (i & h) continue;
       const int u = s[i], v = s[i + h];
-      s[i] = cl(u + v, rg);
-      s[i + h] = cl(u - v, rg);
+      s[i] = clq<CL>(u + v, rg);
+      s[i + h] = clq<CL>(u - v, rg);
     }
 #pragma unroll
     for (int i = 0; i < N; i += 2) {  // pairs of the upper half of every block of 2h
@@ -198,13 +206,16 @@ __device__ __forceinline__ void iident(const int (&in)[N], int (&out)[N]) {
            : N == 16 ? rshift12(5793u * 2u * (unsigned)in[i]) : (int)(4u * (unsigned)in[i]);
 }
 
-template <int TYPE, int N>
+template <int TYPE, int N, bool CL = true>
 __device__ __forceinline__ void inv1d(const int (&in)[N], int (&out)[N], Range rg) {
-  if constexpr (TYPE == I1_DCT) idct<N>(in, out, rg);
+  if constexpr (TYPE == I1_DCT) idct<N, CL>(in, out, rg);
   else if constexpr (TYPE == I1_ADST) {
     if constexpr (N == 4) iadst4(in, out);
-    else iadst<N>(in, out, rg);
+    else iadst<N, CL>(in, out, rg);
   } else iident<N>(in, out);
 }
+// does the transform clamp at all?  (identity and the 4-point ADST do not)
+template <int TYPE, int N>
+constexpr bool inv1d_clamps() { return TYPE == I1_DCT || (TYPE == I1_ADST && N > 4); }
 
 }  // namespace itx

@@ -99,15 +99,23 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
         for (int c = 0; c < C::WI; c++)
           v[c] = (int)((unsigned)v[c] * ((c == 0 && r == 0) ? a.dq_dc : a.dq_ac) + ((unsigned)(v[c] >> 31) & off)) >> a.dq_lts;
       }
+      int l1 = 0;  // sum |input|: decides whether the transform's clamps can change anything (itx1d.cuh)
 #pragma unroll
       for (int c = 0; c < W; c++) {
         if (c >= C::WI) v[c] = 0;
         else {
           if (RECT) v[c] = (int)((unsigned)v[c] * 2896u + 2048u) >> 12;  // round_shift(raw * INV_SQRT2, SQRT2_BITS)
-          v[c] = cl(v[c], a.rg_row);
+          l1 = (int)min((unsigned)l1 + (unsigned)abs(v[c]), 0x40000000u);  // saturating: |INT_MIN| and overflow stay large
         }
       }
-      inv1d<RT, W>(v, o, a.rg_row);
+      // the input clamp and the clamps inside are no-ops when the row's L1 norm stays inside the range
+      if (__all_sync(__activemask(), l1 + NOCLAMP_MARGIN <= a.rg_row.hi)) {
+        inv1d<RT, W, false>(v, o, a.rg_row);
+      } else {
+#pragma unroll
+        for (int c = 0; c < C::WI; c++) v[c] = cl(v[c], a.rg_row);
+        inv1d<RT, W, true>(v, o, a.rg_row);
+      }
       int *dst = s_mid + (b * H + r) * C::STRIDE;
       if (a.row_flip) {  // av1_iflipadst*: the reversed output of the ADST
 #pragma unroll
@@ -129,9 +137,14 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
       const int b = tid / W, c = tid % W;
       const int *col = s_mid + b * H * C::STRIDE + c;
       int v[H], o[H];
+      int l1 = 0;
 #pragma unroll
-      for (int r = 0; r < H; r++) v[r] = r < C::HI ? col[r * C::STRIDE] : 0;
-      inv1d<CT, H>(v, o, a.rg_col);
+      for (int r = 0; r < H; r++) {
+        v[r] = r < C::HI ? col[r * C::STRIDE] : 0;
+        if (r < C::HI) l1 += abs(v[r]);  // |v| <= 2^15 after the row pass' clamp: no overflow
+      }
+      if (__all_sync(__activemask(), l1 + NOCLAMP_MARGIN <= a.rg_col.hi)) inv1d<CT, H, false>(v, o, a.rg_col);
+      else inv1d<CT, H, true>(v, o, a.rg_col);
 #pragma unroll
       for (int r0 = 0; r0 < H; r0 += CH) {
         if (H > 32) {

@@ -132,6 +132,45 @@ def test_inverse_all_pairs_match_oracle(r, ctx, oracle, pb, bd):
     assert pairs == 193
 
 
+@pytest.mark.parametrize("pb,bd", BD)
+def test_inverse_around_the_clamp_shortcut(r, ctx, oracle, pb, bd):
+    """the kernels skip the clamps of a 1-D transform whose inputs have an L1 norm below range - 128 (itx1d.cuh): rows
+    and columns whose norm sits just below, at and above that bound, many per call so that the lanes of a warp disagree,
+    for every 1-D type and length; whole allocation against the oracle"""
+    rng = np.random.default_rng(70 + bd)
+    L = oracle.lib()
+    hi_row, hi_col = (1 << (bd + 7)) - 1, (1 << (max(bd + 6, 16) - 1)) - 1
+    for s, t in ((0, 0), (1, 0), (1, 3), (2, 0), (2, 3), (3, 0), (4, 0), (7, 1), (8, 2), (9, 0), (16, 12), (12, 0), (1, 9), (2, 10)):
+        if not oracle.inv_txfm_valid(s, t):
+            continue
+        w, h = L.r1o_tx_width(s), L.r1o_tx_height(s)
+        cw, ch = min(w, 32), min(h, 32)
+        o, d = twin_plane(r, oracle, ctx, 512, 256, pb, bd, rng, xpad=16, ypad=16)
+        jobs = _grid_jobs(r, rng, 96, w, h, 512, 256)
+        n = jobs.size
+        c = np.zeros((n, ch, cw), dtype=np.int64)
+        for i in range(n):
+            kind = i % 4
+            if kind == 0:  # one row (the DC row or a random one) with a norm around the row bound, spread over a few coefficients
+                row = 0 if i % 8 == 0 else int(rng.integers(0, ch))
+                total = hi_row - 128 + int(rng.integers(-300, 301))
+                k = int(rng.integers(1, min(cw, 6) + 1))
+                parts = rng.multinomial(total, np.ones(k) / k)
+                c[i, row, rng.permutation(cw)[:k]] = parts * rng.choice([-1, 1], k)
+            elif kind == 1:  # a DC that drives one column's inputs to the column bound after the row pass
+                c[i, 0, 0] = int(rng.integers(hi_col // 2, hi_col * 8)) * int(rng.choice([-1, 1]))
+            elif kind == 2:  # every row near the bound: the column norms are far above theirs
+                for row in range(ch):
+                    c[i, row, int(rng.integers(0, cw))] = (hi_row - 128 + int(rng.integers(-64, 65))) * int(rng.choice([-1, 1]))
+            else:  # ordinary residual
+                c[i] = rng.integers(-300, 301, (ch, cw)) * (rng.random((ch, cw)) < 0.2)
+        c = c.reshape(n, -1).astype(np.int32)
+        xy = np.stack([jobs["x"] + o.cfg.xorigin, jobs["y"] + o.cfg.yorigin], 1)
+        oracle.inv_txfm_add_batch(c, o.data, xy, s, t, bd)
+        r.inverse_transform_add(ctx, c, d, jobs, s, t, bd)
+        assert np.array_equal(d.download(), o.data), (s, t)
+
+
 @pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
 def test_dequantize_fused_into_inverse(r, ctx, oracle, pb, bd):
     """r1c_dequant_inv_txfm_add_batch == dequantize (src/quantize.rs:318-334) then inverse_transform_add, for
