@@ -158,3 +158,51 @@ def test_forward_2d_matches_reference_text():
             ref = F.fht(res.reshape(-1), w, h, tx_type, bd)
             assert r1o.fht(res, tx_size, tx_type, bd).reshape(-1).tolist() == ref, (tx_size, tx_type, bd)
     assert pairs == 193
+
+
+def test_inverse_clamp_shortcut_bound_holds_on_the_reference_text():
+    """itx1d.cuh runs a 1-D inverse transform without its clamps when sum |input| + 128 <= range.hi.  The two facts that
+    make the clamps no-ops then are measured here on the reference's OWN functions (transliterated from
+    src/transform/inverse.rs by ref_inv_tx): (1) every value handed to clamp_value, and every output, is a linear
+    combination of the inputs with weights of magnitude <= 1; (2) a rounding error injected at any half_btf reaches
+    every later clamp site / output with gain <= 1, and there are at most 162 of them (drift <= 81 < 128)."""
+    import ref_inv_tx as R
+    ns = R._transliterate(open(R.REF).read())
+    A = 1 << 20
+    st = {"j": -1, "cnt": 0, "m": 0}
+    orig = R.half_btf
+
+    def hb(w0, in0, w1, in1, bit):
+        v = orig(w0, in0, w1, in1, bit)
+        if st["cnt"] == st["j"]:
+            v += A
+        st["cnt"] += 1
+        return v
+
+    def cv(v, bit):
+        st["m"] = max(st["m"], abs(v))
+        return v
+    ns["half_btf"], ns["clamp_value"] = hb, cv
+    names = sorted(k for k in ns if re.fullmatch(r"av1_i(dct|adst)\d+", k))
+    assert len(names) == 8
+    for name in names:
+        n = int(re.search(r"(\d+)$", name).group(1))
+        gain = 0.0
+        for k in range(n):
+            for sg in (1, -1):
+                inp, out = [0] * n, [0] * n
+                inp[k] = sg * A
+                st.update(j=-1, cnt=0, m=0)
+                ns[name](inp, out, 32)
+                gain = max(gain, st["m"] / A, max(abs(o) for o in out) / A)
+        assert gain <= 1.0, (name, gain)
+        calls = st["cnt"]
+        assert calls <= 162, (name, calls)
+        prop = 0.0
+        for j in range(calls):
+            out = [0] * n
+            st.update(j=j, cnt=0, m=0)
+            ns[name]([0] * n, out, 32)
+            prop = max(prop, st["m"] / A, max(abs(o) for o in out) / A)
+        assert prop <= 1.0, (name, prop)
+        assert 0.5 * calls * max(prop, 1.0) < 128
