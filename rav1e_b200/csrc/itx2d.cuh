@@ -40,14 +40,17 @@ struct ItxCfg {
   static constexpr int WI = W < 32 ? W : 32, HI = H < 32 ? H : 32;
   static constexpr int CODED = WI * HI;
   static constexpr int MAXD = W > H ? W : H;
-  // the column pass is the heavy one (H-point transform + the pixel read-modify-write): the CTA takes as many
-  // blocks as give every thread exactly one column; the coded rows are then looped over (tall blocks) or leave
-  // threads idle (wide blocks)
+  // blocks per CTA: as many as give every thread exactly one column (the H-point transform + the pixel
+  // read-modify-write; the coded rows are looped over or leave threads idle), except for the 4:1 wide blocks
+  // (16x4, 32x8, 64x16), where 3 of 4 warps would idle through the long row transforms: those are sized by the
+  // coded rows and loop over the columns (measured: 2:1 blocks and the 64-wide ones with 32 coded rows lose)
   static constexpr int THREADS = 128;
-  static constexpr int BPC = THREADS / W;  // blocks per CTA
+  static constexpr int BPC = THREADS / (W >= 4 * HI ? HI : W);  // blocks per CTA
   static constexpr bool ROWS_ONCE = BPC * HI <= THREADS;
+  static constexpr bool COLS_ONCE = BPC * W <= THREADS;
   static constexpr int STRIDE = W + 1;
-  static constexpr size_t SMEM = (size_t)BPC * H * STRIDE * 4;
+  static constexpr int BLK = HI * STRIDE;  // words per block: the coded rows only
+  static constexpr size_t SMEM = (size_t)BPC * BLK * 4;
 };
 
 template <int W, int H, int CT, int RT, int PB>
@@ -66,13 +69,14 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     // through another pointer could not be moved above it by the compiler: one DRAM latency per row otherwise);
     // blocks up to 32 rows issue them here, so that they are in flight during both transforms
     constexpr int CH = H < 32 ? H : 32;
+    constexpr bool PREFETCH = C::COLS_ONCE && H <= 32;  // one column per thread: its pixels are fetched before the row pass
     const bool col_live = tid < nb * W;
     Px *p = nullptr;
     int px[CH];
-    if (col_live) {
+    if (C::COLS_ONCE && col_live) {
       const r1c_itx_job j = a.jobs[blk0 + tid / W];
       p = (Px *)a.dst.p0 + ((long long)j.y * a.dst.stride + j.x + tid % W);
-      if (H <= 32) {
+      if (PREFETCH) {
 #pragma unroll
         for (int r = 0; r < H; r++) px[r] = p[(long long)r * a.dst.stride];
       }
@@ -116,7 +120,7 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
         for (int c = 0; c < C::WI; c++) v[c] = cl(v[c], a.rg_row);
         inv1d<RT, W, true>(v, o, a.rg_row);
       }
-      int *dst = s_mid + (b * H + r) * C::STRIDE;
+      int *dst = s_mid + b * C::BLK + r * C::STRIDE;
       if (a.row_flip) {  // av1_iflipadst*: the reversed output of the ADST
 #pragma unroll
         for (int c = 0; c < W; c++) dst[W - 1 - c] = cl((o[c] + a.rnd) >> a.sh, a.rg_col);
@@ -133,9 +137,13 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
     __syncthreads();
 
     // ---- columns (:2095-2106) and the add (:2017-2028) ------------------------------------
-    if (col_live) {
-      const int b = tid / W, c = tid % W;
-      const int *col = s_mid + b * H * C::STRIDE + c;
+    auto col_item = [&](int it) {
+      const int b = it / W, c = it % W;
+      if (!C::COLS_ONCE) {
+        const r1c_itx_job j = a.jobs[blk0 + b];
+        p = (Px *)a.dst.p0 + ((long long)j.y * a.dst.stride + j.x + c);
+      }
+      const int *col = s_mid + b * C::BLK + c;
       int v[H], o[H];
       int l1 = 0;
 #pragma unroll
@@ -147,7 +155,7 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
       else inv1d<CT, H, true>(v, o, a.rg_col);
 #pragma unroll
       for (int r0 = 0; r0 < H; r0 += CH) {
-        if (H > 32) {
+        if (!PREFETCH) {
 #pragma unroll
           for (int r = 0; r < CH; r++) px[r] = p[(long long)(r0 + r) * a.dst.stride];
         }
@@ -158,6 +166,11 @@ __global__ void __launch_bounds__(ItxCfg<W, H>::THREADS) itx_kernel(const __grid
           p[(long long)(r0 + r) * a.dst.stride] = (Px)min(max(px[r] + t, 0), a.maxv);
         }
       }
+    };
+    if constexpr (C::COLS_ONCE) {
+      if (col_live) col_item(tid);
+    } else {
+      for (int it = tid; it < nb * W; it += C::THREADS) col_item(it);
     }
     __syncthreads();  // s_mid is rewritten by the next slab's row pass
   }
