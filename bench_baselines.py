@@ -91,6 +91,7 @@ def run(ctx, r, torch, ext, flush, kernels):
     src = r.Plane(ctx, W, H, 0, 0, 88, 88, 2).upload(o_src.data)
     dst = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
     allj = np.concatenate(bench_kernels.mc_jobs(r, rng, lib, W, H, 1))
+    allj = torch.from_numpy(allj.view(np.uint8)).pin_memory().numpy().view(r.MC_JOB)  # page-locked host job list
     px_all = int((allj["w"].astype(np.int64) * allj["h"]).sum())
     sel = allj[_sample(rng, allj.size, 60000)]
     j10 = np.stack([sel[k].astype(np.int32) for k in ("dst_x", "dst_y", "src_x", "src_y", "w", "h", "col_frac", "row_frac",
@@ -116,19 +117,21 @@ def run(ctx, r, torch, ext, flush, kernels):
     kernels["mc_4k10_put_8tap"]["e2e"] = {
         "value": px_all / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "h2d_bytes": int(h_src.numel() * 2 + allj.nbytes),
         "d2h_bytes": int(h_dst.numel() * 2),
-        "path": "r1c_plane_upload + r1c_put_8tap_batch (host job list: the 19 tilings, %.0f Mpx) + r1c_plane_download" % (px_all / 1e6)}
+        "path": "r1c_plane_upload + r1c_put_8tap_batch (page-locked host job list: the 19 tilings, %.0f Mpx) + r1c_plane_download" % (px_all / 1e6)}
     t16 = [j for j in bench_kernels.mc_jobs(r, rng, lib, W, H, 1) if int(j["w"][0]) == 16 and int(j["h"][0]) == 16][0]
     t16["tmp_off"] = np.arange(t16.size, dtype=np.int64) * 256
-    htmp = np.zeros(t16.size * 256, dtype=np.int16)
+    htmp = torch.zeros(t16.size * 256, dtype=torch.int16).pin_memory().numpy()  # page-locked: the DMA target itself
     ms = _time_host(lambda: r.prep_8tap_batch(ctx, htmp, src, t16, BD), 2)
     kernels["mc_4k10_prep_8tap"]["e2e"] = {
         "value": htmp.size / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "h2d_bytes": int(t16.nbytes + htmp.nbytes),
-        "d2h_bytes": int(htmp.nbytes), "path": "r1c_prep_8tap_batch (host job list: the 16x16 tiling, host i16 output; plane resident)"}
+        "d2h_bytes": int(htmp.nbytes), "path": "r1c_prep_8tap_batch (host job list: the 16x16 tiling, page-locked host i16 output; plane resident)"}
     # ---------------------------------------------------------------------------------------------------- TX ----
     n_samples = W * H * 3 // 2
     res = rng.integers(-1023, 1024, size=n_samples, dtype=np.int16)
     ms_cpu = ms_e2e = 0.0
     coeffs = cs = 0
+    h_res = torch.from_numpy(res).pin_memory()  # page-locked host buffers: DMA source / target without a staging copy
+    h_co = torch.empty(n_samples, dtype=torch.int32).pin_memory()
     for ts in range(19):
         w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
         n = n_samples // (w * h)
@@ -137,14 +140,13 @@ def run(ctx, r, torch, ext, flush, kernels):
         co = np.empty(ns * w * h, dtype=np.int32)
         ms_cpu += _time_host(lambda: L.r1o_fht_batch(blk.ctypes.data, co.ctypes.data, ts, 0, BD, ns), 1)
         cs += ns * w * h
-        full = np.ascontiguousarray(res[:n * w * h]).reshape(n, h, w)
-        ms_e2e += _time_host(lambda: r.forward_transform(ctx, full, ts, 0, BD), 1)
+        ms_e2e += _time_host(lambda: ctx.check(lib.r1c_fwd_txfm_batch(ctx.h, ts, 0, BD, h_res.data_ptr(), h_co.data_ptr(), n)), 2)
         coeffs += n * w * h
     k = kernels["tx_4k10_fwd_dct_dct"]
     k["cpu_baseline"] = {"value": cs / 1e6 / (ms_cpu / 1e3), "unit": "Mcoeff/s", "cores": cores, "kind": "port", "note": note,
                          "sample": "0.4 M samples of each of the 19 TxSize (%.1f M coefficients)" % (cs / 1e6)}
     k["e2e"] = {"value": coeffs / 1e6 / (ms_e2e / 1e3), "unit": "Mcoeff/s", "ms": ms_e2e, "h2d_bytes": int(coeffs * 2),
-                "d2h_bytes": int(coeffs * 4), "path": "r1c_fwd_txfm_batch per TxSize (host i16 residual in, host i32 coefficients out)"}
+                "d2h_bytes": int(coeffs * 4), "path": "r1c_fwd_txfm_batch per TxSize (page-locked host i16 residual in, page-locked host i32 coefficients out)"}
     # -------------------------------------------------------------------------------------------- SAD / SATD ----
     o_org = r1o.OPlane(W, H, 0, 0, 88, 88, 2)
     o_org.data[...] = rng.integers(0, 1024, o_org.data.shape)
@@ -158,6 +160,8 @@ def run(ctx, r, torch, ext, flush, kernels):
     px_s = int(sum(lib.r1c_block_width(int(b)) * lib.r1c_block_height(int(b)) for b in sj["bsize"]))
     outv = np.zeros(sj.size, dtype=np.uint32)
     h_org = torch.from_numpy(o_org.data).pin_memory()
+    dj_pin = torch.from_numpy(dj.view(np.uint8)).pin_memory().numpy().view(r.DIST_JOB)  # page-locked job list and result array
+    h_dout = torch.empty(dj.size, dtype=torch.int32).pin_memory()
     for satd, name in ((0, "sad"), (1, "satd")):
         ms = _time_host(lambda: L.r1o_dist_batch(satd, o_org.origin_ptr(), C.byref(o_org.cfg), o_src.origin_ptr(), C.byref(o_src.cfg),
                                                  j5.ctypes.data, sj.size, 2, outv.ctypes.data), 1)
@@ -168,10 +172,11 @@ def run(ctx, r, torch, ext, flush, kernels):
         def e2e_dist():
             ctx.check(lib.r1c_plane_upload(ctx.h, org.h, h_org.data_ptr()))
             ctx.check(lib.r1c_plane_upload(ctx.h, src.h, h_src.data_ptr()))
-            r.sad_batch(ctx, org, src, dj, BD, satd=bool(satd))
+            fn = lib.r1c_satd_batch if satd else lib.r1c_sad_batch
+            ctx.check(fn(ctx.h, org.h, src.h, dj_pin.ctypes.data, dj_pin.size, BD, h_dout.data_ptr()))
         ms = _time_host(e2e_dist, 2)
         kernels["dist_4k10_" + name]["e2e"] = {
             "value": px_all / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms,
             "h2d_bytes": int(h_org.numel() * 2 + h_src.numel() * 2 + dj.nbytes), "d2h_bytes": int(dj.size * 4),
-            "path": "r1c_plane_upload x2 + r1c_%s_batch (host job list: the 19 tilings as one list, host u32 results)" % name}
+            "path": "r1c_plane_upload x2 + r1c_%s_batch (page-locked host job list: the 19 tilings as one list, page-locked host u32 results)" % name}
     kernels["config0_dist_bench"] = config0(ctx, r, r1o)

@@ -89,6 +89,11 @@ static inline bool region_in_plane(const r1c_plane_cfg &c, int64_t x, int64_t y,
 int r1c_set_err(r1c_ctx *ctx, int code, const char *fmt, ...);
 int r1c_stage_host(r1c_ctx *ctx, int slot, size_t bytes, void **out);
 int r1c_scratch_dev(r1c_ctx *ctx, int slot, size_t bytes, void **out);
+// Host side of a copy.  A page-locked caller buffer is the DMA source / target itself (*staged = 0); pageable memory
+// goes through the pinned stage `slot`: r1c_host_src copies the caller's bytes in, r1c_host_dst hands out the stage and
+// the caller copies out after synchronising (*staged = 1).
+int r1c_host_src(r1c_ctx *ctx, int slot, const void *p, size_t bytes, const void **src);
+int r1c_host_dst(r1c_ctx *ctx, int slot, void *p, size_t bytes, void **dst, int *staged);
 // me_sb2.cu: superblock search for 8-bit and 10-bit planes; *handled = 0 -> caller falls back to me_sb.cu
 int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, const r1c_sb_params *p, int bit_depth,
                    const r1c_sb_job *d_jobs, int64_t n, r1c_me_result *d_results, const int2 *d_map, int64_t n_map,

@@ -64,6 +64,34 @@ extern "C" void r1c_destroy(r1c_ctx *ctx) {
   free(ctx);
 }
 
+static bool host_pinned(const void *p) {
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost) return true;
+  (void)cudaGetLastError();
+  return false;
+}
+int r1c_host_src(r1c_ctx *ctx, int slot, const void *p, size_t bytes, const void **src) {
+  if (host_pinned(p)) {
+    *src = p;
+    return R1C_OK;
+  }
+  void *h;
+  int rc = r1c_stage_host(ctx, slot, bytes, &h);
+  if (rc) return rc;
+  memcpy(h, p, bytes);
+  *src = h;
+  return R1C_OK;
+}
+int r1c_host_dst(r1c_ctx *ctx, int slot, void *p, size_t bytes, void **dst, int *staged) {
+  if (host_pinned(p)) {
+    *dst = p;
+    *staged = 0;
+    return R1C_OK;
+  }
+  *staged = 1;
+  return r1c_stage_host(ctx, slot, bytes, dst);
+}
+
 extern "C" int r1c_sync(r1c_ctx *ctx) {
   if (!ctx) return R1C_ERR_ARG;
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

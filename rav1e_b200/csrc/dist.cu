@@ -317,18 +317,19 @@ int dist_batch_host(r1c_ctx *ctx, int use_satd, const r1c_plane *org, const r1c_
                 R1C_ERR_BOUNDS, "job %lld: block leaves the allocated plane", (long long)i);
   }
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  void *h_jobs, *d_jobs, *d_out, *h_out;
+  const void *h_jobs;
+  void *d_jobs, *d_out, *h_out;
+  int staged;
   size_t jb = (size_t)n * sizeof(r1c_dist_job), ob = (size_t)n * sizeof(uint32_t);
-  if ((rc = r1c_stage_host(ctx, 0, jb, &h_jobs))) return rc;
-  if ((rc = r1c_stage_host(ctx, 1, ob, &h_out))) return rc;
+  if ((rc = r1c_host_src(ctx, 0, jobs, jb, &h_jobs))) return rc;  // page-locked buffers: DMA source / target themselves
+  if ((rc = r1c_host_dst(ctx, 1, out, ob, &h_out, &staged))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 0, jb, &d_jobs))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 1, ob, &d_out))) return rc;
-  memcpy(h_jobs, jobs, jb);
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = launch_dist(ctx, use_satd, org, ref, (const r1c_dist_job *)d_jobs, n, (uint32_t *)d_out))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_out, d_out, ob, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  memcpy(out, h_out, ob);
+  if (staged) memcpy(out, h_out, ob);
   return R1C_OK;
 }
 

@@ -625,12 +625,12 @@ extern "C" int r1c_put_8tap_batch(r1c_ctx *ctx, r1c_plane *dst, const r1c_plane 
     // dst region assert of put_8tap, src/mc.rs:415-422
     R1C_REQUIRE(ctx, region_in_plane(dst->cfg, jobs[i].dst_x, jobs[i].dst_y, jobs[i].w, jobs[i].h), R1C_ERR_BOUNDS, "mc job %lld: dst block leaves the allocated plane", (long long)i);
   }
-  void *h_jobs, *d_jobs;
+  const void *h_jobs;
+  void *d_jobs;
   const size_t jb = (size_t)n * sizeof(r1c_mc_job);
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  if ((rc = r1c_stage_host(ctx, 0, jb, &h_jobs))) return rc;
+  if ((rc = r1c_host_src(ctx, 0, jobs, jb, &h_jobs))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 0, jb, &d_jobs))) return rc;
-  memcpy(h_jobs, jobs, jb);
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = launch_mc(ctx, 0, dst, nullptr, src, (const r1c_mc_job *)d_jobs, n, bit_depth))) return rc;
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -648,21 +648,23 @@ extern "C" int r1c_prep_8tap_batch(r1c_ctx *ctx, int16_t *tmp, int64_t tmp_len, 
     // `tmp.len() >= width * height`, src/mc.rs:525-528
     R1C_REQUIRE(ctx, jobs[i].tmp_off >= 0 && (int64_t)jobs[i].tmp_off + (int64_t)jobs[i].w * jobs[i].h <= tmp_len, R1C_ERR_BOUNDS, "mc job %lld: tmp is smaller than the compute block", (long long)i);
   }
-  void *h_jobs, *d_jobs, *h_tmp, *d_tmp;
+  const void *h_jobs, *h_in;
+  void *d_jobs, *h_tmp, *d_tmp;
+  int staged;
   const size_t jb = (size_t)n * sizeof(r1c_mc_job), tb = (size_t)tmp_len * 2;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  if ((rc = r1c_stage_host(ctx, 0, jb, &h_jobs))) return rc;
-  if ((rc = r1c_stage_host(ctx, 1, tb, &h_tmp))) return rc;
+  // page-locked caller buffers are the DMA source / target themselves; elements no job writes keep the caller's values
+  if ((rc = r1c_host_src(ctx, 0, jobs, jb, &h_jobs))) return rc;
+  if ((rc = r1c_host_src(ctx, 1, tmp, tb, &h_in))) return rc;
+  if ((rc = r1c_host_dst(ctx, 1, tmp, tb, &h_tmp, &staged))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 0, jb, &d_jobs))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 1, tb, &d_tmp))) return rc;
-  memcpy(h_jobs, jobs, jb);
-  memcpy(h_tmp, tmp, tb);  // elements no job writes keep the caller's values
   R1C_CUDA(ctx, cudaMemcpyAsync(d_jobs, h_jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
-  R1C_CUDA(ctx, cudaMemcpyAsync(d_tmp, h_tmp, tb, cudaMemcpyHostToDevice, ctx->stream));
+  R1C_CUDA(ctx, cudaMemcpyAsync(d_tmp, h_in, tb, cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = launch_mc(ctx, 1, nullptr, (int16_t *)d_tmp, src, (const r1c_mc_job *)d_jobs, n, bit_depth))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_tmp, d_tmp, tb, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  memcpy(tmp, h_tmp, tb);
+  if (staged) memcpy(tmp, h_tmp, tb);
   return R1C_OK;
 }
 

@@ -101,19 +101,19 @@ extern "C" int r1c_fwd_txfm_batch(r1c_ctx *ctx, int tx_size, int tx_type, int bi
   if (n == 0) return R1C_OK;
   const size_t area = (size_t)r1c_tx_width(tx_size) * r1c_tx_height(tx_size);
   const size_t ib = (size_t)n * area * 2, ob = (size_t)n * area * 4;
-  void *h_in, *h_out, *d_in, *d_out;
-  int rc;
+  const void *h_in;
+  void *h_out, *d_in, *d_out;
+  int rc, staged;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  if ((rc = r1c_stage_host(ctx, 0, ib, &h_in))) return rc;
-  if ((rc = r1c_stage_host(ctx, 1, ob, &h_out))) return rc;
+  if ((rc = r1c_host_src(ctx, 0, residual, ib, &h_in))) return rc;  // page-locked buffers are the DMA source / target themselves
+  if ((rc = r1c_host_dst(ctx, 1, coeffs, ob, &h_out, &staged))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 0, ib, &d_in))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 1, ob, &d_out))) return rc;
-  memcpy(h_in, residual, ib);
   R1C_CUDA(ctx, cudaMemcpyAsync(d_in, h_in, ib, cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = r1c_fwd_txfm_batch_dev(ctx, tx_size, tx_type, bit_depth, (const int16_t *)d_in, (int32_t *)d_out, n))) return rc;
   R1C_CUDA(ctx, cudaMemcpyAsync(h_out, d_out, ob, cudaMemcpyDeviceToHost, ctx->stream));
   R1C_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  memcpy(coeffs, h_out, ob);
+  if (staged) memcpy(coeffs, h_out, ob);
   return R1C_OK;
 }
 

@@ -777,6 +777,30 @@ def test_frame_me_window_equals_frame_by_frame(r, ctx, oracle):
         assert np.array_equal(r.frame_me(ctx, pairs[3][0], pairs[3][1], params, bd), want[3])  # the context is still usable
 
 
+def test_page_locked_host_buffers_are_dma_targets(r, ctx, oracle):
+    """host-array entry points take page-locked buffers as the DMA source / target (no staging copy) and pageable ones
+    through the pinned stage: same results either way (r1c_fwd_txfm_batch, r1c_prep_8tap_batch, r1c_frame_me)"""
+    import torch
+    rng = np.random.default_rng(8)
+    res = rng.integers(-1023, 1024, size=(500, 16, 16)).astype(np.int16)
+    want = r.forward_transform(ctx, res, 2, 0, 10)
+    h_in = torch.from_numpy(res.copy()).pin_memory()
+    h_out = torch.full((res.size,), -1, dtype=torch.int32).pin_memory()
+    ctx.check(ctx.lib.r1c_fwd_txfm_batch(ctx.h, 2, 0, 10, h_in.data_ptr(), h_out.data_ptr(), 500))
+    assert np.array_equal(h_out.numpy().reshape(want.shape), want)
+    assert np.array_equal(want.reshape(-1), oracle.fht_batch(res, 2, 0, 10).reshape(-1))
+    o_src, d_src = twin_plane(r, oracle, ctx, 256, 128, 2, 10, rng)
+    jobs = np.zeros(40, dtype=r.MC_JOB)
+    for i in range(40):
+        jobs[i] = (0, 0, int(rng.integers(0, 240)), int(rng.integers(0, 112)), 16, 16, int(rng.integers(0, 16)), int(rng.integers(0, 16)),
+                   0, 0, 300 * i)
+    a = np.full(40 * 300, 77, dtype=np.int16)
+    r.prep_8tap_batch(ctx, a, d_src, jobs, 10)
+    b = torch.full((40 * 300,), 77, dtype=torch.int16).pin_memory().numpy()
+    r.prep_8tap_batch(ctx, b, d_src, jobs, 10)
+    assert np.array_equal(a, b) and (a.reshape(40, 300)[:, 256:] == 77).all() and (a.reshape(40, 300)[:, :256] != 77).any()
+
+
 def test_profile_hooks_count_launches(r, ctx, oracle):
     o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, 128, 128, 1, 8, 5)
     ctx.check(ctx.lib.r1c_profile(ctx.h, 1))
