@@ -84,9 +84,9 @@ padded = bench_kernels.padded
 
 def ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one me_sb2_kernel launch from the committed `ncu --set full`
-    capture (profiles/ncu_me_sb2_u8_r01h.json), bytes per launch; None when the summary is missing"""
+    capture (profiles/ncu_me_sb2_r02.json), bytes per launch; None when the summary is missing"""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_me_sb2_u8_r01h.json")))
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_me_sb2_r02.json")))
         return int(d["dram__bytes_read.sum"]) + int(d["dram__bytes_write.sum"])
     except Exception:
         return None
