@@ -47,11 +47,14 @@ __device__ __forceinline__ int apply_shift(int v, int entry) {
 
 template <int W, int H>
 struct FhtCfg {
-  static constexpr int MAXD = W > H ? W : H;
-  // blocks per CTA: 256 threads for the small transforms, 128 for 32/64-point
-  // ones (their register footprint is large)
-  static constexpr int BPC = (MAXD >= 32 ? 128 : 256) / MAXD;
-  static constexpr int THREADS = BPC * MAXD;
+  static constexpr int MAXD = W > H ? W : H, MIND = W < H ? W : H;
+  // 256 threads for the small transforms, 128 for 32/64-point ones (their register footprint is large).
+  // Blocks per CTA: THREADS / MAXD -- one column and one row per thread at most -- except for the 4:1 shapes
+  // (4x16, 16x4, 8x32, 32x8, 16x64, 64x16), where the pass with the long transforms would run on a quarter of the
+  // threads (barrier was the top stall, profiles/ncu_fht_r02.md): those take THREADS / MIND blocks, the long pass has one
+  // item per thread and the short one loops
+  static constexpr int THREADS = MAXD >= 32 ? 128 : 256;
+  static constexpr int BPC = THREADS / (MAXD >= 4 * MIND ? MIND : MAXD);
   static constexpr int MID_STRIDE = W + 1;
   // residual blocks of narrow transforms sit 16 / 32 bytes apart in shared memory so that the lanes of a
   // warp that read the same (row, column) of different blocks hit different banks
@@ -198,8 +201,8 @@ __global__ void __launch_bounds__(FhtCfg<W, H>::THREADS) fht_kernel(FhtArgs a) {
     __syncthreads();
 
     // ---- columns (forward.rs:1826-1869) ----------------------------------------
-    if (tid < nb * W) {
-      const int b = tid / W, c = tid % W;
+    for (int itc = tid; itc < nb * W; itc += C::THREADS) {
+      const int b = itc / W, c = itc % W;
       const int16_t *col = s_in + b * BLK16 + c;
       int v[H], o[H];
       if (a.col_flip) {  // :1829-1834 flip upside down
@@ -225,8 +228,8 @@ __global__ void __launch_bounds__(FhtCfg<W, H>::THREADS) fht_kernel(FhtArgs a) {
     // ---- rows (forward.rs:1872-1898) ---------------------------------------------
     int32_t *out = a.coeffs + blk0 * AREA;
     const bool direct = DIRECT_OUT && a.out16;
-    if (tid < nb * H) {
-      int *row = s_mid + tid * C::MID_STRIDE;  // tid = b*H + r
+    for (int itr = tid; itr < nb * H; itr += C::THREADS) {
+      int *row = s_mid + itr * C::MID_STRIDE;  // itr = b*H + r
       int v[W], o[W];
 #pragma unroll
       for (int c = 0; c < W; c++) v[c] = row[c];
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__(FhtCfg<W, H>::THREADS) fht_kernel(FhtArgs a) {
         for (int c = 0; c < W; c++) o[c] = (int)((unsigned)o[c] << a.ls2);
       }
       if (direct) {
-        int4 *d4 = (int4 *)(out + (long long)tid * W);
+        int4 *d4 = (int4 *)(out + (long long)itr * W);
 #pragma unroll
         for (int c = 0; c < W; c += 4) d4[c / 4] = make_int4(o[c], o[c + 1], o[c + 2], o[c + 3]);
       } else {
