@@ -58,11 +58,14 @@ __host__ __device__ inline int box_w_of(int wc, int pb) {
 }
 // Units of the two narrow width classes are owned by one or two threads, so the lanes of a warp read the same (row, word)
 // of different unit slots, and slots are 128-byte aligned (what a tensor load demands: tools/tma_probe3.cu): every lane
-// on one bank.  Their boxes start (unit & STAG) rows higher, which moves a lane's rows by that many row pitches.
+// on one bank.  Their boxes start (unit & STAG) rows higher, which moves a lane's rows by that many row pitches
+// (12 words for the 8-wide u16 box: 4 distinct bank groups).  The 16-wide class (4 strips per unit, row pitch 16 words)
+// has two distinct positions: one extra row.  Measured: 8 phases lose (more bytes, fewer units per batch), and the 32-wide
+// class (8 strips per unit, bound by the XU pipe) does not gain.
 #ifndef MC_TMA_STAG
 #define MC_TMA_STAG 3
 #endif
-__host__ __device__ inline int stag_of(int wc) { return wc <= 1 ? MC_TMA_STAG : 0; }
+__host__ __device__ inline int stag_of(int wc) { return wc <= 1 ? MC_TMA_STAG : (wc == 2 ? 1 : 0); }
 __host__ __device__ inline int box_h_of(int wc, int hc) { return tile_h_of(hc) + 7 + stag_of(wc); }
 // + one row: the last (even, odd) pair of a strip reads one row past the box (it meets a zero tap)
 __host__ __device__ inline int slot_bytes_of(int wc, int hc, int pb) {
