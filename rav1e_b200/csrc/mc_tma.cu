@@ -51,10 +51,13 @@ __host__ __device__ inline int tile_h_of(int hc) { return 4 << hc; }
 // tensor load whose inner coordinate * element size is not a multiple of 16 faults with "illegal instruction";
 // tools/tma_probe2.cu), so the box starts at (src_x - 3) rounded DOWN to 16 bytes and is up to 16 / pb - 1 pixels wider
 // than tile width + 7; rounded up to 16 bytes.
+#ifndef MC_TMA_W2PAD
+#define MC_TMA_W2PAD 0  // 1: the 16-wide u16 box is 16 bytes wider (row pitch 20 words: four bank positions instead of two)
+#endif
 __host__ __device__ inline int box_w_of(int wc, int pb) {
   const int tw = wc == 0 ? 8 : (4 << wc);  // w <= 4 shares the 8-wide box
   const int px16 = 16 / pb;
-  return (tw + 7 + (px16 - 1) + px16 - 1) / px16 * px16;
+  return (tw + 7 + (px16 - 1) + px16 - 1) / px16 * px16 + ((MC_TMA_W2PAD && wc == 2 && pb == 2) ? px16 : 0);
 }
 // Units of the two narrow width classes are owned by one or two threads, so the lanes of a warp read the same (row, word)
 // of different unit slots, and slots are 128-byte aligned (what a tensor load demands: tools/tma_probe3.cu): every lane
@@ -65,11 +68,13 @@ __host__ __device__ inline int box_w_of(int wc, int pb) {
 #ifndef MC_TMA_STAG
 #define MC_TMA_STAG 3
 #endif
-__host__ __device__ inline int stag_of(int wc) { return wc <= 1 ? MC_TMA_STAG : (wc == 2 ? 1 : 0); }
-__host__ __device__ inline int box_h_of(int wc, int hc) { return tile_h_of(hc) + 7 + stag_of(wc); }
+__host__ __device__ inline int stag_of(int wc, int pb) {
+  return wc <= 1 ? MC_TMA_STAG : (wc == 2 ? ((pb == 1 || MC_TMA_W2PAD) ? MC_TMA_STAG : 1) : 0);
+}
+__host__ __device__ inline int box_h_of(int wc, int hc, int pb) { return tile_h_of(hc) + 7 + stag_of(wc, pb); }
 // + one row: the last (even, odd) pair of a strip reads one row past the box (it meets a zero tap)
 __host__ __device__ inline int slot_bytes_of(int wc, int hc, int pb) {
-  return (box_w_of(wc, pb) * pb * (box_h_of(wc, hc) + 1) + 127) & ~127;
+  return (box_w_of(wc, pb) * pb * (box_h_of(wc, hc, pb) + 1) + 127) & ~127;
 }
 __host__ __device__ inline int upb_of(int wc, int hc, int pb) {
   const int a = CT / strips_of(wc), b = STAGE_BYTES / slot_bytes_of(wc, hc, pb);
@@ -356,7 +361,7 @@ __global__ void __launch_bounds__(THREADS, STAGES == 1 ? 5 : 2) mc_tma_kernel(co
       const CUtensorMap *map = &a.map[(wc == 0 ? 0 : wc - 1) * NHC + hc];
       if (it >= STAGES) mbar_wait(&s_empty[st], ((it / STAGES) - 1) & 1);
       const uint32_t u0 = cur.b * cur.upb, nu = min((uint32_t)cur.upb, cur.cnt - u0);
-      if (lane == 0) mbar_expect_tx(&s_full[st], nu * (uint32_t)(box_w_of(wc, PB) * PB * box_h_of(wc, hc)));
+      if (lane == 0) mbar_expect_tx(&s_full[st], nu * (uint32_t)(box_w_of(wc, PB) * PB * box_h_of(wc, hc, PB)));
 #pragma unroll
       for (int k = 0; k < UPL; k++) {
         const uint32_t u = lane + 32 * k;
@@ -372,7 +377,7 @@ __global__ void __launch_bounds__(THREADS, STAGES == 1 ? 5 : 2) mc_tma_kernel(co
           const int x = a.src.xorigin + (int)pw[k][2] + 32 * tx - 3, y = a.src.yorigin + (int)pw[k][3] + 16 * ty - 3;
           const int x_al = x & ~(16 / PB - 1);  // floor to 16 bytes (two's complement: also for negative x)
           rec[7] = (uint32_t)tx | ((uint32_t)ty << 8) | ((uint32_t)(x - x_al) << 16);
-          tma_load_2d(s_px + st * STAGE_BYTES + u * slot, map, x_al, y - (int)(u & (uint32_t)stag_of(wc)), &s_full[st]);
+          tma_load_2d(s_px + st * STAGE_BYTES + u * slot, map, x_al, y - (int)(u & (uint32_t)stag_of(wc, PB)), &s_full[st]);
         }
       }
       mbar_arrive(&s_full[st]);  // release: after this lane's record stores
@@ -423,7 +428,7 @@ __global__ void __launch_bounds__(THREADS, STAGES == 1 ? 5 : 2) mc_tma_kernel(co
             // 0 / 1 pixel (u16) or 0..3 bytes (u8), undone per row by one PRMT / funnel shift per word
             const int boff = (dx + 4 * strip) * PB;
             const uint32_t phase = PB == 1 ? (uint32_t)(boff & 3) * 8u : ((boff & 2) ? 0x5432u : 0x3210u);
-            const unsigned char *rowp = s_px + st * STAGE_BYTES + un * slot + (un & stag_of(wc)) * pitch + (boff & ~3);
+            const unsigned char *rowp = s_px + st * STAGE_BYTES + un * slot + (un & stag_of(wc, PB)) * pitch + (boff & ~3);
             uint8_t *dp;
             long long dstride;
             constexpr int OB = KIND == 1 ? 2 : PB;  // bytes per output element
@@ -558,7 +563,7 @@ bool get_maps(const r1c_plane *src, int device, CUtensorMap *out) {
   const cuuint32_t estr[2] = {1, 1};
   for (int wc = 1; wc < 4; wc++)
     for (int hc = 0; hc < NHC; hc++) {
-      const cuuint32_t box[2] = {(cuuint32_t)box_w_of(wc, e.pb), (cuuint32_t)box_h_of(wc, hc)};
+      const cuuint32_t box[2] = {(cuuint32_t)box_w_of(wc, e.pb), (cuuint32_t)box_h_of(wc, hc, e.pb)};
       const CUresult r = g_encode(&e.map[(wc - 1) * NHC + hc], e.pb == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
                                   const_cast<void *>(e.data), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
