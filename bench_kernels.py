@@ -210,7 +210,8 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
         out["mc_4k10_" + name] = {
             "workload": "4K 10-bit luma tiled by each of the 19 block sizes, %d candidate MVs per block and launch (%.0f Mpx per launch), random fracs / filter pairs / +-32 px" % (K, K * W * H / 1e6),
             "value": px_total / 1e6 / (call_ms / 1e3), "unit": "Mpix/s", "ms": call_ms, "pixels": px_total,
-            "kernel_ms": ms, "kernel_us_by_block_size": by_size[name], "note": "value / ms = whole _dev call (item count + prefix sum + kernel); "
+            "kernel_ms": ms, "kernel_us_by_block_size": by_size[name], "note": ("value / ms = whole _dev call (one launch, no scratch); " if name == "mc_avg" else
+                                      "value / ms = whole _dev call (unit count + scatter + kernel); ") +
                                      "roofline = the main kernel alone (19 launches, CUDA events inside the library)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
                          "alg_bytes_per_px": bpp, "peak_source": hbm_how}}

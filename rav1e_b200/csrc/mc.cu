@@ -390,43 +390,78 @@ struct AvgArgs {
   int dst_stride;
   const int16_t *t1, *t2;
   const r1c_avg_job *jobs;
-  const long long *offs;
   long long n;
   int bit_depth;
+  int lg_g;  // a warp takes 1 << lg_g consecutive jobs
 };
 
 // mc_avg_ref, src/mc.rs:389-408
+// One launch, no scratch: a warp takes a CHUNK of up to 32 consecutive jobs (one per lane), prefix-sums their item
+// counts with shuffles and then walks the chunk's items with all its lanes.  item = 4 pixels of one row: fully
+// parallel, 8-byte loads / stores.  (Round 1 counted the items of the whole list and ran two device-wide scans before
+// a persistent kernel: for 4x4 blocks that scheduling traffic -- 40 bytes per job -- was larger than the 96 bytes of
+// pixels the job moves, and the three extra launches were a third of the call.)  The host picks the chunk size from
+// n alone so that the grid has at least ~32 warps per SM; the hardware block scheduler does the load balancing.
 template <int PB>
 __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
-  const long long total = a.offs[a.n];
+  constexpr int WARPS = MC_THREADS / 32;
+  constexpr unsigned FULL = 0xffffffffu;
+  __shared__ uint4 s_job[WARPS][32];
+  __shared__ int s_pre[WARPS][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long j0 = ((long long)blockIdx.x * WARPS + warp) << a.lg_g;
+  if (j0 >= a.n) return;
+  const int g = (int)min(1ll << a.lg_g, a.n - j0);
   const int ib = a.bit_depth == 12 ? 2 : 4;
   const int maxv = (1 << a.bit_depth) - 1;
-  const int ipj = a.offs[a.n + 1] == -a.offs[a.n + 2] ? (int)a.offs[a.n + 1] : 0;  // min == max items per job
-  // item = 4 pixels of one row: fully parallel, 8-byte loads / stores.  A thread takes U items per trip and issues
-  // all their job reads, then all their loads, before the arithmetic: the kernel lasts only a few DRAM latencies, so
-  // the number of independent requests in flight per thread is what sets its bandwidth.
+  static_assert(sizeof(r1c_avg_job) == 16, "r1c_avg_job is read as one 16-byte word");
+  uint4 jw = make_uint4(0, 0, 0, 0);  // dst_x, dst_y, w | h << 16, tmp_off
+  int c = 0;
+  if (lane < g) {
+    jw = __ldg((const uint4 *)(a.jobs + j0 + lane));
+    c = (((int)(int16_t)(jw.z & 0xffffu) + 3) >> 2) * (int)(int16_t)(jw.z >> 16);
+  }
+  int inc = c;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(FULL, inc, d);
+    if (lane >= d) inc += t;
+  }
+  const int total = __shfl_sync(FULL, inc, 31);
+  const int c0 = __shfl_sync(FULL, c, 0);
+  // every job of the chunk with the same number of items (the usual batch): a shift or a division, no search
+  const bool uniform = __all_sync(FULL, lane >= g || c == c0) && c0 > 0;
+  const int lg_c0 = uniform && (c0 & (c0 - 1)) == 0 ? __ffs(c0) - 1 : -1;
+  s_job[warp][lane] = jw;
+  s_pre[warp][lane] = lane < g ? inc - c : 0x7fffffff;
+  __syncwarp();
+  // A lane takes U items per trip and issues all their loads before the arithmetic: the kernel lasts only a few DRAM
+  // latencies, so the number of independent requests in flight per thread is what sets its bandwidth.
   constexpr int U = 4;
-  const int lg_ipj = ipj > 0 && (ipj & (ipj - 1)) == 0 ? __ffs(ipj) - 1 : -1;  // every BlockSize: a shift
-  const long long stride = (long long)gridDim.x * MC_THREADS;
-  for (long long item0 = (long long)blockIdx.x * MC_THREADS + threadIdx.x; item0 < total; item0 += U * stride) {
+  const bool base8 = ((((uintptr_t)a.t1) | ((uintptr_t)a.t2)) & 7) == 0;  // 8-byte loads need both arrays aligned
+  for (int item0 = lane; item0 < total; item0 += 32 * U) {
     long long o[U];
     uint8_t *d[U];
     int ncols[U];
     bool live[U], vec[U];
 #pragma unroll
     for (int u = 0; u < U; u++) {
-      const long long item = item0 + u * stride;
+      const int item = item0 + 32 * u;
       live[u] = item < total;
-      const long long it = live[u] ? item : item0;
-      // (ncu: with a 64-bit division per item the kernel was bound by its ~250 instructions per item, not by memory)
-      const long long ji = lg_ipj >= 0 ? (it >> lg_ipj)
-                           : ipj      ? (long long)((unsigned long long)it / (unsigned)ipj)
-                                      : find_job(a.offs, a.n, it);
-      static_assert(sizeof(r1c_avg_job) == 16, "r1c_avg_job is read as one 16-byte word");
-      const uint4 jw = __ldg((const uint4 *)(a.jobs + ji));  // dst_x, dst_y, w | h << 16, tmp_off
-      const long long toff = (long long)(int)jw.w;
-      const int jx = (int)jw.x, jy = (int)jw.y, w = (int)(int16_t)(jw.z & 0xffffu);
-      const int local = ipj ? (int)(it - ji * ipj) : (int)(it - a.offs[ji]);
+      const int it = live[u] ? item : item0;
+      int ji;
+      if (lg_c0 >= 0) ji = it >> lg_c0;
+      else if (uniform) ji = (int)((unsigned)it / (unsigned)c0);
+      else {
+        ji = 0;  // largest j with pre[j] <= it (the padding lanes hold INT_MAX)
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1)
+          if (s_pre[warp][ji + s] <= it) ji += s;
+      }
+      const uint4 jb = s_job[warp][ji];
+      const long long toff = (long long)(int)jb.w;
+      const int jx = (int)jb.x, jy = (int)jb.y, w = (int)(int16_t)(jb.z & 0xffffu);
+      const int local = it - (uniform ? ji * c0 : s_pre[warp][ji]);
       const int nstrips = (w + 3) >> 2;
       const int r = (nstrips & (nstrips - 1)) == 0 ? local >> (__ffs(nstrips) - 1) : local / nstrips;
       const int strip = local - r * nstrips;
@@ -434,7 +469,7 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
       ncols[u] = min(4, w - x0);
       o[u] = toff + (long long)r * w + x0;
       d[u] = a.dst0 + ((long long)(jy + r) * a.dst_stride + jx + x0) * PB;
-      vec[u] = ncols[u] == 4 && (o[u] & 3) == 0;
+      vec[u] = base8 && ncols[u] == 4 && (o[u] & 3) == 0;
     }
     uint2 p[U], q[U];
 #pragma unroll
@@ -454,20 +489,20 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
         v[3] = ((int)p[u].y >> 16) + ((int)q[u].y >> 16);
       } else {
 #pragma unroll
-        for (int c = 0; c < 4; c++) v[c] = c < ncols[u] ? (int)a.t1[o[u] + c] + (int)a.t2[o[u] + c] : 0;
+        for (int c2 = 0; c2 < 4; c2++) v[c2] = c2 < ncols[u] ? (int)a.t1[o[u] + c2] + (int)a.t2[o[u] + c2] : 0;
       }
 #pragma unroll
-      for (int c = 0; c < 4; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
+      for (int c2 = 0; c2 < 4; c2++) v[c2] = min(max(rshift_round(v[c2], ib + 1), 0), maxv);
       uint8_t *dp = d[u];
       if (ncols[u] == 4 && ((uintptr_t)dp & (4 * PB - 1)) == 0) {
         if (PB == 1) *(uint32_t *)dp = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
         else *(uint2 *)dp = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
       } else {
 #pragma unroll
-        for (int c = 0; c < 4; c++)
-          if (c < ncols[u]) {
-            if (PB == 1) dp[c] = (uint8_t)v[c];
-            else ((uint16_t *)dp)[c] = (uint16_t)v[c];
+        for (int c2 = 0; c2 < 4; c2++)
+          if (c2 < ncols[u]) {
+            if (PB == 1) dp[c2] = (uint8_t)v[c2];
+            else ((uint16_t *)dp)[c2] = (uint16_t)v[c2];
           }
       }
     }
@@ -672,10 +707,7 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
                       const r1c_avg_job *d_jobs, int64_t n, int bit_depth) {
   if (n == 0) return R1C_OK;
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
-  long long *d_offs;
   R1C_REQUIRE(ctx, ((uintptr_t)d_jobs & 15) == 0, R1C_ERR_ARG, "mc_avg: the job array must be 16-byte aligned");
-  int rc = build_offsets<r1c_avg_job, 1>(ctx, d_jobs, n, &d_offs);
-  if (rc) return rc;
   AvgArgs a;
   PlaneView dv = make_view(dst);
   a.dst0 = (uint8_t *)dv.p0;
@@ -683,12 +715,16 @@ static int launch_avg(r1c_ctx *ctx, r1c_plane *dst, const int16_t *d_t1, const i
   a.t1 = d_t1;
   a.t2 = d_t2;
   a.jobs = d_jobs;
-  a.offs = d_offs;
   a.n = n;
   a.bit_depth = bit_depth;
+  // jobs per warp: as many as leave ~32 warps per SM (a frame of 64x64 blocks is only ~2000 jobs: one per warp)
+  a.lg_g = 5;
+  while (a.lg_g > 0 && (n >> a.lg_g) < (int64_t)ctx->sm_count * 32) a.lg_g--;
+  const int64_t chunks = (n + (1ll << a.lg_g) - 1) >> a.lg_g;
+  const unsigned grid = (unsigned)((chunks + MC_THREADS / 32 - 1) / (MC_THREADS / 32));
   r1c_prof_begin(ctx, R1C_PROF_MC);
-  if (dst->px_bytes == 1) avg_kernel<1><<<grid_for(ctx, avg_kernel<1>), MC_THREADS, 0, ctx->stream>>>(a);
-  else avg_kernel<2><<<grid_for(ctx, avg_kernel<2>), MC_THREADS, 0, ctx->stream>>>(a);
+  if (dst->px_bytes == 1) avg_kernel<1><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
+  else avg_kernel<2><<<grid, MC_THREADS, 0, ctx->stream>>>(a);
   r1c_prof_end(ctx, R1C_PROF_MC);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;

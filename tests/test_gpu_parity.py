@@ -331,6 +331,77 @@ def test_put_8tap_and_avg(r, ctx, oracle, pb, bd):
 
 
 @pytest.mark.parametrize("pb,bd", BD)
+def test_mc_avg_mixed_and_long_lists(r, ctx, oracle, pb, bd):
+    """mc_avg takes chunks of 1..32 consecutive jobs per warp (the chunk size follows the list length): a mixed
+    tiling with every width class incl. ragged ones (chunks that must search), a list long enough for 32-job chunks
+    of one size, and one whose last chunk is short"""
+    rng = np.random.default_rng(2350 + bd)
+    L = oracle.lib()
+    W, H = 2048, 1280
+
+    def run(ab, tlen):
+        t1 = rng.integers(-4000, 20000, size=tlen).astype(np.int16)
+        t2 = rng.integers(-4000, 20000, size=tlen).astype(np.int16)
+        o_dst, d_dst = twin_plane(r, oracle, ctx, W, H, pb, bd, pad=False, xpad=8, ypad=8)
+        r.mc_avg_batch(ctx, d_dst, t1, t2, ab, bd)
+        got = d_dst.download()
+        # the oracle one job at a time is slow for 10^5 jobs: mc_avg_ref is elementwise (src/mc.rs:389-408), so the
+        # whole plane is checked against that formula in numpy and the formula against the oracle on 600 jobs
+        ib = 2 if bd == 12 else 4
+        x0, y0 = o_dst.cfg.xorigin, o_dst.cfg.yorigin
+        want = o_dst.data.copy()
+        for a in ab:
+            x, y, w, h, o = (int(a[k]) for k in ("dst_x", "dst_y", "w", "h", "tmp_off"))
+            s = t1[o:o + w * h].astype(np.int32) + t2[o:o + w * h]
+            want[y0 + y:y0 + y + h, x0 + x:x0 + x + w] = np.clip((s + (1 << ib)) >> (ib + 1), 0, (1 << bd) - 1).reshape(h, w)
+        for a in list(ab[:300]) + list(ab[rng.integers(0, len(ab), 300)]):
+            x, y, w, h, o = (int(a[k]) for k in ("dst_x", "dst_y", "w", "h", "tmp_off"))
+            L.r1o_mc_avg(o_dst.ptr(x, y), o_dst.cfg.stride, t1[o:].ctypes.data, t2[o:].ctypes.data, w, h, bd, pb)
+            assert np.array_equal(o_dst.data[y0 + y:y0 + y + h, x0 + x:x0 + x + w], want[y0 + y:y0 + y + h, x0 + x:x0 + x + w])
+        assert np.array_equal(got, want)
+
+    # (a) bands of mixed heights, each filled with mixed widths: ~5 * 10^3 jobs, one per warp;
+    # (a') the same list three times over (-> chunks of 2 jobs, rarely of one size)
+    jobs, off, y = [], 0, 0
+    heights = [4, 8, 4, 16, 8, 4, 12, 4, 32, 8, 4, 64, 4, 8, 20, 4, 128]
+    while True:
+        h = heights[len(jobs) % len(heights)] if y else 4
+        if y + h > H:
+            break
+        x = 0
+        while x < W:
+            w = int(rng.choice([4, 8, 16, 4, 8, 32, 12, 6, 5, 3, 64, 128]))
+            if x + w > W:
+                break
+            jobs.append((x, y, w, h, off))
+            off += w * h + int(rng.integers(0, 3))  # odd offsets: the 8-byte loads must fall back
+            x += w
+        y += h
+    order = rng.permutation(len(jobs))
+    ab = np.array([jobs[i] for i in order], dtype=r.AVG_JOB)
+    run(ab, off + 8)
+    ab = np.concatenate([ab, ab[::-1], ab[rng.permutation(len(ab))]])
+    assert len(ab) > 148 * 32 * 2 * 3 // 2
+    run(ab, off + 8)
+    # (b) 4x4 blocks over the plane: 163840 jobs -> 32-job chunks of one size
+    xs, ys = np.meshgrid(np.arange(0, W, 4), np.arange(0, H, 4))
+    ab = np.zeros(xs.size, dtype=r.AVG_JOB)
+    ab["dst_x"], ab["dst_y"], ab["w"], ab["h"] = xs.ravel(), ys.ravel(), 4, 4
+    ab["tmp_off"] = rng.permutation(xs.size) * 16
+    run(ab, xs.size * 16)
+    # (c) the same list cut so that the last chunk is short, with a few blocks of another size mixed in
+    ab = ab[:xs.size - 13].copy()
+    big = (ab["dst_x"] % 64 == 0) & (ab["dst_y"] % 64 == 0) & (rng.random(ab.size) < 0.3)
+    ab["w"][big] = 8  # covers its right-hand neighbour: both would write the plane, so compare only ...
+    keep = np.ones(ab.size, bool)
+    nb = {(int(a["dst_x"]) + 4, int(a["dst_y"])) for a in ab[big]}
+    keep &= ~np.array([(int(a["dst_x"]), int(a["dst_y"])) in nb for a in ab])  # ... after dropping that neighbour
+    ab = ab[keep]
+    ab["tmp_off"] = np.arange(ab.size) * 32
+    run(ab, ab.size * 32)
+
+
+@pytest.mark.parametrize("pb,bd", BD)
 def test_mc_one_block_size_lists(r, ctx, oracle, pb, bd):
     """job lists of ONE block size take the two-pass tile kernel (mc_tile_kernel): put into disjoint tiles, prep,
     all four frac cases, every block size incl. segments of 16 rows (h > 16) and short lists / ragged batches"""
