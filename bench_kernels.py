@@ -357,16 +357,18 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
                          "alg_bytes_per_coeff": bpc, "peak_source": hbm_how}}
     # ------------------------------ the fused residual chain of encode_tx_block on a 4K 10-bit luma plane: source = `org`,
     # prediction = source + noise of +-24 held in `rec` (restored from page-locked memory before every launch, outside
-    # the timed kernel), DCT_DCT, the 14 TxSize without a 64-point side; the same work through the four separate kernels
+    # the timed kernel), DCT_DCT, every TxSize; the same work through the four separate kernels
     # is timed next to it (diff + fht, quantize with tx_dist, dequantize + inverse add: three launches)
     rec = r.Plane(ctx, W, H, 0, 0, 88, 88, 2)
     org_host = org.download()
     h_pred = torch.from_numpy(np.clip(org_host.astype(np.int32) + rng.integers(-24, 25, size=org_host.shape), 0, 1023)
                               .astype(np.uint16)).pin_memory()
     del org_host
-    esum = {"fused": 0.0, "chain": 0.0}
-    eper = {}
-    ebytes = epix = 0
+    # two lines: the 14 sizes up to 32x32 and the five with a 64-point side (enc_tx64.cuh)
+    esum = {g: {"fused": 0.0, "chain": 0.0} for g in (0, 1)}
+    eper = {0: {}, 1: {}}
+    ebytes = {0: 0, 1: 0}
+    epix = {0: 0, 1: 0}
     co_tmp = torch.empty(W * H, dtype=torch.int32, device="cuda")
     for ts in ([int(v) for v in only.split(",")] if only else range(19)):
         w, h = lib.r1c_tx_width(ts), lib.r1c_tx_height(ts)
@@ -382,7 +384,9 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
         d_tj = torch.from_numpy(tj.view(np.int32).reshape(-1)).cuda()
         d_ij = torch.from_numpy(ij.view(np.int32).reshape(-1)).cuda()
         qc = r.QuantizationContext().update(lib, ts, 0, 40, 52)
-        scan = torch.from_numpy(np.concatenate([[0], 1 + rng.permutation(w * h - 1)]).astype(np.int16)).cuda()
+        coded = min(w, 32) * min(h, 32)
+        g = int(max(w, h) == 64)
+        scan = torch.from_numpy(np.concatenate([[0], 1 + rng.permutation(coded - 1)]).astype(np.int16)).cuda()
 
         def f_e():
             ctx.check(lib.r1c_plane_upload_async(ctx.h, rec.h, h_pred.data_ptr()))
@@ -403,23 +407,27 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
                 _kernel_ms(ctx, slot)
             _timed(torch, ext, flush, fn, reps)
             k_ms[key] = sum(_kernel_ms(ctx, slot)[0] for slot in (4, 6, 7)) / reps
-            esum[key] += k_ms[key]
-        b = n * (w * h * 10 + 8)  # 2 + 2 B read, 4 B qcoeff + 2 B pixel written per pixel, 8 B tx_dist per block
-        ebytes += b
-        epix += n * w * h
-        eper["%dx%d" % (w, h)] = {"frac": round(b / (k_ms["fused"] / 1e3) / 1e9 / hbm, 3), "us": round(k_ms["fused"] * 1e3, 1),
+            esum[g][key] += k_ms[key]
+        b = n * (w * h * 6 + coded * 4 + 8)  # 2 + 2 B read and 2 B written per pixel, 4 B per coded qcoeff, 8 B tx_dist per block
+        ebytes[g] += b
+        epix[g] += n * w * h
+        eper[g]["%dx%d" % (w, h)] = {"frac": round(b / (k_ms["fused"] / 1e3) / 1e9 / hbm, 3), "us": round(k_ms["fused"] * 1e3, 1),
                                   "separate_kernels_us": round(k_ms["chain"] * 1e3, 1)}
-    if epix:
-        gbs = ebytes / (esum["fused"] / 1e3) / 1e9
-        out["enc_tx_4k10_fused_dct_dct"] = {
-            "workload": "4K 10-bit luma tiled by each of the 14 TxSize up to 32x32: diff + forward DCT_DCT + quantize (qstep 52) + "
+    for g, key, what, bytes_txt in ((0, "enc_tx_4k10_fused_dct_dct", "the 14 TxSize up to 32x32", "10 per pixel (2 + 2 read, 4 + 2 written) + 8 per block"),
+                                    (1, "enc_tx_4k10_fused_dct_dct_64pt", "the 5 TxSize with a 64-point side (this fork's layouts: "
+                                     "min(W,32) * min(H,32) coded coefficients per block)", "6 per pixel + 4 per coded coefficient + 8 per block")):
+        if not epix[g]:
+            continue
+        gbs = ebytes[g] / (esum[g]["fused"] / 1e3) / 1e9
+        out[key] = {
+            "workload": "4K 10-bit luma tiled by each of " + what + ": diff + forward DCT_DCT + quantize (qstep 52) + "
                         "dequantize + inverse transform added back + tx-domain distortion as ONE kernel per size "
                         "(r1c_encode_tx_block_batch_dev); prediction = source +- 24",
-            "value": epix / 1e6 / (esum["fused"] / 1e3), "unit": "Mpix/s", "ms": esum["fused"], "pixels": epix,
-            "separate_kernels_ms": esum["chain"], "speedup_vs_separate_kernels": esum["chain"] / esum["fused"],
-            "by_tx_size": eper,
+            "value": epix[g] / 1e6 / (esum[g]["fused"] / 1e3), "unit": "Mpix/s", "ms": esum[g]["fused"], "pixels": epix[g],
+            "separate_kernels_ms": esum[g]["chain"], "speedup_vs_separate_kernels": esum[g]["chain"] / esum[g]["fused"],
+            "by_tx_size": eper[g],
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
-                         "alg_bytes": "10 per pixel (2 + 2 read, 4 + 2 written) + 8 per block", "peak_source": hbm_how}}
+                         "alg_bytes": bytes_txt, "peak_source": hbm_how}}
     del rec, h_pred, co_tmp
     # ------------------------------ inverse transform + add onto a 4K luma plane (dequantized-like coefficients):
     # 10-bit (u16 plane `dst`) and 8-bit (u8 plane), and the 10-bit case with dequantize fused into the load

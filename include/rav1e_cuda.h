@@ -400,10 +400,12 @@ int r1c_dequantize_batch_dev(r1c_ctx *ctx, int tx_size, uint32_t dc_quant, uint3
  * the reference only if no block's prediction reads another's reconstruction (inter blocks, or
  * intra blocks of one wave front): the jobs of one call must not overlap in `rec`.
  *   jobs[i]   (in_x, in_y) in `input`, (pred_x, pred_y) in `rec`
- *   qcoeffs   block i at qcoeffs + i*W*H (coded area == area: sizes with a 64-point side are
- *             not fused; r1c_encode_tx_block_valid() == 0 for them and for the (size, type)
- *             pairs the reference leaves `unimplemented!`; the batch calls then return
- *             R1C_ERR_UNIMPLEMENTED and the caller chains the separate entry points)
+ *   qcoeffs   block i at qcoeffs + i*min(W,32)*min(H,32) (av1_get_coded_tx_size): all 19 TxSize.
+ *             The five with a 64-point side follow this fork's two layouts (dense 64-wide
+ *             forward rows, of which the quantizer and the inverse see the first coded-area
+ *             words -- the inverse as 32-wide rows), like the separate entry points.
+ *             r1c_encode_tx_block_valid() == 0 for the (size, type) pairs the reference leaves
+ *             `unimplemented!`; the batch calls then return R1C_ERR_UNIMPLEMENTED
  *   tx_dist   optional (`rdo_type.needs_tx_dist()`): sum((coeff - rcoeff)^2) rounded and
  *             shifted by 2*(3 - log_tx_scale), before the bias / dist_scale factors of :1238-1240
  *   qc, scan  as for r1c_quantize_batch

@@ -415,8 +415,8 @@ def encode_tx_block_batch(ctx, plane_in, plane_rec, jobs, tx_size, tx_type, bit_
     """The residual chain of encode_tx_block (src/encoder.rs:1143-1224) for a batch of transform blocks as one kernel:
     diff of `plane_in` and the prediction held in `plane_rec` at jobs[i] -> forward transform -> quantize (qc: a
     QuantizationContext updated for tx_size; scan: the scan order) -> dequantize -> inverse transform added back onto
-    `plane_rec` (when `reconstruct`) -> tx-domain distortion.  Returns (qcoeffs (N, W*H) int32, tx_dist (N,) uint64 or
-    None).  Sizes with a 64-point side raise R1C_ERR_UNIMPLEMENTED: chain the separate calls for them."""
+    `plane_rec` (when `reconstruct`) -> tx-domain distortion.  Returns (qcoeffs (N, min(W,32)*min(H,32)) int32 -- the
+    coded area, av1_get_coded_tx_size -- and tx_dist (N,) uint64 or None).  All 19 TxSize."""
     jobs = _arr(jobs, TX_JOB)
     scan = _arr(scan, np.uint16)
     w, h = ctx.lib.r1c_tx_width(tx_size), ctx.lib.r1c_tx_height(tx_size)

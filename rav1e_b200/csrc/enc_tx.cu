@@ -7,13 +7,15 @@ namespace enc {
 ENC_DECL(k_enc_4x4) ENC_DECL(k_enc_8x8) ENC_DECL(k_enc_16x16) ENC_DECL(k_enc_32x32)
 ENC_DECL(k_enc_4x8) ENC_DECL(k_enc_8x4) ENC_DECL(k_enc_8x16) ENC_DECL(k_enc_16x8) ENC_DECL(k_enc_16x32)
 ENC_DECL(k_enc_32x16) ENC_DECL(k_enc_4x16) ENC_DECL(k_enc_16x4) ENC_DECL(k_enc_8x32) ENC_DECL(k_enc_32x8)
+ENC_DECL(k_enc_64x64) ENC_DECL(k_enc_32x64) ENC_DECL(k_enc_64x32) ENC_DECL(k_enc_16x64) ENC_DECL(k_enc_64x16)
 
-// order of TxSize, src/transform/mod.rs:225-247; the five sizes with a 64-point side are not fused (their forward
-// transform leaves 64-wide rows while the quantizer reads 32-wide ones: two layouts)
+// order of TxSize, src/transform/mod.rs:225-247; the five sizes with a 64-point side have their own kernel
+// (enc_tx64.cuh: their forward transform leaves 64-wide rows while the quantizer and the inverse read the first
+// min(W,32) * min(H,32) words, the inverse as 32-wide rows); their 64-point side is a DCT
 static const enc_launch_fn *const SIZE_TABLES[R1C_TX_SIZES_ALL] = {
-    k_enc_4x4,  k_enc_8x8,  k_enc_16x16, k_enc_32x32, nullptr,   k_enc_4x8,  k_enc_8x4,
-    k_enc_8x16, k_enc_16x8, k_enc_16x32, k_enc_32x16, nullptr,   nullptr,    k_enc_4x16,
-    k_enc_16x4, k_enc_8x32, k_enc_32x8,  nullptr,     nullptr};
+    k_enc_4x4,  k_enc_8x8,  k_enc_16x16, k_enc_32x32, k_enc_64x64, k_enc_4x8,   k_enc_8x4,
+    k_enc_8x16, k_enc_16x8, k_enc_16x32, k_enc_32x16, k_enc_32x64, k_enc_64x32, k_enc_4x16,
+    k_enc_16x4, k_enc_8x32, k_enc_32x8,  k_enc_16x64, k_enc_64x16};
 
 // (column 1-D, row 1-D) of each TxType, src/transform/mod.rs:196-213; 3 = FLIPADST
 static const unsigned char COL_T[R1C_TX_TYPES] = {0, 1, 0, 1, 3, 0, 3, 1, 3, 2, 0, 2, 1, 2, 3, 2};
@@ -58,8 +60,7 @@ extern "C" int r1c_encode_tx_block_batch_dev(r1c_ctx *ctx, const r1c_plane *inpu
   enc::EncArgs a = {};
   enc::enc_launch_fn fn = enc::lookup(tx_size, tx_type, &a.col_flip, &a.row_flip);
   R1C_REQUIRE(ctx, fn != nullptr, R1C_ERR_UNIMPLEMENTED,
-              "encode_tx_block (size %d, type %d): 64-point sizes and type / size pairs the reference leaves unimplemented are "
-              "not fused; chain r1c_diff_fwd_txfm / r1c_quantize / r1c_dequant_inv_txfm_add", tx_size, tx_type);
+              "encode_tx_block (size %d, type %d): a type / size pair the reference leaves unimplemented", tx_size, tx_type);
   if (n == 0) return R1C_OK;
   a.input = make_view(input);
   a.rec = make_view(rec);
@@ -99,9 +100,10 @@ extern "C" int r1c_encode_tx_block_batch(r1c_ctx *ctx, const r1c_plane *input, r
   R1C_REQUIRE(ctx, n >= 0 && (n == 0 || (jobs && scan && qcoeffs)), R1C_ERR_ARG, "null job / scan / qcoeff array");
   R1C_REQUIRE(ctx, r1c_tx_width(tx_size) > 0, R1C_ERR_ARG, "bad tx_size %d", tx_size);
   R1C_REQUIRE(ctx, r1c_encode_tx_block_valid(tx_size, tx_type), tx_type >= 0 && tx_type < R1C_TX_TYPES ? R1C_ERR_UNIMPLEMENTED : R1C_ERR_ARG,
-              "encode_tx_block (size %d, type %d) is not fused", tx_size, tx_type);
+              "encode_tx_block (size %d, type %d): a type / size pair the reference leaves unimplemented", tx_size, tx_type);
   if (n == 0) return R1C_OK;
-  const int w = r1c_tx_width(tx_size), h = r1c_tx_height(tx_size), coded = w * h;
+  const int w = r1c_tx_width(tx_size), h = r1c_tx_height(tx_size);
+  const int coded = (w < 32 ? w : 32) * (h < 32 ? h : 32);  // av1_get_coded_tx_size, src/context.rs:1949-1956
   {  // scan[0] == 0 (the DC has its own quantizer) and every index is hit once
     unsigned char seen[1024] = {0};
     R1C_REQUIRE(ctx, scan[0] == 0, R1C_ERR_ARG, "scan[0] must be the DC coefficient");
