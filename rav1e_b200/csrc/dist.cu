@@ -4,7 +4,7 @@
 // Layout: one warp per job.  Pixels are fetched as aligned 32-bit words and
 // re-aligned with a funnel shift, so a block may sit at any x in either plane.
 //   SAD  u8 : VABSDIFF4.U8.ACC (4 abs-diffs + accumulate in one instruction)
-//   SAD  u16: two 16-bit lanes per word, IABS + IADD
+//   SAD  u16: two 16-bit lanes per word, max - min per half (VIMNMX.U16x2) + IDP.2A
 //   SATD    : lane = one row of one 4x4 / 8x8 tile; horizontal Hadamard in
 //             registers, vertical Hadamard with __shfl_xor butterflies.  The
 //             Hadamard is exact integer arithmetic and the result is a sum of
@@ -40,21 +40,19 @@ __device__ __forceinline__ bool job_in_bounds(const PlaneView &v, int x, int y, 
 template <int PB, int S, bool VEC>
 __device__ __forceinline__ uint32_t tile_sad(const uint8_t *po, int so, const uint8_t *pr, int sr) {
   constexpr int NW = S * PB / 4;
+  // every row of both tiles is requested before the first is used (with a load -> use -> load chain per row the
+  // kernel ran at 48 registers and one row of memory latency at a time: slower than the SATD of the same tiles)
+  uint32_t x[S][NW], y[S][NW];
+#pragma unroll
+  for (int r = 0; r < S; r++) {
+    ld_row<NW, VEC>(po + r * so, x[r]);
+    ld_row<NW, VEC>(pr + r * sr, y[r]);
+  }
   uint32_t acc = 0;
 #pragma unroll
   for (int r = 0; r < S; r++) {
-    uint32_t x[NW], y[NW];
-    ld_row<NW, VEC>(po + r * so, x);
-    ld_row<NW, VEC>(pr + r * sr, y);
 #pragma unroll
-    for (int i = 0; i < NW; i++) {
-      if (PB == 1) {
-        acc = sad4_acc(x[i], y[i], acc);
-      } else {
-        acc = absdiff_acc(x[i] & 0xffffu, y[i] & 0xffffu, acc);
-        acc = absdiff_acc(x[i] >> 16, y[i] >> 16, acc);
-      }
-    }
+    for (int i = 0; i < NW; i++) acc = PB == 1 ? sad4_acc(x[r][i], y[r][i], acc) : sad2_acc(x[r][i], y[r][i], acc);
   }
   return acc;
 }

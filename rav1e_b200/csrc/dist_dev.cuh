@@ -86,9 +86,11 @@ __device__ __forceinline__ void ld_row(const uint8_t *p, uint32_t (&out)[NW]) {
   else ld_words<NW>(p, out);
 }
 
-__device__ __forceinline__ uint32_t absdiff_acc(uint32_t a, uint32_t b, uint32_t acc) {
-  asm("vabsdiff.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(acc) : "r"(a), "r"(b), "r"(acc));
-  return acc;
+// two u16 lanes: |a - b| per half as max - min (two VIMNMX.U16x2 and a subtraction that cannot borrow), both halves
+// added to acc by one IDP.2A with unit weights.  Exact for any u16 values.  (The scalar `vabsdiff.u32 ... .add` of
+// round 1 is emulated on sm_100a: 7 instructions per pixel.)
+__device__ __forceinline__ uint32_t sad2_acc(uint32_t a, uint32_t b, uint32_t acc) {
+  return __dp2a_lo(__vmaxu2(a, b) - __vminu2(a, b), 0x0101u, acc);
 }
 
 // rows of 4 * NW bytes per lane and step
@@ -110,8 +112,7 @@ __device__ __forceinline__ uint32_t sad_rows(const uint8_t *po, int so, const ui
       if (PB == 1) {
         acc = sad4_acc(x[i], y[i], acc);
       } else {
-        acc = absdiff_acc(x[i] & 0xffffu, y[i] & 0xffffu, acc);
-        acc = absdiff_acc(x[i] >> 16, y[i] >> 16, acc);
+        acc = sad2_acc(x[i], y[i], acc);
       }
     }
   }

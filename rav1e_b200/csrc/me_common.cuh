@@ -31,12 +31,11 @@ __device__ __forceinline__ uint32_t sad4_acc(uint32_t a, uint32_t b, uint32_t ac
   asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(acc) : "r"(a), "r"(b), "r"(acc));
   return acc;
 }
-// two u16 lanes
+// two u16 lanes: |a - b| per half as max - min (two VIMNMX.U16x2 and a subtraction that cannot borrow), both halves
+// added to acc by one IDP.2A with unit weights.  Exact for any u16 values.  (The scalar `vabsdiff.u32 ... .add` of
+// round 1 is emulated on sm_100a: 7 instructions per pixel.)
 __device__ __forceinline__ uint32_t sad2_acc(uint32_t a, uint32_t b, uint32_t acc) {
-  uint32_t lo, hi;
-  asm("vabsdiff.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(lo) : "r"(a & 0xffffu), "r"(b & 0xffffu), "r"(acc));
-  asm("vabsdiff.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(hi) : "r"(a >> 16), "r"(b >> 16), "r"(lo));
-  return hi;
+  return __dp2a_lo(__vmaxu2(a, b) - __vminu2(a, b), 0x0101u, acc);
 }
 template <int PB>
 __device__ __forceinline__ uint32_t sad_word(uint32_t a, uint32_t b, uint32_t acc) {
