@@ -376,7 +376,12 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
         }
         continue;
       }
-#pragma unroll
+      // NOT unrolled: the three column offsets unrolled are 3 x 9.5 KB of straight-line code in a kernel of 125 KB.
+      // Alone on the GPU that was 3 % faster (1.24 against 1.28 ms per frame), but the lookahead window runs this kernel
+      // next to me_sb2_kernel (103 KB) of the other stream on the same SMs, and there the smaller loop wins: 597 -> 614
+      // Mpix/s for the window call (measured back to back, two runs each).  Rolling the step-8 loop above or the three
+      // row offsets below as well lost on both counts.
+#pragma unroll 1
       for (int jg = 0; jg < 3; jg++) {
         // predict_inter's get_params (src/predict.rs:267-284), luma, column part
         const int mvc = (int)center.col + step * (jg - 1);
