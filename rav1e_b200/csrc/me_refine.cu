@@ -103,7 +103,7 @@ __device__ __forceinline__ int dp4a_us(uint32_t px, uint32_t taps, int acc) {
   return d;
 }
 
-// horizontal 8-tap sum (halved taps, + the rounding 2 of the >> 2 that follows) at window pixel `b` of the row
+// horizontal 8-tap sum (halved taps, + the rounding `rnd` of the shift that follows: 2 for >> 2, 8 for >> 4 at 12 bits) at window pixel `b` of the row
 // starting at `row` (pixels b .. b+7): u8 = 2 DP4A on funnel-shifted words, u16 = 4 DP2A on pixel pairs
 __device__ __forceinline__ int dp2a_lo_us(uint32_t pair, uint32_t taps, int acc) {
   int d;
@@ -116,20 +116,20 @@ __device__ __forceinline__ int dp2a_hi_us(uint32_t pair, uint32_t taps, int acc)
   return d;
 }
 template <int PB>
-__device__ __forceinline__ int hsum8(const uint8_t *row, int b, uint32_t tlo, uint32_t thi) {
+__device__ __forceinline__ int hsum8(const uint8_t *row, int b, uint32_t tlo, uint32_t thi, int rnd) {
   if (PB == 1) {
     const uint32_t *w = (const uint32_t *)row + (b >> 2);
     const uint32_t sh = (uint32_t)(b & 3) * 8;
     const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
     const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
-    return dp4a_us(hi, thi, dp4a_us(lo, tlo, 2));
+    return dp4a_us(hi, thi, dp4a_us(lo, tlo, rnd));
   } else {
     const uint32_t *w = (const uint32_t *)row + (b >> 1);
     const uint32_t sh = (uint32_t)(b & 1) * 16;
     const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
     const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh),
                    v2 = __funnelshift_r(w2, w3, sh), v3 = __funnelshift_r(w3, w4, sh);
-    return dp2a_hi_us(v3, thi, dp2a_lo_us(v2, thi, dp2a_hi_us(v1, tlo, dp2a_lo_us(v0, tlo, 2))));
+    return dp2a_hi_us(v3, thi, dp2a_lo_us(v2, thi, dp2a_hi_us(v1, tlo, dp2a_lo_us(v0, tlo, rnd))));
   }
 }
 
@@ -140,6 +140,9 @@ __device__ __forceinline__ int hsum8(const uint8_t *row, int b, uint32_t tlo, ui
 //   out = clamp((sum mid * hty + 512) >> 10)  == round_shift(sum mid * ty, 11); round_shift(mid, 4) for
 //                                               row_frac 0; round_shift(sum px * ty, 7) for col_frac 0
 // which are exactly the reference's four branches (no branch here: the lanes of a warp hold different MVs).
+// At 12 bits intermediate_bits = 2: mid = (sum px * htx + 8) >> 4 (px << 2 for col_frac 0) and out = (sum mid * hty + 128)
+// >> 8, which collapse onto the reference's branches the same way ((4 A + 256) >> 9 == (A + 64) >> 7; (128 m + 256) >> 9 ==
+// (m + 2) >> 2).
 // The outer taps (0 and 7) of every row of both banks are zero: a candidate whose rows start `off` rows
 // below the first row of its group is the same 8 DP2A taps shifted by `off` bytes.
 __device__ __forceinline__ int dp2a_lo_ss(uint32_t pair, uint32_t taps, int acc) {
@@ -260,7 +263,11 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
   constexpr int GROUPS = Rc<PB>::RT / S;
   // two candidates share one Hadamard as d1 * 65536 + d0 while |coef| < 2^15: always at 8 bits (64 * 255), at 10
   // bits only for the 4x4 tiles (16 * 1023)
-  constexpr bool PAIR = PB == 1 || S == 4;
+  const bool PAIR = PB == 1 || (S == 4 && a.bit_depth <= 10);  // (a compile-time constant except for u16 4x4 tiles)
+  // intermediate_bits = 4 up to 10 bits, 2 at 12 (src/mc.rs:222): with halved taps the two rounding shifts are
+  // 3 - 1 and 11 - 1, or 5 - 1 and 9 - 1
+  const int hsh = PB == 1 ? 2 : (a.bit_depth == 12 ? 4 : 2), hrnd = PB == 1 ? 2 : (1 << hsh) >> 1;
+  const int vsh = PB == 1 ? 10 : (a.bit_depth == 12 ? 8 : 10), vrnd = PB == 1 ? 512 : (1 << vsh) >> 1;
   const int maxv = (1 << a.bit_depth) - 1;
   const int tid = threadIdx.x, lane = tid & 31, c = tid & (S - 1), grp = tid / S;
   const int nt = t_hi - t_lo;
@@ -397,11 +404,11 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
         {
           const uint2 txw = sh.taps[tbx + cf];
           const uint8_t *row = sh.win + (wyb - 2) * a.wstride;
-          int prev = hsum8<PB>(row, wx - 3, txw.x, txw.y) >> 2;
+          int prev = hsum8<PB>(row, wx - 3, txw.x, txw.y, hrnd) >> hsh;
 #pragma unroll
           for (int n = 0; n < S + 6; n++) {
             row += a.wstride;
-            const int cur = hsum8<PB>(row, wx - 3, txw.x, txw.y) >> 2;
+            const int cur = hsum8<PB>(row, wx - 3, txw.x, txw.y, hrnd) >> hsh;
             P[n] = __byte_perm((uint32_t)prev, (uint32_t)cur, 0x5410);
             prev = cur;
           }
@@ -424,11 +431,11 @@ __device__ __forceinline__ void run_tiles(const RefArgs &a, const Shared &sh, co
           int d[S];  // of a candidate that is not live: computed all the same, never accumulated
 #pragma unroll
           for (int t = 0; t < S; t++) {
-            int v = dp2a_lo_ss(P[t], f0, 512);
+            int v = dp2a_lo_ss(P[t], f0, vrnd);
             v = dp2a_hi_ss(P[t + 2], f0, v);
             v = dp2a_lo_ss(P[t + 4], f1, v);
             v = dp2a_hi_ss(P[t + 6], f1, v);
-            d[t] = oc[t] - min(max(v >> 10, 0), maxv);
+            d[t] = oc[t] - min(max(v >> vsh, 0), maxv);
           }
           if (!PAIR) {
             const uint32_t acc = tile_dist<S>(d, lane, satd);
@@ -638,8 +645,7 @@ int r1c_refine_frame(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, c
   *handled = 0;
   const char *force = getenv("R1C_REFINE_GENERIC");
   const int pb = org->px_bytes;
-  // u16 planes up to 10 bits (intermediate_bits = 4 as at 8 bits; 12-bit uses 2 and stays on the generic path)
-  if ((force && force[0] == '1') || pb != ref->px_bytes || !(pb == 1 || (pb == 2 && bit_depth <= 10))) return R1C_OK;
+  if ((force && force[0] == '1') || pb != ref->px_bytes) return R1C_OK;
   RefArgs a;
   a.winW = 64 + 2 * (p->range_x + MARGIN) + 7;
   a.winH = 64 + 2 * (p->range_y + MARGIN) + 7;

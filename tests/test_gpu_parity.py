@@ -690,7 +690,7 @@ def _frame_pair(r, oracle, ctx, W, H, pb, bd, seed):
 
 
 @pytest.mark.parametrize("pb,bd,refine,use_satd,hp", [(1, 8, 1, 1, 0), (1, 8, 0, 0, 0), (2, 10, 1, 1, 1), (1, 8, 1, 0, 0),
-                                                      (2, 10, 1, 0, 0), (2, 12, 1, 1, 0)])
+                                                      (2, 10, 1, 0, 0), (2, 12, 1, 1, 0), (2, 12, 1, 0, 1), (2, 12, 1, 1, 1)])
 def test_frame_me_matches_per_block_motion_estimation(r, ctx, oracle, pb, bd, refine, use_satd, hp):
     """r1c_frame_me == motion_estimation (src/me.rs:193-271) block by block, every size,
     borders and the partial last superblock row included"""
@@ -704,10 +704,11 @@ def test_frame_me_matches_per_block_motion_estimation(r, ctx, oracle, pb, bd, re
     assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
 
 
-@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10)])
+@pytest.mark.parametrize("pb,bd", [(1, 8), (2, 10), (2, 12)])
 def test_frame_me_extreme_pixels(r, ctx, oracle, pb, bd):
     """pixels at 0 / max only: the largest differences the sub-pel filters, the packed pair Hadamard (4x4 tiles at 10
-    bits, every tile at 8) and the distortion accumulators can see; filter overshoot is clamped on both sides"""
+    bits, every tile at 8, none at 12) and the distortion accumulators can see; filter overshoot is clamped on both sides;
+    12 bits also go through the fused sub-pel kernel, with intermediate_bits = 2"""
     rng = np.random.default_rng(4100 + bd)
     W, H = 136, 128
     maxv = (1 << bd) - 1
