@@ -80,11 +80,13 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
                 with torch.cuda.stream(e):
                     h_cmp.copy_(d_cmp, non_blocking=True)
 
-    up_rows = shard.tile_plane_rows(p_ref.cfg, lo, hi, RANGE)  # the rows of the planes this rank's tile can touch
+    # the rectangle of the planes this rank's tile can touch: one strided copy per plane
+    up_rows = shard.tile_plane_rows(p_ref.cfg, lo, hi, RANGE)
+    up_cols = shard.tile_plane_cols(p_ref.cfg, clo, chi, RANGE)
 
     def step_e2e():
-        ctx.check(lib.r1c_plane_upload_rows_async(ctx.h, p_org.h, h_org.data_ptr(), up_rows[0], up_rows[1]))
-        ctx.check(lib.r1c_plane_upload_rows_async(ctx.h, p_ref.h, h_ref.data_ptr(), up_rows[0], up_rows[1]))
+        ctx.check(lib.r1c_plane_upload_rect_async(ctx.h, p_org.h, h_org.data_ptr(), up_rows[0], up_rows[1], up_cols[0], up_cols[1]))
+        ctx.check(lib.r1c_plane_upload_rect_async(ctx.h, p_ref.h, h_ref.data_ptr(), up_rows[0], up_rows[1], up_cols[0], up_cols[1]))
         up_done.record(ext)
         for e in exts[1:]:
             e.wait_event(up_done)
@@ -136,9 +138,9 @@ def me_strong(ctx, r, torch, dist, ext, flush, rank, world, steps, warmup=2):
         "d2h_bytes_this_rank": int(n_mine * 16), "d2h_copies_this_rank": n_work, "contexts_per_rank": n_work,
         "e2e": {"value": mpix / (ms_e2e / 1e3), "unit": "Mpix/s", "ms_per_frame": ms_e2e,
                 "steps": steps, "timed_region_s": steps * ms_e2e / 1e3,
-                "h2d_bytes_per_rank": int(2 * (up_rows[1] - up_rows[0]) * p_ref.cfg.stride * 2),
-                "note": "every rank uploads the rows of both planes its tile can touch (tile rows +- (range + 16), "
-                        "r1c_plane_upload_rows_async): whole rows, so the upload shrinks with the number of tile ROWS only"},
+                "h2d_bytes_per_rank": int(2 * (up_rows[1] - up_rows[0]) * (up_cols[1] - up_cols[0]) * 2),
+                "note": "every rank uploads the rectangle of both planes its tile can touch (the tile +- (range + 16) in both "
+                        "directions, r1c_plane_upload_rect_async: one strided copy per plane)"},
         "note": "largest tile = %d of %d superblocks: the best possible speed-up is %.2f at N = %d"
                 % (max((b - a) * (d - c) for (a, b), (c, d) in tiles), 34 * 60,
                    34 * 60 / max((b - a) * (d - c) for (a, b), (c, d) in tiles), world)}

@@ -706,6 +706,12 @@ int r1c_plane_upload_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data
  * (rav1e_b200.shard.tile_plane_rows), not the whole planes. */
 int r1c_plane_upload_rows_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data,
                                 int64_t row_lo, int64_t row_hi);
+/* the same for a rectangle of the allocation: rows [row_lo, row_hi) x columns [col_lo, col_hi)
+ * (column 0 = the first padding column; columns in pixels, <= stride).  What a rank needs of a
+ * frame for one tile of a tile GRID: the tile +- (range + 16) in both directions
+ * (rav1e_b200.shard.tile_plane_rows / tile_plane_cols).  One strided DMA (cudaMemcpy2DAsync). */
+int r1c_plane_upload_rect_async(r1c_ctx *ctx, r1c_plane *plane, const void *host_data,
+                                int64_t row_lo, int64_t row_hi, int64_t col_lo, int64_t col_hi);
 
 /* ------------------------------------------------------------------------
  * Block importances of the lookahead:

@@ -225,6 +225,7 @@ SIGNATURES = {
     "r1c_frame_me_compact_dev": (_i, [_vp, _P(FrameMeParams), _vp, _vp]),
     "r1c_plane_upload_async": (_i, [_vp, _vp, _vp]),
     "r1c_plane_upload_rows_async": (_i, [_vp, _vp, _vp, _i64, _i64]),
+    "r1c_plane_upload_rect_async": (_i, [_vp, _vp, _vp, _i64, _i64, _i64, _i64]),
     "r1c_int_peak": (_i, [_vp, _i, _P(C.c_double)]),
     "r1c_profile": (_i, [_vp, _i]),
     "r1c_profile_read": (_i, [_vp, _i, _P(C.c_double), _P(_i64)]),

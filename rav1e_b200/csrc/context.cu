@@ -305,6 +305,19 @@ extern "C" int r1c_plane_upload_rows_async(r1c_ctx *ctx, r1c_plane *p, const voi
   return R1C_OK;
 }
 
+extern "C" int r1c_plane_upload_rect_async(r1c_ctx *ctx, r1c_plane *p, const void *host, int64_t row_lo, int64_t row_hi,
+                                           int64_t col_lo, int64_t col_hi) {
+  if (!ctx || !p || !host) return R1C_ERR_ARG;
+  R1C_REQUIRE(ctx, row_lo >= 0 && row_lo <= row_hi && row_hi <= p->cfg.alloc_height && col_lo >= 0 && col_lo <= col_hi && col_hi <= p->cfg.stride,
+              R1C_ERR_ARG, "upload rect rows [%lld, %lld) x columns [%lld, %lld) outside the allocation of %lld x %lld", (long long)row_lo,
+              (long long)row_hi, (long long)col_lo, (long long)col_hi, (long long)p->cfg.alloc_height, (long long)p->cfg.stride);
+  if (row_lo == row_hi || col_lo == col_hi) return R1C_OK;
+  const size_t pitch = (size_t)p->cfg.stride * p->px_bytes, off = (size_t)row_lo * pitch + (size_t)col_lo * p->px_bytes;
+  R1C_CUDA(ctx, cudaMemcpy2DAsync((uint8_t *)p->d_data + off, pitch, (const uint8_t *)host + off, pitch, (size_t)(col_hi - col_lo) * p->px_bytes,
+                                  (size_t)(row_hi - row_lo), cudaMemcpyHostToDevice, ctx->stream));
+  return R1C_OK;
+}
+
 extern "C" int r1c_plane_download(r1c_ctx *ctx, const r1c_plane *p, void *host) {
   if (!ctx || !p || !host) return R1C_ERR_ARG;
   size_t bytes = (size_t)p->cfg.stride * p->cfg.alloc_height * p->px_bytes;

@@ -71,6 +71,16 @@ def tile_plane_rows(cfg, sb_row_lo, sb_row_hi, range_y):
     return max(lo, 0), min(hi, int(cfg.alloc_height))
 
 
+def tile_plane_cols(cfg, sb_col_lo, sb_col_hi, range_x):
+    """columns [lo, hi) of a plane's ALLOCATION (r1c_plane_upload_rect_async) that the search of superblock columns
+    [sb_col_lo, sb_col_hi) can touch: the tile's columns +- (range_x + 16), like tile_plane_rows; widened to multiples
+    of 64 pixels so that every row of the copy starts and ends on a 128-byte line"""
+    lo = int(cfg.xorigin) + sb_col_lo * 64 - range_x - 16
+    hi = int(cfg.xorigin) + min(sb_col_hi * 64, int(cfg.width)) + range_x + 16
+    lo, hi = max(lo, 0) & ~63, min((hi + 63) & ~63, int(cfg.stride))
+    return lo, hi
+
+
 def shard_slots(width, height, bsize_mask, sb_row_lo, sb_row_hi, sb_col_lo=0, sb_col_hi=0):
     """frame_me result slots (include/rav1e_cuda.h layout) whose block origin lies in superblock rows
     [sb_row_lo, sb_row_hi) and columns [sb_col_lo, sb_col_hi) (0, 0 = all columns), in the order BlockSize, block row,

@@ -806,6 +806,42 @@ def test_tile_search_needs_only_its_rows_of_the_planes(r, ctx, oracle):
     assert e.value.code == r.capi.R1C_ERR_ARG
 
 
+def test_tile_search_needs_only_its_rectangle_of_the_planes(r, ctx, oracle):
+    """r1c_plane_upload_rect_async + shard.tile_plane_rows / tile_plane_cols: planes pre-filled with garbage, only the
+    rectangle a tile of a 2 x 3 tile grid can touch uploaded -- the tile's results equal the whole-frame search on the
+    full planes (8- and 10-bit, sub-pel tail on)"""
+    from rav1e_b200 import shard
+    W, H, RNGE = 704, 256, 16
+    for pb, bd in ((1, 8), (2, 10)):
+        o_org, d_org, o_ref, d_ref = _frame_pair(r, oracle, ctx, W, H, pb, bd, 93)
+        whole = r.frame_me(ctx, d_org, d_ref, r.make_frame_me_params(W, H, RNGE, RNGE, 31), bd)
+        junk = np.full(o_org.data.shape, (1 << bd) - 1, dtype=o_org.data.dtype)
+        junk[::2, 1::3] = 0
+        for (lo, hi) in ((0, 2), (2, 4)):
+            for (clo, chi) in ((0, 4), (4, 8), (8, 11)):
+                g_org = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(junk)
+                g_ref = r.Plane(ctx, W, H, 0, 0, 88, 88, pb).upload(junk)
+                r0, r1 = shard.tile_plane_rows(g_ref.cfg, lo, hi, RNGE)
+                c0, c1 = shard.tile_plane_cols(g_ref.cfg, clo, chi, RNGE)
+                assert c1 - c0 < g_ref.cfg.stride and c0 % 64 == 0  # a real subset, on 128-byte lines
+                for g, o in ((g_org, o_org), (g_ref, o_ref)):
+                    host = np.ascontiguousarray(o.data)
+                    ctx.check(ctx.lib.r1c_plane_upload_rect_async(ctx.h, g.h, host.ctypes.data, r0, r1, c0, c1))
+                ctx.sync()
+                left = g_ref.download()
+                assert np.array_equal(left[r0:r1, c0:c1], o_ref.data[r0:r1, c0:c1])
+                keep = np.ones(left.shape, bool)
+                keep[r0:r1, c0:c1] = False
+                assert np.array_equal(left[keep], junk[keep])  # nothing else was written
+                p = r.make_frame_me_params(W, H, RNGE, RNGE, 31, sb_rows=(lo, hi), sb_cols=(clo, chi))
+                slots = shard.shard_slots(W, H, r.ALL_SIZES_TO_64, lo, hi, clo, chi)
+                got = r.frame_me(ctx, g_org, g_ref, p, bd)
+                assert np.array_equal(got[slots], whole[slots]), (bd, lo, hi, clo, chi)
+    with pytest.raises(r.Rav1eCudaError) as e:
+        ctx.check(ctx.lib.r1c_plane_upload_rect_async(ctx.h, d_org.h, o_org.data.ctypes.data, 0, 8, 0, d_org.cfg.stride + 1))
+    assert e.value.code == r.capi.R1C_ERR_ARG
+
+
 def test_frame_me_window_equals_frame_by_frame(r, ctx, oracle):
     """r1c_frame_me_window(_dev): a lookahead window of frame pairs over two streams == r1c_frame_me pair by pair; host
     form with the planes uploaded by the call (garbage in the planes before), device form with resident planes; odd and
