@@ -520,8 +520,7 @@ def me_frame_line(ctx, r, torch, ext, flush, W, H, BD, RANGE, reps=2):
     return {"workload": "%dx%d %d-bit full-search ME +-%d, 19 sizes, SAD then SATD sub-pel (planes resident)" % (W, H, BD, RANGE),
             "value": W * H / 1e3 / ms, "unit": "Mpix/s", "ms": ms, "launches_per_frame": launches,
             "blocks_per_frame": int(n_res),
-            "kernel_ms": {"me_sb2_kernel": sb_ms, "me_refine_kernel": rf_ms} if BD <= 10 else
-                         {"me_sb_kernel (first generation)": sb_ms, "me_refine_kernel": rf_ms},
-            "roofline": {"bound": "int32_alu", "kernel": "me_sb2_kernel (u16 variant)" if BD <= 10 else "me_sb_kernel (12-bit fallback)", "achieved": ops / (sb_ms / 1e3) / 1e9 if sb_ms else None,
+            "kernel_ms": {"me_sb2_kernel": sb_ms, "me_refine_kernel": rf_ms},
+            "roofline": {"bound": "int32_alu", "kernel": "me_sb2_kernel (u16 variant)" if BD <= 10 else "me_sb2_kernel (u16, 12-bit variant: true SADs in the keys)", "achieved": ops / (sb_ms / 1e3) / 1e9 if sb_ms else None,
                          "peak": ipeak, "unit": "Gop/s", "frac": ops / (sb_ms / 1e3) / 1e9 / ipeak if sb_ms else None,
                          "alg_ops_per_launch": ops, "peak_source": ihow}}

@@ -511,9 +511,9 @@ int r1c_me_sb_batch_dev(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref
  * `static __device__` array of R1C_SB_NOALLOC_SCRATCH_BYTES (8 MiB, held by every GPU that loads
  * the library until exit) instead of the context's grow-on-demand scratch, and the call makes no
  * cudaMalloc / cudaFree / allocating library call.  Limits: only what the second-generation
- * kernel takes (step 1, 8-bit planes or u16 planes up to 10 bits, lambda <= 60000; anything else
+ * kernel takes (step 1, lambda <= 60000, or <= 16000 on 12-bit planes; anything else
  * -> R1C_ERR_UNIMPLEMENTED, there is no fallback kernel here) and
- * n * chunks * 849 * 8 (+ n * 849 * 4 for u16 planes) <= R1C_SB_NOALLOC_SCRATCH_BYTES -- e.g. all
+ * n * chunks * 849 * 8 (+ n * 849 * 4 for u16 planes up to 10 bits) <= R1C_SB_NOALLOC_SCRATCH_BYTES -- e.g. all
  * 510 superblocks of a 1080p 8-bit frame at +-64 (2 chunks, 6.9 MB); more -> R1C_ERR_NOMEM with
  * the sizes in r1c_last_error().  All calls on a device share the array: calls that overlap on
  * the GPU (different streams or contexts) race; calls on one stream are ordered.  Nothing is

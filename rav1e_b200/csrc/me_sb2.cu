@@ -1,4 +1,4 @@
-// me_sb2.cu -- whole-superblock full search, second generation (8-bit planes, and u16 planes up to 10 bits).
+// me_sb2.cu -- whole-superblock full search, second generation (8-bit planes and u16 planes: up to 10 bits, and 12 bits).
 //
 // Same contract as me_sb.cu (the result of the reference's full_search,
 // src/me.rs:943-990, for every block of every size inside a 64x64 region against
@@ -35,7 +35,7 @@
 //  * MV rates come from per-column / per-row tables in shared memory; in border superblocks
 //    only the candidates that are illegal for some block pay for the get_mv_range masks.
 // INT-bound: per (pixel, candidate) 1/4 VABSDIFF4 (u8) or 3/4 full-rate instructions (u16);
-// planes are read once per work item from L2.  Falls back to me_sb.cu for 12-bit planes,
+// planes are read once per work item from L2.  12-bit planes: the D12 variant (Px).  Falls back to me_sb.cu for
 // step 2, huge lambda or windows too small / too large for this layout.
 #include <stdlib.h>
 
@@ -45,11 +45,14 @@ namespace {
 
 constexpr int T2 = 512;
 // per pixel size: u8 planes (PB 1) and 10-bit u16 planes (PB 2)
-template <int PB>
+template <int PB, bool D12 = false>
 struct Px {
   // The 8x8 SAD of the packed-key blocks is < 2^14 at 8 bits but needs 16 bits at 10: the 10-bit kernel has 6
   // bits of `seq` (candidate rows are cut into more chunks) and 18 bits of sad + rl >> 8.
-  static constexpr int SEQ_BITS = PB == 1 ? 9 : 6;
+  // 12 bits (D12): the cells hold the TRUE SAD (sum org of the cell comes off in the search loop, 16 registers), an
+  // 8x8 SAD is < 2^18, the field has 19 bits and `seq` 5 (6 candidate rows per chunk, 22 chunks for +-64); 256 * SAD
+  // + rl of a 64x64 block stays below 2^32 - 1 for lambda <= 16000 (sb2_plan).
+  static constexpr int SEQ_BITS = PB == 1 ? 9 : (D12 ? 5 : 6);
   static constexpr int KSHIFT = 8 + SEQ_BITS;  // sad field of the 32-bit key
   static constexpr int PXW = 4 / PB;           // pixels per window word = phases of the staged window
   static constexpr int NWQ = 4 * PB;           // words of a 16-pixel quadrant row
@@ -258,17 +261,25 @@ __device__ __forceinline__ uint32_t fold_cell(uint32_t c, int nb) {
   return d;
 }
 
-template <bool MASKED, int RSW, int PB>
+template <bool MASKED, int RSW, int PB, bool D12>
 __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &job, const Chunk &ck,
                                            const uint32_t *s_org, const uint32_t *s_ref, uint32_t *s_x,
-                                           const int16_t *s_nbox, const uint32_t *s_rcol, const uint32_t *s_rrow,
+                                           const int16_t *s_nbox, const uint32_t *s_cell, const uint32_t *s_rcol, const uint32_t *s_rrow,
                                            uint32_t (&best)[44], uint32_t (&pc)[5], uint32_t (&ps)[5],
                                            uint32_t (&bc)[5], uint32_t (&bs)[5], const Geo2 &g) {
   const int tid = threadIdx.x, lane = tid & 31, q = tid >> 5;
   const int qx = q & 3, qy = q >> 2;
-  constexpr int SEQ_BITS = Px<PB>::SEQ_BITS, KSHIFT = Px<PB>::KSHIFT, PXW = Px<PB>::PXW, NWQ = Px<PB>::NWQ;
+  constexpr int SEQ_BITS = Px<PB, D12>::SEQ_BITS, KSHIFT = Px<PB, D12>::KSHIFT, PXW = Px<PB>::PXW, NWQ = Px<PB>::NWQ;
   const int rsw = RSW ? RSW : a.rsw;
   const int sdx = 32 % ck.NX, sj = 32 / ck.NX;
+  // 12 bits: sum org of this quadrant's 16 cells + the offset of the box table (see the kernel), taken off every cell
+  uint32_t sa[4][4];
+  if (D12) {
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int k = 0; k < 4; k++) sa[i][k] = s_cell[(qy * 4 + i) * 16 + qx * 4 + k] + 32760u;
+  }
   const int M2 = 2 * a.M;
   // slot of this lane: f = it * 32 + lane = j * NX + dx
   int f = lane, j = lane / ck.NX, dx = lane - j * ck.NX;
@@ -344,6 +355,10 @@ __device__ __forceinline__ void sb2_search(const Sb2Args &a, const r1c_sb_job &j
         for (int k = 0; k < 4; k++) {
           cA[i][k] = fold_cell(cA[i][k], nb[4 * i * bw + 4 * k]);
           cB[i][k] = fold_cell(cB[i][k], nb[(4 * i + 1) * bw + 4 * k]);
+          if (D12) {  // the true SAD of the cell
+            cA[i][k] -= sa[i][k];
+            cB[i][k] -= sa[i][k];
+          }
         }
     }
     // ---- rate terms ---------------------------------------------------------------------
@@ -474,9 +489,10 @@ __device__ __forceinline__ unsigned long long warp_best(uint32_t cost, uint32_t 
   return cmin == NONE32 ? ~0ull : (((unsigned long long)cmin << 32) | rmin);
 }
 
-template <int RSW, int PB>
+template <int RSW, int PB, bool D12 = false>
 __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
-  constexpr int SEQ_BITS = Px<PB>::SEQ_BITS, PXW = Px<PB>::PXW;
+  static_assert(!D12 || PB == 2, "12-bit planes are u16");
+  constexpr int SEQ_BITS = Px<PB, D12>::SEQ_BITS, PXW = Px<PB>::PXW;
   extern __shared__ __align__(16) unsigned char smem[];
   const long long wi = blockIdx.x;
   const long long ji = wi / a.split;
@@ -557,7 +573,9 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
       s_rrow[i] = rate1(mvr - job.pmv[0].row, hp) | (rate1(mvr - job.pmv[1].row, hp) << 16);
     }
   }
-  if (PB == 2 && chunk == 0) {  // sums of org's 4x4 cells (-> s_x, free until the search starts)
+  // sums of org's 4x4 cells: up to 10 bits for the block sums of chunk 0 (-> s_x, free until the search starts);
+  // at 12 bits every chunk takes them off its cells (-> s_sat, which has no other use there)
+  if (PB == 2 && (D12 || chunk == 0)) {
     if (tid < 256) {
       const uint16_t *o = (const uint16_t *)s_org + (tid >> 4) * 4 * 64 + (tid & 15) * 4;
       uint32_t sum = 0;
@@ -565,7 +583,7 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
       for (int r = 0; r < 4; r++)
 #pragma unroll
         for (int c = 0; c < 4; c++) sum += o[r * 64 + c];
-      s_x[tid] = sum;
+      (D12 ? s_sat : s_x)[tid] = sum;
     }
   }
   __syncthreads();
@@ -587,7 +605,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
         int h0 = h4(ylo), h1 = h4(ylo + 1), h2 = h4(ylo + 2);
         for (int y = ylo; y < yhi; y++) {
           const int h3 = h4(y + 3);
-          s_nbox[y * bw + x] = (int16_t)(-(h0 + h1 + h2 + h3));
+          // (12 bits: a box reaches 16 * 4095 = 65520, kept as 32760 - box; the offset leaves with sum org, see sa[][])
+          s_nbox[y * bw + x] = (int16_t)((D12 ? 32760 : 0) - (h0 + h1 + h2 + h3));
           h0 = h1;
           h1 = h2;
           h2 = h3;
@@ -596,7 +615,7 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     }
     // summed-area table of the cell sums: sat[Y][X] = sum of cells [0, Y) x [0, X); the minima are taken on
     // 256 * (SAD + sum org of the block) + rl, and the block sums go to sb2_finalize_kernel once per superblock
-    if (chunk == 0) {
+    if (!D12 && chunk == 0) {
       if (tid < 17 * 17) {
         const int Y = tid / 17, X = tid - Y * 17;
         uint32_t sum = 0;
@@ -642,8 +661,8 @@ __global__ void __launch_bounds__(T2, 1) me_sb2_kernel(Sb2Args a) {
     pc[i] = bc[i] = NONE32;
     ps[i] = bs[i] = 0;
   }
-  if (fast) sb2_search<false, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
-  else sb2_search<true, RSW, PB>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
+  if (fast) sb2_search<false, RSW, PB, D12>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_sat, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
+  else sb2_search<true, RSW, PB, D12>(a, job, ck, s_org, s_ref, s_x, s_nbox, s_sat, s_rcol, s_rrow, best, pc, ps, bc, bs, g);
 
   // ---- reduce over the 32 lanes and write the partial keys ------------------------------
   unsigned long long *out = a.partial + wi * NSLOT;
@@ -749,18 +768,30 @@ struct Sb2Plan {
   int split, rpc, rsw, csz, M;
   size_t smem;
 };
+typedef void (*sb2_kernel_fn)(Sb2Args);
+static sb2_kernel_fn sb2_kernel_of(int px_bytes, int bit_depth, int rsw) {
+  if (px_bytes == 1) return rsw == 48 ? me_sb2_kernel<48, 1> : me_sb2_kernel<0, 1>;
+  if (bit_depth > 10) return rsw == 96 ? me_sb2_kernel<96, 2, true> : me_sb2_kernel<0, 2, true>;
+  return rsw == 96 ? me_sb2_kernel<96, 2> : me_sb2_kernel<0, 2>;
+}
+// the block sums of org that leave the cost in sb2_finalize_kernel: u16 planes up to 10 bits only
+static size_t sb2_bias_bytes(int px_bytes, int bit_depth, int64_t n) {
+  return px_bytes == 2 && bit_depth <= 10 ? (size_t)n * NSLOT * sizeof(uint32_t) : 0;
+}
 static bool sb2_plan(const r1c_ctx *ctx, const r1c_sb_params *p, int px_bytes, int bit_depth, int64_t n, Sb2Plan *pl) {
-  // u16 planes up to 10 bits: packed-key SADs (8x8 <= 64 * 1023) and SAD * 256 + rl of a 64x64 block fit 32 bits
-  if ((px_bytes != 1 && !(px_bytes == 2 && bit_depth <= 10)) || p->step != 1) return false;
-  if (p->lambda > 60000u) return false;  // rl >> 8 must stay below 2^14 (rate <= 65)
-  const int seq_bits = px_bytes == 1 ? Px<1>::SEQ_BITS : Px<2>::SEQ_BITS, pxw = 4 / px_bytes;
+  // u16 planes up to 10 bits: packed-key SADs (8x8 <= 64 * 1023) and SAD * 256 + rl of a 64x64 block fit 32 bits;
+  // 12 bits: the D12 variant (true SADs in the keys)
+  if ((px_bytes != 1 && px_bytes != 2) || p->step != 1) return false;
+  const bool d12 = px_bytes == 2 && bit_depth > 10;
+  if (p->lambda > (d12 ? 16000u : 60000u)) return false;  // rl >> 8 below 2^14 (rate <= 65); D12: 256 * SAD(64x64) + rl < 2^32 - 1
+  const int seq_bits = px_bytes == 1 ? Px<1>::SEQ_BITS : (d12 ? Px<2, true>::SEQ_BITS : Px<2>::SEQ_BITS), pxw = 4 / px_bytes;
   const int NX = 2 * p->range_x + 1, NY = 2 * p->range_y + 1;
   if (p->range_y < 1 || NX > 255) return false;
   const int M = (NX + 31) / 32;
   const int winW = 64 + 2 * p->range_x;
   const int rsw = (winW + pxw - 1) / pxw;  // a copy row holds pixels [p, p + pxw * rsw)
   const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
-  for (int split = 1; split <= 16; split++) {
+  for (int split = 1; split <= 32; split++) {
     const int rpc = 2 * ((NY + 2 * split - 1) / (2 * split));
     const int chunks = (NY + rpc - 1) / rpc;
     if (chunks != split) continue;
@@ -802,7 +833,7 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   R1C_CUDA(ctx, cudaSetDevice(ctx->device));
   void *d_partial;
   const size_t partial_bytes = (size_t)n * pl.split * NSLOT * sizeof(unsigned long long);
-  const size_t bias_bytes = org->px_bytes == 2 ? (size_t)n * NSLOT * sizeof(uint32_t) : 0;
+  const size_t bias_bytes = sb2_bias_bytes(org->px_bytes, bit_depth, n);
   int rc = r1c_scratch_dev(ctx, 15, partial_bytes + bias_bytes, &d_partial);
   if (rc) return rc;
   Sb2Args a;
@@ -819,8 +850,7 @@ int r1c_sb2_search(r1c_ctx *ctx, const r1c_plane *org, const r1c_plane *ref, con
   a.csz = pl.csz;
   a.M = pl.M;
   // 48 / 96 words per window row: the +-64 px window
-  auto kern = org->px_bytes == 1 ? (pl.rsw == 48 ? me_sb2_kernel<48, 1> : me_sb2_kernel<0, 1>)
-                                 : (pl.rsw == 96 ? me_sb2_kernel<96, 2> : me_sb2_kernel<0, 2>);
+  auto kern = sb2_kernel_of(org->px_bytes, bit_depth, pl.rsw);
   R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   r1c_prof_begin(ctx, R1C_PROF_ME_SB);
   kern<<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
@@ -877,11 +907,11 @@ extern "C" int r1c_me_sb_batch_dev_noalloc(r1c_ctx *ctx, const r1c_plane *org, c
   R1C_REQUIRE(ctx, ctx->device >= 0 && ctx->device < 64, R1C_ERR_ARG, "device ordinal %d not supported by the no-alloc path", ctx->device);
   Sb2Plan pl = {};
   R1C_REQUIRE(ctx, sb2_plan(ctx, p, org->px_bytes, bit_depth, n, &pl), R1C_ERR_UNIMPLEMENTED,
-              "no-alloc search: step 1, 8-bit or <= 10-bit planes and a window this kernel's layout can take only "
+              "no-alloc search: step 1, lambda <= 60000 (16000 at 12 bits) and a window this kernel's layout can take only "
               "(range %dx%d, step %d, lambda %u)", p->range_x, p->range_y, p->step, p->lambda);
   if (n == 0) return R1C_OK;
   const size_t partial_bytes = (size_t)n * pl.split * NSLOT * sizeof(unsigned long long);
-  const size_t bias_bytes = org->px_bytes == 2 ? (size_t)n * NSLOT * sizeof(uint32_t) : 0;
+  const size_t bias_bytes = sb2_bias_bytes(org->px_bytes, bit_depth, n);
   R1C_REQUIRE(ctx, partial_bytes + bias_bytes <= (size_t)R1C_SB_NOALLOC_SCRATCH_BYTES, R1C_ERR_NOMEM,
               "no-alloc search: %lld superblocks x %d chunks need %zu bytes of scratch, the static array holds %u "
               "(R1C_SB_NOALLOC_SCRATCH_BYTES); split the job list or use r1c_me_sb_batch_dev",
@@ -911,8 +941,7 @@ extern "C" int r1c_me_sb_batch_dev_noalloc(r1c_ctx *ctx, const r1c_plane *org, c
   a.rsw = pl.rsw;
   a.csz = pl.csz;
   a.M = pl.M;
-  auto kern = org->px_bytes == 1 ? (pl.rsw == 48 ? me_sb2_kernel<48, 1> : me_sb2_kernel<0, 1>)
-                                 : (pl.rsw == 96 ? me_sb2_kernel<96, 2> : me_sb2_kernel<0, 2>);
+  auto kern = sb2_kernel_of(org->px_bytes, bit_depth, pl.rsw);
   R1C_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem));
   kern<<<(unsigned)(n * pl.split), T2, pl.smem, ctx->stream>>>(a);
   R1C_LAUNCH_CHECK(ctx);

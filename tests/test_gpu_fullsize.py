@@ -38,7 +38,7 @@ def _layout(oracle, W, H):
     return total, [(b, off[b], cols[b], rows[b]) for b in range(22) if off[b] >= 0]
 
 
-@pytest.mark.parametrize("pb,bd,W,H,frac", [(1, 8, 1920, 1080, 0.004), (2, 10, 3840, 2160, 0.0006)])
+@pytest.mark.parametrize("pb,bd,W,H,frac", [(1, 8, 1920, 1080, 0.004), (2, 10, 3840, 2160, 0.0006), (2, 12, 1920, 1080, 0.002)])
 def test_frame_me_full_size_sampled_against_oracle(r, ctx, oracle, pb, bd, W, H, frac):
     """configs[1] (and its 4K 10-bit counterpart): full search +-64, 19 sizes, SATD sub-pel tail on the whole frame;
     a stratified sample of blocks of every size -- incl. the frame's corners and edges -- against the oracle"""

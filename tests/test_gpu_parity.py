@@ -722,6 +722,18 @@ def test_frame_me_extreme_pixels(r, ctx, oracle, pb, bd):
     mv, cost = oracle.frame_me(o_org, o_ref, 6, 6, 20, params.bsize_mask, 1, 1, 1, bd)
     assert np.array_equal(got["cost"], cost)
     assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
+    # the largest costs the search can see: every pixel differs by the full range, every candidate ties on the SAD
+    # and the rate decides; lambda at the limit of the fast superblock search (60000, and 16000 at 12 bits, where
+    # 256 * SAD of a 64x64 block + rate * lambda is just below 2^32), full-pel only so that the costs stay SAD-based
+    lam = 16000 if bd == 12 else 60000
+    o_ref, d_ref = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.zeros((H, W), dtype=np.int64))
+    o_org, d_org = twin_plane(r, oracle, ctx, W, H, pb, bd, data=np.full((H, W), maxv, dtype=np.int64))
+    params = r.make_frame_me_params(W, H, 6, 6, lam, refine=0, use_satd=0, allow_hp=0)
+    got = r.frame_me(ctx, d_org, d_ref, params, bd)
+    mv, cost = oracle.frame_me(o_org, o_ref, 6, 6, lam, params.bsize_mask, 0, 0, 0, bd)
+    assert int(cost.max()) >= 256 * 64 * 64 * maxv
+    assert np.array_equal(got["cost"], cost)
+    assert np.array_equal(got["mv"]["row"], mv[:, 0]) and np.array_equal(got["mv"]["col"], mv[:, 1])
 
 
 def test_frame_me_sharded_rows_equal_whole_frame(r, ctx, oracle):

@@ -66,7 +66,9 @@ def test_noalloc_search_equals_allocating_entry_point_twice(r, ctx, oracle):
     # call 2: 10-bit planes (the scratch then also carries the org sums behind the partial keys),
     # another window and job count, so that what call 1 left in the array lies under different slots
     b = _case(r, oracle, ctx, 192, 136, 2, 10, 20, 12, 90, 902)
-    for d_org, d_ref, params, jobs, bd in (a + (8,), b + (10,), a + (8,)):
+    # call 3: 12-bit planes (true SADs in the keys: no org sums in the scratch, more chunks per superblock)
+    c = _case(r, oracle, ctx, 192, 136, 2, 12, 24, 24, 2000, 903)
+    for d_org, d_ref, params, jobs, bd in (a + (8,), b + (10,), c + (12,), a + (8,)):
         want = _search(r, ctx, lib.r1c_me_sb_batch_dev, d_org, d_ref, params, jobs, bd)
         got = _search(r, ctx, lib.r1c_me_sb_batch_dev_noalloc, d_org, d_ref, params, jobs, bd)
         assert (want["cost"] != 12345).any()
