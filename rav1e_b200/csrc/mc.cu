@@ -395,13 +395,117 @@ struct AvgArgs {
   int lg_g;  // a warp takes 1 << lg_g consecutive jobs
 };
 
+// what a lane needs to find the job of an item of its warp's chunk
+struct AvgChunk {
+  const uint4 *job;  // shared memory: the chunk's jobs
+  const int *pre;    // shared memory: exclusive prefix sums of their item counts (INT_MAX behind the last job)
+  int total, c0, lg_c0;
+  bool uniform;
+};
+
+// The items of a chunk, 1 << LGP pixels of one row each, U per lane and trip: all their loads are issued before the
+// arithmetic (the kernel lasts only a few DRAM latencies, so the number of independent requests in flight per thread
+// is what sets its bandwidth).  LGP = 2: 8-byte loads / stores, U = 4; LGP = 3 (every width of the chunk a multiple of
+// 8): 16-byte ones, U = 2 -- the same bytes in flight and registers, half the index arithmetic per pixel (ncu: the
+// 4-pixel walker alone kept the ALU pipe 68 % busy at 0.62 of the HBM peak).
+template <int PB, int LGP, int U>
+__device__ __forceinline__ void avg_walk(const AvgArgs &a, const AvgChunk &ck, int lane) {
+  constexpr int NP = 1 << LGP, NWD = NP / 2;  // pixels / 32-bit words of intermediates per item
+  const int ib = a.bit_depth == 12 ? 2 : 4;
+  const int maxv = (1 << a.bit_depth) - 1;
+  const uintptr_t tbase = ((uintptr_t)a.t1) | ((uintptr_t)a.t2);
+  const bool base_ok = (tbase & (2 * NP - 1)) == 0;  // vector loads need both arrays aligned
+  for (int item0 = lane; item0 < ck.total; item0 += 32 * U) {
+    long long o[U];
+    uint8_t *d[U];
+    int ncols[U];
+    bool live[U], vec[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int item = item0 + 32 * u;
+      live[u] = item < ck.total;
+      const int it = live[u] ? item : item0;
+      int ji;
+      if (ck.lg_c0 >= 0) ji = it >> ck.lg_c0;
+      else if (ck.uniform) ji = (int)((unsigned)it / (unsigned)ck.c0);
+      else {
+        ji = 0;  // largest j with pre[j] <= it
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1)
+          if (ck.pre[ji + s] <= it) ji += s;
+      }
+      const uint4 jb = ck.job[ji];  // dst_x, dst_y, w | h << 16, tmp_off
+      const long long toff = (long long)(int)jb.w;
+      const int jx = (int)jb.x, jy = (int)jb.y, w = (int)(int16_t)(jb.z & 0xffffu);
+      const int local = it - (ck.uniform ? ji * ck.c0 : ck.pre[ji]);
+      const int nstrips = (w + NP - 1) >> LGP;
+      const int r = (nstrips & (nstrips - 1)) == 0 ? local >> (__ffs(nstrips) - 1) : local / nstrips;
+      const int strip = local - r * nstrips;
+      const int x0 = strip << LGP;
+      ncols[u] = min(NP, w - x0);
+      o[u] = toff + (long long)r * w + x0;
+      d[u] = a.dst0 + ((long long)(jy + r) * a.dst_stride + jx + x0) * PB;
+      vec[u] = base_ok && ncols[u] == NP && (o[u] & (NP - 1)) == 0;
+    }
+    uint32_t p[U][NWD], q[U][NWD];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (live[u] && vec[u]) {
+        if (LGP == 3) {
+          const uint4 pv = __ldg((const uint4 *)(a.t1 + o[u])), qv = __ldg((const uint4 *)(a.t2 + o[u]));
+          p[u][0] = pv.x, p[u][1] = pv.y, p[u][NWD - 2] = pv.z, p[u][NWD - 1] = pv.w;
+          q[u][0] = qv.x, q[u][1] = qv.y, q[u][NWD - 2] = qv.z, q[u][NWD - 1] = qv.w;
+        } else {
+          const uint2 pv = __ldg((const uint2 *)(a.t1 + o[u])), qv = __ldg((const uint2 *)(a.t2 + o[u]));
+          p[u][0] = pv.x, p[u][1] = pv.y;
+          q[u][0] = qv.x, q[u][1] = qv.y;
+        }
+      }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (!live[u]) continue;
+      int v[NP];
+      if (vec[u]) {
+#pragma unroll
+        for (int k = 0; k < NWD; k++) {
+          v[2 * k] = (int)(int16_t)p[u][k] + (int)(int16_t)q[u][k];
+          v[2 * k + 1] = ((int)p[u][k] >> 16) + ((int)q[u][k] >> 16);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < NP; c++) v[c] = c < ncols[u] ? (int)a.t1[o[u] + c] + (int)a.t2[o[u] + c] : 0;
+      }
+#pragma unroll
+      for (int c = 0; c < NP; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
+      uint8_t *dp = d[u];
+      if (ncols[u] == NP && ((uintptr_t)dp & (NP * PB - 1)) == 0) {
+        uint32_t wd[NP * PB / 4];
+#pragma unroll
+        for (int k = 0; k < NP * PB / 4; k++)
+          wd[k] = PB == 1 ? ((uint32_t)v[4 * k] | ((uint32_t)v[4 * k + 1] << 8) | ((uint32_t)v[4 * k + 2] << 16) | ((uint32_t)v[4 * k + 3] << 24))
+                          : ((uint32_t)v[2 * k] | ((uint32_t)v[2 * k + 1] << 16));
+        if (NP * PB == 4) *(uint32_t *)dp = wd[0];
+        else if (NP * PB == 8) *(uint2 *)dp = make_uint2(wd[0], wd[1]);
+        else *(uint4 *)dp = make_uint4(wd[0], wd[1], wd[(NP * PB / 4) - 2], wd[(NP * PB / 4) - 1]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < NP; c++)
+          if (c < ncols[u]) {
+            if (PB == 1) dp[c] = (uint8_t)v[c];
+            else ((uint16_t *)dp)[c] = (uint16_t)v[c];
+          }
+      }
+    }
+  }
+}
+
 // mc_avg_ref, src/mc.rs:389-408
 // One launch, no scratch: a warp takes a CHUNK of up to 32 consecutive jobs (one per lane), prefix-sums their item
-// counts with shuffles and then walks the chunk's items with all its lanes.  item = 4 pixels of one row: fully
-// parallel, 8-byte loads / stores.  (Round 1 counted the items of the whole list and ran two device-wide scans before
-// a persistent kernel: for 4x4 blocks that scheduling traffic -- 40 bytes per job -- was larger than the 96 bytes of
-// pixels the job moves, and the three extra launches were a third of the call.)  The host picks the chunk size from
-// n alone so that the grid has at least ~32 warps per SM; the hardware block scheduler does the load balancing.
+// counts with shuffles and then walks the chunk's items with all its lanes (avg_walk).  (Round 1 counted the items of
+// the whole list and ran two device-wide scans before a persistent kernel: for 4x4 blocks that scheduling traffic --
+// 40 bytes per job -- was larger than the 96 bytes of pixels the job moves, and the three extra launches were a third
+// of the call.)  The host picks the chunk size from n alone so that the grid has at least ~32 warps per SM; the
+// hardware block scheduler does the load balancing.
 template <int PB>
 __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   constexpr int WARPS = MC_THREADS / 32;
@@ -412,101 +516,32 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   const long long j0 = ((long long)blockIdx.x * WARPS + warp) << a.lg_g;
   if (j0 >= a.n) return;
   const int g = (int)min(1ll << a.lg_g, a.n - j0);
-  const int ib = a.bit_depth == 12 ? 2 : 4;
-  const int maxv = (1 << a.bit_depth) - 1;
   static_assert(sizeof(r1c_avg_job) == 16, "r1c_avg_job is read as one 16-byte word");
-  uint4 jw = make_uint4(0, 0, 0, 0);  // dst_x, dst_y, w | h << 16, tmp_off
-  int c = 0;
-  if (lane < g) {
-    jw = __ldg((const uint4 *)(a.jobs + j0 + lane));
-    c = (((int)(int16_t)(jw.z & 0xffffu) + 3) >> 2) * (int)(int16_t)(jw.z >> 16);
-  }
+  uint4 jw = make_uint4(0, 0, 8, 0);  // dst_x, dst_y, w | h << 16, tmp_off (padding lanes: w = 8, h = 0)
+  if (lane < g) jw = __ldg((const uint4 *)(a.jobs + j0 + lane));
+  const int w = (int)(int16_t)(jw.z & 0xffffu), h = (int)(int16_t)(jw.z >> 16);
+  // 8 pixels per item when every width of the chunk is a multiple of 8, else 4
+  const bool wide = __all_sync(FULL, (w & 7) == 0);
+  const int c = lane < g ? (wide ? (w >> 3) : ((w + 3) >> 2)) * h : 0;
   int inc = c;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const int t = __shfl_up_sync(FULL, inc, d);
     if (lane >= d) inc += t;
   }
-  const int total = __shfl_sync(FULL, inc, 31);
-  const int c0 = __shfl_sync(FULL, c, 0);
+  AvgChunk ck;
+  ck.total = __shfl_sync(FULL, inc, 31);
+  ck.c0 = __shfl_sync(FULL, c, 0);
   // every job of the chunk with the same number of items (the usual batch): a shift or a division, no search
-  const bool uniform = __all_sync(FULL, lane >= g || c == c0) && c0 > 0;
-  const int lg_c0 = uniform && (c0 & (c0 - 1)) == 0 ? __ffs(c0) - 1 : -1;
+  ck.uniform = __all_sync(FULL, lane >= g || c == ck.c0) && ck.c0 > 0;
+  ck.lg_c0 = ck.uniform && (ck.c0 & (ck.c0 - 1)) == 0 ? __ffs(ck.c0) - 1 : -1;
   s_job[warp][lane] = jw;
   s_pre[warp][lane] = lane < g ? inc - c : 0x7fffffff;
   __syncwarp();
-  // A lane takes U items per trip and issues all their loads before the arithmetic: the kernel lasts only a few DRAM
-  // latencies, so the number of independent requests in flight per thread is what sets its bandwidth.
-  constexpr int U = 4;
-  const bool base8 = ((((uintptr_t)a.t1) | ((uintptr_t)a.t2)) & 7) == 0;  // 8-byte loads need both arrays aligned
-  for (int item0 = lane; item0 < total; item0 += 32 * U) {
-    long long o[U];
-    uint8_t *d[U];
-    int ncols[U];
-    bool live[U], vec[U];
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int item = item0 + 32 * u;
-      live[u] = item < total;
-      const int it = live[u] ? item : item0;
-      int ji;
-      if (lg_c0 >= 0) ji = it >> lg_c0;
-      else if (uniform) ji = (int)((unsigned)it / (unsigned)c0);
-      else {
-        ji = 0;  // largest j with pre[j] <= it (the padding lanes hold INT_MAX)
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1)
-          if (s_pre[warp][ji + s] <= it) ji += s;
-      }
-      const uint4 jb = s_job[warp][ji];
-      const long long toff = (long long)(int)jb.w;
-      const int jx = (int)jb.x, jy = (int)jb.y, w = (int)(int16_t)(jb.z & 0xffffu);
-      const int local = it - (uniform ? ji * c0 : s_pre[warp][ji]);
-      const int nstrips = (w + 3) >> 2;
-      const int r = (nstrips & (nstrips - 1)) == 0 ? local >> (__ffs(nstrips) - 1) : local / nstrips;
-      const int strip = local - r * nstrips;
-      const int x0 = strip * 4;
-      ncols[u] = min(4, w - x0);
-      o[u] = toff + (long long)r * w + x0;
-      d[u] = a.dst0 + ((long long)(jy + r) * a.dst_stride + jx + x0) * PB;
-      vec[u] = base8 && ncols[u] == 4 && (o[u] & 3) == 0;
-    }
-    uint2 p[U], q[U];
-#pragma unroll
-    for (int u = 0; u < U; u++)
-      if (live[u] && vec[u]) {
-        p[u] = __ldg((const uint2 *)(a.t1 + o[u]));
-        q[u] = __ldg((const uint2 *)(a.t2 + o[u]));
-      }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      if (!live[u]) continue;
-      int v[4];
-      if (vec[u]) {
-        v[0] = (int)(int16_t)p[u].x + (int)(int16_t)q[u].x;
-        v[1] = ((int)p[u].x >> 16) + ((int)q[u].x >> 16);
-        v[2] = (int)(int16_t)p[u].y + (int)(int16_t)q[u].y;
-        v[3] = ((int)p[u].y >> 16) + ((int)q[u].y >> 16);
-      } else {
-#pragma unroll
-        for (int c2 = 0; c2 < 4; c2++) v[c2] = c2 < ncols[u] ? (int)a.t1[o[u] + c2] + (int)a.t2[o[u] + c2] : 0;
-      }
-#pragma unroll
-      for (int c2 = 0; c2 < 4; c2++) v[c2] = min(max(rshift_round(v[c2], ib + 1), 0), maxv);
-      uint8_t *dp = d[u];
-      if (ncols[u] == 4 && ((uintptr_t)dp & (4 * PB - 1)) == 0) {
-        if (PB == 1) *(uint32_t *)dp = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
-        else *(uint2 *)dp = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
-      } else {
-#pragma unroll
-        for (int c2 = 0; c2 < 4; c2++)
-          if (c2 < ncols[u]) {
-            if (PB == 1) dp[c2] = (uint8_t)v[c2];
-            else ((uint16_t *)dp)[c2] = (uint16_t)v[c2];
-          }
-      }
-    }
-  }
+  ck.job = s_job[warp];
+  ck.pre = s_pre[warp];
+  if (wide) avg_walk<PB, 3, 2>(a, ck, lane);
+  else avg_walk<PB, 2, 4>(a, ck, lane);
 }
 
 template <typename JOB, int ROWS_PER_ITEM>
