@@ -553,7 +553,8 @@ def _check_sb(r, oracle, o_org, o_ref, params, jobs, out, W4, H4):
     return checked
 
 
-@pytest.mark.parametrize("pb,bd,step,lam", [(1, 8, 1, 0), (1, 8, 1, 700), (1, 8, 2, 33), (2, 10, 1, 90)])
+@pytest.mark.parametrize("pb,bd,step,lam", [(1, 8, 1, 0), (1, 8, 1, 700), (1, 8, 2, 33), (2, 10, 1, 90), (2, 12, 1, 1500),
+                                            (2, 12, 1, 20000)])  # 20000: above the 12-bit limit of the fast search -> me_sb.cu
 def test_me_sb_matches_per_block_full_search(r, ctx, oracle, pb, bd, step, lam):
     """every block of every size of every superblock (borders included) against the
     oracle's full_search run block by block with the reference's window rule"""
@@ -577,9 +578,10 @@ def test_me_sb_matches_per_block_full_search(r, ctx, oracle, pb, bd, step, lam):
     assert n > 849 * 6
 
 
-@pytest.mark.parametrize("pb,bd,kind", [(2, 10, "extremes"), (2, 10, "smooth"), (1, 8, "extremes")])
+@pytest.mark.parametrize("pb,bd,kind", [(2, 10, "extremes"), (2, 10, "smooth"), (1, 8, "extremes"), (2, 12, "extremes"),
+                                        (2, 12, "smooth")])
 def test_me_sb_pm64_window(r, ctx, oracle, pb, bd, kind):
-    """the +-64 px window of the headline workload (the specialised kernel instances), 8- and 10-bit; `extremes` =
+    """the +-64 px window of the headline workload (the specialised kernel instances), 8-, 10- and 12-bit; `extremes` =
     pixels at 0 / max only, so block SADs reach their largest values (key fields, 16-bit half accumulators)"""
     rng = np.random.default_rng(77 + bd)
     W, H = 256, 192
