@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   __syncwarp();
   ck.job = s_job[warp];
   ck.pre = s_pre[warp];
-  if (wide) avg_walk<PB, 3, 2>(a, ck, lane);
+  if (wide) avg_walk<PB, 3, 2>(a, ck, lane);  // (3 or 4 items per trip: 72 / 87 registers, slower everywhere)
   else avg_walk<PB, 2, 4>(a, ck, lane);
 }
 
