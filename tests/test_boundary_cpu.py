@@ -31,6 +31,32 @@ def test_every_header_symbol_is_exported(lib):
         assert hasattr(lib, name), name
 
 
+def test_rust_binding_is_in_step_with_the_header(lib):
+    """bindings/rust/rav1e_cuda_sys.rs (the crate INTEGRATION.md section 1 describes; no Rust toolchain here, so it is
+    generated from the header by tools/gen_rust_ffi.py): regenerating gives the committed text, it binds exactly the
+    functions the header declares and the library exports, and its #[repr(C)] structs have the fields, in order, of
+    the ctypes mirrors the GPU tests call through (whose layout test_struct_layouts_match pins)."""
+    import subprocess
+    import sys
+    from rav1e_b200 import capi
+    assert subprocess.call([sys.executable, os.path.join(ROOT, "tools", "gen_rust_ffi.py"), "--check"]) == 0
+    rs = open(os.path.join(ROOT, "bindings", "rust", "rav1e_cuda_sys.rs")).read()
+    fns = set(re.findall(r"pub fn (r1c_[a-z0-9_]+)\(", rs))
+    assert fns == set(capi.SIGNATURES), fns ^ set(capi.SIGNATURES)
+    for name in fns:
+        assert hasattr(lib, name), name
+    structs = {m.group(1): re.findall(r"pub (?:r#)?([a-z_0-9]+):", m.group(2))
+               for m in re.finditer(r"pub struct (r1c_[a-z0-9_]+) \{\n(.*?)\n\}", rs, flags=re.S)}
+    checked = 0
+    for cname in dir(capi):
+        ct = getattr(capi, cname)
+        if isinstance(ct, type) and issubclass(ct, C.Structure) and ct is not C.Structure and hasattr(ct, "_fields_"):
+            c_name = "r1c_" + re.sub(r"(?<!^)(?=[A-Z])", "_", cname).lower()  # FrameMeParams -> r1c_frame_me_params
+            assert structs[c_name] == [f[0].rstrip("_") for f in ct._fields_], c_name
+            checked += 1
+    assert checked >= 15 and checked == len(structs)
+
+
 def test_struct_layouts_match():
     from rav1e_b200 import api
     for npdt, ct in api.STRUCT_PAIRS:
