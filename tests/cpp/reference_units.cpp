@@ -1,8 +1,8 @@
 // reference_units.cpp -- the reference's own unit tests for the hot path, restated against the C++ mirror
 // (include/rav1e_cuda.hpp) of its interface:
-//   host  (no GPU needed)  get_mv_rate (src/me.rs:1005-1021), get_mv_range (:64-80), Plane::new geometry
-//                          (src/frame/plane.rs:215-244), block / transform size tables, and the loud failure of
-//                          Context without a device
+//   host  (no GPU needed)  test_tx_log_scale and test_divu_pair (src/quantize.rs:160-203), get_mv_rate
+//                          (src/me.rs:1005-1021), get_mv_range (:64-80), Plane::new geometry (src/frame/plane.rs:215-244),
+//                          block / transform size tables, and the loud failure of Context without a device
 //   gpu                    get_sad_same_u8 / _u16, get_satd_same_u8 / _u16 (src/dist.rs:341-465: the 22 known answers
 //                          each), test_plane_pad (src/frame/plane.rs:707-752), roundtrips_u8 / _u16
 //                          (src/transform/mod.rs:589-725: forward + inverse transform returns the source within the
@@ -73,6 +73,32 @@ static void host_tests() {
   for (int ts = 0; ts < 19; ts++)
     for (int tt = 0; tt < R1C_TX_TYPES; tt++) valid += r1c_fwd_txfm_valid(ts, tt);
   CHECK_EQ(valid, 193);  // the (size, type) pairs forward.rs:1702-1769 implements
+  // test_tx_log_scale, src/quantize.rs:176-203
+  static const struct {
+    TxSize tx_size;
+    int scale;
+  } tx_sizes[] = {{R1C_TX_4X4, 0},   {R1C_TX_8X8, 0},   {R1C_TX_16X16, 0}, {R1C_TX_32X32, 1}, {R1C_TX_64X64, 2}, {R1C_TX_4X8, 0},  {R1C_TX_8X4, 0},
+                  {R1C_TX_8X16, 0},  {R1C_TX_16X8, 0},  {R1C_TX_16X32, 1}, {R1C_TX_32X16, 1}, {R1C_TX_32X64, 2}, {R1C_TX_64X32, 2}, {R1C_TX_4X16, 0},
+                  {R1C_TX_16X4, 0},  {R1C_TX_8X32, 0},  {R1C_TX_32X8, 0},  {R1C_TX_16X64, 1}, {R1C_TX_64X16, 1}};
+  for (const auto &t : tx_sizes) CHECK_EQ(r1c_log_tx_scale(t.tx_size), t.scale);
+  // test_divu_pair, src/quantize.rs:160-168: x / d == divu_pair(x, divu_gen(d)) with the (mul, add, shift) triples that
+  // QuantizationContext::update leaves in the context the kernels divide with
+  int bad = 0;
+  for (int d = 1; d < 1024; d++) {
+    r1c_quant_ctx qc;
+    if (r1c_quant_ctx_update(&qc, R1C_TX_8X8, 0, (uint32_t)d, (uint32_t)d) != R1C_OK) {
+      bad++;
+      continue;
+    }
+    for (int x = -1000; x < 1000; x++) {
+      const uint64_t y = (uint64_t)(x < 0 ? -x : x);
+      const int q = (int)((((uint64_t)qc.dc_mul_add[0] * y + qc.dc_mul_add[1]) >> 32) >> qc.dc_mul_add[2]);
+      bad += (x < 0 ? -q : q) != x / d;
+      const int qa = (int)((((uint64_t)qc.ac_mul_add[0] * y + qc.ac_mul_add[1]) >> 32) >> qc.ac_mul_add[2]);
+      bad += (x < 0 ? -qa : qa) != x / d;
+    }
+  }
+  CHECK_EQ(bad, 0);
 }
 
 static void no_device_test() {

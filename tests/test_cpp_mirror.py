@@ -1,6 +1,7 @@
 """The C++ host-side mirror of the reference's interface (include/rav1e_cuda.hpp) and the reference's own unit tests
 restated against it (tests/cpp/reference_units.cpp): get_sad_same / get_satd_same (src/dist.rs:341-465), test_plane_pad
-(src/frame/plane.rs:707-752), roundtrips (src/transform/mod.rs:589-725).  Compiled with g++ against librav1e_cuda.so:
+(src/frame/plane.rs:707-752), roundtrips (src/transform/mod.rs:589-725), test_divu_pair / test_tx_log_scale
+(src/quantize.rs:160-203).  Compiled with g++ against librav1e_cuda.so:
 the C ABI consumed from compiled code, no Python in the path.  Without a GPU the host-only part runs and the Context
 constructor must throw (no CPU fallback); on a GPU box the whole program runs."""
 import os
@@ -48,4 +49,4 @@ def test_cpp_mirror_fails_loudly_without_a_device(exe):
 def test_reference_unit_tests_through_the_cpp_mirror(exe):
     rc, out = _run(exe, "gpu")
     assert rc == 0 and "0 failed" in out, out
-    assert int(out.strip().splitlines()[-1].split()[1]) > 28 + 4 * 22 + 2 * 37 * 4
+    assert int(out.strip().splitlines()[-1].split()[1]) > 48 + 4 * 22 + 2 * 37 * 4
