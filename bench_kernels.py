@@ -259,7 +259,10 @@ def run(ctx, r, torch, ext, flush, reps=3, only=None):
             "workload": "4K 10-bit luma tiled by each of the 19 block sizes, %d candidate reference positions per block and launch (+-32 px; the org block is shared by its candidates, so DRAM reads less than the 4 B per pixel counted)" % MC_CANDS,
             "value": dist_px / 1e6 / (ms / 1e3), "unit": "Mpix/s", "ms": ms, "pixels": dist_px,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s", "frac": gbs / hbm,
-                         "alg_bytes_per_px": 4, "peak_source": hbm_how}}
+                         "alg_bytes_per_px": 4, "peak_source": hbm_how,
+                         "note": "frac = algorithmic bytes (SURVEY 8d) over the copy peak, not DRAM utilisation: ncu "
+                                 "(profiles/ncu_avg_dist_r02.md) counts 45 MB of DRAM reads per launch of 132 MB "
+                                 "algorithmic at 8x8 (34 MB at 32x32); L2 serves the candidates' overlap"}}
     # ---------------------------------------------------- forward transforms, 4K 10-bit 4:2:0
     n_samples = 3840 * 2160 * 3 // 2
     res = torch.from_numpy(rng.integers(-1023, 1024, size=n_samples, dtype=np.int16)).cuda()
