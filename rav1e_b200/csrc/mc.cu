@@ -499,6 +499,81 @@ __device__ __forceinline__ void avg_walk(const AvgArgs &a, const AvgChunk &ck, i
   }
 }
 
+// The same for a chunk whose jobs are all 4 pixels wide with an even height (4x4, 4x8, 4x16): an item is TWO rows of a
+// block = 8 consecutive intermediates (one 16-byte load per array) and two 4-pixel stores a row apart.
+template <int PB, int U>
+__device__ __forceinline__ void avg_walk_w4(const AvgArgs &a, const AvgChunk &ck, int lane) {
+  const int ib = a.bit_depth == 12 ? 2 : 4;
+  const int maxv = (1 << a.bit_depth) - 1;
+  const bool base_ok = ((((uintptr_t)a.t1) | ((uintptr_t)a.t2)) & 15) == 0;
+  const long long row_bytes = (long long)a.dst_stride * PB;
+  for (int item0 = lane; item0 < ck.total; item0 += 32 * U) {
+    long long o[U];
+    uint8_t *d[U];
+    bool live[U], vec[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int item = item0 + 32 * u;
+      live[u] = item < ck.total;
+      const int it = live[u] ? item : item0;
+      int ji;
+      if (ck.lg_c0 >= 0) ji = it >> ck.lg_c0;
+      else if (ck.uniform) ji = (int)((unsigned)it / (unsigned)ck.c0);
+      else {
+        ji = 0;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1)
+          if (ck.pre[ji + s] <= it) ji += s;
+      }
+      const uint4 jb = ck.job[ji];
+      const int local = it - (ck.uniform ? ji * ck.c0 : ck.pre[ji]);  // row pair of the block
+      o[u] = (long long)(int)jb.w + 8 * local;
+      d[u] = a.dst0 + ((long long)((int)jb.y + 2 * local) * a.dst_stride + (int)jb.x) * PB;
+      vec[u] = base_ok && (o[u] & 7) == 0;
+    }
+    uint32_t p[U][4], q[U][4];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (live[u] && vec[u]) {
+        const uint4 pv = __ldg((const uint4 *)(a.t1 + o[u])), qv = __ldg((const uint4 *)(a.t2 + o[u]));
+        p[u][0] = pv.x, p[u][1] = pv.y, p[u][2] = pv.z, p[u][3] = pv.w;
+        q[u][0] = qv.x, q[u][1] = qv.y, q[u][2] = qv.z, q[u][3] = qv.w;
+      }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (!live[u]) continue;
+      int v[8];
+      if (vec[u]) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+          v[2 * k] = (int)(int16_t)p[u][k] + (int)(int16_t)q[u][k];
+          v[2 * k + 1] = ((int)p[u][k] >> 16) + ((int)q[u][k] >> 16);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 8; c++) v[c] = (int)a.t1[o[u] + c] + (int)a.t2[o[u] + c];
+      }
+#pragma unroll
+      for (int c = 0; c < 8; c++) v[c] = min(max(rshift_round(v[c], ib + 1), 0), maxv);
+#pragma unroll
+      for (int rr = 0; rr < 2; rr++) {
+        uint8_t *dp = d[u] + rr * row_bytes;
+        const int *vr = v + 4 * rr;
+        if (((uintptr_t)dp & (4 * PB - 1)) == 0) {
+          if (PB == 1) *(uint32_t *)dp = (uint32_t)vr[0] | ((uint32_t)vr[1] << 8) | ((uint32_t)vr[2] << 16) | ((uint32_t)vr[3] << 24);
+          else *(uint2 *)dp = make_uint2((uint32_t)vr[0] | ((uint32_t)vr[1] << 16), (uint32_t)vr[2] | ((uint32_t)vr[3] << 16));
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            if (PB == 1) dp[c] = (uint8_t)vr[c];
+            else ((uint16_t *)dp)[c] = (uint16_t)vr[c];
+          }
+        }
+      }
+    }
+  }
+}
+
 // mc_avg_ref, src/mc.rs:389-408
 // One launch, no scratch: a warp takes a CHUNK of up to 32 consecutive jobs (one per lane), prefix-sums their item
 // counts with shuffles and then walks the chunk's items with all its lanes (avg_walk).  (Round 1 counted the items of
@@ -507,7 +582,7 @@ __device__ __forceinline__ void avg_walk(const AvgArgs &a, const AvgChunk &ck, i
 // of the call.)  The host picks the chunk size from n alone so that the grid has at least ~32 warps per SM; the
 // hardware block scheduler does the load balancing.
 template <int PB>
-__global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
+__global__ void __launch_bounds__(MC_THREADS, 9) avg_kernel(AvgArgs a) {
   constexpr int WARPS = MC_THREADS / 32;
   constexpr unsigned FULL = 0xffffffffu;
   __shared__ uint4 s_job[WARPS][32];
@@ -520,9 +595,11 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   uint4 jw = make_uint4(0, 0, 8, 0);  // dst_x, dst_y, w | h << 16, tmp_off (padding lanes: w = 8, h = 0)
   if (lane < g) jw = __ldg((const uint4 *)(a.jobs + j0 + lane));
   const int w = (int)(int16_t)(jw.z & 0xffffu), h = (int)(int16_t)(jw.z >> 16);
-  // 8 pixels per item when every width of the chunk is a multiple of 8, else 4
+  // 8 pixels per item when every width of the chunk is a multiple of 8 (one row) or 4 with an even height (two rows),
+  // else 4
   const bool wide = __all_sync(FULL, (w & 7) == 0);
-  const int c = lane < g ? (wide ? (w >> 3) : ((w + 3) >> 2)) * h : 0;
+  const bool pairs = __all_sync(FULL, lane >= g || (w == 4 && (h & 1) == 0));
+  const int c = lane < g ? (wide ? (w >> 3) * h : (pairs ? (h >> 1) : ((w + 3) >> 2) * h)) : 0;
   int inc = c;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
@@ -541,6 +618,7 @@ __global__ void __launch_bounds__(MC_THREADS) avg_kernel(AvgArgs a) {
   ck.job = s_job[warp];
   ck.pre = s_pre[warp];
   if (wide) avg_walk<PB, 3, 2>(a, ck, lane);  // (3 or 4 items per trip: 72 / 87 registers, slower everywhere)
+  else if (pairs) avg_walk_w4<PB, 2>(a, ck, lane);
   else avg_walk<PB, 2, 4>(a, ck, lane);
 }
 
