@@ -31,6 +31,24 @@ def test_every_header_symbol_is_exported(lib):
         assert hasattr(lib, name), name
 
 
+def test_header_is_plain_c99(lib, tmp_path):
+    """the boundary is a C header: it compiles as strict C99 (and as C++11) with every warning an error, and a C
+    program linked against the library can call it"""
+    import subprocess
+    from rav1e_b200 import capi
+    src = tmp_path / "c99.c"
+    src.write_text('#include "rav1e_cuda.h"\n'
+                   'int main(void) { r1c_frame_me_params p; r1c_quant_ctx q; (void)p; (void)q;\n'
+                   '  return r1c_block_width(R1C_BLOCK_8X8) == 8 && r1c_tx_height(R1C_TX_16X64) == 64 ? 0 : 1; }\n')
+    libdir = os.path.dirname(capi.LIB_PATH)
+    exe = str(tmp_path / "c99")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           str(src), "-L", libdir, "-lrav1e_cuda", "-Wl,-rpath," + libdir, "-o", exe])
+    assert subprocess.call([exe]) == 0
+    subprocess.check_call(["g++", "-std=c++11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-fsyntax-only", "-x", "c++",
+                           "-I", os.path.join(ROOT, "include"), str(src)])
+
+
 def test_rust_binding_is_in_step_with_the_header(lib):
     """bindings/rust/rav1e_cuda_sys.rs (the crate INTEGRATION.md section 1 describes; no Rust toolchain here, so it is
     generated from the header by tools/gen_rust_ffi.py): regenerating gives the committed text, it binds exactly the
