@@ -103,26 +103,37 @@ __device__ __forceinline__ void unit_shape(const r1c_mc_job &j, int &cls, int &t
   cls = wclass_of(w) * NHC + hclass_of(h);
 }
 
-// pass 1: units per class.  cursor[0..15] = counts, then (pass 2) running offsets
+// pass 1: units per class.  cursor[0..15] = counts, then (pass 2) running offsets; counts[2 * NCLS] = number of jobs
+// whose size differs from job 0's (or is empty): 0 = a list of ONE block size, the usual batch, for which unit u is tile
+// u % units_per_job of job u / units_per_job -- the scatter pass returns at once and the main kernel needs no unit list
+// (the three passes over the 44-byte job records were 1/6 of a call: a 4x4 job moves 64 bytes of pixels)
 __global__ void mc_count_kernel(const r1c_mc_job *jobs, long long n, uint32_t *counts) {
   __shared__ uint32_t s_cnt[NCLS];
+  __shared__ uint32_t s_odd;
   if (threadIdx.x < NCLS) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_odd = 0;
   __syncthreads();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
     const r1c_mc_job j = jobs[i];
+    const uint32_t wh0 = __ldg((const uint32_t *)jobs + 4);  // w | h << 16 of job 0
+    bool odd = true;
     if (j.w > 0 && j.h > 0) {
       int cls, tx, nu;
       unit_shape(j, cls, tx, nu);
       atomicAdd(&s_cnt[cls], (uint32_t)nu);
+      odd = ((uint32_t)(uint16_t)j.w | ((uint32_t)(uint16_t)j.h << 16)) != wh0;
     }
+    if (__any_sync(__activemask(), odd) && odd) s_odd = 1;
   }
   __syncthreads();
   if (threadIdx.x < NCLS && s_cnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], s_cnt[threadIdx.x]);
+  if (threadIdx.x == 0 && s_odd) atomicAdd(&counts[2 * NCLS], 1u);
 }
 
 // pass 2: scatter (job, tile) into the class-major unit list.  counts[NCLS ..] = cursors (zeroed by the host memset)
 __global__ void mc_scatter_kernel(const r1c_mc_job *jobs, long long n, uint32_t *counts, uint32_t *units) {
+  if (counts[2 * NCLS] == 0) return;  // one block size: no unit list
   __shared__ uint32_t s_cnt[NCLS], s_base[NCLS];
   if (threadIdx.x < NCLS) s_cnt[threadIdx.x] = 0;
   __syncthreads();
@@ -338,13 +349,27 @@ __global__ void __launch_bounds__(THREADS, STAGES == 1 ? 5 : 2) mc_tma_kernel(co
     constexpr int UPL = MAX_UPB / 32;  // units per lane
     uint32_t pw[UPL][7];  // [0] = tile index, [1..6] = words 1..6 of r1c_mc_job
     uint32_t pdx[UPL];
+    // a list of one block size (mc_count_kernel): unit U is tile U % npj of job U / npj, there is no unit list
+    const bool uni = __ldg(&a.cls_count[2 * NCLS]) == 0;
+    uint32_t npj = 1;
+    if (uni) {
+      int c0, t0, n0;
+      unit_shape(a.jobs[0], c0, t0, n0);
+      npj = (uint32_t)n0;
+    }
     auto fetch = [&](const Cursor &c) {
       const uint32_t u0 = c.b * c.upb, nu = min((uint32_t)c.upb, c.cnt - u0);
 #pragma unroll
       for (int k = 0; k < UPL; k++) {
         const uint32_t u = lane + 32 * k;
         if (u < nu) {
-          const uint32_t e = __ldg(&a.units[c.start + u0 + u]);
+          uint32_t e;
+          if (uni) {
+            const uint32_t uu = c.start + u0 + u, jb = uu / npj;
+            e = jb | ((uu - jb * npj) << 26);
+          } else {
+            e = __ldg(&a.units[c.start + u0 + u]);
+          }
           const uint32_t *jw = (const uint32_t *)(a.jobs + (e & 0x3ffffffu));
           pdx[k] = __ldg(jw);
 #pragma unroll
@@ -602,9 +627,9 @@ int r1c_mc_tma_launch(r1c_ctx *ctx, int kind, r1c_plane *dst, int16_t *d_tmp, co
   // unit list: one entry per job, plus one per extra 32x16 tile of the jobs larger than that (at most 32 per job)
   void *d_counts, *d_units;
   int rc;
-  if ((rc = r1c_scratch_dev(ctx, 2, 2 * NCLS * sizeof(uint32_t), &d_counts))) return rc;
+  if ((rc = r1c_scratch_dev(ctx, 2, (2 * NCLS + 4) * sizeof(uint32_t), &d_counts))) return rc;
   if ((rc = r1c_scratch_dev(ctx, 3, (size_t)n * 32 * sizeof(uint32_t), &d_units))) return rc;
-  R1C_CUDA(ctx, cudaMemsetAsync(d_counts, 0, 2 * NCLS * sizeof(uint32_t), ctx->stream));
+  R1C_CUDA(ctx, cudaMemsetAsync(d_counts, 0, (2 * NCLS + 4) * sizeof(uint32_t), ctx->stream));
   const unsigned nb = (unsigned)((n + 255) / 256);
   mc_count_kernel<<<nb, 256, 0, ctx->stream>>>(d_jobs, n, (uint32_t *)d_counts);
   R1C_LAUNCH_CHECK(ctx);
