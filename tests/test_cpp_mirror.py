@@ -50,3 +50,33 @@ def test_reference_unit_tests_through_the_cpp_mirror(exe):
     rc, out = _run(exe, "gpu")
     assert rc == 0 and "0 failed" in out, out
     assert int(out.strip().splitlines()[-1].split()[1]) > 48 + 4 * 22 + 2 * 37 * 4
+
+
+@pytest.fixture(scope="module")
+def example():
+    """examples/lookahead_me.c: the headline call sequence from plain C99"""
+    import __graft_entry__ as g
+    from rav1e_b200 import capi
+    if not os.path.exists(capi.LIB_PATH):
+        g.build()
+    libdir = os.path.dirname(capi.LIB_PATH)
+    out = os.path.join(ROOT, "build", "lookahead_me")
+    os.makedirs(os.path.dirname(out), exist_ok=True)
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "lookahead_me.c"), "-L", libdir, "-lrav1e_cuda",
+                           "-Wl,-rpath," + libdir, "-o", out])
+    return out
+
+
+def test_c_example_builds_and_refuses_to_run_without_a_device(example):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    rc, out = _run(example)
+    assert rc == 2 and "no CPU fallback" in out, out
+
+
+@pytest.mark.gpu
+def test_c_example_finds_the_true_motion(example):
+    rc, out = _run(example, "6")
+    assert rc == 0 and "5 frame pairs" in out, out
