@@ -35,9 +35,6 @@ struct ItxArgs {
   unsigned dq_dc, dq_ac;
 };
 
-#ifndef ITX_T64
-#define ITX_T64 256
-#endif
 template <int W, int H>
 struct ItxCfg {
   static constexpr int WI = W < 32 ? W : 32, HI = H < 32 ? H : 32;
@@ -47,7 +44,7 @@ struct ItxCfg {
   // read-modify-write; the coded rows are looped over or leave threads idle), except for the 4:1 wide blocks
   // (16x4, 32x8, 64x16), where 3 of 4 warps would idle through the long row transforms: those are sized by the
   // coded rows and loop over the columns (measured: 2:1 blocks and the 64-wide ones with 32 coded rows lose)
-  static constexpr int THREADS = (MAXD == 64 && !(W >= 4 * HI)) ? ITX_T64 : 128;
+  static constexpr int THREADS = 128;
   static constexpr int BPC = THREADS / (W >= 4 * HI ? HI : W);  // blocks per CTA
   static constexpr bool ROWS_ONCE = BPC * HI <= THREADS;
   static constexpr bool COLS_ONCE = BPC * W <= THREADS;
