@@ -15,6 +15,10 @@
 
 #include "enc_tx.cuh"
 
+#ifndef ENC64_GROUPS
+#define ENC64_GROUPS 2
+#endif
+
 namespace enc {
 
 template <int W, int H>
@@ -27,7 +31,14 @@ struct Enc64Cfg {
   // 64-wide blocks: the inverse row pass must have exactly one item per thread (load, barrier, store): THREADS / CH blocks.
   // 16 / 32-wide ones (no second layout: coded row r = dense row r, in place): one column per thread
   static constexpr bool TWO_LAYOUTS = W == 64;
-  static constexpr int BPC = THREADS / (TWO_LAYOUTS ? CH : W);
+  // GROUPS such sets of blocks per CTA: a slab pass is 9 000 - 13 600 instructions of straight-line code and ncu's top
+  // stall was no_instruction (3.3 warps per issue at 64x64): with twice the blocks every fetched instruction does twice
+  // the work, and the forward row pass (FR rows per block) has an item for every thread
+  // (measured: 64x64 82 -> 74 us; the other four sizes lose 1 - 27 % with two groups -- shared memory then allows three
+  // CTAs where 64x16 had four, and their transforms are shorter -- and keep one)
+  static constexpr int GROUPS = (W == 64 && H == 64) ? ENC64_GROUPS : 1;
+  static constexpr int BPG = THREADS / (TWO_LAYOUTS ? CH : W);  // blocks per group
+  static constexpr int BPC = GROUPS * BPG;
 #ifndef ENC64_MINB
 #define ENC64_MINB 3
 #endif
@@ -37,7 +48,8 @@ struct Enc64Cfg {
   static constexpr int BLK = ROWS * STRIDE;
   static constexpr int LPB = 32, NCH = CODED / 32;
   static constexpr int LOGW = W == 16 ? 4 : W == 32 ? 5 : 6;
-  static_assert(BPC * BLK * 4 <= 48 * 1024, "static shared memory");
+  static constexpr size_t SMEM = (size_t)BPC * BLK * 4;  // dynamic: up to 66.5 KB, three CTAs per SM
+  static_assert(3 * SMEM <= 220 * 1024, "three CTAs per SM");
 };
 
 template <int W, int H, int CT, int RT>
@@ -45,7 +57,7 @@ __global__ void __launch_bounds__(Enc64Cfg<W, H>::THREADS, Enc64Cfg<W, H>::MINB)
   using C = Enc64Cfg<W, H>;
   constexpr int LW = C::LOGW, LH = H == 16 ? 4 : H == 32 ? 5 : 6;
   constexpr bool RECT = LW - LH == 1 || LH - LW == 1;  // get_rect_tx_log_ratio, inverse.rs:2070
-  __shared__ int s_c[C::BPC * C::BLK];
+  extern __shared__ __align__(16) int s_c[];  // [BPC][BLK]
   const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
   const int nslabs = (int)((a.n + C::BPC - 1) / C::BPC);
   const int lts = (int)a.q.qc.log_tx_scale;
@@ -157,7 +169,7 @@ __global__ void __launch_bounds__(Enc64Cfg<W, H>::THREADS, Enc64Cfg<W, H>::MINB)
 #pragma unroll
         for (int c = C::CW; c < W; c++) v[c] = 0;
       }
-      if (C::TWO_LAYOUTS) __syncthreads();  // (one trip, every thread) also orders 4a's reads before the stores below
+      if (C::TWO_LAYOUTS) __syncthreads();  // (every thread, once per group) also orders 4a's reads before the stores below
       if (live) {
         if (__all_sync(__activemask(), l1 + itx::NOCLAMP_MARGIN <= a.rg_row.hi)) {
           itx::inv1d<RT, W, false>(v, o, a.rg_row);
@@ -177,7 +189,9 @@ __global__ void __launch_bounds__(Enc64Cfg<W, H>::THREADS, Enc64Cfg<W, H>::MINB)
       }
     };
     if constexpr (C::TWO_LAYOUTS) {
-      inv_row(tid);
+      // one group of whole blocks at a time (the hazard is inside a block): load, barrier, store
+#pragma unroll 1
+      for (int g = 0; g < C::GROUPS; g++) inv_row(tid + g * C::THREADS);
     } else {
 #pragma unroll 1
       for (int it = tid; it < nb * C::CH; it += C::THREADS) inv_row(it);
@@ -234,14 +248,15 @@ int enc64_launch(r1c_ctx *ctx, const EncArgs &a) {
   static int per_sm = 0;  // resident CTAs per SM of this instantiation
   if (!per_sm) {
     int nb = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, enc_tx64_kernel<W, H, CT, RT>, C::THREADS, 0);
+    cudaError_t e = cudaFuncSetAttribute(enc_tx64_kernel<W, H, CT, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, enc_tx64_kernel<W, H, CT, RT>, C::THREADS, C::SMEM);
     if (e != cudaSuccess || nb < 1) return r1c_set_err(ctx, R1C_ERR_CUDA, "enc_tx64 kernel does not fit an SM: %s", cudaGetErrorString(e));
     per_sm = nb;
   }
   const long long nslabs = (a.n + C::BPC - 1) / C::BPC;
   const long long full = (long long)ctx->sm_count * per_sm;
   const unsigned grid = (unsigned)(nslabs < full ? nslabs : full);
-  enc_tx64_kernel<W, H, CT, RT><<<grid, C::THREADS, 0, ctx->stream>>>(a);
+  enc_tx64_kernel<W, H, CT, RT><<<grid, C::THREADS, C::SMEM, ctx->stream>>>(a);
   R1C_LAUNCH_CHECK(ctx);
   return R1C_OK;
 }
