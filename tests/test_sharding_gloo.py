@@ -76,6 +76,30 @@ def test_tile_split_is_a_partition_and_balanced():
     assert {(hi - lo, chi - clo) for (lo, hi), (clo, chi) in t8} == {(17, 15)}
 
 
+def test_tile_rectangles_cover_what_a_tile_can_touch():
+    """shard.tile_plane_rows / tile_plane_cols (what a rank uploads with r1c_plane_upload_rect_async): inside the
+    allocation, on 128-byte lines, holding the tile +- (range + 16) pixels, and shrinking with the tile grid"""
+    sys.path.insert(0, ROOT)
+    from rav1e_b200 import api, capi, shard
+    lib = capi.load()
+    for px_bytes in (1, 2):
+        cfg = capi.PlaneCfg()
+        assert lib.r1c_plane_cfg_new(cfg, 3840, 2160, 0, 0, 88, 88, px_bytes) == 0
+        for world in (1, 2, 4, 8):
+            area = 0
+            for (lo, hi), (clo, chi) in shard.split_tiles(3840, 2160, world):
+                r0, r1 = shard.tile_plane_rows(cfg, lo, hi, 64)
+                c0, c1 = shard.tile_plane_cols(cfg, clo, chi, 64)
+                assert 0 <= r0 < r1 <= cfg.alloc_height and 0 <= c0 < c1 <= cfg.stride
+                assert c0 % 64 == 0 and (c1 % 64 == 0 or c1 == cfg.stride)
+                # the tile's pixels +- (64 + 16), clipped to the allocation
+                assert r0 <= max(cfg.yorigin + lo * 64 - 80, 0) and r1 >= min(cfg.yorigin + min(hi * 64, 2160) + 80, cfg.alloc_height)
+                assert c0 <= max(cfg.xorigin + clo * 64 - 80, 0) and c1 >= min(cfg.xorigin + min(chi * 64, 3840) + 80, cfg.stride)
+                area += (r1 - r0) * (c1 - c0)
+            if world == 8:  # 2 x 4 tiles: a rank moves ~ 1/5 of a plane, not all of it
+                assert area / 8 < 0.25 * cfg.alloc_height * cfg.stride
+
+
 @pytest.mark.timeout(300)
 def test_two_rank_gloo_gather_equals_whole_frame():
     import torch.multiprocessing as mp
