@@ -245,11 +245,14 @@ template <int W, int H, int CT, int RT>
 int enc64_launch(r1c_ctx *ctx, const EncArgs &a) {
   using C = Enc64Cfg<W, H>;
   if (a.n == 0) return R1C_OK;
+  // the attribute belongs to the (kernel, device) pair and the process may hold contexts on several devices: set it on
+  // every launch, like me_sb2.cu does (the caller has made ctx->device current)
+  cudaError_t e = cudaFuncSetAttribute(enc_tx64_kernel<W, H, CT, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+  if (e != cudaSuccess) return r1c_set_err(ctx, R1C_ERR_CUDA, "enc_tx64 kernel: %s", cudaGetErrorString(e));
   static int per_sm = 0;  // resident CTAs per SM of this instantiation
   if (!per_sm) {
     int nb = 0;
-    cudaError_t e = cudaFuncSetAttribute(enc_tx64_kernel<W, H, CT, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
-    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, enc_tx64_kernel<W, H, CT, RT>, C::THREADS, C::SMEM);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, enc_tx64_kernel<W, H, CT, RT>, C::THREADS, C::SMEM);
     if (e != cudaSuccess || nb < 1) return r1c_set_err(ctx, R1C_ERR_CUDA, "enc_tx64 kernel does not fit an SM: %s", cudaGetErrorString(e));
     per_sm = nb;
   }
